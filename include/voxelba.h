@@ -1,0 +1,111 @@
+/*
+ * voxelba.h — C ABI of libvoxelba: the B200 (sm_100a) implementation of Voxel-SLAM's voxel-map
+ * bundle-adjustment / point-to-plane hot path.
+ *
+ * The reference has no FFI or plugin API for this path: it is reached by direct
+ * C++ calls on header-defined classes.  Each entry point below therefore names the reference
+ * class member / free function it replaces (file:line into /root/reference/VoxelSLAM/src/).
+ * `include/voxelba_compat.hpp` re-creates the reference's C++ names on top of this ABI.
+ *
+ * Conventions
+ *   - all matrices are COLUMN-MAJOR doubles (Eigen's default, which the reference uses);
+ *   - POD structs mirror the reference's own structs byte-for-byte where one exists;
+ *   - every function returns VX_OK (0) or a negative VX_ERR_* code; vx_last_error() gives text;
+ *   - calls are synchronous unless the name ends in `_async`;
+ *   - there is NO CPU fallback: without a CUDA device every compute call returns VX_ERR_CUDA.
+ */
+#ifndef VOXELBA_H
+#define VOXELBA_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VX_OK 0
+#define VX_ERR_CUDA (-1)      /* CUDA runtime failure or no device */
+#define VX_ERR_ARG (-2)       /* bad argument */
+#define VX_ERR_TOO_FEW (-3)   /* reference: printf("Too Less Voxel"); exit(0)   voxel_map.hpp:399-403 */
+#define VX_ERR_OPT_STATE (-4) /* reference: printf("Error: opt_state"); exit(0)  voxel_map.hpp:1488-1492 */
+#define VX_ERR_NOMEM (-5)
+
+typedef struct vx_ctx vx_ctx;       /* one per host thread: device, stream, scratch */
+typedef struct vx_factor vx_factor; /* class LidarFactor (a.k.a. VOX_HESS), voxel_map.hpp:124-339 */
+
+/* class PointCluster {Matrix3d P; Vector3d v; int N;}  tools.hpp:304-310 (104 bytes, 8-aligned) */
+typedef struct vx_cluster {
+  double P[9];
+  double v[3];
+  int32_t N;
+  int32_t _pad;
+} vx_cluster;
+
+/* the part of struct IMUST the LiDAR factor reads: R (tools.hpp:139) and p (tools.hpp:140) */
+typedef struct vx_pose {
+  double R[9];
+  double p[3];
+} vx_pose;
+
+/* ---- context ------------------------------------------------------------------------------ */
+int vx_ctx_create(int device, vx_ctx **out);
+int vx_ctx_destroy(vx_ctx *ctx);
+int vx_ctx_sync(vx_ctx *ctx);
+void *vx_ctx_stream(vx_ctx *ctx);          /* the cudaStream_t every launch of this ctx uses */
+const char *vx_last_error(void);           /* thread-local text of the last failure */
+int vx_version(void);
+/* number of kernels this library launched on `ctx` since creation (bench.py: gpu_launches) */
+int64_t vx_ctx_launch_count(vx_ctx *ctx);
+
+/* ---- B0: LidarFactor storage -------------------------------------------------------------- */
+/* LidarFactor::LidarFactor(int _w)  voxel_map.hpp:136.  `n_windows` > 1 makes a BATCH of
+ * independent factors that share W (bottom-level GBA windows, voxelslam.cpp:3096): frame f of
+ * window b is global frame b*W+f, outputs are n_windows separate Hess/JacT/cost. */
+int vx_factor_create(vx_ctx *ctx, int win_size, int n_windows, vx_factor **out);
+int vx_factor_free(vx_factor *f);
+/* LidarFactor::clear()  voxel_map.hpp:328-336 */
+int vx_factor_clear(vx_factor *f);
+/* LidarFactor::push_voxel() x V  voxel_map.hpp:139-147.  Dense form = the reference's own layout:
+ * plvec[V][W] (N==0 marks an absent frame), sig_vecs[V], coeffs[V], eig_values[V][3],
+ * eig_vectors[V][9] col-major, pcr_adds[V].  Replaces the factor's content. */
+int vx_factor_upload_dense(vx_factor *f, int64_t V, const vx_cluster *plvec, const vx_cluster *sig_vecs,
+                           const double *coeffs, const double *eig_values, const double *eig_vectors,
+                           const vx_cluster *pcr_adds);
+/* Same content in compressed form for large W (top-level GBA, W~399: >95% of plvec is N==0):
+ * voxel a owns entries [offsets[a], offsets[a+1]) with ascending `frames` (global frame ids)
+ * and their clusters. */
+int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const int32_t *frames,
+                         const vx_cluster *clusters, const vx_cluster *sig_vecs, const double *coeffs,
+                         const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds);
+/* read back what evaluate_only_residual caches  voxel_map.hpp:317-319 */
+int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vectors, vx_cluster *pcr_adds);
+int64_t vx_factor_num_voxels(const vx_factor *f);
+int64_t vx_factor_num_voxel_frames(const vx_factor *f); /* sum over voxels of frames with N != 0 */
+int vx_factor_win_size(const vx_factor *f);
+int vx_factor_num_windows(const vx_factor *f);
+
+/* ---- B1 / B2: evaluation -------------------------------------------------------------------- */
+/* LidarFactor::acc_evaluate2(xs, head, end, Hess, JacT, residual)  voxel_map.hpp:150-282.
+ * poses: n_windows*W entries.  Hess: n_windows x (6W x 6W) col-major, JacT: n_windows x 6W,
+ * residual: n_windows.  Reads the cached eig_values / eig_vectors / pcr_adds (voxel_map.hpp:187-190). */
+int vx_factor_hessian(vx_ctx *ctx, vx_factor *f, const vx_pose *poses, int64_t head, int64_t end,
+                      double *Hess, double *JacT, double *residual);
+/* LidarFactor::evaluate_only_residual(xs, head, end, residual)  voxel_map.hpp:285-325.
+ * Refreshes the cache for voxels in [head,end) (voxel_map.hpp:317-319). */
+int vx_factor_residual(vx_ctx *ctx, vx_factor *f, const vx_pose *poses, int64_t head, int64_t end,
+                       double *residual);
+
+/* Device-resident variants: no host copies, no synchronisation.  Results stay in the factor's
+ * device buffers (vx_factor_device_buffers) so a collective or the next kernel can consume them. */
+int vx_factor_set_poses(vx_ctx *ctx, vx_factor *f, const vx_pose *poses);        /* H2D, async */
+int vx_factor_hessian_async(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end);
+int vx_factor_residual_async(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end);
+/* device pointers: Hess (n_windows*(6W)^2), JacT (n_windows*6W), cost_hess (n_windows),
+ * cost_resid (n_windows); any out pointer may be NULL */
+int vx_factor_device_buffers(vx_factor *f, void **Hess, void **JacT, void **cost_hess, void **cost_resid);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VOXELBA_H */

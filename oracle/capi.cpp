@@ -1,0 +1,177 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see vmath.hpp header). PARITY UNPINNED.
+//
+// capi.cpp — flat C entry points over the oracle so tests/ and bench.py's cpu_baseline leg can
+// drive it through ctypes.  POD layouts deliberately equal the product's (include/voxelba.h) so the
+// same numpy arrays feed both sides; the oracle does NOT include the product header.
+#include "ba.hpp"
+#include "li_ba.hpp"
+#include "octree.hpp"
+#include "gba.hpp"
+#include "lio.hpp"
+#include <chrono>
+
+using namespace orc;
+
+extern "C" {
+
+struct oc_cluster { double P[9]; double v[3]; int32_t N; int32_t _pad; };
+struct oc_pose { double R[9]; double p[3]; };
+
+static PointCluster from_c(const oc_cluster &c) {
+  PointCluster r;
+  for (int i = 0; i < 9; i++) r.P[i] = c.P[i];
+  for (int i = 0; i < 3; i++) r.v[i] = c.v[i];
+  r.N = c.N;
+  return r;
+}
+static void to_c(const PointCluster &r, oc_cluster &c) {
+  for (int i = 0; i < 9; i++) c.P[i] = r.P[i];
+  for (int i = 0; i < 3; i++) c.v[i] = r.v[i];
+  c.N = r.N; c._pad = 0;
+}
+static std::vector<IMUST> poses_in(const oc_pose *p, int n) {
+  std::vector<IMUST> xs(n);
+  for (int i = 0; i < n; i++) {
+    for (int k = 0; k < 9; k++) xs[i].R[k] = p[i].R[k];
+    for (int k = 0; k < 3; k++) xs[i].p[k] = p[i].p[k];
+  }
+  return xs;
+}
+static void poses_out(const std::vector<IMUST> &xs, oc_pose *p) {
+  for (size_t i = 0; i < xs.size(); i++) {
+    for (int k = 0; k < 9; k++) p[i].R[k] = xs[i].R[k];
+    for (int k = 0; k < 3; k++) p[i].p[k] = xs[i].p[k];
+  }
+}
+
+// ---- A1 -------------------------------------------------------------------------------------
+void orc_keys_f64(const double *xyz, int64_t n, double voxel_size, int64_t *out) {
+  for (int64_t i = 0; i < 3 * n; i++) out[i] = key_axis_d(xyz[i], voxel_size);
+}
+void orc_keys_f32(const float *xyz, int64_t n, double voxel_size, int64_t *out) {
+  for (int64_t i = 0; i < 3 * n; i++) out[i] = key_axis_f(xyz[i], voxel_size);
+}
+
+// ---- linear algebra -------------------------------------------------------------------------
+void orc_eig3(const double *A, int64_t n, double *w, double *U) {
+  for (int64_t i = 0; i < n; i++) {
+    M3 a; for (int k = 0; k < 9; k++) a[k] = A[9 * i + k];
+    V3 l; M3 u;
+    eig3_sym(a, l, u);
+    for (int k = 0; k < 3; k++) w[3 * i + k] = l[k];
+    for (int k = 0; k < 9; k++) U[9 * i + k] = u[k];
+  }
+}
+void orc_ldlt_solve(const double *A, const double *b, int n, double *x) {
+  MatX m(n, n); VecX vb(n), vx(n);
+  std::memcpy(m.d.data(), A, sizeof(double) * n * n);
+  for (int i = 0; i < n; i++) vb[i] = b[i];
+  ldlt_solve(m, vb, vx);
+  for (int i = 0; i < n; i++) x[i] = vx[i];
+}
+void orc_inverse15(const double *A, double *out) {
+  M15 a; for (int k = 0; k < 225; k++) a[k] = A[k];
+  M15 r = inverse_lu(a);
+  for (int k = 0; k < 225; k++) out[k] = r[k];
+}
+void orc_exp(const double *w, double *R) { M3 r = Exp(vec3(w[0], w[1], w[2])); for (int k = 0; k < 9; k++) R[k] = r[k]; }
+void orc_log(const double *R, double *w) { M3 r; for (int k = 0; k < 9; k++) r[k] = R[k]; V3 l = Log(r); for (int k = 0; k < 3; k++) w[k] = l[k]; }
+void orc_cluster_transform(const oc_cluster *in, const oc_pose *pose, oc_cluster *out) {
+  std::vector<IMUST> xs = poses_in(pose, 1);
+  PointCluster r; r.transform(from_c(*in), xs[0]);
+  to_c(r, *out);
+}
+
+// ---- B0..B3 ---------------------------------------------------------------------------------
+void *orc_factor_create(int win_size) { return new LidarFactor(win_size); }
+void orc_factor_free(void *h) { delete (LidarFactor *)h; }
+int64_t orc_factor_num_voxels(void *h) { return (int64_t)((LidarFactor *)h)->plvec_voxels.size(); }
+int orc_factor_win_size(void *h) { return ((LidarFactor *)h)->win_size; }
+void orc_factor_set_dense(void *h, int64_t V, const oc_cluster *plvec, const oc_cluster *sig, const double *coe,
+                          const double *eigval, const double *eigvec, const oc_cluster *pcr_adds) {
+  LidarFactor &f = *(LidarFactor *)h;
+  f.clear();
+  const int W = f.win_size;
+  for (int64_t v = 0; v < V; v++) {
+    std::vector<PointCluster> pcrs(W);
+    for (int i = 0; i < W; i++) pcrs[i] = from_c(plvec[v * W + i]);
+    V3 ev; M3 evec;
+    for (int k = 0; k < 3; k++) ev[k] = eigval[3 * v + k];
+    for (int k = 0; k < 9; k++) evec[k] = eigvec[9 * v + k];
+    f.push_voxel(pcrs, from_c(sig[v]), coe[v], ev, evec, from_c(pcr_adds[v]));
+  }
+}
+void orc_factor_get_dense(void *h, oc_cluster *plvec, oc_cluster *sig, double *coe, double *eigval, double *eigvec, oc_cluster *pcr_adds) {
+  LidarFactor &f = *(LidarFactor *)h;
+  const int W = f.win_size;
+  for (size_t v = 0; v < f.plvec_voxels.size(); v++) {
+    if (plvec) for (int i = 0; i < W; i++) to_c(f.plvec_voxels[v][i], plvec[v * W + i]);
+    if (sig) to_c(f.sig_vecs[v], sig[v]);
+    if (coe) coe[v] = f.coeffs[v];
+    if (eigval) for (int k = 0; k < 3; k++) eigval[3 * v + k] = f.eig_values[v][k];
+    if (eigvec) for (int k = 0; k < 9; k++) eigvec[9 * v + k] = f.eig_vectors[v][k];
+    if (pcr_adds) to_c(f.pcr_adds[v], pcr_adds[v]);
+  }
+}
+// number of (voxel, frame) pairs with N != 0
+int64_t orc_factor_num_voxel_frames(void *h) {
+  LidarFactor &f = *(LidarFactor *)h;
+  int64_t n = 0;
+  for (auto &pv : f.plvec_voxels) for (auto &c : pv) if (c.N != 0) n++;
+  return n;
+}
+void orc_factor_hessian(void *h, const oc_pose *poses, int64_t head, int64_t end, double *Hess, double *JacT, double *residual) {
+  LidarFactor &f = *(LidarFactor *)h;
+  std::vector<IMUST> xs = poses_in(poses, f.win_size);
+  int jl = 6 * f.win_size;
+  MatX H(jl, jl); VecX J(jl); double r = 0;
+  f.acc_evaluate2(xs, (int)head, (int)end, H, J, r);
+  std::memcpy(Hess, H.d.data(), sizeof(double) * jl * jl);
+  for (int i = 0; i < jl; i++) JacT[i] = J[i];
+  *residual = r;
+}
+void orc_factor_residual(void *h, const oc_pose *poses, int64_t head, int64_t end, double *residual) {
+  LidarFactor &f = *(LidarFactor *)h;
+  std::vector<IMUST> xs = poses_in(poses, f.win_size);
+  double r = 0;
+  f.evaluate_only_residual(xs, (int)head, (int)end, r);
+  *residual = r;
+}
+// Lidar_BA_Optimizer::divide_thread with `thd_num` ranges, optionally on real threads (CPU baseline)
+double orc_ba_divide_thread(void *h, const oc_pose *poses, int thd_num, int use_threads, double *Hess, double *JacT) {
+  LidarFactor &f = *(LidarFactor *)h;
+  std::vector<IMUST> xs = poses_in(poses, f.win_size);
+  Lidar_BA_Optimizer opt;
+  opt.win_size = f.win_size; opt.jac_leng = 6 * f.win_size; opt.thd_num = thd_num; opt.use_threads = use_threads != 0;
+  MatX H(opt.jac_leng, opt.jac_leng); VecX J(opt.jac_leng);
+  double r = opt.divide_thread(xs, f, H, J);
+  if (Hess) std::memcpy(Hess, H.d.data(), sizeof(double) * opt.jac_leng * opt.jac_leng);
+  if (JacT) for (int i = 0; i < opt.jac_leng; i++) JacT[i] = J[i];
+  return r;
+}
+// returns 1 converged, 0 not, -3 where the reference exits ("Too Less Voxel")
+int orc_ba_lidar(void *h, oc_pose *poses, double *hess_out, double *resis2, int max_iter, int thd_num, int use_threads,
+                 int *accept_trace, int *n_trace) {
+  LidarFactor &f = *(LidarFactor *)h;
+  std::vector<IMUST> xs = poses_in(poses, f.win_size);
+  Lidar_BA_Optimizer opt;
+  opt.thd_num = thd_num; opt.use_threads = use_threads != 0;
+  MatX hess; std::vector<double> resis;
+  bool fatal = false;
+  bool conv = opt.damping_iter(xs, f, &hess, resis, max_iter, false, &fatal);
+  if (fatal) return -3;
+  poses_out(xs, poses);
+  if (hess_out) std::memcpy(hess_out, hess.d.data(), sizeof(double) * hess.d.size());
+  if (resis2) { resis2[0] = resis[0]; resis2[1] = resis[1]; }
+  if (n_trace) {
+    *n_trace = (int)opt.accept_trace.size();
+    if (accept_trace) for (size_t i = 0; i < opt.accept_trace.size(); i++) accept_trace[i] = opt.accept_trace[i];
+  }
+  return conv ? 1 : 0;
+}
+
+double orc_now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // extern "C"

@@ -1,0 +1,181 @@
+"""ctypes binding over oracle/liboracle.so — the CPU restatement of the reference (test infrastructure).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
+
+cluster_dtype = np.dtype([("P", "<f8", (9,)), ("v", "<f8", (3,)), ("N", "<i4"), ("_pad", "<i4")], align=True)
+pose_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,))], align=True)
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            import sys
+            sys.path.insert(0, ROOT)
+            import __graft_entry__ as ge
+            ge.build_oracle()
+        _lib = C.CDLL(LIB_PATH)
+        _lib.orc_factor_create.restype = C.c_void_p
+        _lib.orc_factor_num_voxels.restype = C.c_int64
+        _lib.orc_factor_num_voxel_frames.restype = C.c_int64
+        _lib.orc_ba_divide_thread.restype = C.c_double
+        _lib.orc_now.restype = C.c_double
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def as_poses(poses):
+    if isinstance(poses, np.ndarray) and poses.dtype == pose_dtype:
+        return np.ascontiguousarray(poses)
+    R, p = poses
+    R = np.asarray(R, dtype=np.float64)
+    out = np.zeros(R.shape[0], dtype=pose_dtype)
+    out["R"] = np.transpose(R, (0, 2, 1)).reshape(-1, 9)
+    out["p"] = np.asarray(p, dtype=np.float64)
+    return out
+
+
+def poses_to_Rp(ps):
+    R = np.transpose(ps["R"].reshape(-1, 3, 3), (0, 2, 1)).copy()
+    return R, ps["p"].copy()
+
+
+def keys_f64(xyz, voxel_size):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    out = np.zeros(xyz.shape, dtype=np.int64)
+    lib().orc_keys_f64(_p(xyz), C.c_int64(xyz.size // 3), C.c_double(voxel_size), _p(out))
+    return out
+
+
+def keys_f32(xyz, voxel_size):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+    out = np.zeros(xyz.shape, dtype=np.int64)
+    lib().orc_keys_f32(_p(xyz), C.c_int64(xyz.size // 3), C.c_double(voxel_size), _p(out))
+    return out
+
+
+def eig3(A):
+    """A: (n,3,3) symmetric -> (w (n,3) ascending, U (n,3,3) columns = eigenvectors)."""
+    A = np.ascontiguousarray(np.transpose(np.asarray(A, dtype=np.float64), (0, 2, 1)))
+    n = A.shape[0]
+    w = np.zeros((n, 3)); U = np.zeros((n, 9))
+    lib().orc_eig3(_p(A), C.c_int64(n), _p(w), _p(U))
+    return w, np.transpose(U.reshape(n, 3, 3), (0, 2, 1)).copy()
+
+
+def ldlt_solve(A, b):
+    A = np.asarray(A, dtype=np.float64)
+    n = A.shape[0]
+    Ac = np.ascontiguousarray(A.T)  # column-major
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    x = np.zeros(n)
+    lib().orc_ldlt_solve(_p(Ac), _p(b), C.c_int(n), _p(x))
+    return x
+
+
+def inverse15(A):
+    Ac = np.ascontiguousarray(np.asarray(A, dtype=np.float64).T)
+    out = np.zeros((15, 15))
+    lib().orc_inverse15(_p(Ac), _p(out))
+    return out.T.copy()
+
+
+def so3_exp(w):
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    R = np.zeros(9)
+    lib().orc_exp(_p(w), _p(R))
+    return R.reshape(3, 3).T.copy()
+
+
+def so3_log(R):
+    Rc = np.ascontiguousarray(np.asarray(R, dtype=np.float64).T)
+    w = np.zeros(3)
+    lib().orc_log(_p(Rc), _p(w))
+    return w
+
+
+def cluster_transform(cl, pose):
+    cin = np.zeros(1, dtype=cluster_dtype); cin[0] = cl
+    ps = as_poses(pose)
+    out = np.zeros(1, dtype=cluster_dtype)
+    lib().orc_cluster_transform(_p(cin), _p(ps), _p(out))
+    return out[0]
+
+
+class Factor:
+    """orc::LidarFactor (voxel_map.hpp:124-339 restated)."""
+
+    def __init__(self, win_size, handle=None):
+        self.W = win_size
+        self.h = C.c_void_p(handle if handle is not None else lib().orc_factor_create(C.c_int(win_size)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_factor_free(self.h)
+            self.h = None
+
+    @property
+    def num_voxels(self):
+        return int(lib().orc_factor_num_voxels(self.h))
+
+    @property
+    def num_voxel_frames(self):
+        return int(lib().orc_factor_num_voxel_frames(self.h))
+
+    def set_dense(self, fac):
+        a = [np.ascontiguousarray(fac[k]) for k in ("plvec", "sig", "coe", "eigval", "eigvec", "merged")]
+        lib().orc_factor_set_dense(self.h, C.c_int64(a[1].shape[0]), *[_p(x) for x in a])
+
+    def get_dense(self):
+        V, W = self.num_voxels, self.W
+        fac = dict(plvec=np.zeros((V, W), dtype=cluster_dtype), sig=np.zeros(V, dtype=cluster_dtype), coe=np.zeros(V),
+                   eigval=np.zeros((V, 3)), eigvec=np.zeros((V, 9)), merged=np.zeros(V, dtype=cluster_dtype))
+        lib().orc_factor_get_dense(self.h, *[_p(fac[k]) for k in ("plvec", "sig", "coe", "eigval", "eigvec", "merged")])
+        return fac
+
+    def hessian(self, poses, head=0, end=-1):
+        ps = as_poses(poses)
+        if end < 0:
+            end = self.num_voxels
+        jl = 6 * self.W
+        H = np.zeros((jl, jl)); J = np.zeros(jl); c = C.c_double(0)
+        lib().orc_factor_hessian(self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(H), _p(J), C.byref(c))
+        return H.T.copy(), J, c.value
+
+    def residual(self, poses, head=0, end=-1):
+        ps = as_poses(poses)
+        if end < 0:
+            end = self.num_voxels
+        c = C.c_double(0)
+        lib().orc_factor_residual(self.h, _p(ps), C.c_int64(head), C.c_int64(end), C.byref(c))
+        return c.value
+
+    def divide_thread(self, poses, thd_num=2, use_threads=False, want=True):
+        ps = as_poses(poses)
+        jl = 6 * self.W
+        H = np.zeros((jl, jl)) if want else None
+        J = np.zeros(jl) if want else None
+        r = lib().orc_ba_divide_thread(self.h, _p(ps), C.c_int(thd_num), C.c_int(int(use_threads)), _p(H), _p(J))
+        return (H.T.copy() if want else None), J, r
+
+    def ba_lidar(self, poses, max_iter=3, thd_num=2, use_threads=False):
+        ps = as_poses(poses).copy()
+        jl = 6 * self.W
+        hess = np.zeros((jl, jl)); resis = np.zeros(2)
+        trace = np.zeros(max_iter + 1, dtype=np.int32); nt = C.c_int(0)
+        rc = lib().orc_ba_lidar(self.h, _p(ps), _p(hess), _p(resis), C.c_int(max_iter), C.c_int(thd_num),
+                                C.c_int(int(use_threads)), _p(trace), C.byref(nt))
+        return dict(rc=rc, poses=ps, hess=hess.T.copy(), resis=resis, accept=trace[:nt.value].tolist())

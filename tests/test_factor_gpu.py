@@ -1,0 +1,145 @@
+"""GPU parity for the BA evaluation passes, through the C ABI.
+
+Tolerances: cost / lambda / merged cluster <= 1e-12 relative (FP64, reordered sums);
+Hess / JacT <= 1e-9 relative to max|.| (north_star's FP64 figure)."""
+import numpy as np
+import pytest
+
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300)
+
+
+def check_eigvec(U_gpu, U_cpu, lam):
+    # columns equal up to sign where eigenvalues are separated
+    for k in range(3):
+        d = np.abs(np.sum(U_gpu[:, :, k] * U_cpu[:, :, k], axis=1))
+        gap = np.min(np.abs(lam[:, [k]] - np.delete(lam, k, axis=1)), axis=1) / np.max(np.abs(lam), axis=1)
+        ok = gap > 1e-6
+        assert np.all(d[ok] > 1 - 1e-9), (k, d[ok].min())
+
+
+@pytest.mark.parametrize("V,W,occ", [(1, 2, 1.0), (257, 4, 0.5), (3000, 10, 0.6), (500, 20, 0.3)])
+def test_residual_parity(pkg, ob, ctx, V, W, occ):
+    fac = synth.random_factor(100 + V, V, W, occupancy=occ)
+    poses = synth.perturb_poses(fac["poses"], 7, 0.01, 0.03)
+    of = ob.Factor(W); of.set_dense(fac)
+    r_cpu = of.residual(poses)
+    cpu = of.get_dense()
+    f = pkg.Factor(ctx, W)
+    f.upload_dense(fac)
+    assert f.num_voxels == V and f.num_voxel_frames == of.num_voxel_frames
+    r_gpu = f.residual(poses)
+    assert abs(r_gpu - r_cpu) <= 1e-12 * abs(r_cpu)
+    ev, evec, mrg = f.download_cache()
+    assert rel(ev, cpu["eigval"]) < 1e-12
+    lam_scale = np.max(np.abs(cpu["eigval"]), axis=1, keepdims=True)
+    assert np.max(np.abs(ev - cpu["eigval"]) / lam_scale) < 1e-12
+    assert np.array_equal(mrg["N"], cpu["merged"]["N"])
+    assert rel(mrg["P"], cpu["merged"]["P"]) < 1e-13 and rel(mrg["v"], cpu["merged"]["v"]) < 1e-13
+    check_eigvec(evec.reshape(V, 3, 3).transpose(0, 2, 1), cpu["eigvec"].reshape(V, 3, 3).transpose(0, 2, 1), cpu["eigval"])
+    f.free()
+
+
+@pytest.mark.parametrize("V,W,occ", [(1, 2, 1.0), (2, 3, 1.0), (257, 4, 0.5), (3000, 10, 0.6), (500, 20, 0.3), (4000, 10, 1.0)])
+def test_hessian_parity(pkg, ob, ctx, V, W, occ):
+    fac = synth.random_factor(200 + V, V, W, occupancy=occ)
+    poses = synth.perturb_poses(fac["poses"], 9, 0.01, 0.03)
+    of = ob.Factor(W); of.set_dense(fac)
+    Ho, Jo, co = of.hessian(poses)          # uses the uploaded (push-time) cache, voxel_map.hpp:187-190
+    f = pkg.Factor(ctx, W)
+    f.upload_dense(fac)
+    H, J, c = f.hessian(poses)
+    assert abs(c - co) <= 1e-12 * abs(co)
+    assert rel(J, Jo) < 1e-9
+    assert rel(H, Ho) < 1e-9
+    # structure: lower blocks are exact transposes of upper blocks, diagonal blocks are NOT symmetric
+    for i in range(W):
+        for j in range(i):
+            assert np.array_equal(H[6 * i:6 * i + 6, 6 * j:6 * j + 6], H[6 * j:6 * j + 6, 6 * i:6 * i + 6].T)
+    # CSR upload gives bit-identical results (same kernels, same plan)
+    g = pkg.Factor(ctx, W)
+    g.upload_csr(synth.dense_to_csr(fac))
+    H2, J2, c2 = g.hessian(poses)
+    assert np.array_equal(H, H2) and np.array_equal(J, J2) and c == c2
+    f.free(); g.free()
+
+
+def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx):
+    # stateful cache semantics: B1 reads what the LAST B2 wrote
+    V, W = 800, 8
+    fac = synth.random_factor(301, V, W)
+    p1 = synth.perturb_poses(fac["poses"], 1, 0.02, 0.05)
+    of = ob.Factor(W); of.set_dense(fac)
+    f = pkg.Factor(ctx, W); f.upload_dense(fac)
+    of.residual(p1); f.residual(p1)
+    Ho, Jo, co = of.hessian(p1)
+    H, J, c = f.hessian(p1)
+    assert abs(c - co) <= 1e-12 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+    f.free()
+
+
+def test_head_end_subrange(pkg, ob, ctx):
+    V, W = 600, 5
+    fac = synth.random_factor(401, V, W)
+    poses = fac["poses"]
+    of = ob.Factor(W); of.set_dense(fac)
+    f = pkg.Factor(ctx, W); f.upload_dense(fac)
+    for head, end in [(0, 300), (300, 600), (17, 18), (0, 0)]:
+        Ho, Jo, co = of.hessian(poses, head, end)
+        H, J, c = f.hessian(poses, head, end)
+        if end > head:
+            assert abs(c - co) <= 1e-12 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+        else:
+            assert c == 0 and not H.any() and not J.any()
+        assert abs(f.residual(poses, head, end) - of.residual(poses, head, end)) <= 1e-12 * max(abs(co), 1e-300)
+    f.free()
+
+
+def test_empty_and_reupload(pkg, ctx):
+    f = pkg.Factor(ctx, 4)
+    R, p = synth.random_poses(1, 4)
+    H, J, c = f.hessian((R, p))
+    assert c == 0 and not H.any() and not J.any()
+    assert f.residual((R, p)) == 0
+    fac = synth.random_factor(5, 50, 4)
+    f.upload_dense(fac)
+    r1 = f.residual(fac["poses"])
+    f.upload_dense(synth.random_factor(6, 20, 4))
+    assert f.num_voxels == 20
+    f.upload_dense(fac)
+    assert f.residual(fac["poses"]) == r1     # deterministic
+    f.free()
+
+
+def test_batched_windows_match_single(pkg, ctx):
+    # n_windows independent factors in one launch == each evaluated alone, bit for bit
+    W, NW = 5, 7
+    facs = [synth.random_factor(500 + b, 120 + 10 * b, W) for b in range(NW)]
+    csr = [synth.dense_to_csr(fc) for fc in facs]
+    off = [0]; frames = []; parts = {k: [] for k in ("clusters", "sig", "coe", "eigval", "eigvec", "merged")}
+    for b, c in enumerate(csr):
+        off += (c["offsets"][1:] + off[-1]).tolist()
+        frames.append(c["frames"] + b * W)
+        for k in parts:
+            parts[k].append(c[k])
+    big = {k: np.concatenate(v) for k, v in parts.items()}
+    big["offsets"] = np.array(off, dtype=np.int64)
+    big["frames"] = np.concatenate(frames)
+    R = np.concatenate([fc["poses"][0] for fc in facs]); p = np.concatenate([fc["poses"][1] for fc in facs])
+    fb = pkg.Factor(ctx, W, NW)
+    fb.upload_csr(big)
+    rb = fb.residual((R, p))
+    Hb, Jb, cb = fb.hessian((R, p))
+    for b in range(NW):
+        f1 = pkg.Factor(ctx, W); f1.upload_dense(facs[b])
+        r1 = f1.residual(facs[b]["poses"])
+        H1, J1, c1 = f1.hessian(facs[b]["poses"])
+        assert abs(rb[b] - r1) <= 1e-13 * abs(r1)
+        assert rel(Hb[b], H1) < 1e-12 and rel(Jb[b], J1) < 1e-12 and abs(cb[b] - c1) <= 1e-13 * abs(c1)
+        f1.free()
+    fb.free()

@@ -1,0 +1,189 @@
+"""voxel_slam_b200 — ctypes host binding over libvoxelba.so (the C ABI in include/voxelba.h).
+
+This is plumbing for tests/ and bench.py: every compute call goes through the C ABI into the
+hand-written sm_100a kernels under csrc/.  There is no Python or CPU implementation of the hot
+path here; if the shared library is missing or no CUDA device is present the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvoxelba.so")
+_lib = None
+
+# numpy mirrors of the POD structs in include/voxelba.h
+cluster_dtype = np.dtype([("P", "<f8", (9,)), ("v", "<f8", (3,)), ("N", "<i4"), ("_pad", "<i4")], align=True)
+pose_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,))], align=True)
+assert cluster_dtype.itemsize == 104 and pose_dtype.itemsize == 96
+
+VX_OK = 0
+ERR_NAMES = {-1: "VX_ERR_CUDA", -2: "VX_ERR_ARG", -3: "VX_ERR_TOO_FEW", -4: "VX_ERR_OPT_STATE", -5: "VX_ERR_NOMEM"}
+
+
+class VxError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("%s (%d): %s" % (ERR_NAMES.get(code, "VX_ERR"), code, text))
+        self.code = code
+
+
+def load_library():
+    """dlopen libvoxelba.so; fails loudly when the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libvoxelba.so is missing at %s — run `python __graft_entry__.py` (nvcc, sm_100a). "
+                          "There is no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    lib.vx_last_error.restype = C.c_char_p
+    lib.vx_ctx_stream.restype = C.c_void_p
+    lib.vx_ctx_stream.argtypes = [C.c_void_p]
+    lib.vx_ctx_launch_count.restype = C.c_int64
+    lib.vx_ctx_launch_count.argtypes = [C.c_void_p]
+    for name in ("vx_factor_num_voxels", "vx_factor_num_voxel_frames"):
+        getattr(lib, name).restype = C.c_int64
+        getattr(lib, name).argtypes = [C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def _chk(code):
+    if code != VX_OK:
+        raise VxError(code, load_library().vx_last_error().decode("utf-8", "replace"))
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def as_poses(poses):
+    """(F,3,3) rotations + (F,3) translations, or a pose_dtype array -> contiguous pose_dtype array."""
+    if isinstance(poses, np.ndarray) and poses.dtype == pose_dtype:
+        return np.ascontiguousarray(poses)
+    R, p = poses
+    R = np.asarray(R, dtype=np.float64)
+    out = np.zeros(R.shape[0], dtype=pose_dtype)
+    out["R"] = np.transpose(R, (0, 2, 1)).reshape(-1, 9)  # column-major
+    out["p"] = np.asarray(p, dtype=np.float64)
+    return out
+
+
+class Context:
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        _chk(self.lib.vx_ctx_create(C.c_int(device), C.byref(h)))
+        self.h = h
+        self.device = device
+        self.launch_count_last = 0
+
+    @property
+    def stream(self):
+        return self.lib.vx_ctx_stream(self.h)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.vx_ctx_launch_count(self.h))
+
+    def sync(self):
+        _chk(self.lib.vx_ctx_sync(self.h))
+
+    def close(self):
+        if self.h:
+            self.launch_count_last = self.launch_count
+            self.lib.vx_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class DevArray:
+    """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
+
+    def __init__(self, ptr, shape, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class Factor:
+    """Device-resident LidarFactor / VOX_HESS (voxel_map.hpp:124-339)."""
+
+    def __init__(self, ctx, win_size, n_windows=1):
+        self.ctx, self.lib = ctx, ctx.lib
+        self.W, self.n_win = win_size, n_windows
+        h = C.c_void_p()
+        _chk(self.lib.vx_factor_create(ctx.h, C.c_int(win_size), C.c_int(n_windows), C.byref(h)))
+        self.h = h
+
+    def free(self):
+        if self.h:
+            self.lib.vx_factor_free(self.h)
+            self.h = None
+
+    @property
+    def num_voxels(self):
+        return int(self.lib.vx_factor_num_voxels(self.h))
+
+    @property
+    def num_voxel_frames(self):
+        return int(self.lib.vx_factor_num_voxel_frames(self.h))
+
+    def upload_dense(self, fac):
+        """fac: dict with plvec (V,W) cluster, sig (V,), coe (V,), eigval (V,3), eigvec (V,9), merged (V,)."""
+        V = fac["sig"].shape[0]
+        self._keep = [np.ascontiguousarray(fac[k]) for k in ("plvec", "sig", "coe", "eigval", "eigvec", "merged")]
+        a = self._keep
+        _chk(self.lib.vx_factor_upload_dense(self.h, C.c_int64(V), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(a[5])))
+
+    def upload_csr(self, fac):
+        """fac: dict with offsets (V+1,) i8, frames (nnz,) i4, clusters (nnz,), sig, coe, eigval, eigvec, merged."""
+        V = fac["sig"].shape[0]
+        a = [np.ascontiguousarray(fac["offsets"], dtype=np.int64), np.ascontiguousarray(fac["frames"], dtype=np.int32)] + \
+            [np.ascontiguousarray(fac[k]) for k in ("clusters", "sig", "coe", "eigval", "eigvec", "merged")]
+        self._keep = a
+        _chk(self.lib.vx_factor_upload_csr(self.h, C.c_int64(V), *[_p(x) for x in a]))
+
+    def download_cache(self):
+        V = self.num_voxels
+        ev = np.zeros((V, 3)); evec = np.zeros((V, 9)); mrg = np.zeros(V, dtype=cluster_dtype)
+        _chk(self.lib.vx_factor_download_cache(self.h, _p(ev), _p(evec), _p(mrg)))
+        return ev, evec, mrg
+
+    def hessian(self, poses, head=0, end=-1):
+        ps = as_poses(poses)
+        jl = 6 * self.W
+        H = np.zeros((self.n_win, jl, jl)); J = np.zeros((self.n_win, jl)); c = np.zeros(self.n_win)
+        _chk(self.lib.vx_factor_hessian(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(H), _p(J), _p(c)))
+        H = np.transpose(H, (0, 2, 1))  # column-major -> numpy [row, col]
+        if self.n_win == 1:
+            return H[0], J[0], float(c[0])
+        return H, J, c
+
+    def residual(self, poses, head=0, end=-1):
+        ps = as_poses(poses)
+        c = np.zeros(self.n_win)
+        _chk(self.lib.vx_factor_residual(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(c)))
+        return float(c[0]) if self.n_win == 1 else c
+
+    # device-resident path
+    def set_poses(self, poses):
+        self._poses_keep = as_poses(poses)
+        _chk(self.lib.vx_factor_set_poses(self.ctx.h, self.h, _p(self._poses_keep)))
+
+    def hessian_async(self, head=0, end=-1):
+        _chk(self.lib.vx_factor_hessian_async(self.ctx.h, self.h, C.c_int64(head), C.c_int64(end)))
+
+    def residual_async(self, head=0, end=-1):
+        _chk(self.lib.vx_factor_residual_async(self.ctx.h, self.h, C.c_int64(head), C.c_int64(end)))
+
+    def device_buffers(self):
+        ptrs = [C.c_void_p() for _ in range(4)]
+        _chk(self.lib.vx_factor_device_buffers(self.h, *[C.byref(p) for p in ptrs]))
+        jl = 6 * self.W
+        return (DevArray(ptrs[0].value, (self.n_win, jl, jl)), DevArray(ptrs[1].value, (self.n_win, jl)),
+                DevArray(ptrs[2].value, (self.n_win,)), DevArray(ptrs[3].value, (self.n_win,)))

@@ -1,0 +1,83 @@
+// vx_common.cuh — shared internals of libvoxelba (context, error plumbing, device buffers).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdarg>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/voxelba.h"
+
+namespace vx {
+
+void set_error(const char *fmt, ...);
+
+#define VX_CUDA(call)                                                                        \
+  do {                                                                                       \
+    cudaError_t _e = (call);                                                                 \
+    if (_e != cudaSuccess) {                                                                 \
+      vx::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e));    \
+      return VX_ERR_CUDA;                                                                    \
+    }                                                                                        \
+  } while (0)
+
+#define VX_TRY(call)                 \
+  do {                               \
+    int _s = (call);                 \
+    if (_s != VX_OK) return _s;      \
+  } while (0)
+
+#define VX_ARG(cond)                                                       \
+  do {                                                                     \
+    if (!(cond)) {                                                         \
+      vx::set_error("%s:%d bad argument: %s", __FILE__, __LINE__, #cond);  \
+      return VX_ERR_ARG;                                                   \
+    }                                                                      \
+  } while (0)
+
+// Grow-only device buffer (byte-addressed).  Freed with the owner.
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return VX_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { set_error("cudaMalloc(%zu) -> %s", want, cudaGetErrorString(e)); return VX_ERR_NOMEM; }
+    cap = want;
+    return VX_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T *as() const { return (T *)p; }
+};
+
+}  // namespace vx
+
+struct vx_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int sm_count = 148;
+  int64_t launches = 0;
+  vx::DevBuf scratch;        // CUB temp storage and short-lived work arrays
+  vx::DevBuf scratch2;
+  void *pinned = nullptr;    // small pinned staging area for scalar read-backs
+  size_t pinned_cap = 0;
+};
+
+namespace vx {
+inline int bind(vx_ctx *ctx) {
+  VX_ARG(ctx != nullptr);
+  VX_CUDA(cudaSetDevice(ctx->device));
+  return VX_OK;
+}
+inline int blocks_for(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+}  // namespace vx
+
+#define VX_LAUNCH_CHECK(ctx)                    \
+  do {                                          \
+    (ctx)->launches++;                          \
+    VX_CUDA(cudaGetLastError());                \
+  } while (0)

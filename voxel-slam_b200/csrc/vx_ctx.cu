@@ -1,0 +1,62 @@
+// vx_ctx.cu — context, error text, version.
+#include "vx_common.cuh"
+
+namespace vx {
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+}  // namespace vx
+
+extern "C" {
+
+const char *vx_last_error(void) { return vx::g_err; }
+int vx_version(void) { return 100; }
+
+int vx_ctx_create(int device, vx_ctx **out) {
+  VX_ARG(out != nullptr);
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) {
+    vx::set_error("no CUDA device (cudaGetDeviceCount: %s); libvoxelba has no CPU fallback", cudaGetErrorString(e));
+    return VX_ERR_CUDA;
+  }
+  VX_ARG(device >= 0 && device < ndev);
+  VX_CUDA(cudaSetDevice(device));
+  vx_ctx *c = new vx_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  VX_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  VX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->pinned_cap = 1 << 16;
+  VX_CUDA(cudaMallocHost(&c->pinned, c->pinned_cap));
+  *out = c;
+  return VX_OK;
+}
+
+int vx_ctx_destroy(vx_ctx *ctx) {
+  if (!ctx) return VX_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+  ctx->scratch.release();
+  ctx->scratch2.release();
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  delete ctx;
+  return VX_OK;
+}
+
+int vx_ctx_sync(vx_ctx *ctx) {
+  VX_TRY(vx::bind(ctx));
+  VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VX_OK;
+}
+
+void *vx_ctx_stream(vx_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+int64_t vx_ctx_launch_count(vx_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+}  // extern "C"

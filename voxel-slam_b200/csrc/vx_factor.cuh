@@ -1,0 +1,51 @@
+// vx_factor.cuh — device-resident LidarFactor (reference: class LidarFactor, voxel_map.hpp:124-339).
+//
+// HBM layout (all SoA, "planes" = component-major so a warp reading one component of 32 consecutive
+// records issues one coalesced request):
+//   voxel-major CSR over voxel-frames (a voxel-frame = a (voxel, frame) pair with N != 0):
+//     off[V+1]            int32   first voxel-frame of each voxel
+//     frame[nnz]          int32   global frame id (window*W + frame) of each voxel-frame, ascending per voxel
+//     vox[nnz]            int32   owning voxel
+//     mom[9][nnz]         double  P00 P01 P02 P11 P12 P22 v0 v1 v2 of the scan-local PointCluster
+//     cnt[nnz]            int32   N of the cluster                      -> 76 B per voxel-frame (+8 B index)
+//   per voxel:
+//     fix[10][V]          double  sig_vecs (P6, v3, N)
+//     coe[V]              double
+//     lam[3][V] U[9][V]   double  cached eig_values / eig_vectors (column-major U)
+//     mrg[10][V]          double  cached pcr_adds (P6, v3, N)
+//     win[V]              int32   window of the voxel (batch mode), voxels sorted by window
+#pragma once
+#include "vx_common.cuh"
+
+struct vx_factor {
+  vx_ctx *ctx = nullptr;
+  int W = 0, n_win = 1;
+  int64_t V = 0, nnz = 0;
+  int F() const { return W * n_win; }
+
+  // content
+  vx::DevBuf off, frame, vox, mom, cnt, fix, coe, lam, U, mrg, win, wv_off;
+  // evaluation state
+  vx::DevBuf poses;                 // F x 12 doubles
+  vx::DevBuf H, J, cost_h, cost_r;  // outputs
+  vx::DevBuf cS;                    // [3][V] coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}
+  vx::DevBuf res_v;                 // [V] coe * lambda_0
+  vx::DevBuf G;                     // [nnz][18] per voxel-frame rows g1 g2 w
+  // reduction plans (built on device at upload)
+  bool plan_ready = false;
+  vx::DevBuf fm_order, fm_off;                          // frame-major order of voxel-frames
+  vx::DevBuf dseg_frame, dseg_beg, dseg_end, dseg_off;  // diagonal-tile segments
+  vx::DevBuf pair_ab;                                   // packed (a<<32 | b), sorted by tile
+  vx::DevBuf tile_key, tile_off;                        // tile = (frame_i * F + frame_j), i<j
+  vx::DevBuf oseg_tile, oseg_beg, oseg_end, oseg_off;   // off-diagonal tile segments
+  vx::DevBuf dpart, opart;                              // per-segment partial sums
+  int64_t n_pairs = 0, n_tiles = 0, n_dseg = 0, n_oseg = 0;
+  int seg_len = 1024;
+};
+
+namespace vx {
+// (Re)builds vox[], the frame-major order and the tile/segment plans from off[]/frame[] on device.
+int factor_build_plan(vx_factor *f);
+// Allocates per-voxel / per-voxel-frame arrays for V voxels and nnz voxel-frames.
+int factor_alloc(vx_factor *f, int64_t V, int64_t nnz);
+}  // namespace vx
