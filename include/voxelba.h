@@ -58,6 +58,14 @@ int vx_version(void);
 /* number of kernels this library launched on `ctx` since creation (bench.py: gpu_launches) */
 int64_t vx_ctx_launch_count(vx_ctx *ctx);
 
+/* Per-kernel device timing for bench.py's roofline leg (the reference brackets the same stages with
+ * ros::Time, voxel_map.hpp:639-650).  While enabled, every kernel this library launches on `ctx` is
+ * bracketed by two CUDA events on the ctx stream.  profile_read synchronises, then returns one
+ * entry per kernel name: newline-separated names, summed milliseconds and launch counts. */
+int vx_ctx_profile(vx_ctx *ctx, int enable);   /* also clears what was recorded */
+int vx_ctx_profile_read(vx_ctx *ctx, char *names, size_t names_cap, double *ms, int64_t *counts,
+                        int max_entries, int *n_out);
+
 /* ---- B0: LidarFactor storage -------------------------------------------------------------- */
 /* LidarFactor::LidarFactor(int _w)  voxel_map.hpp:136.  `n_windows` > 1 makes a BATCH of
  * independent factors that share W (bottom-level GBA windows, voxelslam.cpp:3096): frame f of

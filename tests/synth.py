@@ -110,3 +110,105 @@ def dense_to_csr(fac):
     out["frames"] = fi.astype(np.int32)
     out["clusters"] = np.ascontiguousarray(fac["plvec"][vi, fi])
     return out
+
+
+def _rodrigues_batch(w):
+    """(n,3) rotation vectors -> (n,3,3)."""
+    w = np.asarray(w, dtype=np.float64)
+    th = np.linalg.norm(w, axis=1)
+    k = w / np.maximum(th, 1e-300)[:, None]
+    K = np.zeros((w.shape[0], 3, 3))
+    K[:, 0, 1] = -k[:, 2]; K[:, 0, 2] = k[:, 1]
+    K[:, 1, 0] = k[:, 2]; K[:, 1, 2] = -k[:, 0]
+    K[:, 2, 0] = -k[:, 1]; K[:, 2, 1] = k[:, 0]
+    s = np.sin(th)[:, None, None]; c = (1 - np.cos(th))[:, None, None]
+    return np.eye(3)[None] + s * K + c * (K @ K)
+
+
+def batched_factor_csr(seed, n_windows, voxels_per_window, W, occupancy=0.6, noise=0.01, pts_max=24,
+                       min_frames=2, chunk_windows=16):
+    """Vectorised generator of a BATCH of independent LidarFactors in the CSR upload form
+    (include/voxelba.h: vx_factor_upload_csr): `n_windows` bottom-level GBA windows
+    (voxelslam.cpp:3096) of `W` keyframes, `voxels_per_window` plane voxels each; voxel a of window b
+    is seen by a random subset (>= min_frames, the loop_refine.hpp:372-376 gate) of the window's frames.
+    Clusters are exact moments of sampled planar points; the cache (eigval/eigvec/merged) is
+    consistent with the returned poses, as OctreeGBA::recut leaves it (loop_refine.hpp:363-387)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    F = n_windows * W
+    # per-window trajectory: a gentle arc (C1-like: ~1 m / ~4 deg between poses) about a random start
+    yaw = np.cumsum(rng.normal(0.07, 0.02, (n_windows, W)), axis=1)
+    rv = np.zeros((F, 3)); rv[:, 2] = yaw.reshape(-1); rv[:, :2] = rng.normal(0, 0.02, (F, 2))
+    R = _rodrigues_batch(rv)
+    step = np.stack([np.cos(yaw), np.sin(yaw), np.zeros_like(yaw)], axis=2) * rng.uniform(0.8, 1.2, (n_windows, W, 1))
+    p = (np.cumsum(step, axis=1) + rng.uniform(-100, 100, (n_windows, 1, 3)) * np.array([1, 1, 0.02])).reshape(F, 3)
+
+    offs = [np.zeros(1, dtype=np.int64)]
+    out = {k: [] for k in ("frames", "clusters", "sig", "coe", "eigval", "eigvec", "merged")}
+    base = 0
+    for w0 in range(0, n_windows, chunk_windows):
+        nw = min(chunk_windows, n_windows - w0)
+        V = nw * voxels_per_window
+        win = np.repeat(np.arange(w0, w0 + nw), voxels_per_window)
+        n = rng.normal(size=(V, 3)); n /= np.linalg.norm(n, axis=1, keepdims=True)
+        ref = np.where(np.abs(n[:, :1]) < 0.9, np.array([[1.0, 0, 0]]), np.array([[0, 1.0, 0]]))
+        t1 = np.cross(n, ref); t1 /= np.linalg.norm(t1, axis=1, keepdims=True)
+        t2 = np.cross(n, t1)
+        ctr = p[win * W + W // 2] + rng.uniform(-12, 12, (V, 3)) * np.array([1, 1, 0.2])
+        ext = 0.4 * rng.uniform(0.5, 1.5, (V, 2))
+        occ = rng.random((V, W)) < occupancy
+        short = occ.sum(axis=1) < min_frames
+        while short.any():
+            idx = np.nonzero(short)[0]
+            occ[idx, rng.integers(0, W, idx.size)] = True
+            short = occ.sum(axis=1) < min_frames
+        vi, fi = np.nonzero(occ)
+        nnz = vi.size
+        g = win[vi] * W + fi
+        cnt = rng.integers(6, pts_max + 1, nnz)
+        mask = (np.arange(pts_max)[None, :] < cnt[:, None]).astype(np.float64)
+        uv = rng.uniform(-1, 1, (nnz, pts_max, 2)) * ext[vi][:, None, :]
+        wpts = ctr[vi][:, None, :] + uv[:, :, :1] * t1[vi][:, None, :] + uv[:, :, 1:] * t2[vi][:, None, :] \
+            + rng.normal(0, noise, (nnz, pts_max, 1)) * n[vi][:, None, :]
+        loc = np.einsum("npi,nij->npj", wpts - p[g][:, None, :], R[g])      # R^T (w - p)
+        loc_m = loc * mask[:, :, None]
+        w_m = wpts * mask[:, :, None]
+        cl = np.zeros(nnz, dtype=cluster_dtype)
+        cl["P"] = np.einsum("npi,npj->nij", loc_m, loc).reshape(nnz, 9)
+        cl["v"] = loc_m.sum(axis=1)
+        cl["N"] = cnt
+        off = np.zeros(V + 1, dtype=np.int64); off[1:] = np.cumsum(occ.sum(axis=1))
+        Pw = np.add.reduceat(np.einsum("npi,npj->nij", w_m, wpts).reshape(nnz, 9), off[:-1], axis=0)
+        vw = np.add.reduceat(w_m.sum(axis=1), off[:-1], axis=0)
+        Nw = np.add.reduceat(cnt, off[:-1])
+        mg = np.zeros(V, dtype=cluster_dtype)
+        mg["P"] = Pw; mg["v"] = vw; mg["N"] = Nw
+        cen = vw / Nw[:, None]
+        cov = Pw.reshape(V, 3, 3) / Nw[:, None, None] - cen[:, :, None] * cen[:, None, :]
+        lam, U = np.linalg.eigh(cov)
+        out["frames"].append(g.astype(np.int32)); out["clusters"].append(cl)
+        out["sig"].append(np.zeros(V, dtype=cluster_dtype)); out["coe"].append(np.ones(V))
+        out["eigval"].append(lam); out["eigvec"].append(np.transpose(U, (0, 2, 1)).reshape(V, 9))
+        out["merged"].append(mg)
+        offs.append(off[1:] + base); base += nnz
+    fac = {k: np.concatenate(v) for k, v in out.items()}
+    fac["offsets"] = np.concatenate(offs)
+    fac["poses"] = (R, p)
+    fac["W"] = W; fac["n_windows"] = n_windows
+    return fac
+
+
+def csr_window(fac, b):
+    """Extract window b of a batched CSR factor as a dense single-window factor dict (for the oracle)."""
+    W = fac["W"]
+    off = fac["offsets"]
+    fr = fac["frames"]
+    first = fr[off[:-1]] // W
+    vs = np.nonzero(first == b)[0]
+    V = vs.size
+    plvec = np.zeros((V, W), dtype=cluster_dtype)
+    for k, v in enumerate(vs):
+        e0, e1 = off[v], off[v + 1]
+        plvec[k, fr[e0:e1] - b * W] = fac["clusters"][e0:e1]
+    R, p = fac["poses"]
+    return dict(plvec=plvec, sig=fac["sig"][vs], coe=fac["coe"][vs], eigval=fac["eigval"][vs], eigvec=fac["eigvec"][vs],
+                merged=fac["merged"][vs], poses=(R[b * W:(b + 1) * W], p[b * W:(b + 1) * W]))

@@ -1,7 +1,10 @@
 """GPU parity for the BA evaluation passes, through the C ABI.
 
-Tolerances: cost / lambda / merged cluster <= 1e-12 relative (FP64, reordered sums);
-Hess / JacT <= 1e-9 relative to max|.| (north_star's FP64 figure)."""
+Tolerances: cost, Hess, JacT <= 1e-9 relative to max|.| (north_star's FP64 figure); merged cluster
+<= 1e-13 relative (reordered FP64 sums).  Eigenvalues: the reference forms cov = P/N - c c^T
+(tools.hpp:333-337), which cancels |c|^2 against the plane thickness, so lambda is only defined to
+eps * max|P/N| ABSOLUTE; the test bounds |dlambda| by 1e-12 * max|P/N| per voxel, not relative to
+lambda_0 itself."""
 import numpy as np
 import pytest
 
@@ -34,11 +37,10 @@ def test_residual_parity(pkg, ob, ctx, V, W, occ):
     f.upload_dense(fac)
     assert f.num_voxels == V and f.num_voxel_frames == of.num_voxel_frames
     r_gpu = f.residual(poses)
-    assert abs(r_gpu - r_cpu) <= 1e-12 * abs(r_cpu)
+    assert abs(r_gpu - r_cpu) <= 1e-9 * abs(r_cpu)
     ev, evec, mrg = f.download_cache()
-    assert rel(ev, cpu["eigval"]) < 1e-12
-    lam_scale = np.max(np.abs(cpu["eigval"]), axis=1, keepdims=True)
-    assert np.max(np.abs(ev - cpu["eigval"]) / lam_scale) < 1e-12
+    scale = np.max(np.abs(cpu["merged"]["P"]), axis=1, keepdims=True) / cpu["merged"]["N"][:, None]
+    assert np.max(np.abs(ev - cpu["eigval"]) / scale) < 1e-12
     assert np.array_equal(mrg["N"], cpu["merged"]["N"])
     assert rel(mrg["P"], cpu["merged"]["P"]) < 1e-13 and rel(mrg["v"], cpu["merged"]["v"]) < 1e-13
     check_eigvec(evec.reshape(V, 3, 3).transpose(0, 2, 1), cpu["eigvec"].reshape(V, 3, 3).transpose(0, 2, 1), cpu["eigval"])
@@ -54,7 +56,7 @@ def test_hessian_parity(pkg, ob, ctx, V, W, occ):
     f = pkg.Factor(ctx, W)
     f.upload_dense(fac)
     H, J, c = f.hessian(poses)
-    assert abs(c - co) <= 1e-12 * abs(co)
+    assert abs(c - co) <= 1e-9 * abs(co)
     assert rel(J, Jo) < 1e-9
     assert rel(H, Ho) < 1e-9
     # structure: lower blocks are exact transposes of upper blocks, diagonal blocks are NOT symmetric
@@ -79,7 +81,7 @@ def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx):
     of.residual(p1); f.residual(p1)
     Ho, Jo, co = of.hessian(p1)
     H, J, c = f.hessian(p1)
-    assert abs(c - co) <= 1e-12 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+    assert abs(c - co) <= 1e-9 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
     f.free()
 
 
@@ -93,10 +95,10 @@ def test_head_end_subrange(pkg, ob, ctx):
         Ho, Jo, co = of.hessian(poses, head, end)
         H, J, c = f.hessian(poses, head, end)
         if end > head:
-            assert abs(c - co) <= 1e-12 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+            assert abs(c - co) <= 1e-9 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
         else:
             assert c == 0 and not H.any() and not J.any()
-        assert abs(f.residual(poses, head, end) - of.residual(poses, head, end)) <= 1e-12 * max(abs(co), 1e-300)
+        assert abs(f.residual(poses, head, end) - of.residual(poses, head, end)) <= 1e-9 * max(abs(co), 1e-300)
     f.free()
 
 

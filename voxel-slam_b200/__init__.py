@@ -90,6 +90,18 @@ class Context:
     def sync(self):
         _chk(self.lib.vx_ctx_sync(self.h))
 
+    def profile(self, enable=True):
+        """Start (and clear) / stop per-kernel CUDA-event timing of this context's launches."""
+        _chk(self.lib.vx_ctx_profile(self.h, C.c_int(int(enable))))
+
+    def profile_read(self):
+        """-> {kernel name: (total ms, launches)} since profile(True)."""
+        names = C.create_string_buffer(8192)
+        ms = np.zeros(128); cnt = np.zeros(128, dtype=np.int64); n = C.c_int(0)
+        _chk(self.lib.vx_ctx_profile_read(self.h, names, C.c_size_t(8192), _p(ms), _p(cnt), C.c_int(128), C.byref(n)))
+        nm = names.value.decode().split("\n")
+        return {nm[i]: (float(ms[i]), int(cnt[i])) for i in range(n.value)}
+
     def close(self):
         if self.h:
             self.launch_count_last = self.launch_count

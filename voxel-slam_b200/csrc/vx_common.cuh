@@ -54,6 +54,9 @@ struct DevBuf {
   template <class T> T *as() const { return (T *)p; }
 };
 
+// Optional per-kernel device timing (bench.py's roofline leg): when enabled every VX_LAUNCH_CHECK'd
+// launch is bracketed by two events on the context stream; vx_ctx_profile_read sums them by name.
+struct ProfSpan { const char *name; cudaEvent_t a, b; };
 }  // namespace vx
 
 struct vx_ctx {
@@ -61,6 +64,9 @@ struct vx_ctx {
   cudaStream_t stream = nullptr;
   int sm_count = 148;
   int64_t launches = 0;
+  bool profiling = false;
+  std::vector<vx::ProfSpan> spans;
+  cudaEvent_t prof_open = nullptr;
   vx::DevBuf scratch;        // CUB temp storage and short-lived work arrays
   vx::DevBuf scratch2;
   void *pinned = nullptr;    // small pinned staging area for scalar read-backs
@@ -80,4 +86,22 @@ inline int blocks_for(int64_t n, int threads) { return (int)((n + threads - 1) /
   do {                                          \
     (ctx)->launches++;                          \
     VX_CUDA(cudaGetLastError());                \
+  } while (0)
+
+// Launch a kernel under a name: VX_KERNEL(ctx, "k_name", k_name<<<g, b, s, st>>>(args...));
+#define VX_KERNEL(ctx, name, ...)                                           \
+  do {                                                                      \
+    cudaEvent_t _ea = nullptr, _eb = nullptr;                               \
+    if ((ctx)->profiling) {                                                 \
+      VX_CUDA(cudaEventCreate(&_ea));                                       \
+      VX_CUDA(cudaEventCreate(&_eb));                                       \
+      VX_CUDA(cudaEventRecord(_ea, (ctx)->stream));                         \
+    }                                                                       \
+    __VA_ARGS__;                                                            \
+    (ctx)->launches++;                                                      \
+    VX_CUDA(cudaGetLastError());                                            \
+    if ((ctx)->profiling) {                                                 \
+      VX_CUDA(cudaEventRecord(_eb, (ctx)->stream));                         \
+      (ctx)->spans.push_back(vx::ProfSpan{name, _ea, _eb});                 \
+    }                                                                       \
   } while (0)

@@ -43,6 +43,7 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   if (!ctx) return VX_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+  for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
   ctx->scratch.release();
   ctx->scratch2.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
@@ -53,6 +54,47 @@ int vx_ctx_destroy(vx_ctx *ctx) {
 int vx_ctx_sync(vx_ctx *ctx) {
   VX_TRY(vx::bind(ctx));
   VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VX_OK;
+}
+
+int vx_ctx_profile(vx_ctx *ctx, int enable) {
+  VX_TRY(vx::bind(ctx));
+  VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+  ctx->spans.clear();
+  ctx->profiling = enable != 0;
+  return VX_OK;
+}
+
+int vx_ctx_profile_read(vx_ctx *ctx, char *names, size_t names_cap, double *ms, int64_t *counts, int max_entries, int *n_out) {
+  VX_TRY(vx::bind(ctx));
+  VX_ARG(n_out != nullptr);
+  VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  std::vector<const char *> nm;
+  std::vector<double> tot;
+  std::vector<int64_t> cnt;
+  for (auto &s : ctx->spans) {
+    float t = 0.f;
+    VX_CUDA(cudaEventElapsedTime(&t, s.a, s.b));
+    size_t k = 0;
+    for (; k < nm.size(); k++) if (strcmp(nm[k], s.name) == 0) break;
+    if (k == nm.size()) { nm.push_back(s.name); tot.push_back(0.0); cnt.push_back(0); }
+    tot[k] += t; cnt[k] += 1;
+  }
+  int n = 0;
+  size_t used = 0;
+  if (names && names_cap) names[0] = 0;
+  for (size_t k = 0; k < nm.size() && n < max_entries; k++) {
+    size_t len = strlen(nm[k]);
+    if (names) {
+      if (used + len + 2 > names_cap) break;
+      memcpy(names + used, nm[k], len); used += len; names[used++] = '\n'; names[used] = 0;
+    }
+    if (ms) ms[n] = tot[k];
+    if (counts) counts[n] = cnt[k];
+    n++;
+  }
+  *n_out = n;
   return VX_OK;
 }
 

@@ -581,14 +581,12 @@ __global__ void k_fin_off(const int64_t *__restrict__ tile_key, const int32_t *_
 static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   cudaStream_t st = ctx->stream;
   if (f->V > 0) {
-    k_residual<<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>(
+    VX_KERNEL(ctx, "k_residual", k_residual<<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>(
         f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(),
         f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(),
-        f->res_v.as<double>(), f->V, head, end);
-    VX_LAUNCH_CHECK(ctx);
+        f->res_v.as<double>(), f->V, head, end));
   }
-  k_cost<false><<<f->n_win, 256, 0, st>>>(f->res_v.as<double>(), nullptr, f->wv_off.as<int32_t>(), f->cost_r.as<double>(), head, end);
-  VX_LAUNCH_CHECK(ctx);
+  VX_KERNEL(ctx, "k_cost", k_cost<false><<<f->n_win, 256, 0, st>>>(f->res_v.as<double>(), nullptr, f->wv_off.as<int32_t>(), f->cost_r.as<double>(), head, end));
   return VX_OK;
 }
 
@@ -599,37 +597,70 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) 
   VX_CUDA(cudaMemsetAsync(f->H.p, 0, sizeof(double) * jl * jl * f->n_win, st));
   VX_CUDA(cudaMemsetAsync(f->J.p, 0, sizeof(double) * jl * f->n_win, st));
   if (f->V > 0 && f->nnz > 0) {
-    k_voxel_prep<<<blocks_for(f->V, 256), 256, 0, st>>>(f->lam.as<double>(), f->mrg.as<double>(), f->coe.as<double>(), f->cS.as<double>(), f->V);
-    VX_LAUNCH_CHECK(ctx);
+    VX_KERNEL(ctx, "k_voxel_prep", k_voxel_prep<<<blocks_for(f->V, 256), 256, 0, st>>>(f->lam.as<double>(), f->mrg.as<double>(), f->coe.as<double>(), f->cS.as<double>(), f->V));
     if (f->n_dseg > 0) {
-      k_diag<<<(int)f->n_dseg, DIAG_THREADS, 0, st>>>(
+      VX_KERNEL(ctx, "k_diag", k_diag<<<(int)f->n_dseg, DIAG_THREADS, 0, st>>>(
           f->dseg_frame.as<int32_t>(), f->dseg_beg.as<int32_t>(), f->dseg_end.as<int32_t>(), f->fm_order.as<int32_t>(),
           f->vox.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->lam.as<double>(), f->U.as<double>(),
           f->mrg.as<double>(), f->coe.as<double>(), f->cS.as<double>(), f->poses.as<double>(), f->G.as<double>(),
-          f->dpart.as<double>(), f->V, head, end);
-      VX_LAUNCH_CHECK(ctx);
-      k_fin_diag<<<f->F(), 64, 0, st>>>(f->dseg_off.as<int32_t>(), f->dpart.as<double>(), f->H.as<double>(), f->J.as<double>(), f->W);
-      VX_LAUNCH_CHECK(ctx);
+          f->dpart.as<double>(), f->V, head, end));
+      VX_KERNEL(ctx, "k_fin_diag", k_fin_diag<<<f->F(), 64, 0, st>>>(f->dseg_off.as<int32_t>(), f->dpart.as<double>(), f->H.as<double>(), f->J.as<double>(), f->W));
     }
     if (f->n_oseg > 0) {
-      k_offdiag<<<(int)f->n_oseg, DIAG_THREADS, 0, st>>>(
+      VX_KERNEL(ctx, "k_offdiag", k_offdiag<<<(int)f->n_oseg, DIAG_THREADS, 0, st>>>(
           f->oseg_beg.as<int32_t>(), f->oseg_end.as<int32_t>(), f->pair_ab.as<int64_t>(), f->vox.as<int32_t>(),
-          f->cS.as<double>(), f->G.as<double>(), f->opart.as<double>(), f->V, head, end);
-      VX_LAUNCH_CHECK(ctx);
-      k_fin_off<<<(int)f->n_tiles, 64, 0, st>>>(f->tile_key.as<int64_t>(), f->oseg_off.as<int32_t>(), f->opart.as<double>(),
-                                             f->H.as<double>(), f->W, f->F());
-      VX_LAUNCH_CHECK(ctx);
+          f->cS.as<double>(), f->G.as<double>(), f->opart.as<double>(), f->V, head, end));
+      VX_KERNEL(ctx, "k_fin_off", k_fin_off<<<(int)f->n_tiles, 64, 0, st>>>(f->tile_key.as<int64_t>(), f->oseg_off.as<int32_t>(), f->opart.as<double>(),
+                                             f->H.as<double>(), f->W, f->F()));
     }
   }
-  k_cost<true><<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(), f->cost_h.as<double>(), head, end);
-  VX_LAUNCH_CHECK(ctx);
+  VX_KERNEL(ctx, "k_cost", k_cost<true><<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(), f->cost_h.as<double>(), head, end));
   return VX_OK;
 }
 
-// Host staging of the factor content into the SoA planes, then one H2D copy per array.
+// ---- upload: AoS host records -> SoA planes, transposed on the device ---------------------------
+// One thread per voxel-frame: reads the 104-byte reference PointCluster record (tools.hpp:308-310)
+// src[idx ? idx[e] : e] and scatters P's upper triangle, v and N into the component planes.
+__global__ void k_unpack_vf(const vx_cluster *__restrict__ src, const int64_t *__restrict__ idx, double *__restrict__ mom,
+                            int32_t *__restrict__ cnt, int64_t nnz) {
+  int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= nnz) return;
+  const vx_cluster &c = src[idx ? idx[e] : e];
+  mom[0 * nnz + e] = c.P[0]; mom[1 * nnz + e] = c.P[3]; mom[2 * nnz + e] = c.P[6];
+  mom[3 * nnz + e] = c.P[4]; mom[4 * nnz + e] = c.P[7]; mom[5 * nnz + e] = c.P[8];
+  mom[6 * nnz + e] = c.v[0]; mom[7 * nnz + e] = c.v[1]; mom[8 * nnz + e] = c.v[2];
+  cnt[e] = c.N;
+}
+// per voxel: sig_vecs -> fix planes, pcr_adds -> mrg planes, eig_values/eig_vectors -> lam/U planes
+__global__ void k_unpack_voxel(const vx_cluster *__restrict__ sig, const vx_cluster *__restrict__ add,
+                               const double *__restrict__ ev, const double *__restrict__ evec, double *__restrict__ fix,
+                               double *__restrict__ mrg, double *__restrict__ lam, double *__restrict__ U, int64_t V) {
+  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  {
+    const vx_cluster &c = sig[v];
+    fix[0 * V + v] = c.P[0]; fix[1 * V + v] = c.P[3]; fix[2 * V + v] = c.P[6];
+    fix[3 * V + v] = c.P[4]; fix[4 * V + v] = c.P[7]; fix[5 * V + v] = c.P[8];
+    fix[6 * V + v] = c.v[0]; fix[7 * V + v] = c.v[1]; fix[8 * V + v] = c.v[2];
+    fix[9 * V + v] = (double)c.N;
+  }
+  {
+    const vx_cluster &c = add[v];
+    mrg[0 * V + v] = c.P[0]; mrg[1 * V + v] = c.P[3]; mrg[2 * V + v] = c.P[6];
+    mrg[3 * V + v] = c.P[4]; mrg[4 * V + v] = c.P[7]; mrg[5 * V + v] = c.P[8];
+    mrg[6 * V + v] = c.v[0]; mrg[7 * V + v] = c.v[1]; mrg[8 * V + v] = c.v[2];
+    mrg[9 * V + v] = (double)c.N;
+  }
+#pragma unroll
+  for (int k = 0; k < 3; k++) lam[k * V + v] = ev[3 * v + k];
+#pragma unroll
+  for (int k = 0; k < 9; k++) U[k * V + v] = evec[9 * v + k];
+}
+
+// `cl_host` holds n_src records; voxel-frame e is record idx[e] (idx may be null = identity).
 static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &off, const std::vector<int32_t> &frames,
-                         const std::vector<const vx_cluster *> &cl, const vx_cluster *sig_vecs, const double *coeffs,
-                         const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds) {
+                         const vx_cluster *cl_host, int64_t n_src, const std::vector<int64_t> *idx, const vx_cluster *sig_vecs,
+                         const double *coeffs, const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds) {
   vx_ctx *ctx = f->ctx;
   VX_TRY(bind(ctx));
   cudaStream_t st = ctx->stream;
@@ -653,46 +684,39 @@ static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &of
   }
   { int64_t v = 0; for (int w = 0; w <= NW; w++) { while (v < V && win[v] < w) v++; wv_off[w] = (int32_t)v; } }
 
-  std::vector<double> mom(9 * (size_t)std::max<int64_t>(nnz, 1));
-  std::vector<int32_t> cnt(std::max<int64_t>(nnz, 1));
-  for (int64_t e = 0; e < nnz; e++) {
-    const vx_cluster &c = *cl[e];
-    mom[0 * nnz + e] = c.P[0]; mom[1 * nnz + e] = c.P[3]; mom[2 * nnz + e] = c.P[6];
-    mom[3 * nnz + e] = c.P[4]; mom[4 * nnz + e] = c.P[7]; mom[5 * nnz + e] = c.P[8];
-    mom[6 * nnz + e] = c.v[0]; mom[7 * nnz + e] = c.v[1]; mom[8 * nnz + e] = c.v[2];
-    cnt[e] = c.N;
-  }
-  std::vector<double> fix(10 * (size_t)std::max<int64_t>(V, 1)), mrg(10 * (size_t)std::max<int64_t>(V, 1)), lam(3 * (size_t)std::max<int64_t>(V, 1)), U(9 * (size_t)std::max<int64_t>(V, 1));
-  auto pack = [&](std::vector<double> &dst, const vx_cluster &c, int64_t v) {
-    dst[0 * V + v] = c.P[0]; dst[1 * V + v] = c.P[3]; dst[2 * V + v] = c.P[6];
-    dst[3 * V + v] = c.P[4]; dst[4 * V + v] = c.P[7]; dst[5 * V + v] = c.P[8];
-    dst[6 * V + v] = c.v[0]; dst[7 * V + v] = c.v[1]; dst[8 * V + v] = c.v[2];
-    dst[9 * V + v] = (double)c.N;
-  };
-  for (int64_t v = 0; v < V; v++) {
-    pack(fix, sig_vecs[v], v);
-    pack(mrg, pcr_adds[v], v);
-    for (int k = 0; k < 3; k++) lam[k * V + v] = eig_values[3 * v + k];
-    for (int k = 0; k < 9; k++) U[k * V + v] = eig_vectors[9 * v + k];
-  }
-#define VX_H2D(dst, src, bytes) VX_CUDA(cudaMemcpyAsync((dst).p, (src), (bytes), cudaMemcpyHostToDevice, st))
-  VX_H2D(f->off, off.data(), sizeof(int32_t) * (V + 1));
+#define VX_H2D(dst, src, bytes) VX_CUDA(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyHostToDevice, st))
+  VX_H2D(f->off.p, off.data(), sizeof(int32_t) * (V + 1));
+  VX_H2D(f->wv_off.p, wv_off.data(), sizeof(int32_t) * (NW + 1));
+  // staging area for the raw AoS records
+  DevBuf &raw = ctx->scratch2;
+  const size_t b_cl = sizeof(vx_cluster) * (size_t)n_src, b_idx = idx ? sizeof(int64_t) * (size_t)nnz : 0;
+  const size_t b_vc = sizeof(vx_cluster) * (size_t)V, b_ev = sizeof(double) * 3 * (size_t)V, b_evec = sizeof(double) * 9 * (size_t)V;
+  VX_TRY(raw.reserve(b_cl + b_idx + 2 * b_vc + b_ev + b_evec + 64));
+  char *base = raw.as<char>();
+  vx_cluster *d_cl = (vx_cluster *)base;
+  int64_t *d_idx = (int64_t *)(base + b_cl);
+  vx_cluster *d_sig = (vx_cluster *)(base + b_cl + b_idx);
+  vx_cluster *d_add = (vx_cluster *)(base + b_cl + b_idx + b_vc);
+  double *d_ev = (double *)(base + b_cl + b_idx + 2 * b_vc);
+  double *d_evec = (double *)(base + b_cl + b_idx + 2 * b_vc + b_ev);
   if (nnz > 0) {
-    VX_H2D(f->frame, frames.data(), sizeof(int32_t) * nnz);
-    VX_H2D(f->mom, mom.data(), sizeof(double) * 9 * nnz);
-    VX_H2D(f->cnt, cnt.data(), sizeof(int32_t) * nnz);
+    VX_H2D(f->frame.p, frames.data(), sizeof(int32_t) * nnz);
+    VX_H2D(d_cl, cl_host, b_cl);
+    if (idx) VX_H2D(d_idx, idx->data(), b_idx);
+    VX_KERNEL(ctx, "k_unpack_vf", k_unpack_vf<<<blocks_for(nnz, 256), 256, 0, st>>>(d_cl, idx ? d_idx : nullptr, f->mom.as<double>(), f->cnt.as<int32_t>(), nnz));
   }
   if (V > 0) {
-    VX_H2D(f->fix, fix.data(), sizeof(double) * 10 * V);
-    VX_H2D(f->mrg, mrg.data(), sizeof(double) * 10 * V);
-    VX_H2D(f->lam, lam.data(), sizeof(double) * 3 * V);
-    VX_H2D(f->U, U.data(), sizeof(double) * 9 * V);
-    VX_H2D(f->coe, coeffs, sizeof(double) * V);
-    VX_H2D(f->win, win.data(), sizeof(int32_t) * V);
+    VX_H2D(d_sig, sig_vecs, b_vc);
+    VX_H2D(d_add, pcr_adds, b_vc);
+    VX_H2D(d_ev, eig_values, b_ev);
+    VX_H2D(d_evec, eig_vectors, b_evec);
+    VX_H2D(f->coe.p, coeffs, sizeof(double) * V);
+    VX_H2D(f->win.p, win.data(), sizeof(int32_t) * V);
+    VX_KERNEL(ctx, "k_unpack_voxel", k_unpack_voxel<<<blocks_for(V, 256), 256, 0, st>>>(d_sig, d_add, d_ev, d_evec, f->fix.as<double>(), f->mrg.as<double>(),
+                                                                                     f->lam.as<double>(), f->U.as<double>(), V));
   }
-  VX_H2D(f->wv_off, wv_off.data(), sizeof(int32_t) * (NW + 1));
 #undef VX_H2D
-  VX_CUDA(cudaStreamSynchronize(st));
+  VX_CUDA(cudaStreamSynchronize(st));   // host vectors above go out of scope; scratch2 is reused by the plan
   return factor_build_plan(f);
 }
 
@@ -748,16 +772,16 @@ int vx_factor_upload_dense(vx_factor *f, int64_t V, const vx_cluster *plvec, con
   VX_ARG(f->n_win == 1);
   const int W = f->W;
   std::vector<int32_t> off(V + 1, 0), frames;
-  std::vector<const vx_cluster *> cl;
+  std::vector<int64_t> idx;
   for (int64_t v = 0; v < V; v++) {
     for (int i = 0; i < W; i++) {
       const vx_cluster *c = plvec + v * W + i;
-      if (c->N != 0) { frames.push_back(i); cl.push_back(c); }
+      if (c->N != 0) { frames.push_back(i); idx.push_back(v * W + i); }
     }
     VX_ARG(frames.size() < ((size_t)1 << 31));
     off[v + 1] = (int32_t)frames.size();
   }
-  return upload_common(f, V, off, frames, cl, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
+  return upload_common(f, V, off, frames, plvec, V * W, &idx, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
 }
 
 int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const int32_t *frames_in, const vx_cluster *clusters,
@@ -770,9 +794,8 @@ int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const 
   VX_ARG(nnz == 0 || (frames_in && clusters));
   std::vector<int32_t> off(V + 1), frames(frames_in, frames_in + nnz);
   for (int64_t v = 0; v <= V; v++) { VX_ARG(offsets[v] >= 0 && offsets[v] <= nnz && (v == 0 || offsets[v] >= offsets[v - 1])); off[v] = (int32_t)offsets[v]; }
-  std::vector<const vx_cluster *> cl(nnz);
-  for (int64_t e = 0; e < nnz; e++) { VX_ARG(clusters[e].N != 0); cl[e] = clusters + e; }
-  return upload_common(f, V, off, frames, cl, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
+  for (int64_t e = 0; e < nnz; e++) VX_ARG(clusters[e].N != 0);
+  return upload_common(f, V, off, frames, clusters, nnz, nullptr, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
 }
 
 int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vectors, vx_cluster *pcr_adds) {
