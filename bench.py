@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — LiDAR-BA Hessian build throughput (voxel-frames/s) on B200, one JSON line.
+
+Workload (config.workload): the bottom level of the hierarchical global BA of BASELINE.json
+configs[3] — 399 independent 10-keyframe windows (voxelslam.cpp:3033-3034, :3096) evaluated as ONE
+batched LidarFactor (include/voxelba.h: vx_factor_create(n_windows)), synthetic plane voxels.
+A step = one LidarFactor::acc_evaluate2 pass (voxel_map.hpp:150-282) over every window: Hess, JacT and
+cost of all 399 windows.  Per rank the work is fixed (weak scaling, no data-path collective: the
+windows are independent); rank r evaluates its own 2,000-keyframe job.
+
+  value      voxel-frames/s, inputs resident in HBM, CUDA-event timed on the library's stream
+  e2e        same metric through the C ABI with HOST buffers: vx_factor_upload_csr (H2D of the
+             reference-layout PointCluster records) + vx_factor_hessian (H2D poses, D2H Hess/JacT/cost)
+  roofline   dominant kernel of the step, algorithmic bytes / its event-timed duration
+  cpu_baseline  the oracle (CPU restatement of the reference) on a bounded sample of the same windows
+
+--impl reference times the oracle's Lidar_BA_Optimizer::divide_thread on host threads (the reference
+itself needs Eigen/PCL/ROS/GTSAM and cannot be built here: DESIGN.md "Oracle").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "lidar_ba_hessian_build_voxel_frames_per_s"
+UNIT = "voxel-frames/s"
+N_WINDOWS = 399          # (2000 - 10) / 5 + 1, voxelslam.cpp:3137-3138
+WIN = 10                 # wdsize, voxelslam.cpp:3033
+VOX_PER_WIN = 1000
+OCC = 0.6
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--windows", type=int, default=N_WINDOWS)
+    ap.add_argument("--voxels-per-window", type=int, default=VOX_PER_WIN)
+    ap.add_argument("--cpu-sample-windows", type=int, default=24)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def workload_config(args, fac):
+    nnz = int(fac["offsets"][-1]); V = int(fac["sig"].shape[0])
+    return {
+        "workload": "C4 bottom level: %d independent %d-keyframe GBA windows batched in one LidarFactor, %d plane voxels/window, "
+                    "frame occupancy %.1f (synthetic planar patches)" % (args.windows, WIN, args.voxels_per_window, OCC),
+        "windows": args.windows, "win_size": WIN, "voxels": V, "voxel_frames": nnz,
+        "pairs": int(np.sum((np.diff(fac["offsets"]) * (np.diff(fac["offsets"]) - 1)) // 2)),
+        "parallelism": "windows sharded, no collective",
+    }
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index; self.proc = None; self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_workload(args, rank):
+    import synth
+    return synth.batched_factor_csr(20241008 + 3 + 1000 * rank, args.windows, args.voxels_per_window, WIN, occupancy=OCC, pts_max=12)
+
+
+def algorithmic_bytes(nnz, V, n_win, W):
+    """76 B per voxel-frame + 132 B per voxel + poses + the upper block triangle,
+    gradient and cost written once per window."""
+    jl = 6 * W
+    return 76 * nnz + 132 * V + 96 * W * n_win + (8 * jl * (jl + 1) // 2 + 8 * jl + 8) * n_win
+
+
+def algorithmic_flops(fac):
+    k = np.diff(fac["offsets"])
+    return int(900 * k.sum() + 216 * np.sum(k * (k - 1) // 2))
+
+
+def cpu_hessian_sample(fac, windows, threads, repeats=1):
+    """Oracle acc_evaluate2 over `windows` (list of window ids) on `threads` host threads
+    (one window per task).  Returns (voxel-frames processed per pass, best seconds per pass)."""
+    import concurrent.futures as cf
+    import oracle_bind as ob
+    import synth
+    items = []
+    nvf = 0
+    for b in windows:
+        d = synth.csr_window(fac, b)
+        of = ob.Factor(WIN); of.set_dense(d)
+        items.append((of, ob.as_poses(d["poses"])))
+        nvf += of.num_voxel_frames
+    best = float("inf")
+    with cf.ThreadPoolExecutor(max_workers=threads) as ex:
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            list(ex.map(lambda it: it[0].hessian(it[1]), items))
+            best = min(best, time.perf_counter() - t0)
+    return nvf, best
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path (oracle restatement) on all host threads."""
+    if rank != 0:
+        return
+    fac = build_workload(args, 0)
+    cores = os.cpu_count() or 1
+    nwin = min(args.windows, max(args.cpu_sample_windows, 2 * cores))
+    windows = list(range(nwin))
+    # one step = one pass over the sample; warm-up passes first
+    import oracle_bind as ob  # noqa: F401  (builds/loads the oracle)
+    # time K passes back to back on a persistent pool
+    import concurrent.futures as cf
+    import synth
+    items = []
+    for b in windows:
+        d = synth.csr_window(fac, b)
+        of = ob.Factor(WIN); of.set_dense(d)
+        items.append((of, ob.as_poses(d["poses"])))
+    nvf = sum(it[0].num_voxel_frames for it in items)
+    with cf.ThreadPoolExecutor(max_workers=cores) as ex:
+        for _ in range(max(args.warmup, 1)):
+            list(ex.map(lambda it: it[0].hessian(it[1]), items))
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            list(ex.map(lambda it: it[0].hessian(it[1]), items))
+        tot = time.perf_counter() - t0
+    val = nvf * args.steps / tot
+    sample = "%d of %d windows (%d voxel-frames) per step, oracle acc_evaluate2, one window per task" % (nwin, args.windows, nvf)
+    cfg = workload_config(args, fac)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference needs Eigen/PCL/ROS/GTSAM (absent): timed the oracle restatement of its CPU path",
+    }))
+
+
+def pinned_like(a):
+    """Copy a numpy array into page-locked host memory (torch-owned), same dtype/shape view."""
+    import torch
+    raw = torch.empty(max(a.nbytes, 1), dtype=torch.uint8).pin_memory()
+    view = raw.numpy()[:a.nbytes].view(a.dtype).reshape(a.shape)
+    view[...] = a
+    return view, raw
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback (use --impl reference for the CPU leg)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = ge.load_package()
+    pkg.load_library()
+    fac = build_workload(args, rank)
+    nnz = int(fac["offsets"][-1]); V = int(fac["sig"].shape[0])
+    cfg = workload_config(args, fac)
+    ctx = pkg.Context(local_rank)
+    f = pkg.Factor(ctx, WIN, args.windows)
+    f.upload_csr(fac)
+    f.set_poses(fac["poses"])
+    stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local_rank))
+    alg_bytes = algorithmic_bytes(nnz, V, args.windows, WIN)
+    resident = 76 * nnz + 8 * nnz + 132 * V + 104 * V       # what one pass touches besides its own scratch
+    cfg["l2"] = "inputs larger than L2: %.0f MB read per step vs 126 MB L2, no flush" % (alg_bytes / 1e6)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ---------------------------------------------------------------
+    for _ in range(args.warmup):
+        f.hessian_async()
+    barrier()
+    l0 = ctx.launch_count
+    clocks = ClockSampler(local_rank); clocks.start()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        f.hessian_async()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launch_count - l0
+    # keep the GPU busy a little longer so nvidia-smi gets several samples under load
+    t_end = time.time() + 1.5
+    while time.time() < t_end:
+        for _ in range(10):
+            f.hessian_async()
+        ctx.sync()
+    clk = clocks.stop()
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / args.steps
+    value = nnz * world / (ms_step * 1e-3)
+
+    # ---- per-kernel timing (roofline) ---------------------------------------------------------
+    ctx.profile(True)
+    for _ in range(args.steps):
+        f.hessian_async()
+    prof = ctx.profile_read()
+    ctx.profile(False)
+    kern = {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps} for k, v in prof.items()}
+    top = max(kern, key=lambda k: kern[k]["ms_per_step"])
+    pass_ms = sum(v["ms_per_step"] for v in kern.values())
+    import json as _j
+    peaks = {}
+    try:
+        peaks = _j.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = alg_bytes / (pass_ms * 1e-3) / 1e9
+    flops = algorithmic_flops(fac)
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
+                "kernel": "whole acc_evaluate2 pass (sum of its kernels' event times); top kernel = " + top,
+                "algorithmic_bytes_per_step": alg_bytes, "kernels": kern,
+                "fp64": {"algorithmic_flops_per_step": flops, "achieved_tflops": flops / (pass_ms * 1e-3) / 1e12,
+                         "note": "B1 is FP64-FMA bound for k>=3 occupied frames per voxel (DESIGN.md); no FP64 peak in MEASURED_PEAKS.json"}}
+
+    # ---- B2 residual pass, same factor (reported beside the headline) ------------------------
+    for _ in range(args.warmup):
+        f.residual_async()
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        f.residual_async()
+    e1.record(stream)
+    barrier()
+    ms_res = e0.elapsed_time(e1) / args.steps
+    res_bytes = 76 * nnz + (104 + 200) * V
+    extra = {"residual_pass": {"voxel_frames_per_s": nnz / (ms_res * 1e-3), "ms_per_step": ms_res,
+                               "hbm_gbs": res_bytes / (ms_res * 1e-3) / 1e9, "hbm_frac": res_bytes / (ms_res * 1e-3) / 1e9 / peak}}
+
+    # ---- end to end through the C ABI with host buffers ---------------------------------------
+    keys = ("offsets", "frames", "clusters", "sig", "coe", "eigval", "eigvec", "merged")
+    host = {}; owners = []
+    for k in keys:
+        a = np.ascontiguousarray(fac[k], dtype=np.int64 if k == "offsets" else (np.int32 if k == "frames" else None))
+        host[k], o = pinned_like(a); owners.append(o)
+    ps, o = pinned_like(pkg.as_poses(fac["poses"])); owners.append(o)
+    jl = 6 * WIN
+    Hh, o1 = pinned_like(np.zeros((args.windows, jl, jl))); Jh, o2 = pinned_like(np.zeros((args.windows, jl))); ch, o3 = pinned_like(np.zeros(args.windows))
+    owners += [o1, o2, o3]
+    h2d = sum(host[k].nbytes for k in keys) + ps.nbytes
+    d2h = Hh.nbytes + Jh.nbytes + ch.nbytes
+    g = pkg.Factor(ctx, WIN, args.windows)
+
+    def e2e_step():
+        g.upload_csr_raw(host)
+        g.hessian_raw(ps, Hh, Jh, ch)
+
+    n_e2e = max(3, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        e2e_step()
+    barrier()
+    t_e2e = (time.perf_counter() - t0) / n_e2e
+    if world > 1:
+        t = torch.tensor([t_e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_e2e = float(t.item())
+    e2e = {"value": nnz * world / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "ms_per_step": 1e3 * t_e2e, "steps": n_e2e,
+           "what": "vx_factor_upload_csr (pinned host PointCluster records -> device, plan build) + vx_factor_hessian (poses H2D, Hess/JacT/cost D2H), wall clock"}
+    # sanity: e2e result equals the resident result
+    Hd = np.zeros_like(Hh); Jd = np.zeros_like(Jh); cd = np.zeros_like(ch)
+    f.hessian_raw(ps, Hd, Jd, cd)
+    assert np.array_equal(Hd, Hh) and np.array_equal(cd, ch), "e2e and resident paths disagree"
+
+    # ---- cpu baseline (rank 0, N=1 only) ------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        nwin = min(args.windows, args.cpu_sample_windows)
+        nvf, t = cpu_hessian_sample(fac, list(range(nwin)), 2, repeats=3)
+        cpu = {"value": nvf / t, "unit": UNIT, "cores": 2, "kind": "port",
+               "sample": "%d of %d windows (%d voxel-frames), oracle acc_evaluate2 on 2 host threads (the reference's thd_num for "
+                         "LiDAR-only BA, voxel_map.hpp:345), best of 3; host has %d cores" % (nwin, args.windows, nvf, os.cpu_count() or 1)}
+        # parity spot check on the sampled windows (the oracle here is the checker, not the product)
+        import oracle_bind as ob
+        import synth
+        d = synth.csr_window(fac, 0)
+        of = ob.Factor(WIN); of.set_dense(d)
+        Ho, Jo, co = of.hessian(d["poses"])
+        Hg = Hh[0].T
+        err = float(np.max(np.abs(Hg - Ho)) / np.max(np.abs(Ho)))
+        extra["parity_window0_rel_err_H"] = err
+        assert err < 1e-7, err
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic", "config": cfg, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+               "roofline": roofline, "cpu_baseline": cpu}
+        out.update(extra)
+        print(json.dumps(out))
+    f.free(); g.free(); ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

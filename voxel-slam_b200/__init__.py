@@ -160,6 +160,16 @@ class Factor:
         self._keep = a
         _chk(self.lib.vx_factor_upload_csr(self.h, C.c_int64(V), *[_p(x) for x in a]))
 
+    def upload_csr_raw(self, a):
+        """Same as upload_csr but takes already-contiguous (e.g. pinned) arrays and does no copies."""
+        V = a["sig"].shape[0]
+        _chk(self.lib.vx_factor_upload_csr(self.h, C.c_int64(V), *[_p(a[k]) for k in
+                                           ("offsets", "frames", "clusters", "sig", "coe", "eigval", "eigvec", "merged")]))
+
+    def hessian_raw(self, ps, H, J, c, head=0, end=-1):
+        """vx_factor_hessian into caller-owned buffers (H stays column-major per window)."""
+        _chk(self.lib.vx_factor_hessian(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(H), _p(J), _p(c)))
+
     def download_cache(self):
         V = self.num_voxels
         ev = np.zeros((V, 3)); evec = np.zeros((V, 9)); mrg = np.zeros(V, dtype=cluster_dtype)
