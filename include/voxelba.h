@@ -66,6 +66,10 @@ int vx_ctx_profile(vx_ctx *ctx, int enable);   /* also clears what was recorded 
 int vx_ctx_profile_read(vx_ctx *ctx, char *names, size_t names_cap, double *ms, int64_t *counts,
                         int max_entries, int *n_out);
 
+/* FP64 pipe peak of the device, measured in place (MEASURED_PEAKS.json has no FP64 figure):
+ * mode 0 = DFMA on the CUDA cores, mode 1 = mma.sync m8n8k4 f64 on the tensor pipe.  TFLOP/s. */
+int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops);
+
 /* ---- B0: LidarFactor storage -------------------------------------------------------------- */
 /* LidarFactor::LidarFactor(int _w)  voxel_map.hpp:136.  `n_windows` > 1 makes a BATCH of
  * independent factors that share W (bottom-level GBA windows, voxelslam.cpp:3096): frame f of
@@ -88,6 +92,10 @@ int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const 
                          const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds);
 /* read back what evaluate_only_residual caches  voxel_map.hpp:317-319 */
 int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vectors, vx_cluster *pcr_adds);
+/* Evaluation path selection.  acc_evaluate2 has two device formulations: a fused tensor-core kernel for
+ * the window sizes the reference runs (W = 10, 20) and a generic pair-list path for any W (top-level
+ * GBA, W ~ 399).  on != 0 forces the generic path (tests compare the two). */
+int vx_factor_force_generic(vx_factor *f, int on);
 int64_t vx_factor_num_voxels(const vx_factor *f);
 int64_t vx_factor_num_voxel_frames(const vx_factor *f); /* sum over voxels of frames with N != 0 */
 int vx_factor_win_size(const vx_factor *f);

@@ -68,6 +68,13 @@ def test_hessian_parity(pkg, ob, ctx, V, W, occ):
     g.upload_csr(synth.dense_to_csr(fac))
     H2, J2, c2 = g.hessian(poses)
     assert np.array_equal(H, H2) and np.array_equal(J, J2) and c == c2
+    # the generic pair-list path and the fused tensor-core path (W = 10, 20) agree to rounding,
+    # and each is bitwise reproducible run to run (no atomics)
+    g.force_generic(True)
+    H3, J3, c3 = g.hessian(poses)
+    assert rel(H3, Ho) < 1e-9 and rel(J3, Jo) < 1e-9 and rel(H3, H) < 1e-11
+    H4, J4, c4 = f.hessian(poses)
+    assert np.array_equal(H, H4) and np.array_equal(J, J4)
     f.free(); g.free()
 
 
@@ -85,8 +92,9 @@ def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx):
     f.free()
 
 
-def test_head_end_subrange(pkg, ob, ctx):
-    V, W = 600, 5
+@pytest.mark.parametrize("W", [5, 10])
+def test_head_end_subrange(pkg, ob, ctx, W):
+    V = 600
     fac = synth.random_factor(401, V, W)
     poses = fac["poses"]
     of = ob.Factor(W); of.set_dense(fac)
@@ -118,9 +126,9 @@ def test_empty_and_reupload(pkg, ctx):
     f.free()
 
 
-def test_batched_windows_match_single(pkg, ctx):
-    # n_windows independent factors in one launch == each evaluated alone, bit for bit
-    W, NW = 5, 7
+@pytest.mark.parametrize("W,NW", [(5, 7), (10, 5), (20, 3)])
+def test_batched_windows_match_single(pkg, ctx, W, NW):
+    # n_windows independent factors in one launch == each evaluated alone
     facs = [synth.random_factor(500 + b, 120 + 10 * b, W) for b in range(NW)]
     csr = [synth.dense_to_csr(fc) for fc in facs]
     off = [0]; frames = []; parts = {k: [] for k in ("clusters", "sig", "coe", "eigval", "eigvec", "merged")}

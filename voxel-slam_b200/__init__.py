@@ -90,6 +90,12 @@ class Context:
     def sync(self):
         _chk(self.lib.vx_ctx_sync(self.h))
 
+    def fp64_peak(self, mode=0):
+        """Measured FP64 TFLOP/s of this device: mode 0 DFMA (CUDA cores), mode 1 DMMA (tensor pipe)."""
+        t = C.c_double(0)
+        _chk(self.lib.vx_bench_fp64(self.h, C.c_int(mode), C.byref(t)))
+        return t.value
+
     def profile(self, enable=True):
         """Start (and clear) / stop per-kernel CUDA-event timing of this context's launches."""
         _chk(self.lib.vx_ctx_profile(self.h, C.c_int(int(enable))))
@@ -144,6 +150,9 @@ class Factor:
     @property
     def num_voxel_frames(self):
         return int(self.lib.vx_factor_num_voxel_frames(self.h))
+
+    def force_generic(self, on=True):
+        _chk(self.lib.vx_factor_force_generic(self.h, C.c_int(int(on))))
 
     def upload_dense(self, fac):
         """fac: dict with plvec (V,W) cluster, sig (V,), coe (V,), eigval (V,3), eigvec (V,9), merged (V,)."""

@@ -39,8 +39,10 @@ struct vx_factor {
   vx::DevBuf tile_key, tile_off;                        // tile = (frame_i * F + frame_j), i<j
   vx::DevBuf oseg_tile, oseg_beg, oseg_end, oseg_off;   // off-diagonal tile segments
   vx::DevBuf dpart, opart;                              // per-segment partial sums
+  vx::DevBuf part_t, part_d;                            // fused small-window path: per-item tile / diagonal partials
   int64_t n_pairs = 0, n_tiles = 0, n_dseg = 0, n_oseg = 0;
   int seg_len = 1024;
+  bool force_pairlist = false;   // tests: evaluate through the generic pair-list path even when a fused one exists
 };
 
 namespace vx {
@@ -48,4 +50,6 @@ namespace vx {
 int factor_build_plan(vx_factor *f);
 // Allocates per-voxel / per-voxel-frame arrays for V voxels and nnz voxel-frames.
 int factor_alloc(vx_factor *f, int64_t V, int64_t nnz);
+// Fused tensor-core path for small windows (vx_hess_small.cu); *handled=false when W has no instantiation.
+int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled);
 }  // namespace vx
