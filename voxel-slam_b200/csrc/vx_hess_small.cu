@@ -1,42 +1,67 @@
 // vx_hess_small.cu — fused LidarFactor::acc_evaluate2 (voxel_map.hpp:150-282) for small windows
 // (W = 10: LocalBA/win_size and the GBA wdsize, voxelslam.cpp:919 / :3033;  W = 20: config C3).
 //
-// One CTA evaluates one ITEM = a contiguous voxel range of one window and keeps that item's share
-// of the window's 6W x 6W Hessian ON CHIP for the whole item:
-//   phase A  one thread per voxel-frame: closed-form g1, g2, w (18 doubles) and the diagonal-block
-//            corrections + gradient (30 doubles) -> shared memory, field-major, odd stride
-//   phase B  the CTA's warps are ROLES; role r owns the block tiles t = r, r+NROLES, ... of the upper
-//            block triangle.  For every voxel of the chunk (warp-uniform control flow) and every
-//            owned tile (i,j) whose two frames are occupied, ONE FP64 tensor-core instruction
-//            mma.sync.m8n8k4 adds the rank-3 block  sum_m S_m g_m,i g_m,j^T  (k = m, 3 of 4 used;
-//            6 of 8 rows/cols used) into the tile's accumulator fragment, which stays in registers.
-//            A- and B-fragment are the SAME shared-memory element (g_m[r] for lane (r,m)), so a voxel
-//            costs k shared loads per warp; the 36-loads-per-108-FMA operand traffic that bounds a
-//            CUDA-core formulation is gone.
+// The rank-3 part of every block of the window Hessian is  Hess(i,j) = sum_v sum_m S_m g_m,i g_m,j^T
+// (vx_factor.cu header).  Stack the rows g_m of all voxels of a window into one (3V) x (6W) matrix A,
+// absent frames zero: the whole upper block triangle is the symmetric rank-3V update  A^T diag(S) A,
+// a tall-skinny SYRK.  One CTA evaluates one ITEM (a contiguous voxel range of one window) and streams
+// it through shared memory in chunks:
+//   phase A  one thread per voxel-frame: closed-form g1, g2, w (18 doubles) -> rows 3v..3v+2 of the
+//            chunk's A panel in shared memory; diagonal-block corrections + gradient (30 doubles) ->
+//            a compact field-major record
+//   phase B  FP64 tensor cores: the 6W x 6W accumulator is cut into 8x8 tiles, each warp (ROLE) owns a
+//            contiguous run of upper tiles and keeps them in registers for the whole item.  Per 4 panel
+//            rows a warp loads one fragment per tile row/column it needs (conflict-free, leading
+//            dimension = 4 mod 16) and issues one mma.sync.m8n8k4.f64 per owned tile: no per-voxel
+//            control flow, all of m, n and k used.
 //   phase C  fixed owner threads add the per-frame corrections / gradient in voxel order.
-// The item's partial blocks go to HBM once (16 KB at W = 10); k_fin_small adds the items of a window
-// in ascending order and mirrors the upper blocks (voxel_map.hpp:279-281).  No atomics anywhere:
-// the result is bitwise reproducible.
+// The item's partial tiles go to HBM once; k_fin_small adds the items of a window in ascending order,
+// writes the upper blocks and mirrors them (voxel_map.hpp:279-281).  No atomics: bitwise reproducible.
 #include "vx_factor.cuh"
 #include "vx_math.cuh"
 #include "vx_terms.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 using namespace vx;
 
 namespace {
 
-constexpr int NF_G = 18;   // g1[6] g2[6] w[6]
 constexpr int NF_E = 30;   // rot-rot 9 | rot-tra 9 | tra-tra 6 (upper) | gradient 6
-constexpr int NF = NF_G + NF_E;
-constexpr int CHV = 32;    // max voxels per chunk
+constexpr int CHV = 21;    // max voxels per chunk (3 * 21 = 63 panel rows <= ROWS)
+constexpr int ROWS = 64;   // panel rows per chunk
 
-template <int W> struct TileTab {
-  int i[W * (W + 1) / 2], j[W * (W + 1) / 2];
-  constexpr TileTab() : i(), j() {
+template <int W, int NROLES> struct SmallCfg {
+  static constexpr int NC = 6 * W;
+  static constexpr int NT8 = (NC + 7) / 8;                 // 8-wide tile columns
+  static constexpr int LD = NT8 * 8 + 4;                   // leading dimension: 4 or 12 mod 16 -> conflict-free fragments
+  static constexpr int T8 = NT8 * (NT8 + 1) / 2;           // upper tiles
+  static constexpr int TPR = (T8 + NROLES - 1) / NROLES;   // tiles per role
+  static constexpr int NT = 32 * NROLES;                   // threads per CTA = voxel-frames per chunk
+  static constexpr int STRIDE = NT + 1;                    // record NT is an all-zero record
+  static constexpr int NDQ = (W * NF_E + NT - 1) / NT;     // (frame, component) sums owned per thread
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)ROWS * LD + (size_t)NF_E * STRIDE + ROWS) + sizeof(uint16_t) * (size_t)(CHV * W + 8);
+};
+
+template <int NT8> struct TileTab8 {
+  int I[NT8 * (NT8 + 1) / 2], J[NT8 * (NT8 + 1) / 2];
+  constexpr TileTab8() : I(), J() {
     int t = 0;
-    for (int a = 0; a < W; a++)
-      for (int b = a; b < W; b++) { i[t] = a; j[t] = b; t++; }
+    for (int a = 0; a < NT8; a++)
+      for (int b = a; b < NT8; b++) { I[t] = a; J[t] = b; t++; }
+  }
+};
+// does role r need the fragment of tile column b?
+template <int W, int NROLES> struct NeedTab {
+  bool need[NROLES][SmallCfg<W, NROLES>::NT8];
+  constexpr NeedTab() : need() {
+    constexpr int NT8 = SmallCfg<W, NROLES>::NT8, T8 = SmallCfg<W, NROLES>::T8, TPR = SmallCfg<W, NROLES>::TPR;
+    TileTab8<NT8> tab{};
+    for (int r = 0; r < NROLES; r++)
+      for (int s = 0; s < TPR; s++) {
+        int t = r * TPR + s;
+        if (t < T8) { need[r][tab.I[t]] = true; need[r][tab.J[t]] = true; }
+      }
   }
 };
 
@@ -44,61 +69,41 @@ __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-template <int W, int NROLES> struct SmallCfg {
-  static constexpr int T = W * (W + 1) / 2;
-  static constexpr int TPR = (T + NROLES - 1) / NROLES;   // tiles per role
-  static constexpr int NT = 32 * NROLES;                  // threads per CTA = voxel-frames per chunk
-  static constexpr int STRIDE = NT + 1;                   // odd: field-major rows land on distinct banks
-  static constexpr int NDQ = (W * NF_E + NT - 1) / NT;    // (frame, component) sums owned per thread
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)NF * STRIDE + 4 * CHV) + sizeof(uint32_t) * 2 * CHV;
-};
-
-// phase B for one role: all owned tiles of one voxel
+// phase B of one role over the chunk's panel (nks k-steps of 4 rows)
 template <int W, int NROLES, int ROLE>
-__device__ __forceinline__ void role_voxel(double (&C)[SmallCfg<W, NROLES>::TPR][2], const double (&a)[W], double sm, uint32_t mask) {
-  constexpr TileTab<W> tab{};
-  constexpr int T = SmallCfg<W, NROLES>::T, TPR = SmallCfg<W, NROLES>::TPR;
+__device__ __forceinline__ void role_chunk(double (&C)[SmallCfg<W, NROLES>::TPR][2], const double *__restrict__ As,
+                                           const double *__restrict__ Srow, int nks, int lane) {
+  using Cfg = SmallCfg<W, NROLES>;
+  constexpr int NT8 = Cfg::NT8, T8 = Cfg::T8, TPR = Cfg::TPR, LD = Cfg::LD;
+  constexpr TileTab8<NT8> tab{};
+  constexpr NeedTab<W, NROLES> nd{};
+  const double *ap = As + (lane & 3) * LD + (lane >> 2);
+  const double *sp = Srow + (lane & 3);
+#pragma unroll 2
+  for (int ks = 0; ks < nks; ks++) {
+    const double s = sp[4 * ks];
+    double a[NT8], b[NT8];
 #pragma unroll
-  for (int s = 0; s < TPR; s++) {
-    const int t = s * NROLES + ROLE;
-    if (t < T) {
-      const int i = tab.i[t < T ? t : 0], j = tab.j[t < T ? t : 0];
-      if (((mask >> i) & (mask >> j) & 1u) != 0u) dmma884(C[s][0], C[s][1], a[i], a[j] * sm);
+    for (int x = 0; x < NT8; x++) {
+      a[x] = 0.0; b[x] = 0.0;
+      if (nd.need[ROLE][x]) { a[x] = ap[(size_t)ks * 4 * LD + 8 * x]; b[x] = a[x] * s; }
+    }
+#pragma unroll
+    for (int q = 0; q < TPR; q++) {
+      const int t = ROLE * TPR + q;
+      if (t < T8) dmma884(C[q][0], C[q][1], a[tab.I[t < T8 ? t : 0]], b[tab.J[t < T8 ? t : 0]]);
     }
   }
 }
 
+// accumulator fragments -> the item's partial tiles (8x8 row-major each)
 template <int W, int NROLES, int ROLE>
 __device__ __forceinline__ void role_store(const double (&C)[SmallCfg<W, NROLES>::TPR][2], double *__restrict__ part, int lane) {
-  constexpr int T = SmallCfg<W, NROLES>::T, TPR = SmallCfg<W, NROLES>::TPR;
-  const int row = lane >> 2, col = (lane & 3) * 2;
+  constexpr int T8 = SmallCfg<W, NROLES>::T8, TPR = SmallCfg<W, NROLES>::TPR;
 #pragma unroll
-  for (int s = 0; s < TPR; s++) {
-    const int t = s * NROLES + ROLE;
-    if (t < T && row < 6 && col < 6) {
-      part[(size_t)t * 36 + col * 6 + row] = C[s][0];
-      part[(size_t)t * 36 + (col + 1) * 6 + row] = C[s][1];
-    }
-  }
-}
-
-template <int W, int NROLES, int ROLE>
-__device__ __forceinline__ void role_chunk(double (&C)[SmallCfg<W, NROLES>::TPR][2], const double *__restrict__ Gs, const double *__restrict__ Ss,
-                                           const uint32_t *__restrict__ mask_s, const uint32_t *__restrict__ base_s, int nv, int lane) {
-  constexpr int STRIDE = SmallCfg<W, NROLES>::STRIDE;
-  const int m = min(lane & 3, 2), r = min(lane >> 2, 5);
-  const double *gl = Gs + (m * 6 + r) * STRIDE;
-  for (int lv = 0; lv < nv; lv++) {
-    const uint32_t mask = mask_s[lv];
-    const uint32_t base = base_s[lv];
-    const double sm = Ss[lv * 4 + (lane & 3)];
-    double a[W];
-#pragma unroll
-    for (int f = 0; f < W; f++) {
-      a[f] = 0.0;
-      if ((mask >> f) & 1u) a[f] = gl[base + __popc(mask & ((1u << f) - 1u))];
-    }
-    role_voxel<W, NROLES, ROLE>(C, a, sm, mask);
+  for (int q = 0; q < TPR; q++) {
+    const int t = ROLE * TPR + q;
+    if (t < T8) *reinterpret_cast<double2 *>(part + (size_t)t * 64 + (lane >> 2) * 8 + (lane & 3) * 2) = make_double2(C[q][0], C[q][1]);
   }
 }
 
@@ -118,20 +123,20 @@ __device__ __forceinline__ void role_chunk(double (&C)[SmallCfg<W, NROLES>::TPR]
 
 // One CTA per item.  item -> (window w, split s): voxels [lo, hi) = the s-th of `splits` equal parts of
 // [max(head, wv_off[w]), min(end, wv_off[w+1])).
-template <int W, int NROLES>
-__global__ void __launch_bounds__(32 * NROLES)
+template <int W, int NROLES, int MINB>
+__global__ void __launch_bounds__(32 * NROLES, MINB)
 k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const int32_t *__restrict__ vox,
              const double *__restrict__ mom, const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ lam,
              const double *__restrict__ U, const double *__restrict__ mrg, const double *__restrict__ coe,
              const int32_t *__restrict__ wv_off, const double *__restrict__ poses, double *__restrict__ part_t,
              double *__restrict__ part_d, int64_t V, int64_t head, int64_t end, int splits) {
   using Cfg = SmallCfg<W, NROLES>;
-  constexpr int NT = Cfg::NT, STRIDE = Cfg::STRIDE, T = Cfg::T, TPR = Cfg::TPR, NDQ = Cfg::NDQ;
+  constexpr int NT = Cfg::NT, STRIDE = Cfg::STRIDE, LD = Cfg::LD, T8 = Cfg::T8, TPR = Cfg::TPR, NDQ = Cfg::NDQ;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double *Gs = reinterpret_cast<double *>(smem_raw);            // [NF][STRIDE]
-  double *Ss = Gs + (size_t)NF * STRIDE;                        // [CHV][4]  coe*{2/(l0-l1), 2/(l0-l2), -2/NN^2, 0}
-  uint32_t *mask_s = reinterpret_cast<uint32_t *>(Ss + 4 * CHV);  // [CHV] occupied-frame bit mask
-  uint32_t *base_s = mask_s + CHV;                              // [CHV] first record of the voxel in the chunk
+  double *As = reinterpret_cast<double *>(smem_raw);        // [ROWS][LD] the chunk's panel of A
+  double *Es = As + (size_t)ROWS * LD;                      // [NF_E][STRIDE] corrections + gradient per record
+  double *Srow = Es + (size_t)NF_E * STRIDE;                // [ROWS] coe*{2/(l0-l1), 2/(l0-l2), -2/NN^2} per panel row
+  uint16_t *rec_s = reinterpret_cast<uint16_t *>(Srow + ROWS);  // [CHV][W] record of (voxel, frame), NT = absent
   __shared__ int s_nv;
 
   const int tid = threadIdx.x, lane = tid & 31, role = tid >> 5;
@@ -154,6 +159,7 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
   double dacc[NDQ];
 #pragma unroll
   for (int q = 0; q < NDQ; q++) dacc[q] = 0.0;
+  if (tid < NF_E) Es[tid * STRIDE + NT] = 0.0;   // the all-zero record
 
   int64_t v0 = lo;
   while (v0 < hi) {
@@ -165,18 +171,22 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
       const int nvv = __syncthreads_count(ok);
       if (tid == 0) s_nv = nvv;
     }
-    if (tid < CHV) { mask_s[tid] = 0u; }
+    {
+      double2 *z = reinterpret_cast<double2 *>(As);
+      for (int k = tid; k < ROWS * LD / 2; k += NT) z[k] = make_double2(0.0, 0.0);
+      if (tid < ROWS) Srow[tid] = 0.0;
+      for (int k = tid; k < CHV * W; k += NT) rec_s[k] = (uint16_t)NT;
+    }
     __syncthreads();
     const int nv = s_nv;
     const int32_t e1 = off[v0 + nv];
-    if (tid < nv) base_s[tid] = (uint32_t)(off[v0 + tid] - e0);
     // ---- phase A
     const int32_t e = e0 + tid;
     if (e < e1) {
       const int64_t v = vox[e];
       const int lv = (int)(v - v0);
       const int fr = frame[e] - w * W;
-      atomicOr(&mask_s[lv], 1u << fr);
+      rec_s[lv * W + fr] = (uint16_t)tid;
       const double *ps = ps_w + 12 * fr;
       const rot R = load_rot(ps);
       const d3 p = mk3(ps[9], ps[10], ps[11]);
@@ -193,17 +203,18 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
       const double c = coe[v];
       if (e == off[v]) {   // first voxel-frame of the voxel also publishes the voxel's S (voxel_map.hpp:198-201, :265-268)
         const double l0 = lam[v], l1 = lam[V + v], l2 = lam[2 * V + v];
-        Ss[lv * 4 + 0] = c * (2.0 / (l0 - l1));
-        Ss[lv * 4 + 1] = c * (2.0 / (l0 - l2));
-        Ss[lv * 4 + 2] = c * (-2.0 / NN / NN);
-        Ss[lv * 4 + 3] = 0.0;
+        Srow[3 * lv + 0] = c * (2.0 / (l0 - l1));
+        Srow[3 * lv + 1] = c * (2.0 / (l0 - l2));
+        Srow[3 * lv + 2] = c * (-2.0 / NN / NN);
       }
       VfTerms t;
       vf_terms(R, p, P, vi, n, uk, u1, u2, vbar, NN, t);
-      double *g = Gs + tid;
+      double *g = As + (size_t)(3 * lv) * LD + 6 * fr;
 #pragma unroll
-      for (int k = 0; k < NF_G; k++) g[k * STRIDE] = t.g[k];
-      double *ee = g + NF_G * STRIDE;
+      for (int m = 0; m < 3; m++)
+#pragma unroll
+        for (int r = 0; r < 6; r++) g[m * LD + r] = t.g[m * 6 + r];
+      double *ee = Es + tid;
 #pragma unroll
       for (int cc = 0; cc < 3; cc++)
 #pragma unroll
@@ -217,20 +228,20 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
       for (int r = 0; r < 6; r++) ee[(24 + r) * STRIDE] = c * t.jj[r];
     }
     __syncthreads();
-    // ---- phase B: tensor-core rank-3 block updates, one role per warp
-    VX_ROLE_SWITCH(role, role_chunk, C, Gs, Ss, mask_s, base_s, nv, lane)
+    // ---- phase B: tensor-core SYRK of the panel, one role per warp
+    const int nks = (3 * nv + 3) >> 2;
+    VX_ROLE_SWITCH(role, role_chunk, C, As, Srow, nks, lane)
     // ---- phase C: per-frame corrections + gradient, fixed owner threads, voxel order
 #pragma unroll
     for (int q = 0; q < NDQ; q++) {
       const int id = tid + q * NT;
       if (id < W * NF_E) {
         const int fr = id / NF_E, comp = id - fr * NF_E;
-        const double *src = Gs + (NF_G + comp) * STRIDE;
+        const double *src = Es + comp * STRIDE;
+        const uint16_t *rp = rec_s + fr;
         double acc = dacc[q];
-        for (int lv = 0; lv < nv; lv++) {
-          const uint32_t mask = mask_s[lv];
-          if ((mask >> fr) & 1u) acc += src[base_s[lv] + __popc(mask & ((1u << fr) - 1u))];
-        }
+#pragma unroll 4
+        for (int lv = 0; lv < nv; lv++) acc += src[rp[lv * W]];   // absent frames read the zero record
         dacc[q] = acc;
       }
     }
@@ -238,7 +249,7 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
     v0 += nv;
   }
   // ---- item partials
-  double *pt = part_t + (size_t)item * T * 36;
+  double *pt = part_t + (size_t)item * T8 * 64;
   VX_ROLE_SWITCH(role, role_store, C, pt, lane)
   double *pd = part_d + (size_t)item * W * NF_E;
 #pragma unroll
@@ -249,23 +260,35 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
 }
 
 // Adds the items of each window in ascending order and writes Hess (upper blocks + mirrored lower
-// blocks, voxel_map.hpp:279-281) and JacT.  grid = (T, n_win), 64 threads.
-template <int W>
-__global__ void k_fin_small(const double *__restrict__ part_t, const double *__restrict__ part_d, double *__restrict__ H,
-                            double *__restrict__ J, int splits) {
-  constexpr int T = W * (W + 1) / 2;
-  constexpr TileTab<W> tab{};
-  __shared__ int ti[T], tj[T];
-  for (int k = threadIdx.x; k < T; k += blockDim.x) { ti[k] = tab.i[k]; tj[k] = tab.j[k]; }
+// blocks, voxel_map.hpp:279-281) and JacT.  One CTA per window.
+template <int W, int NT8>
+__global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ part_t, const double *__restrict__ part_d,
+                                                   double *__restrict__ H, double *__restrict__ J, int splits) {
+  constexpr int T = W * (W + 1) / 2, T8 = NT8 * (NT8 + 1) / 2;
+  __shared__ unsigned char ti[T], tj[T];
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int a = 0; a < W; a++)
+      for (int b = a; b < W; b++) { ti[t] = (unsigned char)a; tj[t] = (unsigned char)b; t++; }
+  }
   __syncthreads();
-  const int t = blockIdx.x, w = blockIdx.y, x = threadIdx.x;
-  const int i = ti[t], j = tj[t];
+  const int w = blockIdx.x;
   const int64_t jl = 6 * W;
   double *Hw = H + (size_t)w * jl * jl;
-  if (x < 36) {
+  const double *pt = part_t + (size_t)w * splits * T8 * 64;
+  const double *pd = part_d + (size_t)w * splits * W * NF_E;
+  for (int idx = threadIdx.x; idx < T * 36; idx += blockDim.x) {
+    const int t = idx / 36, x = idx - t * 36;
+    const int i = ti[t], j = tj[t];
     const int r = x % 6, c = x / 6;
+    // element (R, Cc) of the symmetric rank-3 sum; only upper 8x8 tiles are stored
+    int R = 6 * i + r, Cc = 6 * j + c;
+    if ((R >> 3) > (Cc >> 3)) { const int tmp = R; R = Cc; Cc = tmp; }
+    const int I = R >> 3, Jt = Cc >> 3;
+    const int t8 = I * NT8 - I * (I - 1) / 2 + (Jt - I);
+    const size_t eo = (size_t)t8 * 64 + (R & 7) * 8 + (Cc & 7);
     double s = 0.0;
-    for (int sp = 0; sp < splits; sp++) s += part_t[((size_t)(w * splits + sp) * T + t) * 36 + x];
+    for (int sp = 0; sp < splits; sp++) s += pt[(size_t)sp * T8 * 64 + eo];
     if (i == j) {
       // corrections: rot-rot 9 | rot-tra 9 (placed at (r,3+c) and (3+c,r)) | tra-tra upper 6
       int comp;
@@ -277,21 +300,22 @@ __global__ void k_fin_small(const double *__restrict__ part_t, const double *__r
         comp = 18 + (a == 0 ? b : (a == 1 ? 2 + b : 5));
       }
       double e = 0.0;
-      for (int sp = 0; sp < splits; sp++) e += part_d[(size_t)(w * splits + sp) * W * NF_E + i * NF_E + comp];
+      for (int sp = 0; sp < splits; sp++) e += pd[(size_t)sp * W * NF_E + i * NF_E + comp];
       Hw[(6 * i + c) * jl + (6 * i + r)] = s + e;
     } else {
       Hw[(6 * j + c) * jl + (6 * i + r)] = s;
       Hw[(6 * i + r) * jl + (6 * j + c)] = s;
     }
-  } else if (x < 42 && i == j) {
-    const int r = x - 36;
+  }
+  for (int idx = threadIdx.x; idx < 6 * W; idx += blockDim.x) {
+    const int i = idx / 6, r = idx - i * 6;
     double g = 0.0;
-    for (int sp = 0; sp < splits; sp++) g += part_d[(size_t)(w * splits + sp) * W * NF_E + i * NF_E + 24 + r];
-    J[(size_t)w * jl + 6 * i + r] = g;
+    for (int sp = 0; sp < splits; sp++) g += pd[(size_t)sp * W * NF_E + i * NF_E + 24 + r];
+    J[(size_t)w * jl + idx] = g;
   }
 }
 
-template <int W, int NROLES>
+template <int W, int NROLES, int MINB>
 int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   using Cfg = SmallCfg<W, NROLES>;
   cudaStream_t st = ctx->stream;
@@ -305,19 +329,19 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
     splits = (int)std::max<int64_t>(1, s);
   }
   const int64_t items = (int64_t)f->n_win * splits;
-  VX_TRY(f->part_t.reserve(sizeof(double) * items * Cfg::T * 36));
+  VX_TRY(f->part_t.reserve(sizeof(double) * items * Cfg::T8 * 64));
   VX_TRY(f->part_d.reserve(sizeof(double) * items * W * NF_E));
   static bool attr_set = false;
   if (!attr_set) {
-    VX_CUDA(cudaFuncSetAttribute(k_hess_small<W, NROLES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+    VX_CUDA(cudaFuncSetAttribute(k_hess_small<W, NROLES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
     attr_set = true;
   }
-  VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES><<<(unsigned)items, Cfg::NT, Cfg::SMEM, st>>>(
+  VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES, MINB><<<(unsigned)items, Cfg::NT, Cfg::SMEM, st>>>(
       f->off.as<int32_t>(), f->frame.as<int32_t>(), f->vox.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
       f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
       f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits));
-  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W><<<dim3(Cfg::T, f->n_win), 64, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
-                                                                                 f->H.as<double>(), f->J.as<double>(), splits));
+  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<f->n_win, 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
+                                                                               f->H.as<double>(), f->J.as<double>(), splits));
   return VX_OK;
 }
 
@@ -328,8 +352,13 @@ namespace vx {
 int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled) {
   *handled = true;
   switch (f->W) {
-    case 10: return launch_small<10, 4>(ctx, f, head, end);
-    case 20: return launch_small<20, 8>(ctx, f, head, end);
+    case 10: {
+      static const int minb = getenv("VX_HS_MINB") ? atoi(getenv("VX_HS_MINB")) : 3;
+      if (minb == 4) return launch_small<10, 4, 4>(ctx, f, head, end);
+      if (minb == 2) return launch_small<10, 4, 2>(ctx, f, head, end);
+      return launch_small<10, 4, 3>(ctx, f, head, end);
+    }
+    case 20: return launch_small<20, 8, 1>(ctx, f, head, end);
     default: *handled = false; return VX_OK;
   }
 }
