@@ -121,6 +121,22 @@ int vx_factor_residual_async(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t en
  * cost_resid (n_windows); any out pointer may be NULL */
 int vx_factor_device_buffers(vx_factor *f, void **Hess, void **JacT, void **cost_hess, void **cost_resid);
 
+/* ---- B3: Lidar_BA_Optimizer::damping_iter(x_stats, voxhess, hess*, resis, max_iter, is_display)
+ * voxel_map.hpp:422-497.  Levenberg-Marquardt on 6W unknowns per window: u=0.01, v=2 (:427), *hess
+ * snapshot before the gauge fix (:446), pose 0 fixed (:452-455), (Hess + u*diag(Hess)).ldlt().solve(-JacT)
+ * on the LOWER triangle (:457-458), retraction R*Exp(dtheta), p+dp (:460-464), gain ratio and damping
+ * update (:465-490), stop at |dr/r| < 1e-6 (:492).  The factor's cache follows the reference's stateful
+ * semantics (after a rejected step it holds the rejected trial).
+ *   poses      in/out, n_windows*W
+ *   hess_out   n_windows x (6W x 6W) col-major, may be NULL        (the reference's MatrixXd* hess)
+ *   resis      n_windows x 2: first and last cost                    (the reference's vector<double>& resis)
+ *   thd_num    only reproduces the reference's "Too Less Voxel" exit (:399-403) -> VX_ERR_TOO_FEW
+ *   converged  n_windows: the reference's bool return (false if any step was rejected), may be NULL
+ *   accept_trace  n_windows x max_iter, 1 accepted / 0 rejected / untouched when not run, may be NULL
+ *   n_iters    n_windows: LM iterations actually run, may be NULL */
+int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter,
+                int thd_num, int *converged, int *accept_trace, int *n_iters);
+
 #ifdef __cplusplus
 }
 #endif

@@ -201,6 +201,18 @@ class Factor:
         _chk(self.lib.vx_factor_residual(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(c)))
         return float(c[0]) if self.n_win == 1 else c
 
+    def ba_lidar(self, poses, max_iter=3, thd_num=2):
+        """Lidar_BA_Optimizer::damping_iter (voxel_map.hpp:422-497) on every window of the factor."""
+        ps = as_poses(poses).copy()
+        jl = 6 * self.W
+        hess = np.zeros((self.n_win, jl, jl)); resis = np.zeros((self.n_win, 2))
+        conv = np.zeros(self.n_win, dtype=np.int32); trace = np.full((self.n_win, max(max_iter, 1)), -1, dtype=np.int32)
+        nit = np.zeros(self.n_win, dtype=np.int32)
+        _chk(self.lib.vx_ba_lidar(self.ctx.h, self.h, _p(ps), _p(hess), _p(resis), C.c_int(max_iter), C.c_int(thd_num),
+                                  _p(conv), _p(trace), _p(nit)))
+        return dict(poses=ps, hess=np.transpose(hess, (0, 2, 1)), resis=resis, converged=conv,
+                    accept=[trace[w, :nit[w]].tolist() for w in range(self.n_win)])
+
     # device-resident path
     def set_poses(self, poses):
         self._poses_keep = as_poses(poses)
