@@ -48,6 +48,13 @@ typedef struct vx_pose {
   double p[3];
 } vx_pose;
 
+/* pcl::PointXYZINormal as the reference stores it (48 bytes: data[4], normal[4], intensity, curvature, pad) */
+typedef struct vx_point48 {
+  float x, y, z, _p0;
+  float normal_x, normal_y, normal_z, _p1;
+  float intensity, curvature, _p2, _p3;
+} vx_point48;
+
 /* ---- context ------------------------------------------------------------------------------ */
 int vx_ctx_create(int device, vx_ctx **out);
 int vx_ctx_destroy(vx_ctx *ctx);
@@ -120,6 +127,17 @@ int vx_factor_residual_async(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t en
 /* device pointers: Hess (n_windows*(6W)^2), JacT (n_windows*6W), cost_hess (n_windows),
  * cost_resid (n_windows); any out pointer may be NULL */
 int vx_factor_device_buffers(vx_factor *f, void **Hess, void **JacT, void **cost_hess, void **cost_resid);
+
+/* ---- A1: the voxel key rule, inlined 7x in the reference (voxel_map.hpp:1907-1918, :1977-1990, :2114-2125,
+ * :2173-2184, :42-52; tools.hpp:206-216; loop_refine.hpp:452-459).  xyz: n x 3 doubles, or floats when
+ * is_float_input (tools.hpp:211 promotes a float coordinate).  out_keys: n x 3 int64 (VOXEL_LOC x,y,z). */
+int vx_keys(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_float_input, int64_t *out_keys);
+
+/* ---- A2: void down_sampling_voxel(pcl::PointCloud<PointType>&, double)  tools.hpp:201-238.
+ * out must hold n points; *out_n = occupied cells.  Per cell the reference's sequential float running
+ * mean is replayed exactly (bit-identical x,y,z and curvature = count; other fields of the cell's first
+ * point kept); cells come out in ascending packed-key order (the reference: unordered_map order). */
+int vx_downsample_voxel(vx_ctx *ctx, const vx_point48 *pts, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n);
 
 /* ---- B3: Lidar_BA_Optimizer::damping_iter(x_stats, voxhess, hess*, resis, max_iter, is_display)
  * voxel_map.hpp:422-497.  Levenberg-Marquardt on 6W unknowns per window: u=0.01, v=2 (:427), *hess

@@ -170,6 +170,32 @@ int orc_ba_lidar(void *h, oc_pose *poses, double *hess_out, double *resis2, int 
   return conv ? 1 : 0;
 }
 
+// ---- A2 ------------------------------------------------------------------------------------
+int64_t orc_downsample_voxel(const PointXYZIN *pts, int64_t n, double voxel_size, PointXYZIN *out) {
+  std::vector<PointXYZIN> pl(pts, pts + n);
+  down_sampling_voxel(pl, voxel_size);
+  for (size_t i = 0; i < pl.size(); i++) out[i] = pl[i];
+  return (int64_t)pl.size();
+}
+
+// ---- A8 + A10: OctreeGBA::cut_voxel per keyframe + OctreeGBA_multi_recut -> a new LidarFactor --
+// gba_params: {gba_voxel_size, gba_min_eigen_value, eigen_value_array[4] (stored = 1/yaml), max_layer}
+void *orc_gba_build(const float *xyz, const int64_t *cloud_off, const oc_pose *poses, int W, double gba_voxel_size,
+                    double gba_min_eigen_value, const double *eig_array4, int max_layer) {
+  Params prm;
+  prm.gba_voxel_size = gba_voxel_size;
+  prm.gba_min_eigen_value = gba_min_eigen_value;
+  for (int k = 0; k < 4; k++) prm.gba_eigen_value_array[k] = eig_array4[k];
+  prm.max_layer = max_layer;
+  std::vector<IMUST> xs = poses_in(poses, W);
+  GbaMap oct_map;
+  for (int i = 0; i < W; i++)
+    gba_cut_voxel(oct_map, xs[i], xyz + 3 * cloud_off[i], (int)(cloud_off[i + 1] - cloud_off[i]), i, W, &prm);
+  LidarFactor *f = new LidarFactor(W);
+  OctreeGBA_multi_recut(oct_map, *f, 1);
+  return f;
+}
+
 double orc_now() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }

@@ -115,6 +115,32 @@ def cluster_transform(cl, pose):
     return out[0]
 
 
+point48_dtype = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("_p0", "<f4"), ("normal_x", "<f4"), ("normal_y", "<f4"),
+                          ("normal_z", "<f4"), ("_p1", "<f4"), ("intensity", "<f4"), ("curvature", "<f4"), ("_p2", "<f4"), ("_p3", "<f4")])
+assert point48_dtype.itemsize == 48
+
+
+def downsample_voxel(pts, voxel_size):
+    pts = np.ascontiguousarray(pts, dtype=point48_dtype)
+    out = np.zeros(pts.shape[0], dtype=point48_dtype)
+    lib().orc_downsample_voxel.restype = C.c_int64
+    n = lib().orc_downsample_voxel(_p(pts), C.c_int64(pts.shape[0]), C.c_double(voxel_size), _p(out))
+    return out[:n]
+
+
+def gba_build(clouds, poses, gba_voxel_size, gba_min_eigen_value, eig_array, max_layer):
+    """clouds: list of (n_i,3) float32 local-frame clouds, one per keyframe -> orc LidarFactor (A8 + A10)."""
+    W = len(clouds)
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(W + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses)
+    ea = np.ascontiguousarray(eig_array, dtype=np.float64)
+    lib().orc_gba_build.restype = C.c_void_p
+    h = lib().orc_gba_build(_p(xyz), _p(off), _p(ps), C.c_int(W), C.c_double(gba_voxel_size), C.c_double(gba_min_eigen_value),
+                            _p(ea), C.c_int(max_layer))
+    return Factor(W, handle=h)
+
+
 class Factor:
     """orc::LidarFactor (voxel_map.hpp:124-339 restated)."""
 
