@@ -99,6 +99,9 @@ int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const 
                          const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds);
 /* read back what evaluate_only_residual caches  voxel_map.hpp:317-319 */
 int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vectors, vx_cluster *pcr_adds);
+/* read back the factor content in the vx_factor_upload_csr form (offsets V+1, frames/clusters nnz, coeffs V);
+ * any pointer may be NULL.  The reference reads these members directly (plvec_voxels, coeffs). */
+int vx_factor_download_csr(vx_factor *f, int64_t *offsets, int32_t *frames, vx_cluster *clusters, double *coeffs);
 /* Evaluation path selection.  acc_evaluate2 has two device formulations: a fused tensor-core kernel for
  * the window sizes the reference runs (W = 10, 20) and a generic pair-list path for any W (top-level
  * GBA, W ~ 399).  on != 0 forces the generic path (tests compare the two). */
@@ -138,6 +141,25 @@ int vx_keys(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_f
  * mean is replayed exactly (bit-identical x,y,z and curvature = count; other fields of the cell's first
  * point kept); cells come out in ascending packed-key order (the reference: unordered_map order). */
 int vx_downsample_voxel(vx_ctx *ctx, const vx_point48 *pts, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n);
+
+/* ---- A8 + A10: OctreeGBA::cut_voxel per keyframe (loop_refine.hpp:446-479) + OctreeGBA_multi_recut
+ * (loop_refine.hpp:483-537) -> LidarFactor, as HBA_add_edge does at voxelslam.cpp:2887-2892.
+ * The thresholds are the reference's globals gba_voxel_size / gba_min_eigen_value / gba_eigen_value_array
+ * (loop_refine.hpp:269-271; the array is stored as 1/yaml, voxelslam.cpp:3023-3024) and max_layer. */
+typedef struct vx_gba_params {
+  double voxel_size;
+  double min_eigen_value;
+  double eigen_value_array[4];
+  int32_t max_layer;   /* 0..3 */
+  int32_t _pad;
+} vx_gba_params;
+/* xyz: local-frame keyframe clouds, float x,y,z triples, cloud c = points [cloud_off[c], cloud_off[c+1]).
+ * Frame g (0 <= g < n_windows*W of `f`, window-major) uses cloud frame_cloud[g] (NULL: g itself) and
+ * poses[g]; overlapping windows (stride 5, size 10: voxelslam.cpp:3137-3138) reference one cloud twice.
+ * Replaces the content of `f` (cache = the recut-time eig_value / eig_vector / pcr_add, as tras_opt /
+ * push_voxel leave it).  Voxels are ordered by (window, root cell, octree path). */
+int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                 const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
 
 /* ---- B3: Lidar_BA_Optimizer::damping_iter(x_stats, voxhess, hess*, resis, max_iter, is_display)
  * voxel_map.hpp:422-497.  Levenberg-Marquardt on 6W unknowns per window: u=0.01, v=2 (:427), *hess

@@ -73,7 +73,7 @@ def scan(rects, R, p, dirs_body, rng, range_noise=0.02, blind=0.5):
     return (dirs_body[ok] * t[:, None]).astype(np.float32)
 
 
-def arc_trajectory(W, seed, step=1.0, yaw_step_deg=4.0, start=(-4.0, -2.0, 1.2), yaw0=0.3):
+def arc_trajectory(W, seed, step=1.0, yaw_step_deg=4.0, start=(-7.0, 0.5, 1.2), yaw0=-0.35):
     rng = np.random.Generator(np.random.PCG64(seed))
     yaw = yaw0 + np.deg2rad(yaw_step_deg) * np.arange(W) + rng.normal(0, 0.005, W)
     rv = np.zeros((W, 3)); rv[:, 2] = yaw; rv[:, :2] = rng.normal(0, 0.01, (W, 2))

@@ -18,6 +18,11 @@ cluster_dtype = np.dtype([("P", "<f8", (9,)), ("v", "<f8", (3,)), ("N", "<i4"), 
 pose_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,))], align=True)
 assert cluster_dtype.itemsize == 104 and pose_dtype.itemsize == 96
 
+gba_params_dtype = np.dtype([("voxel_size", "<f8"), ("min_eigen_value", "<f8"), ("eigen_value_array", "<f8", (4,)), ("max_layer", "<i4"), ("_pad", "<i4")])
+point48_dtype = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("_p0", "<f4"), ("normal_x", "<f4"), ("normal_y", "<f4"),
+                          ("normal_z", "<f4"), ("_p1", "<f4"), ("intensity", "<f4"), ("curvature", "<f4"), ("_p2", "<f4"), ("_p3", "<f4")])
+assert gba_params_dtype.itemsize == 56 and point48_dtype.itemsize == 48
+
 VX_OK = 0
 ERR_NAMES = {-1: "VX_ERR_CUDA", -2: "VX_ERR_ARG", -3: "VX_ERR_TOO_FEW", -4: "VX_ERR_OPT_STATE", -5: "VX_ERR_NOMEM"}
 
@@ -121,6 +126,24 @@ class Context:
         self.close()
 
 
+def keys(ctx, xyz, voxel_size):
+    """A1: (n,3) float64 or float32 coordinates -> (n,3) int64 VOXEL_LOC (bit-exact reference rule)."""
+    xyz = np.ascontiguousarray(xyz)
+    assert xyz.dtype in (np.float32, np.float64)
+    out = np.zeros(xyz.shape, dtype=np.int64)
+    _chk(ctx.lib.vx_keys(ctx.h, _p(xyz), C.c_int64(xyz.size // 3), C.c_double(voxel_size), C.c_int(int(xyz.dtype == np.float32)), _p(out)))
+    return out
+
+
+def downsample_voxel(ctx, pts, voxel_size):
+    """A2: down_sampling_voxel (tools.hpp:201-238); returns the cells in ascending packed-key order."""
+    pts = np.ascontiguousarray(pts, dtype=point48_dtype)
+    out = np.zeros(pts.shape[0], dtype=point48_dtype)
+    n = C.c_int64(0)
+    _chk(ctx.lib.vx_downsample_voxel(ctx.h, _p(pts), C.c_int64(pts.shape[0]), C.c_double(voxel_size), _p(out), C.byref(n)))
+    return out[:n.value]
+
+
 class DevArray:
     """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
 
@@ -178,6 +201,24 @@ class Factor:
     def hessian_raw(self, ps, H, J, c, head=0, end=-1):
         """vx_factor_hessian into caller-owned buffers (H stays column-major per window)."""
         _chk(self.lib.vx_factor_hessian(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(H), _p(J), _p(c)))
+
+    def download_csr(self):
+        V, nnz = self.num_voxels, self.num_voxel_frames
+        off = np.zeros(V + 1, dtype=np.int64); fr = np.zeros(nnz, dtype=np.int32); cl = np.zeros(nnz, dtype=cluster_dtype); coe = np.zeros(V)
+        _chk(self.lib.vx_factor_download_csr(self.h, _p(off), _p(fr), _p(cl), _p(coe)))
+        ev, evec, mrg = self.download_cache()
+        return dict(offsets=off, frames=fr, clusters=cl, coe=coe, eigval=ev, eigvec=evec, merged=mrg)
+
+    def gba_build(self, clouds, poses, voxel_size, min_eigen_value, eig_array, max_layer, frame_cloud=None):
+        """OctreeGBA::cut_voxel per frame + OctreeGBA_multi_recut (loop_refine.hpp:446-537) into this factor.
+        clouds: list of (n,3) float32 local-frame clouds; frame g uses clouds[frame_cloud[g]] (default g)."""
+        xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+        off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+        ps = as_poses(poses)
+        prm = np.zeros(1, dtype=gba_params_dtype)
+        prm["voxel_size"] = voxel_size; prm["min_eigen_value"] = min_eigen_value; prm["eigen_value_array"] = eig_array; prm["max_layer"] = max_layer
+        fc = None if frame_cloud is None else np.ascontiguousarray(frame_cloud, dtype=np.int32)
+        _chk(self.lib.vx_gba_build(self.ctx.h, xyz.ctypes.data_as(C.c_void_p), _p(off), C.c_int(len(clouds)), _p(fc), _p(ps), _p(prm), self.h))
 
     def download_cache(self):
         V = self.num_voxels

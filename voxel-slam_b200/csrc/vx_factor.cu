@@ -757,6 +757,38 @@ int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vecto
   return VX_OK;
 }
 
+int vx_factor_download_csr(vx_factor *f, int64_t *offsets, int32_t *frames, vx_cluster *clusters, double *coeffs) {
+  VX_ARG(f != nullptr);
+  vx_ctx *ctx = f->ctx;
+  VX_TRY(bind(ctx));
+  const int64_t V = f->V, nnz = f->nnz;
+  cudaStream_t st = ctx->stream;
+  if (offsets) {
+    std::vector<int32_t> off(V + 1, 0);
+    if (V > 0) VX_CUDA(cudaMemcpyAsync(off.data(), f->off.p, sizeof(int32_t) * (V + 1), cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    for (int64_t v = 0; v <= V; v++) offsets[v] = off[v];
+  }
+  if (coeffs && V > 0) VX_CUDA(cudaMemcpyAsync(coeffs, f->coe.p, sizeof(double) * V, cudaMemcpyDeviceToHost, st));
+  if (frames && nnz > 0) VX_CUDA(cudaMemcpyAsync(frames, f->frame.p, sizeof(int32_t) * nnz, cudaMemcpyDeviceToHost, st));
+  if (clusters && nnz > 0) {
+    std::vector<double> mom(9 * (size_t)nnz);
+    std::vector<int32_t> cnt(nnz);
+    VX_CUDA(cudaMemcpyAsync(mom.data(), f->mom.p, sizeof(double) * 9 * nnz, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaMemcpyAsync(cnt.data(), f->cnt.p, sizeof(int32_t) * nnz, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    for (int64_t e = 0; e < nnz; e++) {
+      vx_cluster &c = clusters[e];
+      c.P[0] = mom[0 * nnz + e]; c.P[1] = c.P[3] = mom[1 * nnz + e]; c.P[2] = c.P[6] = mom[2 * nnz + e];
+      c.P[4] = mom[3 * nnz + e]; c.P[5] = c.P[7] = mom[4 * nnz + e]; c.P[8] = mom[5 * nnz + e];
+      c.v[0] = mom[6 * nnz + e]; c.v[1] = mom[7 * nnz + e]; c.v[2] = mom[8 * nnz + e];
+      c.N = cnt[e]; c._pad = 0;
+    }
+  }
+  VX_CUDA(cudaStreamSynchronize(st));
+  return VX_OK;
+}
+
 int vx_factor_force_generic(vx_factor *f, int on) {
   VX_ARG(f != nullptr);
   f->force_pairlist = on != 0;

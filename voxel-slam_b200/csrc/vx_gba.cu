@@ -1,0 +1,518 @@
+// vx_gba.cu — the global-BA voxel map as a sort/segment pass (SURVEY §8a rows A8 + A10):
+//   OctreeGBA::cut_voxel          loop_refine.hpp:446-479   world = R*local + p, root key, per-frame point lists
+//   OctreeGBA::recut / subdivide  loop_refine.hpp:323-405   eigen-solve, plane test, split to max_layer
+//   OctreeGBA_multi_recut         loop_refine.hpp:483-537   -> LidarFactor::push_voxel for every accepted plane
+// The reference grows a pointer octree per root voxel.  Here the octree is a KEY: every point's path
+// through the (up to max_layer) subdivisions is a pure function of the point and its root cell —
+// child = 4*[x>cx] + 2*[y>cy] + [z>cz] against centres built by +-quater_length (loop_refine.hpp:331-347) —
+// so a node of layer l is a run of equal (window, root key, first 3l path bits) in the sorted point
+// array, and "recut" is a segmented reduction + a per-node decision, evaluated for all layers at once:
+//   1. per point instance: world point (no FMA contraction, so cells are bit-exact), packed root key, path
+//   2. stable radix sorts -> order (window, root key, path, frame, original order)
+//   3. head flags + scans -> segments (finest leaf, frame) and the nodes of every layer
+//   4. one warp per segment: scan-local and world moments (P, v, N)
+//   5. per node: merged world cluster, 3x3 eigen-solve, plane / accept / subdivide flags, top-down liveness
+//   6. accepted planes -> voxels (ordered by position), segments -> (voxel, frame) clusters -> device LidarFactor
+#include "vx_factor.cuh"
+#include "vx_math.cuh"
+#include "vx_voxelize.cuh"
+#include <cub/cub.cuh>
+#include <algorithm>
+
+using namespace vx;
+
+namespace {
+
+constexpr int MAXL = 3;          // max_layer supported (reference default 2)
+constexpr int FRAME_BITS = 22;
+
+struct GbaP {
+  double vs, min_eig, thr[4];
+  int L;
+};
+
+// world = R*local + p exactly as a straight-line double evaluation without contraction:
+// ((R(r,0)*l0 + R(r,1)*l1) + R(r,2)*l2) + p[r]
+__device__ __forceinline__ d3 world_of(const double *__restrict__ ps, double lx, double ly, double lz) {
+  d3 w;
+  w.x = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ps[0], lx), __dmul_rn(ps[3], ly)), __dmul_rn(ps[6], lz)), ps[9]);
+  w.y = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ps[1], lx), __dmul_rn(ps[4], ly)), __dmul_rn(ps[7], lz)), ps[10]);
+  w.z = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ps[2], lx), __dmul_rn(ps[5], ly)), __dmul_rn(ps[8], lz)), ps[11]);
+  return w;
+}
+
+__device__ __forceinline__ int frame_of(const int64_t *__restrict__ inst_off, int F, int64_t j) {
+  int lo = 0, hi = F;   // largest g with inst_off[g] <= j
+  while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (inst_off[mid] <= j) lo = mid; else hi = mid; }
+  return lo;
+}
+
+// 1. keys
+__global__ void k_gba_point(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
+                            const int64_t *__restrict__ inst_off, int F, const double *__restrict__ poses, GbaP prm, int64_t NI,
+                            uint32_t *__restrict__ key1, uint64_t *__restrict__ key2, int32_t *__restrict__ idx, int *__restrict__ bad) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= NI) return;
+  const int g = frame_of(inst_off, F, j);
+  const int64_t pt = cloud_off[frame_cloud[g]] + (j - inst_off[g]);
+  const double lx = (double)xyz[3 * pt], ly = (double)xyz[3 * pt + 1], lz = (double)xyz[3 * pt + 2];
+  const d3 w = world_of(poses + 12 * (int64_t)g, lx, ly, lz);
+  const int64_t kx = key_axis_d(w.x, prm.vs), ky = key_axis_d(w.y, prm.vs), kz = key_axis_d(w.z, prm.vs);
+  uint64_t k2;
+  if (!pack_key(kx, ky, kz, k2)) *bad = 1;
+  // path: centre of the root = (0.5 + key) * voxel_size (loop_refine.hpp:469-471), quater_length = voxel_size/4 as float (:472)
+  double cx = __dmul_rn(__dadd_rn(0.5, (double)kx), prm.vs), cy = __dmul_rn(__dadd_rn(0.5, (double)ky), prm.vs), cz = __dmul_rn(__dadd_rn(0.5, (double)kz), prm.vs);
+  float q = (float)(prm.vs / 4.0);
+  uint32_t path = 0;
+  for (int l = 0; l < prm.L; l++) {
+    const int bx = w.x > cx, by = w.y > cy, bz = w.z > cz;
+    path = (path << 3) | (uint32_t)(4 * bx + 2 * by + bz);
+    const double dq = (double)q;
+    cx = __dadd_rn(cx, bx ? dq : -dq); cy = __dadd_rn(cy, by ? dq : -dq); cz = __dadd_rn(cz, bz ? dq : -dq);
+    q = q / 2.0f;
+  }
+  key1[j] = (path << FRAME_BITS) | (uint32_t)g;
+  key2[j] = k2;
+  idx[j] = (int32_t)j;
+}
+
+template <class T>
+__global__ void k_gather(const T *__restrict__ src, const int32_t *__restrict__ idx, T *__restrict__ dst, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx[i]];
+}
+__global__ void k_gather_win(const uint32_t *__restrict__ key1, const int32_t *__restrict__ idx, int W, uint32_t *__restrict__ win, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) win[i] = (key1[idx[i]] & ((1u << FRAME_BITS) - 1u)) / (uint32_t)W;
+}
+
+// 3. head flags for the segments and for the nodes of every layer (sorted order)
+__global__ void k_gba_heads(const uint32_t *__restrict__ k1, const uint64_t *__restrict__ k2, int W, int L, int64_t n, int32_t *__restrict__ hseg,
+                            int32_t *__restrict__ hn0, int32_t *__restrict__ hn1, int32_t *__restrict__ hn2, int32_t *__restrict__ hn3) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t fm = (1u << FRAME_BITS) - 1u;
+  const uint32_t a1 = k1[i];
+  int32_t *hn[4] = {hn0, hn1, hn2, hn3};
+  if (i == 0) { hseg[0] = 1; for (int l = 0; l <= L; l++) hn[l][0] = 1; return; }
+  const uint32_t b1 = k1[i - 1];
+  const bool root_new = k2[i] != k2[i - 1] || (a1 & fm) / (uint32_t)W != (b1 & fm) / (uint32_t)W;
+  const uint32_t pa = a1 >> FRAME_BITS, pb = b1 >> FRAME_BITS;
+  bool leaf_new = root_new;
+  for (int l = 0; l <= L; l++) {
+    const int sh = 3 * (L - l);
+    const bool nn = root_new || (pa >> sh) != (pb >> sh);
+    hn[l][i] = nn ? 1 : 0;
+    if (l == L) leaf_new = nn;
+  }
+  hseg[i] = (leaf_new || (a1 & fm) != (b1 & fm)) ? 1 : 0;
+}
+// start[id] = position of the head with inclusive-scan value id+1; start[total] = n
+__global__ void k_starts(const int32_t *__restrict__ flag, const int32_t *__restrict__ incl, int64_t n, int32_t *__restrict__ start) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flag[i]) start[incl[i] - 1] = (int32_t)i;
+  if (i == n - 1) start[incl[i]] = (int32_t)n;
+}
+
+// 4. one warp per segment = (finest leaf, frame): scan-local moments (what LidarFactor stores per
+// voxel-frame, loop_refine.hpp:382-385) and world moments (pcr_add, loop_refine.hpp:320).
+// seg planes: [0..8] local P6 v3, [9..17] world P6 v3, all [19][nseg]; N in segN.
+__global__ void __launch_bounds__(256)
+k_seg_moments(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
+              const int64_t *__restrict__ inst_off, const double *__restrict__ poses, const int32_t *__restrict__ sidx,
+              const uint32_t *__restrict__ k1, const int32_t *__restrict__ seg_start, int64_t nseg, double *__restrict__ segm,
+              int32_t *__restrict__ segN, int32_t *__restrict__ segF) {
+  const int64_t s = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (s >= nseg) return;
+  const int32_t b = seg_start[s], e = seg_start[s + 1];
+  const int g = (int)(k1[b] & ((1u << FRAME_BITS) - 1u));
+  const double *ps = poses + 12 * (int64_t)g;
+  const int64_t base = cloud_off[frame_cloud[g]] - inst_off[g];
+  double a[18];
+#pragma unroll
+  for (int k = 0; k < 18; k++) a[k] = 0.0;
+  for (int32_t i = b + lane; i < e; i += 32) {
+    const int64_t pt = base + sidx[i];
+    const double lx = (double)xyz[3 * pt], ly = (double)xyz[3 * pt + 1], lz = (double)xyz[3 * pt + 2];
+    const d3 w = world_of(ps, lx, ly, lz);
+    a[0] += lx * lx; a[1] += lx * ly; a[2] += lx * lz; a[3] += ly * ly; a[4] += ly * lz; a[5] += lz * lz;
+    a[6] += lx; a[7] += ly; a[8] += lz;
+    a[9] += w.x * w.x; a[10] += w.x * w.y; a[11] += w.x * w.z; a[12] += w.y * w.y; a[13] += w.y * w.z; a[14] += w.z * w.z;
+    a[15] += w.x; a[16] += w.y; a[17] += w.z;
+  }
+#pragma unroll
+  for (int k = 0; k < 18; k++) {
+    double x = a[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0) segm[(size_t)k * nseg + s] = x;
+  }
+  if (lane == 0) { segN[s] = e - b; segF[s] = g; }
+}
+
+// 5a. per node of one layer: merged world cluster over its segments (in order), frame span, eigen-solve, flags
+// nodeS: [10][nn] world P6 v3 N ; nodeE: [12][nn] lam3 U9 ; flags bit0 big(N>10) bit1 plane bit2 accept
+__global__ void k_node_stats(const int32_t *__restrict__ node_start, const int32_t *__restrict__ segid_incl, int64_t nn, int64_t nseg,
+                             const double *__restrict__ segm, const int32_t *__restrict__ segN, const int32_t *__restrict__ segF, GbaP prm, int layer,
+                             double *__restrict__ nodeS, double *__restrict__ nodeE, int32_t *__restrict__ flags, int32_t *__restrict__ first_seg) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= nn) return;
+  const int32_t s0 = segid_incl[node_start[k]] - 1;
+  const int32_t s1 = (k + 1 < nn) ? segid_incl[node_start[k + 1]] - 1 : (int32_t)nseg;
+  first_seg[k] = s0;
+  if (k == nn - 1) first_seg[nn] = (int32_t)nseg;
+  double a[9];
+#pragma unroll
+  for (int c = 0; c < 9; c++) a[c] = 0.0;
+  int64_t N = 0;
+  int fmin = 0x7fffffff, fmax = -1;
+  for (int32_t s = s0; s < s1; s++) {
+#pragma unroll
+    for (int c = 0; c < 9; c++) a[c] += segm[(size_t)(9 + c) * nseg + s];
+    N += segN[s];
+    const int f = segF[s];
+    fmin = min(fmin, f); fmax = max(fmax, f);
+  }
+#pragma unroll
+  for (int c = 0; c < 9; c++) nodeS[(size_t)c * nn + k] = a[c];
+  nodeS[(size_t)9 * nn + k] = (double)N;
+  int fl = 0;
+  double l[3] = {0, 0, 0}, u[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  if (N > 10) {   // loop_refine.hpp:360
+    fl |= 1;
+    const double dn = (double)N;
+    const double cx = a[6] / dn, cy = a[7] / dn, cz = a[8] / dn;   // PointCluster::cov, tools.hpp:333-337
+    s33 C;
+    C.xx = a[0] / dn - cx * cx; C.xy = a[1] / dn - cx * cy; C.xz = a[2] / dn - cx * cz;
+    C.yy = a[3] / dn - cy * cy; C.yz = a[4] / dn - cy * cz; C.zz = a[5] / dn - cz * cz;
+    eig3_jacobi(C, l, u);
+    const bool plane = l[0] < prm.min_eig && (l[0] / l[2]) < prm.thr[layer];   // plane_judge, loop_refine.hpp:310-314
+    if (plane) {
+      fl |= 2;
+      // accept: >= 2 occupied frames (:372-376) and lambda0/lambda1 <= 0.12 (:378)
+      if (fmin != fmax && !(l[0] / l[1] > 0.12)) fl |= 4;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; c++) nodeE[(size_t)c * nn + k] = l[c];
+#pragma unroll
+  for (int c = 0; c < 9; c++) nodeE[(size_t)(3 + c) * nn + k] = u[c];
+  flags[k] = fl;
+}
+
+// 5b. top-down liveness: a node exists iff every ancestor was subdivided (N>10, not a plane, layer < max_layer)
+// flags bit3 alive, bit4 emit
+__global__ void k_node_alive(const int32_t *__restrict__ node_start, int64_t nn, int layer, int L, const int32_t *__restrict__ parent_incl,
+                             const int32_t *__restrict__ parent_flags, int32_t *__restrict__ flags, int32_t *__restrict__ emit_at) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= nn) return;
+  int fl = flags[k];
+  bool alive = true;
+  if (layer > 0) {
+    const int pf = parent_flags[parent_incl[node_start[k]] - 1];
+    alive = (pf & 8) && (pf & 1) && !(pf & 2);   // parent alive and subdivided (parent layer < L by construction)
+  }
+  if (alive) fl |= 8;
+  if (alive && (fl & 4)) { fl |= 16; emit_at[node_start[k]] = 1; }
+  flags[k] = fl;
+}
+
+// 6a. voxel records of the emitted nodes of one layer
+__global__ void k_emit_voxels(const int32_t *__restrict__ node_start, const int32_t *__restrict__ flags, int64_t nn, const int32_t *__restrict__ vid_excl,
+                              const double *__restrict__ nodeS, const double *__restrict__ nodeE, int64_t V, double *__restrict__ lam,
+                              double *__restrict__ U, double *__restrict__ mrg, double *__restrict__ fix, double *__restrict__ coe) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= nn || !(flags[k] & 16)) return;
+  const int64_t v = vid_excl[node_start[k]];
+#pragma unroll
+  for (int c = 0; c < 10; c++) { mrg[(size_t)c * V + v] = nodeS[(size_t)c * nn + k]; fix[(size_t)c * V + v] = 0.0; }
+#pragma unroll
+  for (int c = 0; c < 3; c++) lam[(size_t)c * V + v] = nodeE[(size_t)c * nn + k];
+#pragma unroll
+  for (int c = 0; c < 9; c++) U[(size_t)c * V + v] = nodeE[(size_t)(3 + c) * nn + k];
+  coe[v] = 1.0;   // loop_refine.hpp:380
+}
+
+struct LevelPtrs {
+  const int32_t *start[MAXL + 1];
+  const int32_t *incl[MAXL + 1];
+  const int32_t *flags[MAXL + 1];
+};
+// 6b. segment -> key (voxel << 32 | frame) of the emitted ancestor, or ~0
+__global__ void k_seg_voxel(const int32_t *__restrict__ seg_start, const int32_t *__restrict__ segF, int64_t nseg, LevelPtrs lp, int L,
+                            const int32_t *__restrict__ vid_excl, uint64_t *__restrict__ key, int32_t *__restrict__ val) {
+  const int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (s >= nseg) return;
+  const int32_t i0 = seg_start[s];
+  uint64_t kk = ~0ull;
+  for (int l = L; l >= 0; l--) {
+    const int32_t k = lp.incl[l][i0] - 1;
+    if (lp.flags[l][k] & 16) { kk = ((uint64_t)(uint32_t)vid_excl[lp.start[l][k]] << 32) | (uint32_t)segF[s]; break; }
+  }
+  key[s] = kk;
+  val[s] = (int32_t)s;
+}
+__global__ void k_vf_heads(const uint64_t *__restrict__ key, int64_t n, int32_t *__restrict__ flag) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  flag[i] = (key[i] != ~0ull && (i == 0 || key[i] != key[i - 1])) ? 1 : 0;
+}
+// 6c. one thread per voxel-frame: sum its segments' scan-local moments in order
+__global__ void k_vf_fill(const uint64_t *__restrict__ key, const int32_t *__restrict__ sval, const int32_t *__restrict__ vf_start, int64_t nnz,
+                          int64_t nvalid, const double *__restrict__ segm, const int32_t *__restrict__ segN, int64_t nseg, double *__restrict__ mom,
+                          int32_t *__restrict__ cnt, int32_t *__restrict__ frame, int32_t *__restrict__ vox) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= nnz) return;
+  const int32_t b = vf_start[e], en = (e + 1 < nnz) ? vf_start[e + 1] : (int32_t)nvalid;
+  double a[9];
+#pragma unroll
+  for (int c = 0; c < 9; c++) a[c] = 0.0;
+  int32_t N = 0;
+  for (int32_t i = b; i < en; i++) {
+    const int32_t s = sval[i];
+#pragma unroll
+    for (int c = 0; c < 9; c++) a[c] += segm[(size_t)c * nseg + s];
+    N += segN[s];
+  }
+#pragma unroll
+  for (int c = 0; c < 9; c++) mom[(size_t)c * nnz + e] = a[c];
+  cnt[e] = N;
+  frame[e] = (int32_t)(key[b] & 0xffffffffu);
+  vox[e] = (int32_t)(key[b] >> 32);
+}
+// off[v] = first voxel-frame of voxel v (vox[] ascending), off[V] = nnz ; win[v], wv_off
+__global__ void k_vox_off(const int32_t *__restrict__ vox, int64_t nnz, int64_t V, int32_t *__restrict__ off) {
+  const int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v > V) return;
+  int64_t lo = 0, hi = nnz;
+  while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (vox[mid] < v) lo = mid + 1; else hi = mid; }
+  off[v] = (int32_t)lo;
+}
+__global__ void k_vox_win(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, int64_t V, int W, int32_t *__restrict__ win) {
+  const int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v < V) win[v] = frame[off[v]] / W;
+}
+__global__ void k_win_off(const int32_t *__restrict__ win, int64_t V, int NW, int32_t *__restrict__ wv_off) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w > NW) return;
+  int64_t lo = 0, hi = V;
+  while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (win[mid] < w) lo = mid + 1; else hi = mid; }
+  wv_off[w] = (int32_t)lo;
+}
+
+}  // namespace
+
+namespace {
+
+struct Tmp {   // RAII set of temporary device buffers
+  std::vector<DevBuf *> all;
+  ~Tmp() { for (DevBuf *b : all) { b->release(); delete b; } }
+  DevBuf &make() { all.push_back(new DevBuf()); return *all.back(); }
+};
+
+int incl_scan(vx_ctx *ctx, const int32_t *in, int32_t *out, int64_t n) {
+  size_t tb = 0;
+  VX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tb, in, out, (int)n, ctx->stream));
+  VX_TRY(ctx->scratch.reserve(tb));
+  VX_CUDA(cub::DeviceScan::InclusiveSum(ctx->scratch.p, tb, in, out, (int)n, ctx->stream));
+  ctx->launches += 2;
+  return VX_OK;
+}
+int excl_scan(vx_ctx *ctx, const int32_t *in, int32_t *out, int64_t n) {
+  size_t tb = 0;
+  VX_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, in, out, (int)n, ctx->stream));
+  VX_TRY(ctx->scratch.reserve(tb));
+  VX_CUDA(cub::DeviceScan::ExclusiveSum(ctx->scratch.p, tb, in, out, (int)n, ctx->stream));
+  ctx->launches += 2;
+  return VX_OK;
+}
+template <class K>
+int sort_pairs(vx_ctx *ctx, const K *kin, K *kout, const int32_t *vin, int32_t *vout, int64_t n, int begin_bit, int end_bit) {
+  size_t tb = 0;
+  VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, kin, kout, vin, vout, (int)n, begin_bit, end_bit, ctx->stream));
+  VX_TRY(ctx->scratch.reserve(tb));
+  VX_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, tb, kin, kout, vin, vout, (int)n, begin_bit, end_bit, ctx->stream));
+  ctx->launches += 4;
+  return VX_OK;
+}
+int read_last(vx_ctx *ctx, const int32_t *d, int64_t n, int32_t *h) {
+  VX_CUDA(cudaMemcpyAsync(h, d + (n - 1), sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VX_OK;
+}
+int bits_for(int64_t n) { int b = 1; while (((int64_t)1 << b) < n) b++; return b; }
+
+}  // namespace
+
+extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                            const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
+  VX_ARG(f != nullptr && params != nullptr && cloud_off != nullptr && poses != nullptr && n_clouds >= 1);
+  VX_TRY(bind(ctx));
+  cudaStream_t st = ctx->stream;
+  const int W = f->W, NW = f->n_win, F = W * NW;
+  VX_ARG(params->max_layer >= 0 && params->max_layer <= MAXL && params->voxel_size > 0);
+  VX_ARG(F < (1 << FRAME_BITS));
+  VX_ARG(frame_cloud != nullptr || n_clouds == F);
+  GbaP prm;
+  prm.vs = params->voxel_size; prm.min_eig = params->min_eigen_value; prm.L = params->max_layer;
+  for (int k = 0; k < 4; k++) prm.thr[k] = params->eigen_value_array[k];
+  const int L = prm.L;
+  const int64_t NP = cloud_off[n_clouds];
+  std::vector<int32_t> fc(F);
+  std::vector<int64_t> inst_off(F + 1, 0);
+  for (int g = 0; g < F; g++) {
+    fc[g] = frame_cloud ? frame_cloud[g] : g;
+    VX_ARG(fc[g] >= 0 && fc[g] < n_clouds);
+    inst_off[g + 1] = inst_off[g] + (cloud_off[fc[g] + 1] - cloud_off[fc[g]]);
+  }
+  const int64_t NI = inst_off[F];
+  VX_ARG(NI < ((int64_t)1 << 31) && NP >= 0);
+  if (NI == 0) return vx_factor_clear(f);
+  VX_ARG(xyz != nullptr);
+
+  Tmp T;
+  DevBuf &d_xyz = T.make(), &d_coff = T.make(), &d_fc = T.make(), &d_ioff = T.make(), &d_poses = T.make(), &d_bad = T.make();
+  VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1))); VX_TRY(d_coff.reserve(8 * (n_clouds + 1))); VX_TRY(d_fc.reserve(4 * F));
+  VX_TRY(d_ioff.reserve(8 * (F + 1))); VX_TRY(d_poses.reserve(sizeof(vx_pose) * F)); VX_TRY(d_bad.reserve(4));
+  VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, st));
+  VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (n_clouds + 1), cudaMemcpyHostToDevice, st));
+  VX_CUDA(cudaMemcpyAsync(d_fc.p, fc.data(), 4 * F, cudaMemcpyHostToDevice, st));
+  VX_CUDA(cudaMemcpyAsync(d_ioff.p, inst_off.data(), 8 * (F + 1), cudaMemcpyHostToDevice, st));
+  VX_CUDA(cudaMemcpyAsync(d_poses.p, poses, sizeof(vx_pose) * F, cudaMemcpyHostToDevice, st));
+  VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
+
+  // ---- 1. keys (kept in instance order; only the permutation travels through the sorts)
+  DevBuf &k1i = T.make(), &k2i = T.make(), &k1t = T.make(), &k2t = T.make(), &k2u = T.make(), &ia = T.make(), &ib = T.make();
+  VX_TRY(k1i.reserve(4 * NI)); VX_TRY(k2i.reserve(8 * NI)); VX_TRY(k1t.reserve(4 * NI)); VX_TRY(k2t.reserve(8 * NI)); VX_TRY(k2u.reserve(8 * NI));
+  VX_TRY(ia.reserve(4 * NI)); VX_TRY(ib.reserve(4 * NI));
+  VX_KERNEL(ctx, "k_gba_point", k_gba_point<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), F,
+                                                                                d_poses.as<double>(), prm, NI, k1i.as<uint32_t>(), k2i.as<uint64_t>(), ia.as<int32_t>(), d_bad.as<int>()));
+  // ---- 2. stable sorts: (path, frame), then root key, then window
+  VX_TRY(sort_pairs<uint32_t>(ctx, k1i.as<uint32_t>(), k1t.as<uint32_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, FRAME_BITS + 3 * L));
+  VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), ib.as<int32_t>(), k2t.as<uint64_t>(), NI));
+  VX_TRY(sort_pairs<uint64_t>(ctx, k2t.as<uint64_t>(), k2u.as<uint64_t>(), ib.as<int32_t>(), ia.as<int32_t>(), NI, 0, 63));
+  int32_t *sidx = ia.as<int32_t>();
+  if (NW > 1) {
+    VX_KERNEL(ctx, "k_gather_win", k_gather_win<<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), ia.as<int32_t>(), W, k1t.as<uint32_t>(), NI));
+    VX_TRY(sort_pairs<uint32_t>(ctx, k1t.as<uint32_t>(), reinterpret_cast<uint32_t *>(k2t.p), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, bits_for(NW)));
+    sidx = ib.as<int32_t>();
+  }
+  uint32_t *k1s = k1t.as<uint32_t>();
+  uint64_t *k2s = k2u.as<uint64_t>();
+  VX_KERNEL(ctx, "k_gather", k_gather<uint32_t><<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), sidx, k1s, NI));
+  VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), sidx, k2s, NI));
+  {
+    int bad = 0;
+    VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (bad) { set_error("OctreeGBA::cut_voxel: a root cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+  }
+  k2i.release(); k2t.release();
+
+  // ---- 3. heads, ids, starts
+  DevBuf &hseg = T.make(), &iseg = T.make(), &seg_start = T.make();
+  DevBuf *hn[MAXL + 1], *in[MAXL + 1], *nstart[MAXL + 1];
+  VX_TRY(hseg.reserve(4 * NI)); VX_TRY(iseg.reserve(4 * NI));
+  for (int l = 0; l <= MAXL; l++) {
+    hn[l] = &T.make(); in[l] = &T.make(); nstart[l] = &T.make();
+    if (l <= L) { VX_TRY(hn[l]->reserve(4 * NI)); VX_TRY(in[l]->reserve(4 * NI)); }
+  }
+  VX_KERNEL(ctx, "k_gba_heads", k_gba_heads<<<blocks_for(NI, 256), 256, 0, st>>>(k1s, k2s, W, L, NI, hseg.as<int32_t>(), hn[0]->as<int32_t>(), hn[1]->as<int32_t>(),
+                                                                                hn[2]->as<int32_t>(), hn[3]->as<int32_t>()));
+  VX_TRY(incl_scan(ctx, hseg.as<int32_t>(), iseg.as<int32_t>(), NI));
+  int32_t nseg = 0, nn[MAXL + 1] = {0, 0, 0, 0};
+  VX_TRY(read_last(ctx, iseg.as<int32_t>(), NI, &nseg));
+  VX_TRY(seg_start.reserve(4 * ((size_t)nseg + 1)));
+  VX_KERNEL(ctx, "k_starts", k_starts<<<blocks_for(NI, 256), 256, 0, st>>>(hseg.as<int32_t>(), iseg.as<int32_t>(), NI, seg_start.as<int32_t>()));
+  for (int l = 0; l <= L; l++) {
+    VX_TRY(incl_scan(ctx, hn[l]->as<int32_t>(), in[l]->as<int32_t>(), NI));
+    VX_TRY(read_last(ctx, in[l]->as<int32_t>(), NI, &nn[l]));
+    VX_TRY(nstart[l]->reserve(4 * ((size_t)nn[l] + 1)));
+    VX_KERNEL(ctx, "k_starts", k_starts<<<blocks_for(NI, 256), 256, 0, st>>>(hn[l]->as<int32_t>(), in[l]->as<int32_t>(), NI, nstart[l]->as<int32_t>()));
+  }
+
+  // ---- 4. segment moments
+  DevBuf &segm = T.make(), &segN = T.make(), &segF = T.make();
+  VX_TRY(segm.reserve(sizeof(double) * 18 * (size_t)nseg)); VX_TRY(segN.reserve(4 * (size_t)nseg)); VX_TRY(segF.reserve(4 * (size_t)nseg));
+  VX_KERNEL(ctx, "k_seg_moments", k_seg_moments<<<blocks_for((int64_t)nseg * 32, 256), 256, 0, st>>>(
+      d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg,
+      segm.as<double>(), segN.as<int32_t>(), segF.as<int32_t>()));
+
+  // ---- 5. node statistics, decisions, liveness (top-down), emission marks
+  DevBuf *nodeS[MAXL + 1], *nodeE[MAXL + 1], *nflag[MAXL + 1], *nfs[MAXL + 1];
+  DevBuf &emit_at = T.make(), &vid = T.make();
+  VX_TRY(emit_at.reserve(4 * NI)); VX_TRY(vid.reserve(4 * NI));
+  VX_CUDA(cudaMemsetAsync(emit_at.p, 0, 4 * NI, st));
+  for (int l = 0; l <= L; l++) {
+    nodeS[l] = &T.make(); nodeE[l] = &T.make(); nflag[l] = &T.make(); nfs[l] = &T.make();
+    VX_TRY(nodeS[l]->reserve(sizeof(double) * 10 * (size_t)nn[l])); VX_TRY(nodeE[l]->reserve(sizeof(double) * 12 * (size_t)nn[l]));
+    VX_TRY(nflag[l]->reserve(4 * (size_t)nn[l])); VX_TRY(nfs[l]->reserve(4 * ((size_t)nn[l] + 1)));
+    VX_KERNEL(ctx, "k_node_stats", k_node_stats<<<blocks_for(nn[l], 128), 128, 0, st>>>(nstart[l]->as<int32_t>(), iseg.as<int32_t>(), nn[l], nseg, segm.as<double>(),
+                                                                                     segN.as<int32_t>(), segF.as<int32_t>(), prm, l, nodeS[l]->as<double>(),
+                                                                                     nodeE[l]->as<double>(), nflag[l]->as<int32_t>(), nfs[l]->as<int32_t>()));
+    VX_KERNEL(ctx, "k_node_alive", k_node_alive<<<blocks_for(nn[l], 256), 256, 0, st>>>(nstart[l]->as<int32_t>(), nn[l], l, L, l > 0 ? in[l - 1]->as<int32_t>() : nullptr,
+                                                                                     l > 0 ? nflag[l - 1]->as<int32_t>() : nullptr, nflag[l]->as<int32_t>(),
+                                                                                     emit_at.as<int32_t>()));
+  }
+  VX_TRY(excl_scan(ctx, emit_at.as<int32_t>(), vid.as<int32_t>(), NI));
+  int32_t V = 0;
+  {
+    int32_t last_e = 0, last_f = 0;
+    VX_TRY(read_last(ctx, vid.as<int32_t>(), NI, &last_e));
+    VX_TRY(read_last(ctx, emit_at.as<int32_t>(), NI, &last_f));
+    V = last_e + last_f;
+  }
+  if (V == 0) return vx_factor_clear(f);
+
+  // ---- 6. segments -> (voxel, frame) entries
+  DevBuf &sk = T.make(), &sk2 = T.make(), &sv = T.make(), &sv2 = T.make(), &vfh = T.make(), &vfi = T.make(), &vfs = T.make();
+  VX_TRY(sk.reserve(8 * (size_t)nseg)); VX_TRY(sk2.reserve(8 * (size_t)nseg)); VX_TRY(sv.reserve(4 * (size_t)nseg)); VX_TRY(sv2.reserve(4 * (size_t)nseg));
+  VX_TRY(vfh.reserve(4 * (size_t)nseg)); VX_TRY(vfi.reserve(4 * (size_t)nseg));
+  LevelPtrs lp;
+  for (int l = 0; l <= MAXL; l++) {
+    lp.start[l] = l <= L ? nstart[l]->as<int32_t>() : nullptr;
+    lp.incl[l] = l <= L ? in[l]->as<int32_t>() : nullptr;
+    lp.flags[l] = l <= L ? nflag[l]->as<int32_t>() : nullptr;
+  }
+  VX_KERNEL(ctx, "k_seg_voxel", k_seg_voxel<<<blocks_for(nseg, 256), 256, 0, st>>>(seg_start.as<int32_t>(), segF.as<int32_t>(), nseg, lp, L, vid.as<int32_t>(),
+                                                                                sk.as<uint64_t>(), sv.as<int32_t>()));
+  VX_TRY(sort_pairs<uint64_t>(ctx, sk.as<uint64_t>(), sk2.as<uint64_t>(), sv.as<int32_t>(), sv2.as<int32_t>(), nseg, 0, 64));
+  VX_KERNEL(ctx, "k_vf_heads", k_vf_heads<<<blocks_for(nseg, 256), 256, 0, st>>>(sk2.as<uint64_t>(), nseg, vfh.as<int32_t>()));
+  VX_TRY(incl_scan(ctx, vfh.as<int32_t>(), vfi.as<int32_t>(), nseg));
+  int32_t nnz = 0;
+  VX_TRY(read_last(ctx, vfi.as<int32_t>(), nseg, &nnz));
+  VX_TRY(vfs.reserve(4 * ((size_t)nnz + 1)));
+  VX_KERNEL(ctx, "k_starts", k_starts<<<blocks_for(nseg, 256), 256, 0, st>>>(vfh.as<int32_t>(), vfi.as<int32_t>(), nseg, vfs.as<int32_t>()));
+  // number of segments that belong to an emitted voxel = position of the first ~0 key
+  int64_t nvalid = nseg;
+  {
+    std::vector<int32_t> hN(1);
+    // valid keys sort before ~0; count them with a reduction over the head flags' complement is not needed:
+    // the last voxel-frame ends where the first invalid key starts, found on the host by binary search
+    int64_t lo = 0, hi = nseg;
+    while (lo < hi) {
+      int64_t mid = (lo + hi) >> 1; uint64_t kv = 0;
+      VX_CUDA(cudaMemcpyAsync(&kv, sk2.as<uint64_t>() + mid, 8, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+      if (kv != ~0ull) lo = mid + 1; else hi = mid;
+    }
+    nvalid = lo;
+  }
+
+  // ---- 7. the device LidarFactor
+  VX_TRY(factor_alloc(f, V, nnz));
+  VX_KERNEL(ctx, "k_vf_fill", k_vf_fill<<<blocks_for(nnz, 128), 128, 0, st>>>(sk2.as<uint64_t>(), sv2.as<int32_t>(), vfs.as<int32_t>(), nnz, nvalid, segm.as<double>(),
+                                                                             segN.as<int32_t>(), nseg, f->mom.as<double>(), f->cnt.as<int32_t>(), f->frame.as<int32_t>(),
+                                                                             f->vox.as<int32_t>()));
+  for (int l = 0; l <= L; l++)
+    VX_KERNEL(ctx, "k_emit_voxels", k_emit_voxels<<<blocks_for(nn[l], 256), 256, 0, st>>>(nstart[l]->as<int32_t>(), nflag[l]->as<int32_t>(), nn[l], vid.as<int32_t>(),
+                                                                                       nodeS[l]->as<double>(), nodeE[l]->as<double>(), V, f->lam.as<double>(), f->U.as<double>(),
+                                                                                       f->mrg.as<double>(), f->fix.as<double>(), f->coe.as<double>()));
+  VX_KERNEL(ctx, "k_vox_off", k_vox_off<<<blocks_for((int64_t)V + 1, 256), 256, 0, st>>>(f->vox.as<int32_t>(), nnz, V, f->off.as<int32_t>()));
+  VX_KERNEL(ctx, "k_vox_win", k_vox_win<<<blocks_for(V, 256), 256, 0, st>>>(f->off.as<int32_t>(), f->frame.as<int32_t>(), V, W, f->win.as<int32_t>()));
+  VX_KERNEL(ctx, "k_win_off", k_win_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(f->win.as<int32_t>(), V, NW, f->wv_off.as<int32_t>()));
+  VX_CUDA(cudaStreamSynchronize(st));
+  return factor_build_plan(f);
+}
