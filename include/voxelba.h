@@ -177,6 +177,34 @@ int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_
 int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter,
                 int thd_num, int *converged, int *accept_trace, int *n_iters);
 
+/* ---- C1h: VOXEL_SLAM::HBA_add_edge(p_xs, p_smps, gba_edges, maps, max_iter, thread_num, plptr)
+ * voxelslam.cpp:2822-3015 (the session filter :2836-2857 stays with the caller: pass only connected frames).
+ * For every window: up to max_iter outer iterations of {rebuild the GBA voxel map at the current poses,
+ * damping_iter with up = 4}; the last / first-converged pass swaps the GBA thresholds for the LocalBA ones
+ * (:2873-2883); then pose-graph edges for all i < j with cov_k = 1/|hess(6i+k, 6j+k)|, dropped when any
+ * |.| < 1e-6 (:2926-2951).  n_windows > 1 = independent windows in one call (bottom level, :3096). */
+typedef struct vx_hba_params {
+  vx_gba_params gba;                 /* GBA/voxel_size, GBA/min_eigen_value, 1/GBA/eigen_value_array, LocalBA/max_layer */
+  double voxel_size;                 /* Odometry/voxel_size          (fine pass) */
+  double min_eigen_value;            /* Odometry/min_eigen_value     (fine pass) */
+  double plane_eigen_value_thre[4];  /* 1/LocalBA/plane_eigen_value_thre (fine pass) */
+} vx_hba_params;
+/* PGO_Edge payload pushed by PGO_Edges::push (loop_refine.hpp:163-235) */
+typedef struct vx_pgo_edge {
+  int32_t m1, m2, id1, id2;
+  double rot[9];   /* R_i^T R_j, column-major */
+  double tra[3];   /* R_i^T (p_j - p_i) */
+  double cov[6];
+} vx_pgo_edge;
+/* frame_id / frame_mp: Keyframe::id / Keyframe::mp per frame (may be NULL).  edges: n_windows * W(W-1)/2 slots,
+ * window b writes n_edges[b] edges from slot b*W(W-1)/2.  hess_out: n_windows x (6W)^2 (may be NULL),
+ * resis_out: n_windows x 2 of the last damping_iter, n_voxels_out / status_out per window (status
+ * VX_ERR_TOO_FEW where the reference prints "Too Less Voxel" and exits). */
+int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                    const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int n_windows,
+                    const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
+                    double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out);
+
 #ifdef __cplusplus
 }
 #endif

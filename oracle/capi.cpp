@@ -196,6 +196,46 @@ void *orc_gba_build(const float *xyz, const int64_t *cloud_off, const oc_pose *p
   return f;
 }
 
+// ---- C1h: HBA_add_edge for one window.  local3 = {voxel_size, min_eigen_value} + plane_eigen_value_thre[4];
+// gba = {gba_voxel_size, gba_min_eigen_value} + eig_array[4]; returns number of edges, -3 when fatal.
+struct oc_edge { int32_t m1, m2, id1, id2; double rot[9]; double tra[3]; double cov[6]; };
+int64_t orc_hba_add_edge(const float *xyz, const int64_t *cloud_off, const int32_t *ids, const int32_t *mps, oc_pose *poses, int W,
+                         double voxel_size, double min_eigen_value, const double *plane_thre4, double gba_voxel_size,
+                         double gba_min_eigen_value, const double *gba_eig4, int max_layer, int max_iter, int thread_num,
+                         oc_edge *edges, double *hess_out, double *resis_first, double *resis_last, int32_t *n_voxels, int *n_outer,
+                         int want_cloud, PointXYZIN *merged, int64_t *merged_n) {
+  Params prm;
+  prm.voxel_size = voxel_size; prm.min_eigen_value = min_eigen_value; prm.max_layer = max_layer;
+  prm.gba_voxel_size = gba_voxel_size; prm.gba_min_eigen_value = gba_min_eigen_value;
+  for (int k = 0; k < 4; k++) { prm.plane_eigen_value_thre[k] = plane_thre4[k]; prm.gba_eigen_value_array[k] = gba_eig4[k]; }
+  std::vector<IMUST> xs = poses_in(poses, W);
+  std::vector<KeyframeCloud> smps(W);
+  std::vector<int> maps;
+  for (int i = 0; i < W; i++) {
+    smps[i].xyz = xyz + 3 * cloud_off[i]; smps[i].n = (int)(cloud_off[i + 1] - cloud_off[i]);
+    smps[i].id = ids ? ids[i] : i; smps[i].mp = mps ? mps[i] : 0;
+    bool has = false; for (int m : maps) if (m == smps[i].mp) has = true;
+    if (!has) maps.push_back(smps[i].mp);
+  }
+  HbaResult out;
+  HBA_add_edge(xs, smps, maps, max_iter, thread_num, want_cloud != 0, prm, out, false);
+  if (n_outer) *n_outer = (int)out.n_voxels.size();
+  for (size_t k = 0; k < out.n_voxels.size(); k++) if (n_voxels) n_voxels[k] = out.n_voxels[k];
+  for (size_t k = 0; k < out.resis_first.size(); k++) { if (resis_first) resis_first[k] = out.resis_first[k]; if (resis_last) resis_last[k] = out.resis_last[k]; }
+  if (out.fatal) return -3;
+  poses_out(out.xs, poses);
+  if (hess_out) std::memcpy(hess_out, out.hess.d.data(), sizeof(double) * out.hess.d.size());
+  for (size_t k = 0; k < out.edges.size(); k++) {
+    oc_edge &e = edges[k]; const PgoEdge &s = out.edges[k];
+    e.m1 = s.m1; e.m2 = s.m2; e.id1 = s.id1; e.id2 = s.id2;
+    for (int q = 0; q < 9; q++) e.rot[q] = s.rot[q];
+    for (int q = 0; q < 3; q++) e.tra[q] = s.tra[q];
+    for (int q = 0; q < 6; q++) e.cov[q] = s.cov[q];
+  }
+  if (want_cloud && merged) { for (size_t k = 0; k < out.merged.size(); k++) merged[k] = out.merged[k]; if (merged_n) *merged_n = (int64_t)out.merged.size(); }
+  return (int64_t)out.edges.size();
+}
+
 double orc_now() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }

@@ -141,6 +141,32 @@ def gba_build(clouds, poses, gba_voxel_size, gba_min_eigen_value, eig_array, max
     return Factor(W, handle=h)
 
 
+edge_dtype = np.dtype([("m1", "<i4"), ("m2", "<i4"), ("id1", "<i4"), ("id2", "<i4"), ("rot", "<f8", (9,)), ("tra", "<f8", (3,)), ("cov", "<f8", (6,))])
+assert edge_dtype.itemsize == 160
+
+
+def hba_add_edge(clouds, poses, local, gba, max_layer, max_iter, thread_num=2, ids=None, mps=None, want_cloud=False):
+    """HBA_add_edge (voxelslam.cpp:2822-3015) for one window.  local = (voxel_size, min_eig, thre4), gba likewise."""
+    W = len(clouds)
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(W + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses).copy()
+    jl = 6 * W
+    edges = np.zeros(W * (W - 1) // 2, dtype=edge_dtype); hess = np.zeros((jl, jl))
+    rf = np.zeros(max(max_iter, 1)); rl = np.zeros(max(max_iter, 1)); nv = np.zeros(max(max_iter, 1), dtype=np.int32); no = C.c_int(0)
+    merged = np.zeros(xyz.shape[0] // 3 if want_cloud else 1, dtype=point48_dtype); mn = C.c_int64(0)
+    ids_ = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32)
+    mps_ = None if mps is None else np.ascontiguousarray(mps, dtype=np.int32)
+    lt = np.ascontiguousarray(local[2], dtype=np.float64); gt = np.ascontiguousarray(gba[2], dtype=np.float64)
+    lib().orc_hba_add_edge.restype = C.c_int64
+    ne = lib().orc_hba_add_edge(_p(xyz), _p(off), _p(ids_), _p(mps_), _p(ps), C.c_int(W), C.c_double(local[0]), C.c_double(local[1]), _p(lt),
+                                C.c_double(gba[0]), C.c_double(gba[1]), _p(gt), C.c_int(max_layer), C.c_int(max_iter), C.c_int(thread_num),
+                                _p(edges), _p(hess), _p(rf), _p(rl), _p(nv), C.byref(no), C.c_int(int(want_cloud)), _p(merged), C.byref(mn))
+    k = no.value
+    return dict(n_edges=int(ne), edges=edges[:max(ne, 0)], poses=ps, hess=hess.T.copy(), resis_first=rf[:k], resis_last=rl[:k], n_voxels=nv[:k],
+                merged=merged[:mn.value])
+
+
 class Factor:
     """orc::LidarFactor (voxel_map.hpp:124-339 restated)."""
 

@@ -144,6 +144,33 @@ def downsample_voxel(ctx, pts, voxel_size):
     return out[:n.value]
 
 
+hba_params_dtype = np.dtype([("gba", gba_params_dtype), ("voxel_size", "<f8"), ("min_eigen_value", "<f8"), ("plane_eigen_value_thre", "<f8", (4,))])
+edge_dtype = np.dtype([("m1", "<i4"), ("m2", "<i4"), ("id1", "<i4"), ("id2", "<i4"), ("rot", "<f8", (9,)), ("tra", "<f8", (3,)), ("cov", "<f8", (6,))])
+assert hba_params_dtype.itemsize == 104 and edge_dtype.itemsize == 160
+
+
+def hba_add_edge(ctx, clouds, poses, W, n_windows, local, gba, max_layer, max_iter, thread_num=2, frame_cloud=None, ids=None, mps=None):
+    """VOXEL_SLAM::HBA_add_edge (voxelslam.cpp:2822-3015) for n_windows independent windows of W frames.
+    local = (voxel_size, min_eigen_value, thre4 as stored = 1/yaml); gba = (gba_voxel_size, gba_min_eigen_value, eig4)."""
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses).copy()
+    prm = np.zeros(1, dtype=hba_params_dtype)
+    prm["gba"]["voxel_size"] = gba[0]; prm["gba"]["min_eigen_value"] = gba[1]; prm["gba"]["eigen_value_array"] = gba[2]; prm["gba"]["max_layer"] = max_layer
+    prm["voxel_size"] = local[0]; prm["min_eigen_value"] = local[1]; prm["plane_eigen_value_thre"] = local[2]
+    cap = W * (W - 1) // 2
+    jl = 6 * W
+    edges = np.zeros(n_windows * cap, dtype=edge_dtype); ne = np.zeros(n_windows, dtype=np.int64)
+    hess = np.zeros((n_windows, jl, jl)); resis = np.zeros((n_windows, 2)); nv = np.zeros(n_windows, dtype=np.int32); st = np.zeros(n_windows, dtype=np.int32)
+    fc = None if frame_cloud is None else np.ascontiguousarray(frame_cloud, dtype=np.int32)
+    ids_ = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32)
+    mps_ = None if mps is None else np.ascontiguousarray(mps, dtype=np.int32)
+    _chk(ctx.lib.vx_hba_add_edge(ctx.h, xyz.ctypes.data_as(C.c_void_p), _p(off), C.c_int(len(clouds)), _p(fc), _p(ids_), _p(mps_), _p(ps), C.c_int(W),
+                                 C.c_int(n_windows), _p(prm), C.c_int(max_iter), C.c_int(thread_num), _p(edges), _p(ne), _p(hess), _p(resis), _p(nv), _p(st)))
+    return dict(poses=ps, edges=[edges[b * cap:b * cap + ne[b]] for b in range(n_windows)], hess=np.transpose(hess, (0, 2, 1)), resis=resis,
+                n_voxels=nv, status=st)
+
+
 class DevArray:
     """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
 

@@ -72,19 +72,29 @@ void ldlt_lower_solve(double *A, int n, const double *b, double *x, std::vector<
 
 }  // namespace
 
-extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
-                           int *converged, int *accept_trace, int *n_iters) {
+namespace vx {
+// win_status (optional, n_windows): when given, a window with fewer voxels than thd_num is flagged
+// VX_ERR_TOO_FEW and left untouched instead of failing the whole batch.
+int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
+                  int *converged, int *accept_trace, int *n_iters, int *win_status) {
   VX_ARG(f != nullptr && poses != nullptr && max_iter >= 0);
   VX_TRY(bind(ctx));
   const int W = f->W, NW = f->n_win, jl = 6 * W, F = W * NW;
+  std::vector<char> few;
   // Lidar_BA_Optimizer::only_residual exits the process when a problem has fewer voxels than threads
   // (voxel_map.hpp:399-403); the drop-in reports it instead.
   {
     std::vector<int32_t> wv(NW + 1);
     VX_CUDA(cudaMemcpyAsync(wv.data(), f->wv_off.p, sizeof(int32_t) * (NW + 1), cudaMemcpyDeviceToHost, ctx->stream));
     VX_CUDA(cudaStreamSynchronize(ctx->stream));
-    for (int w = 0; w < NW; w++)
-      if (wv[w + 1] - wv[w] < thd_num) { set_error("Too Less Voxel: window %d has %d voxels < thd_num %d", w, wv[w + 1] - wv[w], thd_num); return VX_ERR_TOO_FEW; }
+    few.assign(NW, 0);
+    for (int w = 0; w < NW; w++) {
+      if (win_status) win_status[w] = VX_OK;
+      if (wv[w + 1] - wv[w] < thd_num) {
+        if (!win_status) { set_error("Too Less Voxel: window %d has %d voxels < thd_num %d", w, wv[w + 1] - wv[w], thd_num); return VX_ERR_TOO_FEW; }
+        win_status[w] = VX_ERR_TOO_FEW; few[w] = 1;
+      }
+    }
   }
   const size_t hsz = (size_t)jl * jl;
   std::vector<double> Hess(hsz * NW), JacT((size_t)jl * NW), Hnew(hsz * NW), Jnew((size_t)jl * NW), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
@@ -94,6 +104,7 @@ extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *he
   std::vector<vx_pose> x(poses, poses + F), xt(poses, poses + F);
   if (hess_out) std::fill(hess_out, hess_out + hsz * NW, 0.0);
   if (resis) std::fill(resis, resis + 2 * (size_t)NW, 0.0);
+  for (int w = 0; w < NW; w++) if (few[w]) { active[w] = 0; conv[w] = 0; }
 
   for (int it = 0; it < max_iter; it++) {
     bool any_active = false, any_calc = false;
@@ -167,4 +178,10 @@ extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *he
   }
   std::copy(x.begin(), x.end(), poses);
   return VX_OK;
+}
+}  // namespace vx
+
+extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
+                           int *converged, int *accept_trace, int *n_iters) {
+  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr);
 }

@@ -346,8 +346,13 @@ int bits_for(int64_t n) { int b = 1; while (((int64_t)1 << b) < n) b++; return b
 
 }  // namespace
 
-extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
-                            const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
+namespace {
+struct View { const void *p; template <class X> const X *as() const { return (const X *)p; } };
+}
+namespace vx {
+// d_xyz / d_coff: the clouds already on the device (uploaded once per HBA_add_edge call); cloud_off: host copy.
+int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
   VX_ARG(f != nullptr && params != nullptr && cloud_off != nullptr && poses != nullptr && n_clouds >= 1);
   VX_TRY(bind(ctx));
   cudaStream_t st = ctx->stream;
@@ -370,14 +375,13 @@ extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_
   const int64_t NI = inst_off[F];
   VX_ARG(NI < ((int64_t)1 << 31) && NP >= 0);
   if (NI == 0) return vx_factor_clear(f);
-  VX_ARG(xyz != nullptr);
+  VX_ARG(d_xyz_in != nullptr && d_coff_in != nullptr);
 
   Tmp T;
-  DevBuf &d_xyz = T.make(), &d_coff = T.make(), &d_fc = T.make(), &d_ioff = T.make(), &d_poses = T.make(), &d_bad = T.make();
-  VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1))); VX_TRY(d_coff.reserve(8 * (n_clouds + 1))); VX_TRY(d_fc.reserve(4 * F));
+  View d_xyz{d_xyz_in}, d_coff{d_coff_in};
+  DevBuf &d_fc = T.make(), &d_ioff = T.make(), &d_poses = T.make(), &d_bad = T.make();
+  VX_TRY(d_fc.reserve(4 * F));
   VX_TRY(d_ioff.reserve(8 * (F + 1))); VX_TRY(d_poses.reserve(sizeof(vx_pose) * F)); VX_TRY(d_bad.reserve(4));
-  VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, st));
-  VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (n_clouds + 1), cudaMemcpyHostToDevice, st));
   VX_CUDA(cudaMemcpyAsync(d_fc.p, fc.data(), 4 * F, cudaMemcpyHostToDevice, st));
   VX_CUDA(cudaMemcpyAsync(d_ioff.p, inst_off.data(), 8 * (F + 1), cudaMemcpyHostToDevice, st));
   VX_CUDA(cudaMemcpyAsync(d_poses.p, poses, sizeof(vx_pose) * F, cudaMemcpyHostToDevice, st));
@@ -515,4 +519,26 @@ extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_
   VX_KERNEL(ctx, "k_win_off", k_win_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(f->win.as<int32_t>(), V, NW, f->wv_off.as<int32_t>()));
   VX_CUDA(cudaStreamSynchronize(st));
   return factor_build_plan(f);
+}
+}  // namespace vx
+
+extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                            const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
+  VX_ARG(cloud_off != nullptr && n_clouds >= 1);
+  VX_TRY(bind(ctx));
+  const int64_t NP = cloud_off[n_clouds];
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  DevBuf d_xyz, d_coff;
+  int s = VX_OK;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
+    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, ctx->stream));
+    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
+    return gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f);
+  };
+  s = body();
+  cudaStreamSynchronize(ctx->stream);
+  d_xyz.release(); d_coff.release();
+  return s;
 }

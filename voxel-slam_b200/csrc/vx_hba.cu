@@ -1,0 +1,145 @@
+// vx_hba.cu — VOXEL_SLAM::HBA_add_edge (voxelslam.cpp:2822-3015) over the device path:
+//   per outer iteration: OctreeGBA::cut_voxel + OctreeGBA_multi_recut (vx_gba.cu) -> Lidar_BA_Optimizer::damping_iter
+//   with up = 4 (vx_ba.cu); coarse -> fine threshold swap (:2873-2883); convergence logic (:2906-2917);
+//   pose-graph edges from the pre-gauge Hessian snapshot (:2926-2951).
+// A call may carry a BATCH of independent windows (the 399 bottom-level windows of a 2,000-keyframe
+// session, voxelslam.cpp:3096): each window keeps its own converge_flag / threshold state; windows that
+// want the coarse and the fine thresholds in the same outer iteration are built as two sub-batches.
+#include "vx_factor.cuh"
+#include <cmath>
+#include <algorithm>
+
+namespace vx {
+int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
+int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
+                  int *converged, int *accept_trace, int *n_iters, int *win_status);
+}
+using namespace vx;
+
+extern "C" int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                               const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int n_windows,
+                               const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
+                               double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out) {
+  VX_ARG(prm != nullptr && poses != nullptr && cloud_off != nullptr && W >= 2 && n_windows >= 1 && max_iter >= 0 && n_clouds >= 1);
+  VX_TRY(bind(ctx));
+  const int NW = n_windows, F = W * NW, jl = 6 * W;
+  const size_t hsz = (size_t)jl * jl;
+  const int64_t NP = cloud_off[n_clouds];
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  const int64_t cap = (int64_t)W * (W - 1) / 2;   // edge slots per window
+
+  // clouds go to the device once for the whole call
+  DevBuf d_xyz, d_coff;
+  int rc = VX_OK;
+  std::vector<double> hess(hsz * NW, 0.0);
+  std::vector<int> cflag(NW, 0), done(NW, 0), status(NW, VX_OK), nvox(NW, 0);
+  std::vector<double> cthre(NW, 0.05);
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
+    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, ctx->stream));
+    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
+    const int up = 4;   // voxelslam.cpp:2867
+    for (int iterCnt = 0; iterCnt < max_iter; iterCnt++) {
+      // which thresholds does each live window use in this outer iteration?
+      std::vector<int> group[2];
+      for (int w = 0; w < NW; w++) {
+        if (done[w]) continue;
+        const bool fine = cflag[w] == 1 || iterCnt == max_iter - 1;   // voxelslam.cpp:2873
+        group[fine ? 1 : 0].push_back(w);
+      }
+      if (group[0].empty() && group[1].empty()) break;
+      for (int gi = 0; gi < 2; gi++) {
+        const std::vector<int> &ws = group[gi];
+        if (ws.empty()) continue;
+        const int ns = (int)ws.size();
+        vx_gba_params gp = prm->gba;
+        if (gi == 1) {   // gba_* <- LocalBA thresholds (voxelslam.cpp:2875-2882)
+          gp.voxel_size = prm->voxel_size; gp.min_eigen_value = prm->min_eigen_value;
+          for (int k = 0; k < 4; k++) gp.eigen_value_array[k] = prm->plane_eigen_value_thre[k];
+        }
+        std::vector<int32_t> fc((size_t)ns * W);
+        std::vector<vx_pose> ps((size_t)ns * W);
+        for (int a = 0; a < ns; a++)
+          for (int i = 0; i < W; i++) {
+            const int g = ws[a] * W + i;
+            fc[(size_t)a * W + i] = frame_cloud ? frame_cloud[g] : g;
+            ps[(size_t)a * W + i] = poses[g];
+          }
+        vx_factor *fac = nullptr;
+        VX_TRY(vx_factor_create(ctx, W, ns, &fac));
+        std::vector<double> hs(hsz * ns), rs(2 * (size_t)ns);
+        std::vector<int> conv(ns), wst(ns);
+        int s = gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, fc.data(), ps.data(), &gp, fac);
+        if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hs.data(), rs.data(), up, thread_num, conv.data(), nullptr, nullptr, wst.data());
+        std::vector<int32_t> wv(ns + 1, 0);
+        if (s == VX_OK && fac->V > 0) {
+          cudaMemcpyAsync(wv.data(), fac->wv_off.p, sizeof(int32_t) * (ns + 1), cudaMemcpyDeviceToHost, ctx->stream);
+          cudaStreamSynchronize(ctx->stream);
+        }
+        vx_factor_free(fac);
+        VX_TRY(s);
+        for (int a = 0; a < ns; a++) {
+          const int w = ws[a];
+          nvox[w] = wv[a + 1] - wv[a];
+          if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
+          for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
+          std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
+          const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
+          if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
+          // voxelslam.cpp:2906-2917
+          if ((std::fabs(r0 - r1) / r0 < cthre[w] && conv[a]) || (iterCnt == max_iter - 2 && cflag[w] == 0)) {
+            cthre[w] = 0.01;
+            if (cflag[w] == 0) cflag[w] = 1;
+            else if (cflag[w] == 1) done[w] = 1;
+          }
+        }
+      }
+    }
+    return VX_OK;
+  };
+  rc = body();
+  cudaStreamSynchronize(ctx->stream);
+  d_xyz.release(); d_coff.release();
+  VX_TRY(rc);
+
+  // pose-graph edges (voxelslam.cpp:2926-2951): cov_k = 1/|hess(6i+k, 6j+k)| of the pre-gauge snapshot
+  for (int w = 0; w < NW; w++) {
+    int64_t ne = 0;
+    if (status[w] == VX_OK && edges) {
+      const double *H = hess.data() + hsz * w;
+      for (int i = 0; i < W - 1; i++)
+        for (int j = i + 1; j < W; j++) {
+          vx_pgo_edge e;
+          bool add = true;
+          for (int k = 0; k < 6; k++) {
+            const double hc = std::fabs(H[(size_t)(6 * j + k) * jl + (6 * i + k)]);
+            if (hc < 1e-6) { add = false; break; }
+            e.cov[k] = 1.0 / hc;
+          }
+          if (!add) continue;
+          const vx_pose &a = poses[w * W + i], &b = poses[w * W + j];
+          e.m1 = frame_mp ? frame_mp[w * W + i] : 0; e.m2 = frame_mp ? frame_mp[w * W + j] : 0;
+          e.id1 = frame_id ? frame_id[w * W + i] : i; e.id2 = frame_id ? frame_id[w * W + j] : j;
+          const double d[3] = {b.p[0] - a.p[0], b.p[1] - a.p[1], b.p[2] - a.p[2]};
+          for (int r = 0; r < 3; r++) {   // R_i^T (p_j - p_i), R_i^T R_j  (column-major)
+            double sacc = 0.0;
+            for (int k = 0; k < 3; k++) sacc += a.R[r * 3 + k] * d[k];
+            e.tra[r] = sacc;
+            for (int c = 0; c < 3; c++) {
+              double m = 0.0;
+              for (int k = 0; k < 3; k++) m += a.R[r * 3 + k] * b.R[c * 3 + k];
+              e.rot[c * 3 + r] = m;
+            }
+          }
+          edges[(size_t)w * cap + ne++] = e;
+        }
+    }
+    if (n_edges) n_edges[w] = ne;
+    if (status_out) status_out[w] = status[w];
+    if (n_voxels_out) n_voxels_out[w] = nvox[w];
+  }
+  if (hess_out) std::copy(hess.begin(), hess.end(), hess_out);
+  return VX_OK;
+}
