@@ -205,6 +205,40 @@ int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int
                     const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
                     double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out);
 
+/* ---- D1 / D2: LIO ESIKF point-to-plane update -----------------------------------------------------------
+ * The voxel map as OctoTree::match reads it (voxel_map.hpp:1649-1721), flattened by the caller: one record per
+ * OctoTree node; root voxels (the unordered_map<VOXEL_LOC, OctoTree*> of voxel_map.hpp:2167-2205) by key. */
+typedef struct vx_map_node {
+  double center[3];        /* OctoTree::voxel_center */
+  float quater_length;     /* OctoTree::quater_length (float, voxel_map.hpp:1067) */
+  int32_t octo_state;      /* 0 leaf, 1 subdivided */
+  int32_t child[8];        /* node index of leaves[4x+2y+z] or -1 */
+  int32_t is_plane;        /* Plane::is_plane */
+  float radius;            /* Plane::radius (float, voxel_map.hpp:89) */
+  double p_center[3], p_normal[3];
+  double plane_var[36];    /* Plane::plane_var 6x6 column-major */
+} vx_map_node;
+typedef struct vx_planemap vx_planemap;
+/* struct pointVar {Vector3d pnt; Matrix3d var;}  voxel_map.hpp:18-34 (var column-major) */
+typedef struct vx_point_var { double pnt[3]; double var[9]; } vx_point_var;
+/* the part of IMUST the update touches (tools.hpp:135-199): R, p, v, bg, ba and the 15x15 covariance, column-major */
+typedef struct vx_lio_state { double R[9], p[3], v[3], bg[3], ba[3], cov[225]; } vx_lio_state;
+
+int vx_planemap_create(vx_ctx *ctx, const int64_t *root_keys /* n_roots x 3 */, const int32_t *root_node, int64_t n_roots,
+                       const vx_map_node *nodes, int64_t n_nodes, double voxel_size, vx_planemap **out);
+int vx_planemap_free(vx_planemap *map);
+/* One pass of the per-point loop of lio_state_estimation (voxelslam.cpp:1005-1050): var_world, wld, cached-leaf fast
+ * path / match(), residual and Jacobian, HTH (6x6) / HTz (6) / sum n n^T (3x3) / match_num.  leaf_cache: in/out node
+ * index per point (-1 none; NULL = no cache), the reference's `octos` vector (voxelslam.cpp:1020-1028).  flags: per
+ * point association flag (may be NULL).  rot_var / tsl_var: x_curr.cov blocks (0,0) and (3,3), column-major. */
+int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, const vx_pose *pose,
+                            const double *rot_var9, const double *tsl_var9, int32_t *leaf_cache, double *HTH36, double *HTz6,
+                            double *nnt9, int32_t *match_num, int32_t *flags);
+/* bool VOXEL_SLAM::lio_state_estimation(PVecPtr pptr)  voxelslam.cpp:962-1098: <= 4 iterations, 15x15 gain on the host,
+ * points and leaf cache stay on the device.  *healthy = the reference's return (lambda_min(sum n n^T) >= 14). */
+int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy,
+                            int32_t *iters, int32_t *match_nums4);
+
 #ifdef __cplusplus
 }
 #endif

@@ -236,6 +236,167 @@ int64_t orc_hba_add_edge(const float *xyz, const int64_t *cloud_off, const int32
   return (int64_t)out.edges.size();
 }
 
+// ---- local sliding-window map session (voxelslam.cpp:1888-2043 without the LIO/BA steps: poses are given) ----
+struct LocalSession {
+  MapCtx ctx;
+  SurfMap surf_map, surf_map_slide;
+  std::vector<std::vector<SlideWindow *>> sws;
+  std::vector<IMUST> x_buf;
+  std::vector<PVecPtr> pvec_buf;
+  LidarFactor voxhess{1};
+  int win_size = 10, win_count = 0, thread_num = 5;
+  double dept_err = 0.02, beam_err = 0.05, jour = 0;
+  std::vector<OctoTree *> flat;   // last export order
+};
+void *orc_local_create(int win_size, double voxel_size, double min_eigen_value, const double *thre4, int max_layer, int thread_num,
+                       double dept_err, double beam_err) {
+  LocalSession *s = new LocalSession();
+  s->win_size = win_size; s->thread_num = thread_num; s->dept_err = dept_err; s->beam_err = beam_err;
+  s->ctx.prm.voxel_size = voxel_size; s->ctx.prm.min_eigen_value = min_eigen_value; s->ctx.prm.max_layer = max_layer;
+  for (int k = 0; k < 4; k++) s->ctx.prm.plane_eigen_value_thre[k] = thre4[k];
+  s->ctx.mp.resize(win_size);
+  for (int i = 0; i < win_size; i++) s->ctx.mp[i] = i;    // voxelslam.cpp:3158-3160
+  s->sws.resize(thread_num);
+  s->voxhess.win_size = win_size;
+  return s;
+}
+static IMUST state_in(const oc_pose *pose, const double *cov225) {
+  IMUST x;
+  for (int k = 0; k < 9; k++) x.R[k] = pose->R[k];
+  for (int k = 0; k < 3; k++) x.p[k] = pose->p[k];
+  if (cov225) for (int k = 0; k < 225; k++) x.cov[k] = cov225[k];
+  return x;
+}
+// points: float xyz in the body frame (extrinsic = identity).  Returns the pointVar records (pnt body frame,
+// var AFTER pvec_update = world-frame covariance, voxelslam.hpp:242-265) when pv_out != null.
+void orc_local_push(void *h, const float *xyz, int n, const oc_pose *pose, const double *cov225, double *pv_out /* n x 12 */) {
+  LocalSession &S = *(LocalSession *)h;
+  std::vector<PointXYZIN> pl(n);
+  for (int i = 0; i < n; i++) { std::memset(&pl[i], 0, sizeof(PointXYZIN)); pl[i].x = xyz[3 * i]; pl[i].y = xyz[3 * i + 1]; pl[i].z = xyz[3 * i + 2]; }
+  IMUST ext;   // identity extrinsic
+  PVecPtr pptr(new PVec());
+  var_init(ext, pl, *pptr, S.dept_err, S.beam_err);
+  IMUST x_curr = state_in(pose, cov225);
+  std::vector<V3> pwld;
+  pvec_update(*pptr, x_curr, pwld);
+  if (pv_out)
+    for (int i = 0; i < n; i++) {
+      for (int k = 0; k < 3; k++) pv_out[12 * i + k] = (*pptr)[i].pnt[k];
+      for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = (*pptr)[i].var[k];
+    }
+  S.win_count++;
+  S.x_buf.push_back(x_curr);
+  S.pvec_buf.push_back(pptr);
+  S.voxhess.clear();
+  S.voxhess.win_size = S.win_size;
+  cut_voxel_multi(S.surf_map, *S.pvec_buf[S.win_count - 1], S.win_count - 1, S.surf_map_slide, S.win_size, pwld, S.sws, &S.ctx);
+  multi_recut(S.surf_map_slide, S.win_count, S.x_buf, S.voxhess, S.sws, S.thread_num);
+  if (S.win_count >= S.win_size) {
+    const int mgsize = 1;
+    multi_margi(S.surf_map_slide, S.jour, S.win_count, S.x_buf, S.voxhess, S.sws[0], S.thread_num);
+    for (int i = 0; i < S.win_size; i++) { S.ctx.mp[i] += mgsize; if (S.ctx.mp[i] >= S.win_size) S.ctx.mp[i] -= S.win_size; }
+    for (int i = mgsize; i < S.win_count; i++) { S.x_buf[i - mgsize] = S.x_buf[i]; std::swap(S.pvec_buf[i - mgsize], S.pvec_buf[i]); }
+    for (int i = S.win_count - mgsize; i < S.win_count; i++) { S.x_buf.pop_back(); S.pvec_buf.pop_back(); }
+    S.win_count -= mgsize;
+  }
+}
+int64_t orc_local_factor_voxels(void *h) { return (int64_t)((LocalSession *)h)->voxhess.plvec_voxels.size(); }
+// flattened export of surf_map: node record = what OctoTree::match / inside read (voxel_map.hpp:1649-1721, :1836-1848)
+struct oc_map_node {
+  double center[3];
+  float quater_length; int32_t octo_state;
+  int32_t child[8];
+  int32_t is_plane; float radius;
+  double p_center[3], p_normal[3];
+  double plane_var[36];
+};
+static void flatten(OctoTree *t, std::vector<OctoTree *> &out, std::vector<int> &idx_of_parent_slot) {
+  (void)idx_of_parent_slot;
+  out.push_back(t);
+  if (t->octo_state == 1) for (int i = 0; i < 8; i++) if (t->leaves[i]) flatten(t->leaves[i], out, idx_of_parent_slot);
+}
+int64_t orc_local_export_count(void *h, int64_t *n_roots) {
+  LocalSession &S = *(LocalSession *)h;
+  S.flat.clear();
+  std::vector<int> dummy;
+  for (auto &kv : S.surf_map) flatten(kv.second, S.flat, dummy);
+  *n_roots = (int64_t)S.surf_map.size();
+  return (int64_t)S.flat.size();
+}
+void orc_local_export(void *h, int64_t *root_keys /* n_roots x 3 */, int32_t *root_node, oc_map_node *nodes) {
+  LocalSession &S = *(LocalSession *)h;
+  std::unordered_map<OctoTree *, int> id;
+  for (size_t i = 0; i < S.flat.size(); i++) id[S.flat[i]] = (int)i;
+  int64_t r = 0;
+  for (auto &kv : S.surf_map) {
+    root_keys[3 * r] = kv.first.x; root_keys[3 * r + 1] = kv.first.y; root_keys[3 * r + 2] = kv.first.z;
+    root_node[r] = id[kv.second];
+    r++;
+  }
+  for (size_t i = 0; i < S.flat.size(); i++) {
+    OctoTree *t = S.flat[i];
+    oc_map_node &nd = nodes[i];
+    std::memset(&nd, 0, sizeof(nd));
+    for (int k = 0; k < 3; k++) nd.center[k] = t->voxel_center[k];
+    nd.quater_length = t->quater_length; nd.octo_state = t->octo_state;
+    for (int k = 0; k < 8; k++) nd.child[k] = (t->octo_state == 1 && t->leaves[k]) ? id[t->leaves[k]] : -1;
+    nd.is_plane = t->plane.is_plane ? 1 : 0; nd.radius = t->plane.radius;
+    for (int k = 0; k < 3; k++) { nd.p_center[k] = t->plane.center[k]; nd.p_normal[k] = t->plane.normal[k]; }
+    for (int k = 0; k < 36; k++) nd.plane_var[k] = t->plane.plane_var[k];
+  }
+}
+void orc_local_free(void *h) { delete (LocalSession *)h; }
+
+// ---- D1 / D2 over the session's surf_map ---------------------------------------------------------------
+// pv: n x 12 (pnt 3 + var 9 col-major, var = body-frame covariance as var_init leaves it).
+static PVec pvec_in(const double *pv, int n) {
+  PVec v(n);
+  for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) v[i].pnt[k] = pv[12 * i + k]; for (int k = 0; k < 9; k++) v[i].var[k] = pv[12 * i + 3 + k]; }
+  return v;
+}
+void orc_var_init(const float *xyz, int n, double dept_err, double beam_err, double *pv_out) {
+  std::vector<PointXYZIN> pl(n);
+  for (int i = 0; i < n; i++) { std::memset(&pl[i], 0, sizeof(PointXYZIN)); pl[i].x = xyz[3 * i]; pl[i].y = xyz[3 * i + 1]; pl[i].z = xyz[3 * i + 2]; }
+  IMUST ext; PVec pvec;
+  var_init(ext, pl, pvec, dept_err, beam_err);
+  for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) pv_out[12 * i + k] = pvec[i].pnt[k]; for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = pvec[i].var[k]; }
+}
+// one pass (voxelslam.cpp:1005-1050); leaf cache in/out as indices into the last export (-1 = none)
+void orc_lio_pass(void *h, const double *pv, int n, const oc_pose *pose, const double *cov225, int32_t *leaf_cache, double *HTH36, double *HTz6,
+                  double *nnt9, int *match_num, int32_t *flags) {
+  LocalSession &S = *(LocalSession *)h;
+  PVec pvec = pvec_in(pv, n);
+  IMUST x = state_in(pose, cov225);
+  std::unordered_map<OctoTree *, int> id;
+  for (size_t i = 0; i < S.flat.size(); i++) id[S.flat[i]] = (int)i;
+  std::vector<OctoTree *> octos(n, nullptr);
+  for (int i = 0; i < n; i++) if (leaf_cache && leaf_cache[i] >= 0) octos[i] = S.flat[leaf_cache[i]];
+  LioPassOut o; std::vector<int> fl;
+  lio_pass(S.surf_map, pvec, x, octos, &S.ctx, o, &fl);
+  for (int k = 0; k < 36; k++) HTH36[k] = o.HTH[k];
+  for (int k = 0; k < 6; k++) HTz6[k] = o.HTz[k];
+  for (int k = 0; k < 9; k++) nnt9[k] = o.nnt[k];
+  *match_num = o.match_num;
+  for (int i = 0; i < n; i++) { if (flags) flags[i] = fl[i]; if (leaf_cache) leaf_cache[i] = octos[i] ? id[octos[i]] : -1; }
+}
+// full lio_state_estimation (voxelslam.cpp:962-1098); state15 in/out = [R(9) p(3) v(3) bg(3) ba(3)], cov in/out
+int orc_lio_state_estimation(void *h, const double *pv, int n, double *state21, double *cov225, int *iters, int *match_nums4) {
+  LocalSession &S = *(LocalSession *)h;
+  PVec pvec = pvec_in(pv, n);
+  IMUST x;
+  for (int k = 0; k < 9; k++) x.R[k] = state21[k];
+  for (int k = 0; k < 3; k++) { x.p[k] = state21[9 + k]; x.v[k] = state21[12 + k]; x.bg[k] = state21[15 + k]; x.ba[k] = state21[18 + k]; }
+  for (int k = 0; k < 225; k++) x.cov[k] = cov225[k];
+  LioTrace tr;
+  bool ok = lio_state_estimation(S.surf_map, pvec, x, &S.ctx, &tr);
+  for (int k = 0; k < 9; k++) state21[k] = x.R[k];
+  for (int k = 0; k < 3; k++) { state21[9 + k] = x.p[k]; state21[12 + k] = x.v[k]; state21[15 + k] = x.bg[k]; state21[18 + k] = x.ba[k]; }
+  for (int k = 0; k < 225; k++) cov225[k] = x.cov[k];
+  if (iters) *iters = tr.iters;
+  if (match_nums4) for (int k = 0; k < tr.iters && k < 4; k++) match_nums4[k] = tr.passes[k].match_num;
+  return ok ? 1 : 0;
+}
+
 double orc_now() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }

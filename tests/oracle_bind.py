@@ -231,3 +231,72 @@ class Factor:
         rc = lib().orc_ba_lidar(self.h, _p(ps), _p(hess), _p(resis), C.c_int(max_iter), C.c_int(thd_num),
                                 C.c_int(int(use_threads)), _p(trace), C.byref(nt))
         return dict(rc=rc, poses=ps, hess=hess.T.copy(), resis=resis, accept=trace[:nt.value].tolist())
+
+
+map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("octo_state", "<i4"), ("child", "<i4", (8,)), ("is_plane", "<i4"),
+                           ("radius", "<f4"), ("p_center", "<f8", (3,)), ("p_normal", "<f8", (3,)), ("plane_var", "<f8", (36,))])
+assert map_node_dtype.itemsize == 408
+
+
+def var_init(xyz, dept_err, beam_err):
+    """calcBodyVar + var_init (voxelslam.hpp:180-234), identity extrinsic -> (n,12): pnt 3 + var 9 (col-major)."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+    out = np.zeros((xyz.shape[0], 12))
+    lib().orc_var_init(_p(xyz), C.c_int(xyz.shape[0]), C.c_double(dept_err), C.c_double(beam_err), _p(out))
+    return out
+
+
+def default_cov():
+    """IMUST::setZero covariance (tools.hpp:188-197)."""
+    cov = np.eye(15) * 0.0001
+    cov[9:, 9:] = np.eye(6) * 0.00001
+    return cov
+
+
+class LocalMap:
+    """The sliding-window voxel map session of voxelslam.cpp:1888-2043 (poses given, no LIO/BA)."""
+
+    def __init__(self, win_size=10, voxel_size=1.0, min_eigen_value=0.0025, thre=(1, 1, 1, 1), max_layer=2, thread_num=5, dept_err=0.01, beam_err=0.01):
+        t = np.ascontiguousarray(thre, dtype=np.float64)
+        lib().orc_local_create.restype = C.c_void_p
+        self.h = C.c_void_p(lib().orc_local_create(C.c_int(win_size), C.c_double(voxel_size), C.c_double(min_eigen_value), _p(t), C.c_int(max_layer),
+                                                   C.c_int(thread_num), C.c_double(dept_err), C.c_double(beam_err)))
+        self.voxel_size = voxel_size
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_local_free(self.h); self.h = None
+
+    def push(self, xyz, pose, cov=None):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        ps = as_poses(pose)
+        cv = None if cov is None else np.ascontiguousarray(np.asarray(cov, dtype=np.float64).T)
+        lib().orc_local_push(self.h, _p(xyz), C.c_int(xyz.shape[0]), _p(ps), _p(cv), None)
+
+    def export(self):
+        nr = C.c_int64(0)
+        lib().orc_local_export_count.restype = C.c_int64
+        nn = lib().orc_local_export_count(self.h, C.byref(nr))
+        keys = np.zeros((nr.value, 3), dtype=np.int64); rn = np.zeros(nr.value, dtype=np.int32); nodes = np.zeros(nn, dtype=map_node_dtype)
+        lib().orc_local_export(self.h, _p(keys), _p(rn), _p(nodes))
+        return keys, rn, nodes
+
+    def lio_pass(self, pv, pose, cov, leaf_cache=None):
+        pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+        ps = as_poses(pose); cv = np.ascontiguousarray(np.asarray(cov, dtype=np.float64).T)
+        lc = np.full(n, -1, dtype=np.int32) if leaf_cache is None else np.ascontiguousarray(leaf_cache, dtype=np.int32).copy()
+        HTH = np.zeros((6, 6)); HTz = np.zeros(6); nnt = np.zeros((3, 3)); mn = C.c_int(0); fl = np.zeros(n, dtype=np.int32)
+        lib().orc_lio_pass(self.h, _p(pv), C.c_int(n), _p(ps), _p(cv), _p(lc), _p(HTH), _p(HTz), _p(nnt), C.byref(mn), _p(fl))
+        return dict(HTH=HTH.T.copy(), HTz=HTz, nnt=nnt.T.copy(), match_num=mn.value, flags=fl, leaf_cache=lc)
+
+    def lio_state_estimation(self, pv, R, p, cov, v=None, bg=None, ba=None):
+        pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+        st = np.zeros(21); st[:9] = np.asarray(R).T.reshape(9); st[9:12] = p
+        if v is not None: st[12:15] = v
+        if bg is not None: st[15:18] = bg
+        if ba is not None: st[18:21] = ba
+        cv = np.ascontiguousarray(np.asarray(cov, dtype=np.float64).T).copy()
+        it = C.c_int(0); mn = np.zeros(4, dtype=np.int32)
+        ok = lib().orc_lio_state_estimation(self.h, _p(pv), C.c_int(n), _p(st), _p(cv), C.byref(it), _p(mn))
+        return dict(ok=bool(ok), R=st[:9].reshape(3, 3).T.copy(), p=st[9:12].copy(), v=st[12:15].copy(), bg=st[15:18].copy(), ba=st[18:21].copy(),
+                    cov=cv.reshape(15, 15).T.copy(), iters=it.value, match_nums=mn[:it.value].tolist())

@@ -171,6 +171,54 @@ def hba_add_edge(ctx, clouds, poses, W, n_windows, local, gba, max_layer, max_it
                 n_voxels=nv, status=st)
 
 
+map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("octo_state", "<i4"), ("child", "<i4", (8,)), ("is_plane", "<i4"),
+                           ("radius", "<f4"), ("p_center", "<f8", (3,)), ("p_normal", "<f8", (3,)), ("plane_var", "<f8", (36,))])
+lio_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)), ("cov", "<f8", (225,))])
+assert map_node_dtype.itemsize == 408 and lio_state_dtype.itemsize == 8 * (21 + 225)
+
+
+class PlaneMap:
+    """Flattened OctoTree voxel map on the device (what OctoTree::match reads, voxel_map.hpp:1649-1721)."""
+
+    def __init__(self, ctx, root_keys, root_node, nodes, voxel_size):
+        self.ctx, self.lib = ctx, ctx.lib
+        rk = np.ascontiguousarray(root_keys, dtype=np.int64); rn = np.ascontiguousarray(root_node, dtype=np.int32)
+        nd = np.ascontiguousarray(nodes, dtype=map_node_dtype)
+        h = C.c_void_p()
+        _chk(self.lib.vx_planemap_create(ctx.h, _p(rk), _p(rn), C.c_int64(rk.shape[0]), _p(nd), C.c_int64(nd.shape[0]), C.c_double(voxel_size), C.byref(h)))
+        self.h = h
+
+    def free(self):
+        if self.h:
+            self.lib.vx_planemap_free(self.h); self.h = None
+
+    def lio_pass(self, pv, pose, cov, leaf_cache=None):
+        """One pass of voxelslam.cpp:1005-1050.  pv: (n,12) pnt + var (col-major); cov: 15x15 state covariance."""
+        pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+        ps = as_poses(pose); cov = np.asarray(cov, dtype=np.float64)
+        rv = np.ascontiguousarray(cov[0:3, 0:3].T); tv = np.ascontiguousarray(cov[3:6, 3:6].T)
+        lc = np.full(n, -1, dtype=np.int32) if leaf_cache is None else np.ascontiguousarray(leaf_cache, dtype=np.int32).copy()
+        HTH = np.zeros((6, 6)); HTz = np.zeros(6); nnt = np.zeros((3, 3)); mn = C.c_int32(0); fl = np.zeros(n, dtype=np.int32)
+        _chk(self.lib.vx_lio_match_accumulate(self.ctx.h, self.h, _p(pv), C.c_int64(n), _p(ps), _p(rv), _p(tv), _p(lc), _p(HTH), _p(HTz), _p(nnt),
+                                              C.byref(mn), _p(fl)))
+        return dict(HTH=HTH.T.copy(), HTz=HTz, nnt=nnt.T.copy(), match_num=mn.value, flags=fl, leaf_cache=lc)
+
+    def lio_state_estimation(self, pv, R, p, cov, v=None, bg=None, ba=None):
+        """VOXEL_SLAM::lio_state_estimation (voxelslam.cpp:962-1098)."""
+        pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+        st = np.zeros(1, dtype=lio_state_dtype)
+        st["R"] = np.asarray(R, dtype=np.float64).T.reshape(9); st["p"] = p
+        if v is not None: st["v"] = v
+        if bg is not None: st["bg"] = bg
+        if ba is not None: st["ba"] = ba
+        st["cov"] = np.asarray(cov, dtype=np.float64).T.reshape(225)
+        ok = C.c_int32(0); it = C.c_int32(0); mn = np.zeros(4, dtype=np.int32)
+        _chk(self.lib.vx_lio_state_estimation(self.ctx.h, self.h, _p(pv), C.c_int64(n), _p(st), C.byref(ok), C.byref(it), _p(mn)))
+        s = st[0]
+        return dict(ok=bool(ok.value), R=s["R"].reshape(3, 3).T.copy(), p=s["p"].copy(), v=s["v"].copy(), bg=s["bg"].copy(), ba=s["ba"].copy(),
+                    cov=s["cov"].reshape(15, 15).T.copy(), iters=it.value, match_nums=mn[:it.value].tolist())
+
+
 class DevArray:
     """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
 
