@@ -94,3 +94,39 @@ def config1(seed=20241008 + 1, W=10, pts_per_scan=24000, shape="avia"):
         d = avia_dirs(pts_per_scan, rng) if shape == "avia" else xt32_dirs()
         clouds.append(scan(rects, R[i], p[i], d, rng))
     return clouds, (R, p)
+
+
+def np_keys(xyz, vs):
+    """numpy restatement of the key rule (second, independent coding of A1; float32 arithmetic)."""
+    loc = (np.asarray(xyz, dtype=np.float64) / vs).astype(np.float32)
+    loc = np.where(loc < 0, loc - np.float32(1.0), loc).astype(np.float32)
+    return loc.astype(np.int64)
+
+
+def synthetic_plane_map(points_world, voxel_size=1.0, min_eigen_value=0.0025, node_dtype=None):
+    """A layer-0 voxel-plane map (root voxels only, every root a leaf) from world points, in the flattened form
+    vx_planemap_create takes: per occupied cell the centroid / smallest-eigenvector plane, plane_var = 1e-6 I.
+    Bench input only (no parity claim): the real map comes from the host-side OctoTree."""
+    k = np_keys(points_world, voxel_size)
+    uk, inv = np.unique(k, axis=0, return_inverse=True)
+    inv = inv.reshape(-1)
+    n = uk.shape[0]
+    cnt = np.bincount(inv, minlength=n).astype(np.float64)
+    cen = np.stack([np.bincount(inv, weights=points_world[:, a], minlength=n) for a in range(3)], axis=1) / cnt[:, None]
+    d = points_world - cen[inv]
+    cov = np.zeros((n, 3, 3))
+    for a in range(3):
+        for b in range(3):
+            cov[:, a, b] = np.bincount(inv, weights=d[:, a] * d[:, b], minlength=n) / cnt
+    lam, U = np.linalg.eigh(cov)
+    nodes = np.zeros(n, dtype=node_dtype)
+    nodes["center"] = (uk + 0.5) * voxel_size
+    nodes["quater_length"] = voxel_size / 4
+    nodes["octo_state"] = 0
+    nodes["child"] = -1
+    nodes["is_plane"] = ((cnt > 5) & (lam[:, 0] < min_eigen_value)).astype(np.int32)
+    nodes["radius"] = lam[:, 2]
+    nodes["p_center"] = cen
+    nodes["p_normal"] = U[:, :, 0]
+    nodes["plane_var"] = (np.eye(6) * 1e-6).reshape(36)[None, :]
+    return uk, np.arange(n, dtype=np.int32), nodes

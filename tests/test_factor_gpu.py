@@ -153,3 +153,35 @@ def test_batched_windows_match_single(pkg, ctx, W, NW):
         assert rel(Hb[b], H1) < 1e-12 and rel(Jb[b], J1) < 1e-12 and abs(cb[b] - c1) <= 1e-13 * abs(c1)
         f1.free()
     fb.free()
+
+
+def test_upload_csr_validation_on_device(pkg, ctx):
+    # malformed CSR input is rejected by the device-side validation pass (k_validate_vox / k_unpack_vf), error text kept
+    W, NW = 5, 3
+    good = synth.batched_factor_csr(11, NW, 40, W, occupancy=0.7)
+    f = pkg.Factor(ctx, W, NW)
+    f.upload_csr(good)
+    assert f.num_voxels == 120
+
+    def broken(mut):
+        bad = {k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in good.items()}
+        mut(bad)
+        with pytest.raises(pkg.VxError) as e:
+            f.upload_csr(bad)
+        assert e.value.code == -2
+        return str(e.value)
+
+    o = good["offsets"]
+    def swap(b): b["frames"][[o[3], o[3] + 1]] = b["frames"][[o[3] + 1, o[3]]]
+    assert "ascending" in broken(swap)
+    def span(b): b["frames"][o[4] - 1] = W            # last frame of voxel 3 (window 0) points into window 1
+    assert "spans" in broken(span)
+    def oob(b): b["frames"][o[120] - 1] = W * NW
+    assert "bad frame" in broken(oob)
+    def order(b): b["frames"][o[0]:o[1]] = W * 2 + np.arange(o[1] - o[0])   # voxel 0 in window 2 before window 0 voxels
+    assert "grouped" in broken(order)
+    def zero(b): b["clusters"]["N"][7] = 0
+    assert "N == 0" in broken(zero)
+    f.upload_csr(good)                                  # still usable afterwards
+    assert np.isfinite(f.residual(good["poses"])).all()
+    f.free()

@@ -130,6 +130,19 @@ static int scan_i32(vx_ctx *ctx, const int32_t *in, int32_t *out, int64_t n) {
   return VX_OK;
 }
 
+// vox[e] = owning voxel of voxel-frame e (needed by every evaluation path); the pair-list plans are built
+// lazily by the first generic-path Hessian (the fused small-window path does not need them).
+int factor_finish_upload(vx_factor *f) {
+  vx_ctx *ctx = f->ctx;
+  VX_TRY(bind(ctx));
+  f->plan_ready = false;
+  f->n_pairs = f->n_tiles = f->n_dseg = f->n_oseg = 0;
+  if (f->V == 0 || f->nnz == 0) { f->plan_ready = true; return VX_OK; }
+  k_fill_vox<<<blocks_for(f->V, 256), 256, 0, ctx->stream>>>(f->off.as<int32_t>(), f->vox.as<int32_t>(), f->V);
+  VX_LAUNCH_CHECK(ctx);
+  return VX_OK;
+}
+
 int factor_build_plan(vx_factor *f) {
   vx_ctx *ctx = f->ctx;
   VX_TRY(bind(ctx));
@@ -524,12 +537,14 @@ static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end)
 
 static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   cudaStream_t st = ctx->stream;
-  if (!f->plan_ready) VX_TRY(factor_build_plan(f));
   const size_t jl = (size_t)6 * f->W;
-  VX_CUDA(cudaMemsetAsync(f->H.p, 0, sizeof(double) * jl * jl * f->n_win, st));
-  VX_CUDA(cudaMemsetAsync(f->J.p, 0, sizeof(double) * jl * f->n_win, st));
   bool fused = false;
-  if (f->V > 0 && f->nnz > 0 && !f->force_pairlist) VX_TRY(hessian_small(ctx, f, head, end, &fused));
+  if (f->V > 0 && f->nnz > 0 && !f->force_pairlist) VX_TRY(hessian_small(ctx, f, head, end, &fused));   // overwrites all of H, J
+  if (!fused) {
+    if (!f->plan_ready) VX_TRY(factor_build_plan(f));
+    VX_CUDA(cudaMemsetAsync(f->H.p, 0, sizeof(double) * jl * jl * f->n_win, st));
+    VX_CUDA(cudaMemsetAsync(f->J.p, 0, sizeof(double) * jl * f->n_win, st));
+  }
   if (!fused && f->V > 0 && f->nnz > 0) {
     VX_KERNEL(ctx, "k_voxel_prep", k_voxel_prep<<<blocks_for(f->V, 256), 256, 0, st>>>(f->lam.as<double>(), f->mrg.as<double>(), f->coe.as<double>(), f->cS.as<double>(), f->V));
     if (f->n_dseg > 0) {
@@ -556,10 +571,11 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) 
 // One thread per voxel-frame: reads the 104-byte reference PointCluster record (tools.hpp:308-310)
 // src[idx ? idx[e] : e] and scatters P's upper triangle, v and N into the component planes.
 __global__ void k_unpack_vf(const vx_cluster *__restrict__ src, const int64_t *__restrict__ idx, double *__restrict__ mom,
-                            int32_t *__restrict__ cnt, int64_t nnz) {
+                            int32_t *__restrict__ cnt, int64_t nnz, int *__restrict__ err) {
   int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (e >= nnz) return;
   const vx_cluster &c = src[idx ? idx[e] : e];
+  if (c.N == 0) atomicMax(err, 4);
   mom[0 * nnz + e] = c.P[0]; mom[1 * nnz + e] = c.P[3]; mom[2 * nnz + e] = c.P[6];
   mom[3 * nnz + e] = c.P[4]; mom[4 * nnz + e] = c.P[7]; mom[5 * nnz + e] = c.P[8];
   mom[6 * nnz + e] = c.v[0]; mom[7 * nnz + e] = c.v[1]; mom[8 * nnz + e] = c.v[2];
@@ -591,36 +607,43 @@ __global__ void k_unpack_voxel(const vx_cluster *__restrict__ sig, const vx_clus
   for (int k = 0; k < 9; k++) U[k * V + v] = evec[9 * v + k];
 }
 
-// `cl_host` holds n_src records; voxel-frame e is record idx[e] (idx may be null = identity).
-static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &off, const std::vector<int32_t> &frames,
+// Device-side validation of the CSR structure + window of each voxel.  err: 1 bad frame id / voxel spans windows,
+// 2 frames not strictly ascending, 3 voxels not grouped by ascending window, 5 empty voxel in a batched factor.
+__global__ void k_validate_vox(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, int64_t V, int W, int NW, int32_t *__restrict__ win,
+                               int *__restrict__ err) {
+  const int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  const int32_t b = off[v], e = off[v + 1];
+  if (e < b) { atomicMax(err, 1); win[v] = 0; return; }
+  if (e == b) { if (NW > 1) atomicMax(err, 5); win[v] = 0; return; }
+  const int32_t w = frame[b] / W;
+  for (int32_t x = b; x < e; x++) {
+    const int32_t fr = frame[x];
+    if (fr < 0 || fr >= W * NW || fr / W != w) atomicMax(err, 1);
+    if (x > b && fr <= frame[x - 1]) atomicMax(err, 2);
+  }
+  win[v] = w;
+  if (v > 0 && off[v] > off[v - 1] && frame[off[v - 1]] / W > w) atomicMax(err, 3);
+}
+__global__ void k_win_offsets(const int32_t *__restrict__ win, int64_t V, int NW, int32_t *__restrict__ wv_off) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w > NW) return;
+  int64_t lo = 0, hi = V;
+  while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (win[mid] < w) lo = mid + 1; else hi = mid; }
+  wv_off[w] = (int32_t)lo;
+}
+
+// `cl_host` holds n_src records; voxel-frame e is record idx[e] (idx may be null = identity).  `frames`: nnz ids.
+static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &off, const int32_t *frames, int64_t nnz,
                          const vx_cluster *cl_host, int64_t n_src, const std::vector<int64_t> *idx, const vx_cluster *sig_vecs,
                          const double *coeffs, const double *eig_values, const double *eig_vectors, const vx_cluster *pcr_adds) {
   vx_ctx *ctx = f->ctx;
   VX_TRY(bind(ctx));
   cudaStream_t st = ctx->stream;
-  const int64_t nnz = (int64_t)frames.size();
   const int W = f->W, NW = f->n_win;
   VX_TRY(factor_alloc(f, V, nnz));
-  // window of each voxel (from its first frame); voxels must be grouped by ascending window
-  std::vector<int32_t> win(V, 0), wv_off(NW + 1, 0);
-  int32_t prev = 0;
-  for (int64_t v = 0; v < V; v++) {
-    int32_t w = 0;
-    if (off[v + 1] > off[v]) {
-      w = frames[off[v]] / W;
-      for (int32_t e = off[v]; e < off[v + 1]; e++) {
-        if (frames[e] < 0 || frames[e] >= W * NW || frames[e] / W != w) { set_error("voxel %lld spans windows or has a bad frame id", (long long)v); return VX_ERR_ARG; }
-        if (e > off[v] && frames[e] <= frames[e - 1]) { set_error("voxel %lld: frames not strictly ascending", (long long)v); return VX_ERR_ARG; }
-      }
-    } else w = prev;
-    if (w < prev) { set_error("voxels must be grouped by ascending window"); return VX_ERR_ARG; }
-    win[v] = w; prev = w;
-  }
-  { int64_t v = 0; for (int w = 0; w <= NW; w++) { while (v < V && win[v] < w) v++; wv_off[w] = (int32_t)v; } }
-
 #define VX_H2D(dst, src, bytes) VX_CUDA(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyHostToDevice, st))
   VX_H2D(f->off.p, off.data(), sizeof(int32_t) * (V + 1));
-  VX_H2D(f->wv_off.p, wv_off.data(), sizeof(int32_t) * (NW + 1));
   // staging area for the raw AoS records
   DevBuf &raw = ctx->scratch2;
   const size_t b_cl = sizeof(vx_cluster) * (size_t)n_src, b_idx = idx ? sizeof(int64_t) * (size_t)nnz : 0;
@@ -633,11 +656,13 @@ static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &of
   vx_cluster *d_add = (vx_cluster *)(base + b_cl + b_idx + b_vc);
   double *d_ev = (double *)(base + b_cl + b_idx + 2 * b_vc);
   double *d_evec = (double *)(base + b_cl + b_idx + 2 * b_vc + b_ev);
+  int *d_err = (int *)(base + b_cl + b_idx + 2 * b_vc + b_ev + b_evec);
+  VX_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), st));
   if (nnz > 0) {
-    VX_H2D(f->frame.p, frames.data(), sizeof(int32_t) * nnz);
+    VX_H2D(f->frame.p, frames, sizeof(int32_t) * nnz);
     VX_H2D(d_cl, cl_host, b_cl);
     if (idx) VX_H2D(d_idx, idx->data(), b_idx);
-    VX_KERNEL(ctx, "k_unpack_vf", k_unpack_vf<<<blocks_for(nnz, 256), 256, 0, st>>>(d_cl, idx ? d_idx : nullptr, f->mom.as<double>(), f->cnt.as<int32_t>(), nnz));
+    VX_KERNEL(ctx, "k_unpack_vf", k_unpack_vf<<<blocks_for(nnz, 256), 256, 0, st>>>(d_cl, idx ? d_idx : nullptr, f->mom.as<double>(), f->cnt.as<int32_t>(), nnz, d_err));
   }
   if (V > 0) {
     VX_H2D(d_sig, sig_vecs, b_vc);
@@ -645,13 +670,23 @@ static int upload_common(vx_factor *f, int64_t V, const std::vector<int32_t> &of
     VX_H2D(d_ev, eig_values, b_ev);
     VX_H2D(d_evec, eig_vectors, b_evec);
     VX_H2D(f->coe.p, coeffs, sizeof(double) * V);
-    VX_H2D(f->win.p, win.data(), sizeof(int32_t) * V);
     VX_KERNEL(ctx, "k_unpack_voxel", k_unpack_voxel<<<blocks_for(V, 256), 256, 0, st>>>(d_sig, d_add, d_ev, d_evec, f->fix.as<double>(), f->mrg.as<double>(),
                                                                                      f->lam.as<double>(), f->U.as<double>(), V));
+    VX_KERNEL(ctx, "k_validate_vox", k_validate_vox<<<blocks_for(V, 256), 256, 0, st>>>(f->off.as<int32_t>(), f->frame.as<int32_t>(), V, W, NW, f->win.as<int32_t>(), d_err));
   }
+  VX_KERNEL(ctx, "k_win_offsets", k_win_offsets<<<blocks_for(NW + 1, 128), 128, 0, st>>>(f->win.as<int32_t>(), V, NW, f->wv_off.as<int32_t>()));
 #undef VX_H2D
-  VX_CUDA(cudaStreamSynchronize(st));   // host vectors above go out of scope; scratch2 is reused by the plan
-  return factor_build_plan(f);
+  int err = 0;
+  VX_CUDA(cudaMemcpyAsync(&err, d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+  VX_CUDA(cudaStreamSynchronize(st));   // host staging goes out of scope
+  if (err) {
+    const char *what[] = {"", "a voxel spans windows or has a bad frame id", "frames of a voxel are not strictly ascending",
+                          "voxels must be grouped by ascending window", "a voxel-frame cluster has N == 0", "a batched factor has a voxel without frames"};
+    set_error("factor upload: %s", what[err < 6 ? err : 1]);
+    f->V = 0; f->nnz = 0;
+    return VX_ERR_ARG;
+  }
+  return factor_finish_upload(f);
 }
 
 extern "C" {
@@ -715,7 +750,7 @@ int vx_factor_upload_dense(vx_factor *f, int64_t V, const vx_cluster *plvec, con
     VX_ARG(frames.size() < ((size_t)1 << 31));
     off[v + 1] = (int32_t)frames.size();
   }
-  return upload_common(f, V, off, frames, plvec, V * W, &idx, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
+  return upload_common(f, V, off, frames.data(), (int64_t)frames.size(), plvec, V * W, &idx, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
 }
 
 int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const int32_t *frames_in, const vx_cluster *clusters,
@@ -726,10 +761,9 @@ int vx_factor_upload_csr(vx_factor *f, int64_t V, const int64_t *offsets, const 
   VX_ARG(nnz >= 0 && nnz < ((int64_t)1 << 31));
   VX_ARG(V == 0 || (sig_vecs && coeffs && eig_values && eig_vectors && pcr_adds));
   VX_ARG(nnz == 0 || (frames_in && clusters));
-  std::vector<int32_t> off(V + 1), frames(frames_in, frames_in + nnz);
+  std::vector<int32_t> off(V + 1);
   for (int64_t v = 0; v <= V; v++) { VX_ARG(offsets[v] >= 0 && offsets[v] <= nnz && (v == 0 || offsets[v] >= offsets[v - 1])); off[v] = (int32_t)offsets[v]; }
-  for (int64_t e = 0; e < nnz; e++) VX_ARG(clusters[e].N != 0);
-  return upload_common(f, V, off, frames, clusters, nnz, nullptr, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
+  return upload_common(f, V, off, frames_in, nnz, clusters, nnz, nullptr, sig_vecs, coeffs, eig_values, eig_vectors, pcr_adds);
 }
 
 int vx_factor_download_cache(vx_factor *f, double *eig_values, double *eig_vectors, vx_cluster *pcr_adds) {

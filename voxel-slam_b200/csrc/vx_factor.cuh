@@ -48,6 +48,8 @@ struct vx_factor {
 namespace vx {
 // (Re)builds vox[], the frame-major order and the tile/segment plans from off[]/frame[] on device.
 int factor_build_plan(vx_factor *f);
+// Fills vox[] after off[]/frame[] changed and invalidates the plans (rebuilt lazily by the generic path).
+int factor_finish_upload(vx_factor *f);
 // Allocates per-voxel / per-voxel-frame arrays for V voxels and nnz voxel-frames.
 int factor_alloc(vx_factor *f, int64_t V, int64_t nnz);
 // Fused tensor-core path for small windows (vx_hess_small.cu); *handled=false when W has no instantiation.

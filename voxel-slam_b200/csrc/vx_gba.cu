@@ -518,7 +518,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   VX_KERNEL(ctx, "k_vox_win", k_vox_win<<<blocks_for(V, 256), 256, 0, st>>>(f->off.as<int32_t>(), f->frame.as<int32_t>(), V, W, f->win.as<int32_t>()));
   VX_KERNEL(ctx, "k_win_off", k_win_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(f->win.as<int32_t>(), V, NW, f->wv_off.as<int32_t>()));
   VX_CUDA(cudaStreamSynchronize(st));
-  return factor_build_plan(f);
+  return factor_finish_upload(f);
 }
 }  // namespace vx
 
