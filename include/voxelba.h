@@ -177,6 +177,46 @@ int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_
 int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter,
                 int thd_num, int *converged, int *accept_trace, int *n_iters);
 
+/* ---- B6: class IMU_PRE  preintegration.hpp:11-303 — host-side, a POD the caller owns.
+ * 3x3 / 15x15 members are column-major.  noise = the reference's globals imupre_scale_gravity, noiseMeas, noiseWalk
+ * (preintegration.hpp:8-9; filled at voxelslam.cpp:934-939). */
+typedef struct vx_imu_pre {
+  double R_delta[9], p_delta[3], v_delta[3], bg[3], ba[3];
+  double R_bg[9], p_bg[9], p_ba[9], v_bg[9], v_ba[9];
+  double dtime;
+  double dbg[3], dba[3], dbg_buf[3], dba_buf[3];
+  double cov[225];
+} vx_imu_pre;
+typedef struct vx_imu_noise { double scale_gravity; double noise_meas[36]; double noise_walk[36]; } vx_imu_noise;
+typedef struct vx_imu_sample { double t, gyr[3], acc[3]; } vx_imu_sample;
+/* the IMUST members the LI optimizers read and write (tools.hpp:135-199): R, p, v, bg, ba, g */
+typedef struct vx_imu_state { double R[9], p[3], v[3], bg[3], ba[3], g[3]; } vx_imu_state;
+
+int vx_imu_pre_init(vx_imu_pre *pre, const double *bg3, const double *ba3);                 /* ctor, preintegration.hpp:32-48 */
+int vx_imu_pre_push(vx_imu_pre *pre, const vx_imu_noise *nz, const vx_imu_sample *s, int n); /* push_imu :50-73 (mid-point rule) */
+int vx_imu_pre_add(vx_imu_pre *pre, const vx_imu_noise *nz, const double *gyr3, const double *acc3, double dt); /* add_imu :75-135 */
+/* give_evaluate (:137-212, with_gravity=0: 30 columns) / give_evaluate_g (:214-294, with_gravity=1: 33 columns).
+ * jtj (nc x nc col-major) and gg (nc) are written when both are non-NULL (the reference's jac_enable); *cost = rr^T cov^-1 rr. */
+int vx_imu_pre_evaluate(const vx_imu_pre *pre, const vx_imu_state *st1, const vx_imu_state *st2, int with_gravity, double *jtj,
+                        double *gg, double *cost);
+int vx_imu_pre_update_state(vx_imu_pre *pre, const double *dxi15);                          /* :296-303 */
+
+/* ---- B4: LI_BA_Optimizer::damping_iter(x_stats, voxhess, imus_factor, hess*)  voxel_map.hpp:624-713.
+ * 15W unknowns [theta p v bg ba]; IMU chain 30x30 blocks on the host, scaled by imu_coef (:565-567); LiDAR 6x6 blocks
+ * from the device factor scattered stride 6 -> 15 (hess_plus :509-517); gauge fixes all 15 of pose 0 (:653-656); 3 fixed
+ * iterations (:643); bias linearisation shifted by update_state and rolled back on reject (:670-671, :701-705).
+ *   x          in/out, W states              imus   W-1 factors, in/out (dbg/dba move)
+ *   hess_out   (15W)^2 col-major, may be NULL      accept_trace  3 ints, may be NULL     n_iters may be NULL
+ * The factor must be a single window (n_windows == 1). */
+int vx_ba_li(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imus, double imu_coef, double *hess_out,
+             int *accept_trace, int *n_iters);
+/* ---- B5: LI_BA_OptimizerGravity::damping_iter(x_stats, voxhess, imus_factor, resis, hess*, max_iter=2)
+ * voxel_map.hpp:878-975.  15W+3 unknowns (gravity last, :921); 33x33 factor blocks scattered into pose-pose / pose-g /
+ * g-pose / g-g (:785-795); gauge fixes the first 6 only (:906-909); g += dxi.tail(3) copied to every frame (:921-930).
+ *   resis2: first and last cost;  hess_out (15W+3)^2. */
+int vx_ba_li_gravity(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imus, double imu_coef, double *resis2,
+                     double *hess_out, int max_iter, int *accept_trace, int *n_iters);
+
 /* ---- C1h: VOXEL_SLAM::HBA_add_edge(p_xs, p_smps, gba_edges, maps, max_iter, thread_num, plptr)
  * voxelslam.cpp:2822-3015 (the session filter :2836-2857 stays with the caller: pass only connected frames).
  * For every window: up to max_iter outer iterations of {rebuild the GBA voxel map at the current poses,

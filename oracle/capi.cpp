@@ -12,6 +12,9 @@
 
 using namespace orc;
 
+template <class A> static void cp_in(A &dst, const double *src, int n) { for (int k = 0; k < n; k++) dst[k] = src[k]; }
+template <class A> static void cp_out(const A &src, double *dst, int n) { for (int k = 0; k < n; k++) dst[k] = src[k]; }
+
 extern "C" {
 
 struct oc_cluster { double P[9]; double v[3]; int32_t N; int32_t _pad; };
@@ -395,6 +398,106 @@ int orc_lio_state_estimation(void *h, const double *pv, int n, double *state21, 
   if (iters) *iters = tr.iters;
   if (match_nums4) for (int k = 0; k < tr.iters && k < 4; k++) match_nums4[k] = tr.passes[k].match_num;
   return ok ? 1 : 0;
+}
+
+// ---- B6 / B4 / B5 ---------------------------------------------------------------------------
+struct oc_imu_pre {
+  double R_delta[9], p_delta[3], v_delta[3], bg[3], ba[3];
+  double R_bg[9], p_bg[9], p_ba[9], v_bg[9], v_ba[9];
+  double dtime;
+  double dbg[3], dba[3], dbg_buf[3], dba_buf[3];
+  double cov[225];
+};
+struct oc_imu_noise { double scale_gravity; double noise_meas[36]; double noise_walk[36]; };
+struct oc_imu_sample { double t, gyr[3], acc[3]; };
+struct oc_imu_state { double R[9], p[3], v[3], bg[3], ba[3], g[3]; };
+
+static ImuNoise noise_in(const oc_imu_noise *n) {
+  ImuNoise z; z.scale_gravity = n->scale_gravity;
+  for (int k = 0; k < 36; k++) { z.noiseMeas[k] = n->noise_meas[k]; z.noiseWalk[k] = n->noise_walk[k]; }
+  return z;
+}
+static void pre_in(const oc_imu_pre *p, IMU_PRE &q) {
+  cp_in(q.R_delta, p->R_delta, 9); cp_in(q.p_delta, p->p_delta, 3); cp_in(q.v_delta, p->v_delta, 3); cp_in(q.bg, p->bg, 3); cp_in(q.ba, p->ba, 3);
+  cp_in(q.R_bg, p->R_bg, 9); cp_in(q.p_bg, p->p_bg, 9); cp_in(q.p_ba, p->p_ba, 9); cp_in(q.v_bg, p->v_bg, 9); cp_in(q.v_ba, p->v_ba, 9);
+  q.dtime = p->dtime;
+  cp_in(q.dbg, p->dbg, 3); cp_in(q.dba, p->dba, 3); cp_in(q.dbg_buf, p->dbg_buf, 3); cp_in(q.dba_buf, p->dba_buf, 3);
+  cp_in(q.cov, p->cov, 225);
+}
+static void pre_out(const IMU_PRE &q, oc_imu_pre *p) {
+  cp_out(q.R_delta, p->R_delta, 9); cp_out(q.p_delta, p->p_delta, 3); cp_out(q.v_delta, p->v_delta, 3); cp_out(q.bg, p->bg, 3); cp_out(q.ba, p->ba, 3);
+  cp_out(q.R_bg, p->R_bg, 9); cp_out(q.p_bg, p->p_bg, 9); cp_out(q.p_ba, p->p_ba, 9); cp_out(q.v_bg, p->v_bg, 9); cp_out(q.v_ba, p->v_ba, 9);
+  p->dtime = q.dtime;
+  cp_out(q.dbg, p->dbg, 3); cp_out(q.dba, p->dba, 3); cp_out(q.dbg_buf, p->dbg_buf, 3); cp_out(q.dba_buf, p->dba_buf, 3);
+  cp_out(q.cov, p->cov, 225);
+}
+static IMUST imu_state_in(const oc_imu_state &s) {
+  IMUST x;
+  cp_in(x.R, s.R, 9); cp_in(x.p, s.p, 3); cp_in(x.v, s.v, 3); cp_in(x.bg, s.bg, 3); cp_in(x.ba, s.ba, 3); cp_in(x.g, s.g, 3);
+  return x;
+}
+static void state_out(const IMUST &x, oc_imu_state &s) {
+  cp_out(x.R, s.R, 9); cp_out(x.p, s.p, 3); cp_out(x.v, s.v, 3); cp_out(x.bg, s.bg, 3); cp_out(x.ba, s.ba, 3); cp_out(x.g, s.g, 3);
+}
+
+void orc_imu_pre_init(oc_imu_pre *pre, const double *bg, const double *ba) {
+  ImuNoise nz;
+  IMU_PRE q(&nz, vec3(bg[0], bg[1], bg[2]), vec3(ba[0], ba[1], ba[2]));
+  pre_out(q, pre);
+}
+void orc_imu_pre_push(oc_imu_pre *pre, const oc_imu_noise *noise, const oc_imu_sample *s, int n) {
+  ImuNoise nz = noise_in(noise);
+  IMU_PRE q(&nz);
+  pre_in(pre, q);
+  std::vector<ImuSample> v(n);
+  for (int k = 0; k < n; k++) { v[k].t = s[k].t; cp_in(v[k].gyr, s[k].gyr, 3); cp_in(v[k].acc, s[k].acc, 3); }
+  q.push_imu(v);
+  pre_out(q, pre);
+}
+void orc_imu_pre_evaluate(const oc_imu_pre *pre, const oc_imu_state *st1, const oc_imu_state *st2, int with_gravity, double *jtj, double *gg,
+                          double *cost) {
+  ImuNoise nz;
+  IMU_PRE q(&nz);
+  pre_in(pre, q);
+  IMUST a = imu_state_in(*st1), b = imu_state_in(*st2);
+  const bool jac = jtj && gg;
+  if (with_gravity) {
+    Mat<33, 33> h; Mat<33, 1> g;
+    *cost = q.evaluate<33>(a, b, h, g, jac);
+    if (jac) { cp_out(h, jtj, 33 * 33); cp_out(g, gg, 33); }
+  } else {
+    Mat<30, 30> h; Mat<30, 1> g;
+    *cost = q.evaluate<30>(a, b, h, g, jac);
+    if (jac) { cp_out(h, jtj, 30 * 30); cp_out(g, gg, 30); }
+  }
+}
+// LI_BA_Optimizer (gravity = 0, max_iter ignored: 3) / LI_BA_OptimizerGravity (gravity = 1)
+void orc_ba_li(void *h, oc_imu_state *xs, oc_imu_pre *pres, double imu_coef, int gravity, int max_iter, int use_threads, double *resis2,
+               double *hess_out, int *accept_trace, int *n_trace) {
+  LidarFactor &f = *(LidarFactor *)h;
+  const int W = f.win_size;
+  ImuNoise nz;
+  std::vector<IMUST> x(W);
+  for (int i = 0; i < W; i++) x[i] = imu_state_in(xs[i]);
+  std::deque<IMU_PRE *> imus;
+  for (int i = 0; i + 1 < W; i++) { IMU_PRE *q = new IMU_PRE(&nz); pre_in(&pres[i], *q); imus.push_back(q); }
+  MatX hess; std::vector<double> resis;
+  std::vector<int> trace;
+  if (gravity) {
+    LI_BA_OptimizerGravity opt; opt.imu_coef = imu_coef; opt.use_threads = use_threads != 0;
+    opt.damping_iter(x, f, imus, resis, &hess, max_iter);
+    trace = opt.accept_trace;
+  } else {
+    LI_BA_Optimizer opt; opt.imu_coef = imu_coef; opt.use_threads = use_threads != 0;
+    opt.damping_iter(x, f, imus, &hess);
+    trace = opt.accept_trace;
+  }
+  for (int i = 0; i < W; i++) state_out(x[i], xs[i]);
+  for (int i = 0; i + 1 < W; i++) { pre_out(*imus[i], &pres[i]); delete imus[i]; }
+  if (hess_out) std::memcpy(hess_out, hess.d.data(), sizeof(double) * hess.d.size());
+  if (resis2 && resis.size() >= 2) { resis2[0] = resis[0]; resis2[1] = resis[1]; }
+  if (n_trace) *n_trace = (int)trace.size();
+  if (accept_trace) for (size_t i = 0; i < trace.size(); i++) accept_trace[i] = trace[i];
 }
 
 double orc_now() {

@@ -233,6 +233,41 @@ class Factor:
         return dict(rc=rc, poses=ps, hess=hess.T.copy(), resis=resis, accept=trace[:nt.value].tolist())
 
 
+    def ba_li(self, states, imus, imu_coef=1e-4, gravity=False, max_iter=2, use_threads=False):
+        """LI_BA_Optimizer (gravity False) / LI_BA_OptimizerGravity (True) ::damping_iter."""
+        x = np.ascontiguousarray(states, dtype=imu_state_dtype).copy(); pr = np.ascontiguousarray(imus, dtype=imu_pre_dtype).copy()
+        n = 15 * self.W + (3 if gravity else 0)
+        hess = np.zeros((n, n)); resis = np.zeros(2); trace = np.zeros(max(max_iter, 3) + 1, dtype=np.int32); nt = C.c_int(0)
+        lib().orc_ba_li(self.h, _p(x), _p(pr), C.c_double(imu_coef), C.c_int(int(gravity)), C.c_int(max_iter), C.c_int(int(use_threads)),
+                        _p(resis), _p(hess), _p(trace), C.byref(nt))
+        return dict(states=x, imus=pr, hess=hess.T.copy(), resis=resis, accept=trace[:nt.value].tolist())
+
+
+imu_pre_dtype = np.dtype([("R_delta", "<f8", (9,)), ("p_delta", "<f8", (3,)), ("v_delta", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)),
+                          ("R_bg", "<f8", (9,)), ("p_bg", "<f8", (9,)), ("p_ba", "<f8", (9,)), ("v_bg", "<f8", (9,)), ("v_ba", "<f8", (9,)),
+                          ("dtime", "<f8"), ("dbg", "<f8", (3,)), ("dba", "<f8", (3,)), ("dbg_buf", "<f8", (3,)), ("dba_buf", "<f8", (3,)),
+                          ("cov", "<f8", (225,))])
+imu_noise_dtype = np.dtype([("scale_gravity", "<f8"), ("noise_meas", "<f8", (36,)), ("noise_walk", "<f8", (36,))])
+imu_sample_dtype = np.dtype([("t", "<f8"), ("gyr", "<f8", (3,)), ("acc", "<f8", (3,))])
+imu_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)), ("g", "<f8", (3,))])
+
+
+def imu_pre_new(samples, noise, bg=(0, 0, 0), ba=(0, 0, 0)):
+    pre = np.zeros(1, dtype=imu_pre_dtype)
+    bg = np.ascontiguousarray(bg, dtype=np.float64); ba = np.ascontiguousarray(ba, dtype=np.float64)
+    lib().orc_imu_pre_init(_p(pre), _p(bg), _p(ba))
+    s = np.ascontiguousarray(samples, dtype=imu_sample_dtype)
+    lib().orc_imu_pre_push(_p(pre), _p(np.ascontiguousarray(noise, dtype=imu_noise_dtype)), _p(s), C.c_int(s.shape[0]))
+    return pre
+
+
+def imu_pre_evaluate(pre, st1, st2, with_gravity=False, jac=True):
+    nc = 33 if with_gravity else 30
+    jtj = np.zeros((nc, nc)); gg = np.zeros(nc); cost = np.zeros(1)
+    lib().orc_imu_pre_evaluate(_p(pre), _p(st1), _p(st2), C.c_int(int(with_gravity)), _p(jtj) if jac else None, _p(gg) if jac else None, _p(cost))
+    return float(cost[0]), jtj.T.copy(), gg
+
+
 map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("octo_state", "<i4"), ("child", "<i4", (8,)), ("is_plane", "<i4"),
                            ("radius", "<f4"), ("p_center", "<f8", (3,)), ("p_normal", "<f8", (3,)), ("plane_var", "<f8", (36,))])
 assert map_node_dtype.itemsize == 408

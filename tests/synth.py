@@ -212,3 +212,60 @@ def csr_window(fac, b):
     R, p = fac["poses"]
     return dict(plvec=plvec, sig=fac["sig"][vs], coe=fac["coe"][vs], eigval=fac["eigval"][vs], eigvec=fac["eigvec"][vs],
                 merged=fac["merged"][vs], poses=(R[b * W:(b + 1) * W], p[b * W:(b + 1) * W]))
+
+
+# ---- synthetic IMU for the LiDAR-inertial optimizers (200 Hz IMU from an analytic trajectory) ----
+imu_sample_dtype = np.dtype([("t", "<f8"), ("gyr", "<f8", (3,)), ("acc", "<f8", (3,))])
+imu_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)), ("g", "<f8", (3,))])
+
+
+def _euler_R(psi, th, phi):
+    cz, sz, cy, sy, cx, sx = np.cos(psi), np.sin(psi), np.cos(th), np.sin(th), np.cos(phi), np.sin(phi)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1.0]]); Ry = np.array([[cy, 0, sy], [0, 1.0, 0], [-sy, 0, cy]])
+    Rx = np.array([[1.0, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    return Rz @ Ry @ Rx
+
+
+def imu_trajectory(seed, W, frame_dt=0.1, rate=200, gyr_sigma=0.0, acc_sigma=0.0, bg=(0.002, -0.001, 0.0015), ba=(0.02, -0.01, 0.015),
+                   g=(0, 0, -9.8)):
+    """Analytic trajectory sampled at W frame times + IMU samples between consecutive frames (each segment includes both
+    end points, as push_imu expects).  Measurement model of the reference: gyr = w_body + bg, acc = R^T (a_world - g) + ba."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    A = rng.uniform(0.5, 1.5, 3) * np.array([2.0, 1.0, 0.2]); wv = rng.uniform(0.5, 1.2, 3); v0 = np.array([1.0, 0.2, 0.0])
+    a_psi, a_th, a_phi = 0.4, 0.05 * rng.uniform(0.5, 1.5), 0.04 * rng.uniform(0.5, 1.5)
+    g = np.asarray(g, dtype=np.float64); bg = np.asarray(bg, dtype=np.float64); ba = np.asarray(ba, dtype=np.float64)
+
+    def pos(t): return v0 * t + A * np.sin(wv * t)
+    def vel(t): return v0 + A * wv * np.cos(wv * t)
+    def acc(t): return -A * wv * wv * np.sin(wv * t)
+    def eul(t): return a_psi * t + 0.1 * np.sin(t), a_th * np.sin(0.9 * t), a_phi * np.sin(1.3 * t)
+    def eul_d(t): return a_psi + 0.1 * np.cos(t), 0.9 * a_th * np.cos(0.9 * t), 1.3 * a_phi * np.cos(1.3 * t)
+
+    def body_rate(t):
+        psi, th, phi = eul(t); dpsi, dth, dphi = eul_d(t)
+        return np.array([dphi - dpsi * np.sin(th), dth * np.cos(phi) + dpsi * np.sin(phi) * np.cos(th),
+                         -dth * np.sin(phi) + dpsi * np.cos(phi) * np.cos(th)])
+
+    states = np.zeros(W, dtype=imu_state_dtype)
+    segs = []
+    n_sub = int(round(frame_dt * rate))
+    for i in range(W):
+        t = i * frame_dt
+        R = _euler_R(*eul(t))
+        states[i]["R"] = R.T.reshape(9); states[i]["p"] = pos(t); states[i]["v"] = vel(t)
+        states[i]["bg"] = bg; states[i]["ba"] = ba; states[i]["g"] = g
+        if i + 1 < W:
+            s = np.zeros(n_sub + 1, dtype=imu_sample_dtype)
+            for k in range(n_sub + 1):
+                tk = t + k * frame_dt / n_sub
+                Rk = _euler_R(*eul(tk))
+                s[k]["t"] = tk
+                s[k]["gyr"] = body_rate(tk) + bg + rng.normal(0, gyr_sigma, 3)
+                s[k]["acc"] = Rk.T @ (acc(tk) - g) + ba + rng.normal(0, acc_sigma, 3)
+            segs.append(s)
+    return states, segs
+
+
+def states_poses(states):
+    R = np.transpose(states["R"].reshape(-1, 3, 3), (0, 2, 1)).copy()
+    return R, states["p"].copy()

@@ -219,6 +219,45 @@ class PlaneMap:
                     cov=s["cov"].reshape(15, 15).T.copy(), iters=it.value, match_nums=mn[:it.value].tolist())
 
 
+# ---- B6 / B4 / B5: IMU preintegration factor (host) and the LiDAR-inertial optimizers -------------------------
+imu_pre_dtype = np.dtype([("R_delta", "<f8", (9,)), ("p_delta", "<f8", (3,)), ("v_delta", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)),
+                          ("R_bg", "<f8", (9,)), ("p_bg", "<f8", (9,)), ("p_ba", "<f8", (9,)), ("v_bg", "<f8", (9,)), ("v_ba", "<f8", (9,)),
+                          ("dtime", "<f8"), ("dbg", "<f8", (3,)), ("dba", "<f8", (3,)), ("dbg_buf", "<f8", (3,)), ("dba_buf", "<f8", (3,)),
+                          ("cov", "<f8", (225,))])
+imu_noise_dtype = np.dtype([("scale_gravity", "<f8"), ("noise_meas", "<f8", (36,)), ("noise_walk", "<f8", (36,))])
+imu_sample_dtype = np.dtype([("t", "<f8"), ("gyr", "<f8", (3,)), ("acc", "<f8", (3,))])
+imu_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)), ("g", "<f8", (3,))])
+
+
+def imu_noise(cov_gyr, cov_acc, rand_walk_gyr, rand_walk_acc, scale_gravity=1.0):
+    """voxelslam.cpp:934-939: diagonal noiseMeas / noiseWalk."""
+    nz = np.zeros(1, dtype=imu_noise_dtype)
+    nz["scale_gravity"] = scale_gravity
+    nz["noise_meas"][0] = np.diag([cov_gyr] * 3 + [cov_acc] * 3).reshape(-1)
+    nz["noise_walk"][0] = np.diag([rand_walk_gyr] * 3 + [rand_walk_acc] * 3).reshape(-1)
+    return nz
+
+
+def imu_pre_new(samples, noise, bg=(0, 0, 0), ba=(0, 0, 0), lib=None):
+    """IMU_PRE(bg, ba) + push_imu(samples) (preintegration.hpp:32-73); needs no GPU."""
+    lib = lib or load_library()
+    pre = np.zeros(1, dtype=imu_pre_dtype)
+    bg = np.ascontiguousarray(bg, dtype=np.float64); ba = np.ascontiguousarray(ba, dtype=np.float64)
+    _chk(lib.vx_imu_pre_init(_p(pre), _p(bg), _p(ba)))
+    s = np.ascontiguousarray(samples, dtype=imu_sample_dtype)
+    _chk(lib.vx_imu_pre_push(_p(pre), _p(noise), _p(s), C.c_int(s.shape[0])))
+    return pre
+
+
+def imu_pre_evaluate(pre, st1, st2, with_gravity=False, jac=True, lib=None):
+    """give_evaluate / give_evaluate_g (preintegration.hpp:137-294) -> (cost, jtj (nc,nc), gg (nc,))."""
+    lib = lib or load_library()
+    nc = 33 if with_gravity else 30
+    jtj = np.zeros((nc, nc)); gg = np.zeros(nc); cost = np.zeros(1)
+    _chk(lib.vx_imu_pre_evaluate(_p(pre), _p(st1), _p(st2), C.c_int(int(with_gravity)), _p(jtj) if jac else None, _p(gg) if jac else None, _p(cost)))
+    return float(cost[0]), jtj.T.copy(), gg
+
+
 class DevArray:
     """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
 
@@ -328,6 +367,22 @@ class Factor:
                                   _p(conv), _p(trace), _p(nit)))
         return dict(poses=ps, hess=np.transpose(hess, (0, 2, 1)), resis=resis, converged=conv,
                     accept=[trace[w, :nit[w]].tolist() for w in range(self.n_win)])
+
+    def ba_li(self, states, imus, imu_coef=1e-4):
+        """LI_BA_Optimizer::damping_iter (voxel_map.hpp:624-713).  states: (W,) imu_state_dtype; imus: (W-1,) imu_pre_dtype."""
+        x = np.ascontiguousarray(states, dtype=imu_state_dtype).copy(); pr = np.ascontiguousarray(imus, dtype=imu_pre_dtype).copy()
+        n = 15 * self.W
+        hess = np.zeros((n, n)); trace = np.full(3, -1, dtype=np.int32); nit = np.zeros(1, dtype=np.int32)
+        _chk(self.lib.vx_ba_li(self.ctx.h, self.h, _p(x), _p(pr), C.c_double(imu_coef), _p(hess), _p(trace), _p(nit)))
+        return dict(states=x, imus=pr, hess=hess.T.copy(), accept=trace[:nit[0]].tolist())
+
+    def ba_li_gravity(self, states, imus, imu_coef=1e-4, max_iter=2):
+        """LI_BA_OptimizerGravity::damping_iter (voxel_map.hpp:878-975)."""
+        x = np.ascontiguousarray(states, dtype=imu_state_dtype).copy(); pr = np.ascontiguousarray(imus, dtype=imu_pre_dtype).copy()
+        n = 15 * self.W + 3
+        hess = np.zeros((n, n)); trace = np.full(max(max_iter, 1), -1, dtype=np.int32); nit = np.zeros(1, dtype=np.int32); resis = np.zeros(2)
+        _chk(self.lib.vx_ba_li_gravity(self.ctx.h, self.h, _p(x), _p(pr), C.c_double(imu_coef), _p(resis), _p(hess), C.c_int(max_iter), _p(trace), _p(nit)))
+        return dict(states=x, imus=pr, hess=hess.T.copy(), resis=resis, accept=trace[:nit[0]].tolist())
 
     # device-resident path
     def set_poses(self, poses):

@@ -6,6 +6,7 @@
 // windows, voxelslam.cpp:3096): every window keeps its own damping state (u, v), accept/reject
 // sequence and stop test, and each device pass evaluates all windows at once.
 #include "vx_factor.cuh"
+#include "vx_hostmat.hpp"
 #include <cmath>
 #include <limits>
 #include <algorithm>
@@ -29,45 +30,6 @@ void retract_rot(const double *R, const double *w, double *out) {
   }
   for (int c = 0; c < 3; c++)
     for (int r = 0; r < 3; r++) out[c * 3 + r] = R[0 * 3 + r] * E[c * 3 + 0] + R[1 * 3 + r] * E[c * 3 + 1] + R[2 * 3 + r] * E[c * 3 + 2];
-}
-
-// LDL^T with diagonal pivoting on the LOWER triangle (what Eigen's MatrixXd::ldlt() reads, voxel_map.hpp:458;
-// Hess is not exactly symmetric — SURVEY appendix A.7), then solve A x = b.  A is n x n column-major, destroyed.
-void ldlt_lower_solve(double *A, int n, const double *b, double *x, std::vector<int> &tr, std::vector<double> &tmp) {
-  tr.resize(n); tmp.resize(n);
-#define AT(r, c) A[(size_t)(c) * n + (r)]
-  for (int k = 0; k < n; k++) {
-    int big = k; double best = std::fabs(AT(k, k));
-    for (int i = k + 1; i < n; i++) { const double v = std::fabs(AT(i, i)); if (v > best) { best = v; big = i; } }
-    tr[k] = big;
-    if (big != k) {   // symmetric row/column interchange restricted to the lower triangle
-      for (int j = 0; j < k; j++) std::swap(AT(k, j), AT(big, j));
-      for (int i = big + 1; i < n; i++) std::swap(AT(i, k), AT(i, big));
-      std::swap(AT(k, k), AT(big, big));
-      for (int i = k + 1; i < big; i++) std::swap(AT(i, k), AT(big, i));
-    }
-    if (k > 0) {
-      double acc = 0.0;
-      for (int j = 0; j < k; j++) { tmp[j] = AT(j, j) * AT(k, j); acc += AT(k, j) * tmp[j]; }
-      AT(k, k) -= acc;
-      for (int j = 0; j < k; j++) {
-        const double tj = tmp[j];
-        if (tj == 0.0) continue;
-        for (int i = k + 1; i < n; i++) AT(i, k) -= AT(i, j) * tj;
-      }
-    }
-    const double akk = AT(k, k);
-    if (std::fabs(akk) > 0.0)
-      for (int i = k + 1; i < n; i++) AT(i, k) /= akk;
-  }
-  for (int i = 0; i < n; i++) x[i] = b[i];
-  for (int k = 0; k < n; k++) if (tr[k] != k) std::swap(x[k], x[tr[k]]);
-  for (int j = 0; j < n; j++) { const double xj = x[j]; if (xj != 0.0) for (int i = j + 1; i < n; i++) x[i] -= AT(i, j) * xj; }
-  const double tol = 1.0 / std::numeric_limits<double>::max();
-  for (int i = 0; i < n; i++) x[i] = std::fabs(AT(i, i)) > tol ? x[i] / AT(i, i) : 0.0;
-  for (int j = n - 1; j >= 0; j--) { double s = x[j]; for (int i = j + 1; i < n; i++) s -= AT(i, j) * x[i]; x[j] = s; }
-  for (int k = n - 1; k >= 0; k--) if (tr[k] != k) std::swap(x[k], x[tr[k]]);
-#undef AT
 }
 
 }  // namespace
@@ -131,7 +93,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       for (int r = 0; r < jl; r++) D[r] = H[(size_t)r * jl + r];
       std::copy(H, H + hsz, A.begin());
       for (int r = 0; r < jl; r++) { A[(size_t)r * jl + r] += u[w] * D[r]; nb[r] = -J[r]; }
-      ldlt_lower_solve(A.data(), jl, nb.data(), dxi.data(), tr, tmp);
+      hm::ldlt_lower_solve(A.data(), jl, nb.data(), dxi.data(), tr, tmp);
       for (int j = 0; j < W; j++) {
         const vx_pose &s = x[(size_t)w * W + j];
         vx_pose &d = xt[(size_t)w * W + j];
