@@ -279,6 +279,19 @@ int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *p
 int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy,
                             int32_t *iters, int32_t *match_nums4);
 
+/* ---- A5: calcBodyVar voxelslam.hpp:180-200, var_init :210-234, pvec_update :242-265.
+ * vx_var_init: per-point 3x3 measurement covariance from range (dept_err) and bearing (beam_err, degrees) noise, point and
+ * covariance rotated by the extrinsic `ext`; float xyz triples in (12 B/point), vx_point_var out (96 B/point).
+ * vx_pvec_update: var <- R var R^T + hat(p) rot_var hat(p)^T + tsl_var and pwld = R p + t (pwld may be NULL); pv_out may be
+ * pv_in.  rot_var / tsl_var: x_curr.cov blocks (0,0) and (3,3), column-major. */
+int vx_var_init(vx_ctx *ctx, const float *xyz, int64_t n, const vx_pose *ext, double dept_err, double beam_err, vx_point_var *out);
+int vx_pvec_update(vx_ctx *ctx, const vx_point_var *pv_in, int64_t n, const vx_pose *x, const double *rot_var9, const double *tsl_var9,
+                   vx_point_var *pv_out, double *pwld);
+/* lio_state_estimation fed with the raw scan: xyz is uploaded (12 B/point instead of 96), var_init runs on the device
+ * (voxelslam.cpp:1880-1890 call order: var_init(extrin_para, pl, pptr, dept_err, beam_err) then lio_state_estimation(pptr)). */
+int vx_lio_state_estimation_xyz(vx_ctx *ctx, vx_planemap *map, const float *xyz, int64_t n, const vx_pose *ext, double dept_err,
+                                double beam_err, vx_lio_state *x, int32_t *healthy, int32_t *iters, int32_t *match_nums4);
+
 #ifdef __cplusplus
 }
 #endif

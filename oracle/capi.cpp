@@ -364,6 +364,24 @@ void orc_var_init(const float *xyz, int n, double dept_err, double beam_err, dou
   var_init(ext, pl, pvec, dept_err, beam_err);
   for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) pv_out[12 * i + k] = pvec[i].pnt[k]; for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = pvec[i].var[k]; }
 }
+void orc_var_init_ext(const float *xyz, int n, const oc_pose *ext_pose, double dept_err, double beam_err, double *pv_out) {
+  std::vector<PointXYZIN> pl(n);
+  for (int i = 0; i < n; i++) { std::memset(&pl[i], 0, sizeof(PointXYZIN)); pl[i].x = xyz[3 * i]; pl[i].y = xyz[3 * i + 1]; pl[i].z = xyz[3 * i + 2]; }
+  IMUST ext = poses_in(ext_pose, 1)[0]; PVec pvec;
+  var_init(ext, pl, pvec, dept_err, beam_err);
+  for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) pv_out[12 * i + k] = pvec[i].pnt[k]; for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = pvec[i].var[k]; }
+}
+void orc_pvec_update(const double *pv, int n, const oc_pose *pose, const double *cov225, double *pv_out, double *pwld) {
+  PVec pvec = pvec_in(pv, n);
+  IMUST x = state_in(pose, cov225);
+  std::vector<V3> w;
+  pvec_update(pvec, x, w);
+  for (int i = 0; i < n; i++) {
+    for (int k = 0; k < 3; k++) pv_out[12 * i + k] = pvec[i].pnt[k];
+    for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = pvec[i].var[k];
+    for (int k = 0; k < 3; k++) pwld[3 * i + k] = w[i][k];
+  }
+}
 // one pass (voxelslam.cpp:1005-1050); leaf cache in/out as indices into the last export (-1 = none)
 void orc_lio_pass(void *h, const double *pv, int n, const oc_pose *pose, const double *cov225, int32_t *leaf_cache, double *HTH36, double *HTz6,
                   double *nnt9, int *match_num, int32_t *flags) {

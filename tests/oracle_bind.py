@@ -281,6 +281,20 @@ def var_init(xyz, dept_err, beam_err):
     return out
 
 
+def var_init_ext(xyz, pose, dept_err, beam_err):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+    out = np.zeros((xyz.shape[0], 12))
+    lib().orc_var_init_ext(_p(xyz), C.c_int(xyz.shape[0]), _p(as_poses(pose)), C.c_double(dept_err), C.c_double(beam_err), _p(out))
+    return out
+
+
+def pvec_update(pv, pose, cov):
+    pv = np.ascontiguousarray(pv, dtype=np.float64)
+    out = np.zeros_like(pv); pw = np.zeros((pv.shape[0], 3))
+    lib().orc_pvec_update(_p(pv), C.c_int(pv.shape[0]), _p(as_poses(pose)), _p(np.ascontiguousarray(cov.T)), _p(out), _p(pw))
+    return out, pw
+
+
 def default_cov():
     """IMUST::setZero covariance (tools.hpp:188-197)."""
     cov = np.eye(15) * 0.0001

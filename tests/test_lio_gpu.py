@@ -83,3 +83,57 @@ def test_lio_state_estimation_parity(pkg, ob, ctx, world, rot_deg, tra):
     assert rel(out["cov"], ref["cov"]) < 1e-9
     assert np.max(np.abs(out["p"] - pt)) < 0.2 * np.max(np.abs(p0[0] - pt))     # the update converged toward the planted truth
     gm.free()
+
+
+# ---- A5: calcBodyVar / var_init / pvec_update on the device (voxelslam.hpp:180-265) ----------------------------
+def _raw_scan(seed, n=20000):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    q = scene.scan(scene.room(), np.eye(3), np.array([-7.0, 0.5, 1.2]), scene.xt32_dirs(700), rng, range_noise=0.01, blind=0.7)[:n].astype(np.float32)
+    q[5, 2] = 0.0; q[17, 2] = -0.0          # calcBodyVar's pb[2] == 0 patch (:182-183) changes the stored point too
+    return q
+
+
+@pytest.mark.parametrize("dept,beam", [(0.01, 0.01), (0.02, 0.05)])
+def test_var_init_parity(pkg, ob, ctx, dept, beam):
+    q = _raw_scan(41)
+    ext = synth.random_poses(8, 1, rot_sigma=0.05, tra_sigma=0.1)
+    ref = ob.var_init_ext(q, ext, dept, beam)
+    out = pkg.var_init(ctx, q, ext, dept, beam)
+    assert np.abs(out[:, :3] - ref[:, :3]).max() <= 1e-14 * np.abs(ref[:, :3]).max()
+    scale = np.abs(ref[:, 3:]).max(axis=1, keepdims=True)
+    assert (np.abs(out[:, 3:] - ref[:, 3:]) <= 1e-12 * scale).all()
+    ident = ob.var_init(q, dept, beam)      # the identity-extrinsic entry the map tests use
+    out_i = pkg.var_init(ctx, q, (np.eye(3)[None], np.zeros((1, 3))), dept, beam)
+    assert (np.abs(out_i - ident) <= 1e-12 * np.maximum(np.abs(ident).max(axis=1, keepdims=True), 1e-300)).all()
+    assert out_i[5, 2] == 0.0001 and out_i[17, 2] == 0.0001
+    assert pkg.var_init(ctx, q[:0], ext, dept, beam).shape == (0, 12)
+
+
+def test_pvec_update_parity(pkg, ob, ctx):
+    q = _raw_scan(42, n=7001)               # ragged last block
+    pv = ob.var_init(q, 0.01, 0.01)
+    pose = synth.random_poses(9, 1, rot_sigma=0.4, tra_sigma=3.0)
+    rng = np.random.Generator(np.random.PCG64(3))
+    A = rng.normal(size=(15, 15)); cov = A @ A.T * 1e-4
+    ref, ref_w = ob.pvec_update(pv, pose, cov)
+    out, out_w = pkg.pvec_update(ctx, pv, pose, cov)
+    assert (out[:, :3] == ref[:, :3]).all()                                   # pnt is carried through untouched
+    scale = np.abs(ref[:, 3:]).max(axis=1, keepdims=True)
+    assert (np.abs(out[:, 3:] - ref[:, 3:]) <= 1e-12 * scale).all()
+    assert np.abs(out_w - ref_w).max() <= 1e-14 * np.abs(ref_w).max()
+
+
+def test_lio_state_estimation_from_raw_scan(pkg, ob, ctx, world):
+    # 12 B/point upload + var_init on the device == host var_init + 96 B/point upload (same association, same state)
+    keys, rn, nodes = world["export"]
+    gm = pkg.PlaneMap(ctx, keys, rn, nodes, 1.0)
+    rng = np.random.Generator(np.random.PCG64(77))
+    Rt, pt = world["truth"]
+    q = scene.scan(scene.room(), Rt, pt, scene.xt32_dirs(1000), rng, range_noise=0.01, blind=0.7).astype(np.float32)
+    R0, p0 = synth.perturb_poses((Rt[None], pt[None]), 9, np.deg2rad(0.3), 0.03, fix_first=False)
+    cov = ob.default_cov()
+    ref = world["map"].lio_state_estimation(ob.var_init(q, 0.01, 0.01), R0[0], p0[0], cov)
+    out = gm.lio_state_estimation(q, R0[0], p0[0], cov, xyz_ext=((np.eye(3)[None], np.zeros((1, 3))), 0.01, 0.01))
+    assert out["iters"] == ref["iters"] and out["match_nums"] == ref["match_nums"] and out["ok"] == ref["ok"]
+    assert np.max(np.abs(out["R"] - ref["R"])) < 1e-10 and np.max(np.abs(out["p"] - ref["p"])) < 1e-10
+    gm.free()

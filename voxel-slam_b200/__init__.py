@@ -177,6 +177,24 @@ lio_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8",
 assert map_node_dtype.itemsize == 408 and lio_state_dtype.itemsize == 8 * (21 + 225)
 
 
+def var_init(ctx, xyz, ext, dept_err, beam_err):
+    """calcBodyVar + var_init (voxelslam.hpp:180-234) on the device -> (n,12): pnt 3 + var 9 (col-major)."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32); n = xyz.shape[0]
+    out = np.zeros((n, 12))
+    _chk(ctx.lib.vx_var_init(ctx.h, _p(xyz), C.c_int64(n), _p(as_poses(ext)), C.c_double(dept_err), C.c_double(beam_err), _p(out)))
+    return out
+
+
+def pvec_update(ctx, pv, pose, cov):
+    """pvec_update (voxelslam.hpp:242-265) -> (pv_out (n,12), pwld (n,3)).  cov: 15x15 state covariance."""
+    pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+    cov = np.asarray(cov, dtype=np.float64)
+    rv = np.ascontiguousarray(cov[0:3, 0:3].T); tv = np.ascontiguousarray(cov[3:6, 3:6].T)
+    out = np.zeros((n, 12)); pw = np.zeros((n, 3))
+    _chk(ctx.lib.vx_pvec_update(ctx.h, _p(pv), C.c_int64(n), _p(as_poses(pose)), _p(rv), _p(tv), _p(out), _p(pw)))
+    return out, pw
+
+
 class PlaneMap:
     """Flattened OctoTree voxel map on the device (what OctoTree::match reads, voxel_map.hpp:1649-1721)."""
 
@@ -203,9 +221,14 @@ class PlaneMap:
                                               C.byref(mn), _p(fl)))
         return dict(HTH=HTH.T.copy(), HTz=HTz, nnt=nnt.T.copy(), match_num=mn.value, flags=fl, leaf_cache=lc)
 
-    def lio_state_estimation(self, pv, R, p, cov, v=None, bg=None, ba=None):
-        """VOXEL_SLAM::lio_state_estimation (voxelslam.cpp:962-1098)."""
-        pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]
+    def lio_state_estimation(self, pv, R, p, cov, v=None, bg=None, ba=None, xyz_ext=None):
+        """VOXEL_SLAM::lio_state_estimation (voxelslam.cpp:962-1098).  xyz_ext=(ext_pose, dept_err, beam_err): `pv` is the raw
+        (n,3) float scan and var_init runs on the device (vx_lio_state_estimation_xyz)."""
+        if xyz_ext is None:
+            pv = np.ascontiguousarray(pv, dtype=np.float64)
+        else:
+            pv = np.ascontiguousarray(pv, dtype=np.float32)
+        n = pv.shape[0]
         st = np.zeros(1, dtype=lio_state_dtype)
         st["R"] = np.asarray(R, dtype=np.float64).T.reshape(9); st["p"] = p
         if v is not None: st["v"] = v
@@ -213,7 +236,12 @@ class PlaneMap:
         if ba is not None: st["ba"] = ba
         st["cov"] = np.asarray(cov, dtype=np.float64).T.reshape(225)
         ok = C.c_int32(0); it = C.c_int32(0); mn = np.zeros(4, dtype=np.int32)
-        _chk(self.lib.vx_lio_state_estimation(self.ctx.h, self.h, _p(pv), C.c_int64(n), _p(st), C.byref(ok), C.byref(it), _p(mn)))
+        if xyz_ext is None:
+            _chk(self.lib.vx_lio_state_estimation(self.ctx.h, self.h, _p(pv), C.c_int64(n), _p(st), C.byref(ok), C.byref(it), _p(mn)))
+        else:
+            ext = as_poses(xyz_ext[0])
+            _chk(self.lib.vx_lio_state_estimation_xyz(self.ctx.h, self.h, _p(pv), C.c_int64(n), _p(ext), C.c_double(xyz_ext[1]),
+                                                      C.c_double(xyz_ext[2]), _p(st), C.byref(ok), C.byref(it), _p(mn)))
         s = st[0]
         return dict(ok=bool(ok.value), R=s["R"].reshape(3, 3).T.copy(), p=s["p"].copy(), v=s["v"].copy(), bg=s["bg"].copy(), ba=s["ba"].copy(),
                     cov=s["cov"].reshape(15, 15).T.copy(), iters=it.value, match_nums=mn[:it.value].tolist())

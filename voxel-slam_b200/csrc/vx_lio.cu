@@ -10,6 +10,7 @@
 // so point->plane association is bit-exact; only the sums over points are re-ordered.
 #include "vx_common.cuh"
 #include "vx_voxelize.cuh"
+#include "vx_frontend.cuh"
 #include <cmath>
 #include <algorithm>
 
@@ -397,17 +398,26 @@ int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *p
   return VX_OK;
 }
 
-int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy, int32_t *iters,
-                            int32_t *match_nums4) {
-  VX_ARG(map != nullptr && x != nullptr && n >= 0 && (n == 0 || pts));
+}  // extern "C"
+
+namespace {
+// pts != NULL: points with covariances from the host; else raw xyz + var_init on the device
+int lio_state_estimation_impl(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, const float *xyz, const vx_pose *ext, double dept_err,
+                              double beam_err, int64_t n, vx_lio_state *x, int32_t *healthy, int32_t *iters, int32_t *match_nums4) {
+  VX_ARG(map != nullptr && x != nullptr && n >= 0 && (n == 0 || pts || (xyz && ext)));
   VX_TRY(bind(ctx));
-  DevBuf d_pts, d_cache;
+  DevBuf d_pts, d_cache, d_xyz;
   int rc = VX_OK;
   double nnt[9] = {0};
   int n_it = 0;
   auto body = [&]() -> int {
     VX_TRY(d_pts.reserve(sizeof(vx_point_var) * std::max<int64_t>(n, 1))); VX_TRY(d_cache.reserve(4 * std::max<int64_t>(n, 1)));
-    if (n) VX_CUDA(cudaMemcpyAsync(d_pts.p, pts, sizeof(vx_point_var) * n, cudaMemcpyHostToDevice, ctx->stream));
+    if (n && pts) VX_CUDA(cudaMemcpyAsync(d_pts.p, pts, sizeof(vx_point_var) * n, cudaMemcpyHostToDevice, ctx->stream));
+    if (n && !pts) {
+      VX_TRY(d_xyz.reserve(sizeof(float) * 3 * n));
+      VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, ctx->stream));
+      VX_TRY(var_init_device(ctx, d_xyz.as<float>(), n, *ext, dept_err, beam_err, d_pts.as<vx_point_var>()));
+    }
     VX_CUDA(cudaMemsetAsync(d_cache.p, 0xff, 4 * std::max<int64_t>(n, 1), ctx->stream));
     const vx_lio_state x_prop = *x;
     const int num_max_iter = 4;   // voxelslam.cpp:968
@@ -471,11 +481,26 @@ int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *p
   };
   rc = body();
   cudaStreamSynchronize(ctx->stream);
-  d_pts.release(); d_cache.release();
+  d_pts.release(); d_cache.release(); d_xyz.release();
   VX_TRY(rc);
   if (iters) *iters = n_it;
   if (healthy) *healthy = !(min_eig3(nnt) < 14) ? 1 : 0;   // voxelslam.cpp:1090-1097
   return VX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy, int32_t *iters,
+                            int32_t *match_nums4) {
+  VX_ARG(n == 0 || pts);
+  return lio_state_estimation_impl(ctx, map, pts, nullptr, nullptr, 0, 0, n, x, healthy, iters, match_nums4);
+}
+
+int vx_lio_state_estimation_xyz(vx_ctx *ctx, vx_planemap *map, const float *xyz, int64_t n, const vx_pose *ext, double dept_err, double beam_err,
+                                vx_lio_state *x, int32_t *healthy, int32_t *iters, int32_t *match_nums4) {
+  VX_ARG(ext != nullptr && (n == 0 || xyz));
+  return lio_state_estimation_impl(ctx, map, nullptr, xyz, ext, dept_err, beam_err, n, x, healthy, iters, match_nums4);
 }
 
 }  // extern "C"
