@@ -54,6 +54,8 @@ typedef struct vx_point48 {
   float normal_x, normal_y, normal_z, _p1;
   float intensity, curvature, _p2, _p3;
 } vx_point48;
+/* struct pointVar  voxel_map.hpp:18-34: point + 3x3 covariance (column-major) */
+typedef struct vx_point_var { double pnt[3]; double var[9]; } vx_point_var;
 
 /* ---- context ------------------------------------------------------------------------------ */
 int vx_ctx_create(int device, vx_ctx **out);
@@ -141,6 +143,13 @@ int vx_keys(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_f
  * mean is replayed exactly (bit-identical x,y,z and curvature = count; other fields of the cell's first
  * point kept); cells come out in ascending packed-key order (the reference: unordered_map order). */
 int vx_downsample_voxel(vx_ctx *ctx, const vx_point48 *pts, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n);
+/* A4 down_sampling_close(pl, voxel_size)  tools.hpp:240-302: per cell the float centroid (sequential sums), then the INPUT
+ * point nearest to it is kept whole (timestamps in `curvature` survive for de-skew).  Same ordering note as above. */
+int vx_downsample_close(vx_ctx *ctx, const vx_point48 *pts, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n);
+/* A3 down_sampling_pvec(pvec, voxel_size, pl_keep)  voxel_map.hpp:39-81: cells keyed on the DOUBLE point, running double mean
+ * (x*c + p)/(c+1) of point and covariance; out = centroid as float xyz, diag(var) in normal_xyz, other fields as a
+ * default-constructed pcl::PointXYZINormal (data[3] = 1, rest 0). */
+int vx_downsample_pvec(vx_ctx *ctx, const vx_point_var *pvec, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n);
 
 /* ---- A8 + A10: OctreeGBA::cut_voxel per keyframe (loop_refine.hpp:446-479) + OctreeGBA_multi_recut
  * (loop_refine.hpp:483-537) -> LidarFactor, as HBA_add_edge does at voxelslam.cpp:2887-2892.
@@ -260,7 +269,6 @@ typedef struct vx_map_node {
 } vx_map_node;
 typedef struct vx_planemap vx_planemap;
 /* struct pointVar {Vector3d pnt; Matrix3d var;}  voxel_map.hpp:18-34 (var column-major) */
-typedef struct vx_point_var { double pnt[3]; double var[9]; } vx_point_var;
 /* the part of IMUST the update touches (tools.hpp:135-199): R, p, v, bg, ba and the 15x15 covariance, column-major */
 typedef struct vx_lio_state { double R[9], p[3], v[3], bg[3], ba[3], cov[225]; } vx_lio_state;
 

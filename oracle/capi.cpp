@@ -174,6 +174,20 @@ int orc_ba_lidar(void *h, oc_pose *poses, double *hess_out, double *resis2, int 
 }
 
 // ---- A2 ------------------------------------------------------------------------------------
+int64_t orc_downsample_close(const PointXYZIN *pts, int64_t n, double voxel_size, PointXYZIN *out) {
+  std::vector<PointXYZIN> pl(pts, pts + n);
+  down_sampling_close(pl, voxel_size);
+  std::copy(pl.begin(), pl.end(), out);
+  return (int64_t)pl.size();
+}
+int64_t orc_downsample_pvec(const double *pv, int64_t n, double voxel_size, PointXYZIN *out) {
+  PVec pvec(n);
+  for (int64_t i = 0; i < n; i++) { for (int k = 0; k < 3; k++) pvec[i].pnt[k] = pv[12 * i + k]; for (int k = 0; k < 9; k++) pvec[i].var[k] = pv[12 * i + 3 + k]; }
+  std::vector<PointXYZIN> keep;
+  down_sampling_pvec(pvec, voxel_size, keep);
+  std::copy(keep.begin(), keep.end(), out);
+  return (int64_t)keep.size();
+}
 int64_t orc_downsample_voxel(const PointXYZIN *pts, int64_t n, double voxel_size, PointXYZIN *out) {
   std::vector<PointXYZIN> pl(pts, pts + n);
   down_sampling_voxel(pl, voxel_size);

@@ -500,6 +500,7 @@ inline void down_sampling_pvec(PVec &pvec, double voxel_size, std::vector<PointX
   pl_keep.reserve(feat_map.size());
   PointXYZIN ap;
   std::memset(&ap, 0, sizeof(ap));
+  (&ap.x)[3] = 1.0f;   // pcl::PointXYZINormal() (PCL 1.10 point_types.hpp) sets data[3] = 1
   for (auto iter = feat_map.begin(); iter != feat_map.end(); ++iter) {
     pointVar &pv = iter->second.first;
     ap.x = (float)pv.pnt[0]; ap.y = (float)pv.pnt[1]; ap.z = (float)pv.pnt[2];

@@ -128,6 +128,22 @@ def downsample_voxel(pts, voxel_size):
     return out[:n]
 
 
+def downsample_close(pts, voxel_size):
+    pts = np.ascontiguousarray(pts, dtype=point48_dtype)
+    out = np.zeros(pts.shape[0], dtype=point48_dtype)
+    lib().orc_downsample_close.restype = C.c_int64
+    n = lib().orc_downsample_close(_p(pts), C.c_int64(pts.shape[0]), C.c_double(voxel_size), _p(out))
+    return out[:n]
+
+
+def downsample_pvec(pv, voxel_size):
+    pv = np.ascontiguousarray(pv, dtype=np.float64)
+    out = np.zeros(pv.shape[0], dtype=point48_dtype)
+    lib().orc_downsample_pvec.restype = C.c_int64
+    n = lib().orc_downsample_pvec(_p(pv), C.c_int64(pv.shape[0]), C.c_double(voxel_size), _p(out))
+    return out[:n]
+
+
 def gba_build(clouds, poses, gba_voxel_size, gba_min_eigen_value, eig_array, max_layer):
     """clouds: list of (n_i,3) float32 local-frame clouds, one per keyframe -> orc LidarFactor (A8 + A10)."""
     W = len(clouds)

@@ -66,6 +66,43 @@ def test_downsample_small_voxel_is_identity(pkg, ob, ctx):
     assert np.array_equal(out, pts)
 
 
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.mark.parametrize("n,vs", [(1, 0.1), (5000, 0.1), (60000, 0.2), (24000, 0.5)])
+def test_downsample_close(pkg, ob, ctx, n, vs):
+    # A4 (tools.hpp:240-302): the kept record is an INPUT point, so compare whole 48-byte records as sets
+    rng = np.random.Generator(np.random.PCG64(100 + n))
+    pts = np.zeros(n, dtype=ob.point48_dtype)
+    pts["x"] = rng.uniform(-8, 8, n); pts["y"] = rng.uniform(-6, 6, n); pts["z"] = rng.normal(0, 0.05, n)
+    pts["intensity"] = rng.uniform(0, 255, n); pts["curvature"] = np.arange(n) * 1e-5          # per-point timestamp
+    ref = ob.downsample_close(pts, vs)
+    out = pkg.downsample_close(ctx, pts, vs)
+    assert out.shape == ref.shape
+    key = lambda a: np.argsort(a["curvature"], kind="stable")
+    assert np.array_equal(out[key(out)].view(np.uint8), ref[key(ref)].view(np.uint8))
+    assert np.array_equal(pkg.downsample_close(ctx, pts, 0.0005), pts)                          # tools.hpp:242
+    assert pkg.downsample_close(ctx, pts[:0], vs).shape == (0,)
+
+
+@pytest.mark.parametrize("n,vs", [(1, 0.05), (7000, 0.05), (64000, 0.1)])
+def test_downsample_pvec(pkg, ob, ctx, n, vs):
+    # A3 (voxel_map.hpp:39-81): double running means, bit-identical after the float cast; order differs (sorted by cell)
+    rng = np.random.Generator(np.random.PCG64(200 + n))
+    pv = np.zeros((n, 12))
+    pv[:, 0] = rng.uniform(-8, 8, n); pv[:, 1] = rng.uniform(-6, 6, n); pv[:, 2] = rng.normal(0, 0.05, n)
+    A = rng.normal(0, 0.01, (n, 3, 3)); pv[:, 3:] = (A @ np.transpose(A, (0, 2, 1))).reshape(n, 9)
+    ref = ob.downsample_pvec(pv, vs)
+    out = pkg.downsample_pvec(ctx, pv, vs)
+    assert out.shape == ref.shape
+    key = lambda a: np.lexsort((a["z"], a["y"], a["x"]))
+    r = ref[key(ref)]; o = out[key(out)]
+    for fld in ("x", "y", "z", "normal_x", "normal_y", "normal_z", "_p0", "intensity", "curvature"):
+        assert np.array_equal(_bits(o[fld]), _bits(r[fld])), fld
+    assert pkg.downsample_pvec(ctx, pv[:0], vs).shape == (0,)
+
+
 def canon(fac, W):
     """order voxels by merged centroid (unique per voxel) and expand to dense (V, W) N / moments"""
     m = fac["merged"]

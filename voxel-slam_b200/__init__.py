@@ -144,6 +144,24 @@ def downsample_voxel(ctx, pts, voxel_size):
     return out[:n.value]
 
 
+def downsample_close(ctx, pts, voxel_size):
+    """A4: down_sampling_close (tools.hpp:240-302); cells in ascending packed-key order."""
+    pts = np.ascontiguousarray(pts, dtype=point48_dtype)
+    out = np.zeros(pts.shape[0], dtype=point48_dtype)
+    n = C.c_int64(0)
+    _chk(ctx.lib.vx_downsample_close(ctx.h, _p(pts), C.c_int64(pts.shape[0]), C.c_double(voxel_size), _p(out), C.byref(n)))
+    return out[:n.value]
+
+
+def downsample_pvec(ctx, pv, voxel_size):
+    """A3: down_sampling_pvec (voxel_map.hpp:39-81); pv (n,12) pointVar rows; cells in ascending packed-key order."""
+    pv = np.ascontiguousarray(pv, dtype=np.float64)
+    out = np.zeros(pv.shape[0], dtype=point48_dtype)
+    n = C.c_int64(0)
+    _chk(ctx.lib.vx_downsample_pvec(ctx.h, _p(pv), C.c_int64(pv.shape[0]), C.c_double(voxel_size), _p(out), C.byref(n)))
+    return out[:n.value]
+
+
 hba_params_dtype = np.dtype([("gba", gba_params_dtype), ("voxel_size", "<f8"), ("min_eigen_value", "<f8"), ("plane_eigen_value_thre", "<f8", (4,))])
 edge_dtype = np.dtype([("m1", "<i4"), ("m2", "<i4"), ("id1", "<i4"), ("id2", "<i4"), ("rot", "<f8", (9,)), ("tra", "<f8", (3,)), ("cov", "<f8", (6,))])
 assert hba_params_dtype.itemsize == 104 and edge_dtype.itemsize == 160
