@@ -287,6 +287,55 @@ int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *p
 int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy,
                             int32_t *iters, int32_t *match_nums4);
 
+/* ---- A6 / A7 / A9 / A11 / A12: the sliding-window voxel map on the device ------------------------------------------
+ * class OctoTree voxel_map.hpp:1047-1881, class SlideWindow :1009-1042, cut_voxel / cut_voxel_multi :1896-2096,
+ * cut_voxel (fixed points) :2108-2152, drivers multi_recut voxelslam.cpp:1682-1737 and multi_margi :1590-1679.
+ * The map lives in HBM as a node table (the vx_map_node match view + moments, 9x9 cov_add, per-slot clusters) under a
+ * root-voxel hash; the window's raw points stay in per-slot scan buffers with one leaf id per point, so "subdivide" is a
+ * re-labelling + segmented sum instead of list surgery.  The reference's globals (voxel_map.hpp:98-104, `mp` :1046) are
+ * fields of vx_map_params / internal state. */
+typedef struct vx_map vx_map;
+typedef struct vx_map_params {
+  double voxel_size, min_eigen_value;
+  double plane_eigen_value_thre[4];   /* stored inverted, voxelslam.cpp:930-931 */
+  double min_point[4];                /* voxelslam.cpp:917 */
+  int32_t max_layer, max_points;      /* voxel_map.hpp:98-104 */
+  int32_t win_size, thread_num;       /* thread_num only reproduces the "fewer roots than threads" early-outs */
+} vx_map_params;
+/* inspection record, one per node (tests / debugging); keyed by (root cell, layer, path), path = 3 bits per level */
+typedef struct vx_map_node_state {
+  int64_t root_key[3];
+  int32_t layer, path, octo_state, isexist, has_sw, is_plane, last_num, opt_state, in_slide, n_window_pts, n_fix_pts, _pad;
+  vx_cluster pcr_add, pcr_fix;
+  double eig_value[3];
+  double cov_add_trace;
+} vx_map_node_state;
+
+int vx_map_create(vx_ctx *ctx, const vx_map_params *params, vx_map **out);
+int vx_map_free(vx_map *map);
+/* cut_voxel_multi(surf_map, pvec, win_count, surf_map_slide, win_size, pwld, sws)  voxel_map.hpp:1964-2096.
+ * pvec[i].pnt is in the scan-local frame, pvec[i].var the world covariance (after pvec_update), pwld the world points;
+ * `ord` = the frame's position in the window (win_count - 1).  Keeps the ":2044-2045" quirk: when the scan touches fewer
+ * root voxels than thread_num the roots are created / marked but no point is inserted. */
+int vx_map_cut_voxel(vx_ctx *ctx, vx_map *map, const vx_point_var *pvec, const double *pwld, int64_t n, int ord);
+/* cut_voxel(feat_map, pvec, wdsize, jour)  voxel_map.hpp:2108-2152: already-world-frame points into pcr_fix / pcr_add only */
+int vx_map_cut_voxel_fix(vx_ctx *ctx, vx_map *map, const vx_point_var *pvec, int64_t n, double jour);
+/* multi_recut(surf_map_slide, win_count, x_buf, voxhess, sws)  voxelslam.cpp:1682-1737: OctoTree::recut on every root of the
+ * slide set (eigen-solve, plane test, subdivision with the CURRENT poses), then tras_opt: the LidarFactor of all live
+ * plane leaves is written into `f` on the device (f: win_size frames, single window).  poses: win_count entries. */
+int vx_map_recut(vx_ctx *ctx, vx_map *map, const vx_pose *poses, int win_count, vx_factor *f);
+/* multi_margi(surf_map_slide, jour, win_count, x_buf, voxhess, sws[0])  voxelslam.cpp:1590-1679 with mgsize frames folded
+ * into pcr_fix; reads the optimizer cache of `f` (voxel_map.hpp:1495-1501); erases dead roots from the slide set.
+ * VX_ERR_OPT_STATE where the reference prints and exits (voxel_map.hpp:1488-1492). */
+int vx_map_margi(vx_ctx *ctx, vx_map *map, const vx_pose *poses, int win_count, int mgsize, vx_factor *f, double jour);
+/* the `mp` ring rotation of voxelslam.cpp:2014-2019 */
+int vx_map_shift_window(vx_map *map, int mgsize);
+/* non-owning match view for vx_lio_* (valid until the next map-mutating call) */
+int vx_map_planemap(vx_map *map, vx_planemap **view);
+int64_t vx_map_num_nodes(const vx_map *map);
+int64_t vx_map_num_roots(const vx_map *map);
+int vx_map_export(vx_map *map, vx_map_node_state *states, vx_map_node *nodes);   /* num_nodes records each; either may be NULL */
+
 /* ---- A5: calcBodyVar voxelslam.hpp:180-200, var_init :210-234, pvec_update :242-265.
  * vx_var_init: per-point 3x3 measurement covariance from range (dept_err) and bearing (beam_err, degrees) noise, point and
  * covariance rotated by the extrinsic `ext`; float xyz triples in (12 B/point), vx_point_var out (96 B/point).

@@ -277,6 +277,11 @@ void *orc_local_create(int win_size, double voxel_size, double min_eigen_value, 
   s->voxhess.win_size = win_size;
   return s;
 }
+static PVec pvec_in(const double *pv, int n) {
+  PVec v(n);
+  for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) v[i].pnt[k] = pv[12 * i + k]; for (int k = 0; k < 9; k++) v[i].var[k] = pv[12 * i + 3 + k]; }
+  return v;
+}
 static IMUST state_in(const oc_pose *pose, const double *cov225) {
   IMUST x;
   for (int k = 0; k < 9; k++) x.R[k] = pose->R[k];
@@ -285,8 +290,9 @@ static IMUST state_in(const oc_pose *pose, const double *cov225) {
   return x;
 }
 // points: float xyz in the body frame (extrinsic = identity).  Returns the pointVar records (pnt body frame,
-// var AFTER pvec_update = world-frame covariance, voxelslam.hpp:242-265) when pv_out != null.
-void orc_local_push(void *h, const float *xyz, int n, const oc_pose *pose, const double *cov225, double *pv_out /* n x 12 */) {
+// var AFTER pvec_update = world-frame covariance, voxelslam.hpp:242-265) when pv_out != null, the world points when pw_out != null.
+// voxelslam.cpp:1905-1917: window bookkeeping + voxhess.clear() + cut_voxel_multi
+void orc_local_insert(void *h, const float *xyz, int n, const oc_pose *pose, const double *cov225, double *pv_out /* n x 12 */, double *pw_out /* n x 3 */) {
   LocalSession &S = *(LocalSession *)h;
   std::vector<PointXYZIN> pl(n);
   for (int i = 0; i < n; i++) { std::memset(&pl[i], 0, sizeof(PointXYZIN)); pl[i].x = xyz[3 * i]; pl[i].y = xyz[3 * i + 1]; pl[i].z = xyz[3 * i + 2]; }
@@ -296,26 +302,53 @@ void orc_local_push(void *h, const float *xyz, int n, const oc_pose *pose, const
   IMUST x_curr = state_in(pose, cov225);
   std::vector<V3> pwld;
   pvec_update(*pptr, x_curr, pwld);
-  if (pv_out)
-    for (int i = 0; i < n; i++) {
-      for (int k = 0; k < 3; k++) pv_out[12 * i + k] = (*pptr)[i].pnt[k];
-      for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = (*pptr)[i].var[k];
-    }
+  for (int i = 0; i < n; i++) {
+    if (pv_out) { for (int k = 0; k < 3; k++) pv_out[12 * i + k] = (*pptr)[i].pnt[k]; for (int k = 0; k < 9; k++) pv_out[12 * i + 3 + k] = (*pptr)[i].var[k]; }
+    if (pw_out) for (int k = 0; k < 3; k++) pw_out[3 * i + k] = pwld[i][k];
+  }
   S.win_count++;
   S.x_buf.push_back(x_curr);
   S.pvec_buf.push_back(pptr);
   S.voxhess.clear();
   S.voxhess.win_size = S.win_size;
   cut_voxel_multi(S.surf_map, *S.pvec_buf[S.win_count - 1], S.win_count - 1, S.surf_map_slide, S.win_size, pwld, S.sws, &S.ctx);
+}
+void orc_local_recut(void *h) {   // voxelslam.cpp:1919
+  LocalSession &S = *(LocalSession *)h;
   multi_recut(S.surf_map_slide, S.win_count, S.x_buf, S.voxhess, S.sws, S.thread_num);
-  if (S.win_count >= S.win_size) {
-    const int mgsize = 1;
-    multi_margi(S.surf_map_slide, S.jour, S.win_count, S.x_buf, S.voxhess, S.sws[0], S.thread_num);
-    for (int i = 0; i < S.win_size; i++) { S.ctx.mp[i] += mgsize; if (S.ctx.mp[i] >= S.win_size) S.ctx.mp[i] -= S.win_size; }
-    for (int i = mgsize; i < S.win_count; i++) { S.x_buf[i - mgsize] = S.x_buf[i]; std::swap(S.pvec_buf[i - mgsize], S.pvec_buf[i]); }
-    for (int i = S.win_count - mgsize; i < S.win_count; i++) { S.x_buf.pop_back(); S.pvec_buf.pop_back(); }
-    S.win_count -= mgsize;
-  }
+}
+// voxelslam.cpp:1966-2040 without the optimizer: multi_margi, mp rotation, buffer shift.  Returns 1 when the window was full,
+// -1 where the reference prints "Error: opt_state" and exits.
+int orc_local_margi(void *h) {
+  LocalSession &S = *(LocalSession *)h;
+  if (S.win_count < S.win_size) return 0;
+  const int mgsize = 1;
+  bool ok = multi_margi(S.surf_map_slide, S.jour, S.win_count, S.x_buf, S.voxhess, S.sws[0], S.thread_num);
+  for (int i = 0; i < S.win_size; i++) { S.ctx.mp[i] += mgsize; if (S.ctx.mp[i] >= S.win_size) S.ctx.mp[i] -= S.win_size; }
+  for (int i = mgsize; i < S.win_count; i++) { S.x_buf[i - mgsize] = S.x_buf[i]; std::swap(S.pvec_buf[i - mgsize], S.pvec_buf[i]); }
+  for (int i = S.win_count - mgsize; i < S.win_count; i++) { S.x_buf.pop_back(); S.pvec_buf.pop_back(); }
+  S.win_count -= mgsize;
+  return ok ? 1 : -1;
+}
+void orc_local_push(void *h, const float *xyz, int n, const oc_pose *pose, const double *cov225, double *pv_out /* n x 12 */) {
+  orc_local_insert(h, xyz, n, pose, cov225, pv_out, nullptr);
+  orc_local_recut(h);
+  orc_local_margi(h);
+}
+int orc_local_win_count(void *h) { return ((LocalSession *)h)->win_count; }
+void orc_local_get_poses(void *h, oc_pose *poses) { LocalSession &S = *(LocalSession *)h; poses_out(S.x_buf, poses); }
+void orc_local_set_poses(void *h, const oc_pose *poses) {   // the optimizer's write-back into x_buf (R, p only)
+  LocalSession &S = *(LocalSession *)h;
+  for (int i = 0; i < S.win_count; i++) { for (int k = 0; k < 9; k++) S.x_buf[i].R[k] = poses[i].R[k]; for (int k = 0; k < 3; k++) S.x_buf[i].p[k] = poses[i].p[k]; }
+}
+void *orc_local_factor(void *h) { return &((LocalSession *)h)->voxhess; }   // borrowed: do not orc_factor_free
+void orc_local_set_max_points(void *h, int max_points) { ((LocalSession *)h)->ctx.prm.max_points = max_points; }
+void orc_local_set_jour(void *h, double jour) { ((LocalSession *)h)->jour = jour; }
+// cut_voxel(feat_map, pvec, wdsize, jour)  voxel_map.hpp:2108-2152; pv rows: world pnt 3 + var 9
+void orc_local_insert_fix(void *h, const double *pv, int n, double jour) {
+  LocalSession &S = *(LocalSession *)h;
+  PVec pvec = pvec_in(pv, n);
+  cut_voxel_fix(S.surf_map, pvec, S.win_size, jour, &S.ctx);
 }
 int64_t orc_local_factor_voxels(void *h) { return (int64_t)((LocalSession *)h)->voxhess.plvec_voxels.size(); }
 // flattened export of surf_map: node record = what OctoTree::match / inside read (voxel_map.hpp:1649-1721, :1836-1848)
@@ -362,15 +395,38 @@ void orc_local_export(void *h, int64_t *root_keys /* n_roots x 3 */, int32_t *ro
     for (int k = 0; k < 36; k++) nd.plane_var[k] = t->plane.plane_var[k];
   }
 }
+// extended per-node record in the order of the last orc_local_export_count (layout = vx_map_node_state of the product header)
+struct oc_node_state {
+  int64_t root_key[3];
+  int32_t layer, path, octo_state, isexist, has_sw, is_plane, last_num, opt_state, in_slide, n_window_pts, n_fix_pts, _pad;
+  oc_cluster pcr_add, pcr_fix;
+  double eig_value[3];
+  double cov_add_trace;
+};
+static void state_walk(LocalSession &S, OctoTree *t, const VOXEL_LOC &key, int path, bool in_slide, std::unordered_map<OctoTree *, oc_node_state> &out) {
+  oc_node_state st;
+  std::memset(&st, 0, sizeof(st));
+  st.root_key[0] = key.x; st.root_key[1] = key.y; st.root_key[2] = key.z;
+  st.layer = t->layer; st.path = path; st.octo_state = t->octo_state; st.isexist = t->isexist ? 1 : 0; st.has_sw = t->sw != nullptr ? 1 : 0;
+  st.is_plane = t->plane.is_plane ? 1 : 0; st.last_num = t->last_num; st.opt_state = t->opt_state; st.in_slide = in_slide ? 1 : 0;
+  if (t->sw) for (auto &v : t->sw->points) st.n_window_pts += (int)v.size();
+  st.n_fix_pts = (int)t->point_fix.size();
+  to_c(t->pcr_add, st.pcr_add); to_c(t->pcr_fix, st.pcr_fix);
+  for (int k = 0; k < 3; k++) st.eig_value[k] = t->eig_value[k];
+  for (int k = 0; k < 9; k++) st.cov_add_trace += t->cov_add(k, k);
+  out[t] = st;
+  if (t->octo_state == 1) for (int i = 0; i < 8; i++) if (t->leaves[i]) state_walk(S, t->leaves[i], key, path | (i << (3 * t->layer)), in_slide, out);
+}
+void orc_local_export_states(void *h, oc_node_state *states) {
+  LocalSession &S = *(LocalSession *)h;
+  std::unordered_map<OctoTree *, oc_node_state> all;
+  for (auto &kv : S.surf_map) state_walk(S, kv.second, kv.first, 0, S.surf_map_slide.find(kv.first) != S.surf_map_slide.end(), all);
+  for (size_t i = 0; i < S.flat.size(); i++) states[i] = all[S.flat[i]];
+}
 void orc_local_free(void *h) { delete (LocalSession *)h; }
 
 // ---- D1 / D2 over the session's surf_map ---------------------------------------------------------------
 // pv: n x 12 (pnt 3 + var 9 col-major, var = body-frame covariance as var_init leaves it).
-static PVec pvec_in(const double *pv, int n) {
-  PVec v(n);
-  for (int i = 0; i < n; i++) { for (int k = 0; k < 3; k++) v[i].pnt[k] = pv[12 * i + k]; for (int k = 0; k < 9; k++) v[i].var[k] = pv[12 * i + 3 + k]; }
-  return v;
-}
 void orc_var_init(const float *xyz, int n, double dept_err, double beam_err, double *pv_out) {
   std::vector<PointXYZIN> pl(n);
   for (int i = 0; i < n; i++) { std::memset(&pl[i], 0, sizeof(PointXYZIN)); pl[i].x = xyz[3 * i]; pl[i].y = xyz[3 * i + 1]; pl[i].z = xyz[3 * i + 2]; }

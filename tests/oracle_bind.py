@@ -186,13 +186,15 @@ def hba_add_edge(clouds, poses, local, gba, max_layer, max_iter, thread_num=2, i
 class Factor:
     """orc::LidarFactor (voxel_map.hpp:124-339 restated)."""
 
-    def __init__(self, win_size, handle=None):
+    def __init__(self, win_size, handle=None, borrowed=False):
         self.W = win_size
+        self.borrowed = borrowed
         self.h = C.c_void_p(handle if handle is not None else lib().orc_factor_create(C.c_int(win_size)))
 
     def __del__(self):
         if getattr(self, "h", None):
-            lib().orc_factor_free(self.h)
+            if not self.borrowed:
+                lib().orc_factor_free(self.h)
             self.h = None
 
     @property
@@ -318,6 +320,12 @@ def default_cov():
     return cov
 
 
+node_state_dtype = np.dtype([("root_key", "<i8", (3,)), ("layer", "<i4"), ("path", "<i4"), ("octo_state", "<i4"), ("isexist", "<i4"), ("has_sw", "<i4"),
+                             ("is_plane", "<i4"), ("last_num", "<i4"), ("opt_state", "<i4"), ("in_slide", "<i4"), ("n_window_pts", "<i4"),
+                             ("n_fix_pts", "<i4"), ("_pad", "<i4"), ("pcr_add", cluster_dtype), ("pcr_fix", cluster_dtype), ("eig_value", "<f8", (3,)),
+                             ("cov_add_trace", "<f8")])
+
+
 class LocalMap:
     """The sliding-window voxel map session of voxelslam.cpp:1888-2043 (poses given, no LIO/BA)."""
 
@@ -345,6 +353,54 @@ class LocalMap:
         keys = np.zeros((nr.value, 3), dtype=np.int64); rn = np.zeros(nr.value, dtype=np.int32); nodes = np.zeros(nn, dtype=map_node_dtype)
         lib().orc_local_export(self.h, _p(keys), _p(rn), _p(nodes))
         return keys, rn, nodes
+
+    # ---- step-wise session (voxelslam.cpp:1905-2040 without the optimizer) ----
+    def insert(self, xyz, pose, cov=None):
+        """window bookkeeping + cut_voxel_multi; returns (pv (n,12): local pnt + world var, pwld (n,3))."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32); n = xyz.shape[0]
+        ps = as_poses(pose)
+        cv = None if cov is None else np.ascontiguousarray(np.asarray(cov, dtype=np.float64).T)
+        pv = np.zeros((n, 12)); pw = np.zeros((n, 3))
+        lib().orc_local_insert(self.h, _p(xyz), C.c_int(n), _p(ps), _p(cv), _p(pv), _p(pw))
+        return pv, pw
+
+    def recut(self):
+        lib().orc_local_recut(self.h)
+
+    def margi(self):
+        return int(lib().orc_local_margi(self.h))
+
+    @property
+    def win_count(self):
+        return int(lib().orc_local_win_count(self.h))
+
+    def get_poses(self):
+        ps = np.zeros(self.win_count, dtype=pose_dtype)
+        lib().orc_local_get_poses(self.h, _p(ps))
+        return ps
+
+    def set_poses(self, poses):
+        ps = as_poses(poses)
+        assert ps.shape[0] == self.win_count
+        lib().orc_local_set_poses(self.h, _p(ps))
+
+    def factor(self, win_size):
+        lib().orc_local_factor.restype = C.c_void_p
+        return Factor(win_size, handle=lib().orc_local_factor(self.h), borrowed=True)
+
+    def insert_fix(self, pv, jour=0.0):
+        pv = np.ascontiguousarray(pv, dtype=np.float64)
+        lib().orc_local_insert_fix(self.h, _p(pv), C.c_int(pv.shape[0]), C.c_double(jour))
+
+    def export_states(self):
+        nr = C.c_int64(0)
+        lib().orc_local_export_count.restype = C.c_int64
+        nn = lib().orc_local_export_count(self.h, C.byref(nr))
+        keys = np.zeros((nr.value, 3), dtype=np.int64); rn = np.zeros(nr.value, dtype=np.int32); nodes = np.zeros(nn, dtype=map_node_dtype)
+        lib().orc_local_export(self.h, _p(keys), _p(rn), _p(nodes))
+        st = np.zeros(nn, dtype=node_state_dtype)
+        lib().orc_local_export_states(self.h, _p(st))
+        return st, nodes
 
     def lio_pass(self, pv, pose, cov, leaf_cache=None):
         pv = np.ascontiguousarray(pv, dtype=np.float64); n = pv.shape[0]

@@ -225,8 +225,9 @@ class PlaneMap:
         self.h = h
 
     def free(self):
-        if self.h:
-            self.lib.vx_planemap_free(self.h); self.h = None
+        if self.h and not getattr(self, "view", False):
+            self.lib.vx_planemap_free(self.h)
+        self.h = None
 
     def lio_pass(self, pv, pose, cov, leaf_cache=None):
         """One pass of voxelslam.cpp:1005-1050.  pv: (n,12) pnt + var (col-major); cov: 15x15 state covariance."""
@@ -263,6 +264,77 @@ class PlaneMap:
         s = st[0]
         return dict(ok=bool(ok.value), R=s["R"].reshape(3, 3).T.copy(), p=s["p"].copy(), v=s["v"].copy(), bg=s["bg"].copy(), ba=s["ba"].copy(),
                     cov=s["cov"].reshape(15, 15).T.copy(), iters=it.value, match_nums=mn[:it.value].tolist())
+
+
+# ---- A6 / A7 / A9 / A11 / A12: the sliding-window voxel map on the device ------------------------------------------
+map_params_dtype = np.dtype([("voxel_size", "<f8"), ("min_eigen_value", "<f8"), ("plane_eigen_value_thre", "<f8", (4,)), ("min_point", "<f8", (4,)),
+                             ("max_layer", "<i4"), ("max_points", "<i4"), ("win_size", "<i4"), ("thread_num", "<i4")])
+node_state_dtype = np.dtype([("root_key", "<i8", (3,)), ("layer", "<i4"), ("path", "<i4"), ("octo_state", "<i4"), ("isexist", "<i4"), ("has_sw", "<i4"),
+                             ("is_plane", "<i4"), ("last_num", "<i4"), ("opt_state", "<i4"), ("in_slide", "<i4"), ("n_window_pts", "<i4"),
+                             ("n_fix_pts", "<i4"), ("_pad", "<i4"), ("pcr_add", cluster_dtype), ("pcr_fix", cluster_dtype), ("eig_value", "<f8", (3,)),
+                             ("cov_add_trace", "<f8")])
+
+
+class VoxelMap:
+    """vx_map: surf_map + surf_map_slide of voxelslam.cpp (OctoTree / SlideWindow, voxel_map.hpp:1009-1881) in device memory."""
+
+    def __init__(self, ctx, win_size=10, voxel_size=1.0, min_eigen_value=0.0025, thre=(1, 1, 1, 1), max_layer=2, max_points=100, thread_num=5,
+                 min_point=(5, 5, 5, 5)):
+        self.ctx = ctx; self.lib = ctx.lib; self.W = win_size; self.voxel_size = voxel_size
+        pr = np.zeros(1, dtype=map_params_dtype)
+        pr["voxel_size"] = voxel_size; pr["min_eigen_value"] = min_eigen_value; pr["plane_eigen_value_thre"] = thre; pr["min_point"] = min_point
+        pr["max_layer"] = max_layer; pr["max_points"] = max_points; pr["win_size"] = win_size; pr["thread_num"] = thread_num
+        h = C.c_void_p()
+        _chk(self.lib.vx_map_create(ctx.h, _p(pr), C.byref(h)))
+        self.h = h
+        self.lib.vx_map_num_nodes.restype = C.c_int64; self.lib.vx_map_num_nodes.argtypes = [C.c_void_p]
+        self.lib.vx_map_num_roots.restype = C.c_int64; self.lib.vx_map_num_roots.argtypes = [C.c_void_p]
+
+    def free(self):
+        if self.h:
+            _chk(self.lib.vx_map_free(self.h)); self.h = None
+
+    @property
+    def num_nodes(self):
+        return int(self.lib.vx_map_num_nodes(self.h))
+
+    @property
+    def num_roots(self):
+        return int(self.lib.vx_map_num_roots(self.h))
+
+    def cut_voxel(self, pv, pwld, ord_):
+        """cut_voxel_multi (voxel_map.hpp:1964-2096): pv (n,12) local pnt + world var, pwld (n,3), ord_ = win_count - 1."""
+        pv = np.ascontiguousarray(pv, dtype=np.float64); pw = np.ascontiguousarray(pwld, dtype=np.float64)
+        _chk(self.lib.vx_map_cut_voxel(self.ctx.h, self.h, _p(pv), _p(pw), C.c_int64(pv.shape[0]), C.c_int(ord_)))
+
+    def cut_voxel_fix(self, pv, jour=0.0):
+        pv = np.ascontiguousarray(pv, dtype=np.float64)
+        _chk(self.lib.vx_map_cut_voxel_fix(self.ctx.h, self.h, _p(pv), C.c_int64(pv.shape[0]), C.c_double(jour)))
+
+    def recut(self, poses, factor):
+        ps = as_poses(poses)
+        _chk(self.lib.vx_map_recut(self.ctx.h, self.h, _p(ps), C.c_int(ps.shape[0]), factor.h))
+
+    def margi(self, poses, factor, mgsize=1, jour=0.0):
+        ps = as_poses(poses)
+        _chk(self.lib.vx_map_margi(self.ctx.h, self.h, _p(ps), C.c_int(ps.shape[0]), C.c_int(mgsize), factor.h, C.c_double(jour)))
+
+    def shift_window(self, mgsize=1):
+        _chk(self.lib.vx_map_shift_window(self.h, C.c_int(mgsize)))
+
+    def planemap(self):
+        """non-owning PlaneMap view for lio_pass / lio_state_estimation (valid until the map changes)."""
+        v = C.c_void_p()
+        _chk(self.lib.vx_map_planemap(self.h, C.byref(v)))
+        pm = PlaneMap.__new__(PlaneMap)
+        pm.ctx = self.ctx; pm.lib = self.lib; pm.h = v; pm.view = True
+        return pm
+
+    def export(self):
+        n = self.num_nodes
+        st = np.zeros(n, dtype=node_state_dtype); nd = np.zeros(n, dtype=map_node_dtype)
+        _chk(self.lib.vx_map_export(self.h, _p(st), _p(nd)))
+        return st, nd
 
 
 # ---- B6 / B4 / B5: IMU preintegration factor (host) and the LiDAR-inertial optimizers -------------------------

@@ -11,25 +11,13 @@
 #include "vx_common.cuh"
 #include "vx_voxelize.cuh"
 #include "vx_frontend.cuh"
+#include "vx_planemap.cuh"
 #include <cmath>
 #include <algorithm>
 
 using namespace vx;
 
-struct vx_planemap {
-  vx_ctx *ctx = nullptr;
-  DevBuf hkeys, hvals, nodes;
-  uint64_t hmask = 0;
-  int64_t n_nodes = 0, n_roots = 0;
-  double voxel_size = 1.0;
-};
-
 namespace {
-
-__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
-  x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31;
-  return x;
-}
 
 struct M3d { double m[9]; };   // row-major m[r*3+c]
 __device__ __forceinline__ double mad_rn(double acc, double a, double b) { return __dadd_rn(acc, __dmul_rn(a, b)); }
@@ -364,6 +352,7 @@ int vx_planemap_create(vx_ctx *ctx, const int64_t *root_keys, const int32_t *roo
 
 int vx_planemap_free(vx_planemap *m) {
   if (!m) return VX_OK;
+  if (!m->owns) { set_error("vx_planemap_free: this handle is a view owned by a vx_map"); return VX_ERR_ARG; }
   cudaSetDevice(m->ctx->device);
   cudaStreamSynchronize(m->ctx->stream);
   m->hkeys.release(); m->hvals.release(); m->nodes.release();
