@@ -254,6 +254,14 @@ int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int
                     const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
                     double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out);
 
+/* The merged submap cloud HBA_add_edge returns through plptr (voxelslam.cpp:2954-2985): every keyframe cloud of a window moved
+ * into the frame of the window's first keyframe with the (optimized) poses, intensity = the keyframe's session id (frame_mp),
+ * then down_sampling_voxel(pl, voxel_size / 8).  Windows are written back to back, window w = out[win_off[w], win_off[w+1]);
+ * cells in ascending packed-key order inside a window. */
+int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                        const int32_t *frame_mp, const vx_pose *poses, int W, int n_windows, double voxel_size, vx_point48 *out,
+                        int64_t out_cap, int64_t *win_off);
+
 /* ---- D1 / D2: LIO ESIKF point-to-plane update -----------------------------------------------------------
  * The voxel map as OctoTree::match reads it (voxel_map.hpp:1649-1721), flattened by the caller: one record per
  * OctoTree node; root voxels (the unordered_map<VOXEL_LOC, OctoTree*> of voxel_map.hpp:2167-2205) by key. */

@@ -170,7 +170,7 @@ def hba_add_edge(clouds, poses, local, gba, max_layer, max_iter, thread_num=2, i
     jl = 6 * W
     edges = np.zeros(W * (W - 1) // 2, dtype=edge_dtype); hess = np.zeros((jl, jl))
     rf = np.zeros(max(max_iter, 1)); rl = np.zeros(max(max_iter, 1)); nv = np.zeros(max(max_iter, 1), dtype=np.int32); no = C.c_int(0)
-    merged = np.zeros(xyz.shape[0] // 3 if want_cloud else 1, dtype=point48_dtype); mn = C.c_int64(0)
+    merged = np.zeros(xyz.shape[0] if want_cloud else 1, dtype=point48_dtype); mn = C.c_int64(0)
     ids_ = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32)
     mps_ = None if mps is None else np.ascontiguousarray(mps, dtype=np.int32)
     lt = np.ascontiguousarray(local[2], dtype=np.float64); gt = np.ascontiguousarray(gba[2], dtype=np.float64)

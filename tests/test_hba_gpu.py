@@ -58,3 +58,31 @@ def test_hba_batched_bottom_level(pkg, ob, ctx):
         assert out["n_voxels"][b] == ref["n_voxels"][-1]
         assert pose_err(out["poses"][b * W:(b + 1) * W], ref["poses"]) < 1e-8
         check_edges(out["edges"][b], ref["edges"])
+
+
+def test_hba_merged_submap_cloud(pkg, ob, ctx):
+    # voxelslam.cpp:2954-2985: clouds moved into keyframe 0's frame with the optimized poses, intensity = session id,
+    # down_sampling_voxel(voxel_size / 8).  Same cells, same counts, bit-identical float centroids (order: sorted by cell).
+    clouds, (R, p) = scene.config1(W=15, pts_per_scan=4000)
+    W = 10
+    start = synth.perturb_poses((R, p), 3, np.deg2rad(0.5), 0.05)
+    mps = np.arange(15) % 3
+    key = lambda a: np.lexsort((a["z"], a["y"], a["x"]))
+    for s0 in (0, 5):
+        sl = slice(s0, s0 + W)
+        ref = ob.hba_add_edge(clouds[sl], (start[0][sl], start[1][sl]), LOCAL, GBA, 2, 1, ids=np.arange(W), mps=mps[sl], want_cloud=True)
+        # the cloud is built from the poses HBA_add_edge leaves behind: feed the oracle's optimized poses to the device path
+        got = pkg.hba_merge_clouds(ctx, clouds[sl], ref["poses"], W, 1, LOCAL[0], mps=mps[sl])[0]
+        r = ref["merged"]
+        assert got.shape == r.shape and r.shape[0] > 1000
+        g = got[key(got)]; r = r[key(r)]
+        for fld in ("x", "y", "z", "intensity", "curvature"):
+            assert np.array_equal(g[fld].view(np.uint32), r[fld].view(np.uint32)), fld
+        assert int(got["curvature"].sum()) == sum(c.shape[0] for c in clouds[sl])
+    # two windows in one call == each alone
+    fc = np.concatenate([np.arange(0, W), np.arange(5, 5 + W)]).astype(np.int32)
+    both = pkg.hba_merge_clouds(ctx, clouds, (start[0][fc], start[1][fc]), W, 2, LOCAL[0], frame_cloud=fc, mps=mps[fc])
+    for b, s0 in enumerate((0, 5)):
+        sl = slice(s0, s0 + W)
+        one = pkg.hba_merge_clouds(ctx, clouds[sl], (start[0][sl], start[1][sl]), W, 1, LOCAL[0], mps=mps[sl])[0]
+        assert np.array_equal(both[b].view(np.uint8), one.view(np.uint8))

@@ -189,6 +189,22 @@ def hba_add_edge(ctx, clouds, poses, W, n_windows, local, gba, max_layer, max_it
                 n_voxels=nv, status=st)
 
 
+def hba_merge_clouds(ctx, clouds, poses, W, n_windows, voxel_size, frame_cloud=None, mps=None):
+    """The merged submap cloud of HBA_add_edge (voxelslam.cpp:2954-2985), one per window -> list of point48 arrays."""
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses)
+    fc = None if frame_cloud is None else np.ascontiguousarray(frame_cloud, dtype=np.int32)
+    mps_ = None if mps is None else np.ascontiguousarray(mps, dtype=np.int32)
+    sizes = np.diff(off)
+    idx = np.arange(W * n_windows) if fc is None else fc
+    cap = int(sizes[idx].sum())
+    out = np.zeros(max(cap, 1), dtype=point48_dtype); wo = np.zeros(n_windows + 1, dtype=np.int64)
+    _chk(ctx.lib.vx_hba_merge_clouds(ctx.h, _p(xyz), _p(off), C.c_int(len(clouds)), _p(fc), _p(mps_), _p(ps), C.c_int(W), C.c_int(n_windows),
+                                     C.c_double(voxel_size), _p(out), C.c_int64(cap), _p(wo)))
+    return [out[wo[b]:wo[b + 1]].copy() for b in range(n_windows)]
+
+
 map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("octo_state", "<i4"), ("child", "<i4", (8,)), ("is_plane", "<i4"),
                            ("radius", "<f4"), ("p_center", "<f8", (3,)), ("p_normal", "<f8", (3,)), ("plane_var", "<f8", (36,))])
 lio_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)), ("cov", "<f8", (225,))])

@@ -6,6 +6,7 @@
 // session, voxelslam.cpp:3096): each window keeps its own converge_flag / threshold state; windows that
 // want the coarse and the fine thresholds in the same outer iteration are built as two sub-batches.
 #include "vx_factor.cuh"
+#include "vx_voxelize.cuh"
 #include <cmath>
 #include <algorithm>
 
@@ -142,4 +143,80 @@ extern "C" int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *clo
   }
   if (hess_out) std::copy(hess.begin(), hess.end(), hess_out);
   return VX_OK;
+}
+
+// ---- merged submap cloud of HBA_add_edge (voxelslam.cpp:2954-2985) ---------------------------------------------------
+namespace {
+struct RelPose { double dR[9]; double dp[3]; float mp; };   // dR row-major
+// every point of keyframe i into the frame of keyframe 0: v3 = dR * v3 + dp (double), stored back as float (:2963-2969)
+__global__ void k_merge_transform(const float *__restrict__ xyz, int64_t beg, int64_t n, RelPose rp, vx_point48 *__restrict__ out) {
+  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const float *s = xyz + 3 * (beg + k);
+  const double x = (double)s[0], y = (double)s[1], z = (double)s[2];
+  vx_point48 ap;
+  ap._p0 = 0.0f; ap.normal_x = ap.normal_y = ap.normal_z = ap._p1 = 0.0f; ap.curvature = 0.0f; ap._p2 = ap._p3 = 0.0f;
+  double v[3];
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+    v[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(rp.dR[r * 3], x), __dmul_rn(rp.dR[r * 3 + 1], y)), __dmul_rn(rp.dR[r * 3 + 2], z)), rp.dp[r]);
+  ap.x = (float)v[0]; ap.y = (float)v[1]; ap.z = (float)v[2];
+  ap.intensity = rp.mp;
+  out[k] = ap;
+}
+}  // namespace
+
+extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                                   const int32_t *frame_mp, const vx_pose *poses, int W, int n_windows, double voxel_size, vx_point48 *out,
+                                   int64_t out_cap, int64_t *win_off) {
+  VX_ARG(ctx && cloud_off && poses && win_off && W >= 1 && n_windows >= 1 && n_clouds >= 1 && voxel_size > 0 && out_cap >= 0);
+  VX_TRY(bind(ctx));
+  const int64_t NP = cloud_off[n_clouds];
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  cudaStream_t st = ctx->stream;
+  DevBuf d_xyz, d_in, d_out;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, st));
+    int64_t written = 0;
+    win_off[0] = 0;
+    for (int w = 0; w < n_windows; w++) {
+      int64_t total = 0;
+      for (int i = 0; i < W; i++) { const int c = frame_cloud ? frame_cloud[w * W + i] : w * W + i; VX_ARG(c >= 0 && c < n_clouds); total += cloud_off[c + 1] - cloud_off[c]; }
+      if (total > 0) {
+        VX_TRY(d_in.reserve(sizeof(vx_point48) * total)); VX_TRY(d_out.reserve(sizeof(vx_point48) * total));
+        const vx_pose &xc = poses[(size_t)w * W];
+        int64_t at = 0;
+        for (int i = 0; i < W; i++) {
+          const int g = w * W + i, c = frame_cloud ? frame_cloud[g] : g;
+          const int64_t n = cloud_off[c + 1] - cloud_off[c];
+          if (n == 0) continue;
+          const vx_pose &xi = poses[g];
+          RelPose rp;
+          // dp = xc.R^T (xs[i].p - xc.p), dR = xc.R^T xs[i].R   (:2958-2959); R column-major: R(r,c) = R[c*3+r]
+          double d[3] = {xi.p[0] - xc.p[0], xi.p[1] - xc.p[1], xi.p[2] - xc.p[2]};
+          for (int r = 0; r < 3; r++) {
+            double s = 0; for (int k = 0; k < 3; k++) s += xc.R[r * 3 + k] * d[k];
+            rp.dp[r] = s;
+            for (int cc = 0; cc < 3; cc++) { double t = 0; for (int k = 0; k < 3; k++) t += xc.R[r * 3 + k] * xi.R[cc * 3 + k]; rp.dR[r * 3 + cc] = t; }
+          }
+          rp.mp = (float)(frame_mp ? frame_mp[g] : 0);
+          VX_KERNEL(ctx, "k_merge_transform", k_merge_transform<<<blocks_for(n, 256), 256, 0, st>>>(d_xyz.as<float>(), cloud_off[c], n, rp, d_in.as<vx_point48>() + at));
+          at += n;
+        }
+        int32_t ncell = 0;
+        VX_TRY(downsample_device(ctx, d_in.p, total, voxel_size / 8, DS_MEAN, d_out.as<vx_point48>(), &ncell));   // :2978
+        if (written + ncell > out_cap) { set_error("vx_hba_merge_clouds: output capacity %lld too small", (long long)out_cap); return VX_ERR_ARG; }
+        VX_CUDA(cudaMemcpyAsync(out + written, d_out.p, sizeof(vx_point48) * ncell, cudaMemcpyDeviceToHost, st));
+        written += ncell;
+      }
+      win_off[w + 1] = written;
+    }
+    VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  d_xyz.release(); d_in.release(); d_out.release();
+  return rc;
 }

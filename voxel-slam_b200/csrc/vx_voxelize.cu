@@ -120,26 +120,25 @@ __global__ void k_ds_pvec(const vx_point_var *__restrict__ pts, const int32_t *_
   out[c] = ap;
 }
 
-enum DsMode { DS_MEAN, DS_CLOSE, DS_PVEC };
+}  // namespace
 
-// Shared driver of the three down-sampling operators: key -> stable sort -> cell starts -> one thread per cell replaying the
-// reference's sequential arithmetic in input order.  Output order = ascending packed cell key.
-int downsample_cells(vx_ctx *ctx, const void *pts, size_t rec, int64_t n, double voxel_size, DsMode mode, vx_point48 *out, int64_t *out_n) {
-  VX_TRY(bind(ctx));
+namespace vx {
+// Shared driver of the three down-sampling operators on DEVICE-resident input: key -> stable sort -> cell starts -> one
+// thread per cell replaying the reference's sequential arithmetic in input order.  Output order = ascending packed cell key.
+int downsample_device(vx_ctx *ctx, const void *d_pts, int64_t n, double voxel_size, DsMode mode, vx_point48 *d_out, int32_t *ncell_out) {
   VX_ARG(n < ((int64_t)1 << 31));
   cudaStream_t st = ctx->stream;
-  if (n == 0) { *out_n = 0; return VX_OK; }
-  DevBuf d_pts, d_out, d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad;
+  *ncell_out = 0;
+  if (n == 0) return VX_OK;
+  DevBuf d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad;
   auto body = [&]() -> int {
-    VX_TRY(d_pts.reserve(rec * n)); VX_TRY(d_out.reserve(sizeof(vx_point48) * n));
     VX_TRY(d_k0.reserve(8 * n)); VX_TRY(d_k1.reserve(8 * n)); VX_TRY(d_i0.reserve(4 * n)); VX_TRY(d_i1.reserve(4 * n));
     VX_TRY(d_flag.reserve(4 * n)); VX_TRY(d_incl.reserve(4 * n)); VX_TRY(d_start.reserve(4 * (n + 1))); VX_TRY(d_bad.reserve(4));
-    VX_CUDA(cudaMemcpyAsync(d_pts.p, pts, rec * n, cudaMemcpyHostToDevice, st));
     VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
     if (mode == DS_PVEC)
-      VX_KERNEL(ctx, "k_ds_key_pvec", k_ds_key_pvec<<<blocks_for(n, 256), 256, 0, st>>>(d_pts.as<vx_point_var>(), n, voxel_size, d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
+      VX_KERNEL(ctx, "k_ds_key_pvec", k_ds_key_pvec<<<blocks_for(n, 256), 256, 0, st>>>((const vx_point_var *)d_pts, n, voxel_size, d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
     else
-      VX_KERNEL(ctx, "k_ds_key", k_ds_key<<<blocks_for(n, 256), 256, 0, st>>>(d_pts.as<vx_point48>(), n, voxel_size, d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
+      VX_KERNEL(ctx, "k_ds_key", k_ds_key<<<blocks_for(n, 256), 256, 0, st>>>((const vx_point48 *)d_pts, n, voxel_size, d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
     size_t tb = 0;
     VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)n, 0, 63, st));
     VX_TRY(ctx->scratch.reserve(tb));
@@ -158,11 +157,33 @@ int downsample_cells(vx_ctx *ctx, const void *pts, size_t rec, int64_t n, double
     if (bad) { set_error("down-sampling: a cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
     const int nb = blocks_for(ncell, 128);
     if (mode == DS_MEAN)
-      VX_KERNEL(ctx, "k_ds_mean", k_ds_mean<<<nb, 128, 0, st>>>(d_pts.as<vx_point48>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out.as<vx_point48>()));
+      VX_KERNEL(ctx, "k_ds_mean", k_ds_mean<<<nb, 128, 0, st>>>((const vx_point48 *)d_pts, d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out));
     else if (mode == DS_CLOSE)
-      VX_KERNEL(ctx, "k_ds_close", k_ds_close<<<nb, 128, 0, st>>>(d_pts.as<vx_point48>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out.as<vx_point48>()));
+      VX_KERNEL(ctx, "k_ds_close", k_ds_close<<<nb, 128, 0, st>>>((const vx_point48 *)d_pts, d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out));
     else
-      VX_KERNEL(ctx, "k_ds_pvec", k_ds_pvec<<<nb, 128, 0, st>>>(d_pts.as<vx_point_var>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out.as<vx_point48>()));
+      VX_KERNEL(ctx, "k_ds_pvec", k_ds_pvec<<<nb, 128, 0, st>>>((const vx_point_var *)d_pts, d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_out));
+    *ncell_out = ncell;
+    return VX_OK;
+  };
+  const int status = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : {&d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad}) b->release();
+  return status;
+}
+}  // namespace vx
+
+namespace {
+int downsample_cells(vx_ctx *ctx, const void *pts, size_t rec, int64_t n, double voxel_size, DsMode mode, vx_point48 *out, int64_t *out_n) {
+  VX_TRY(bind(ctx));
+  VX_ARG(n < ((int64_t)1 << 31));
+  cudaStream_t st = ctx->stream;
+  if (n == 0) { *out_n = 0; return VX_OK; }
+  DevBuf d_pts, d_out;
+  auto body = [&]() -> int {
+    VX_TRY(d_pts.reserve(rec * n)); VX_TRY(d_out.reserve(sizeof(vx_point48) * n));
+    VX_CUDA(cudaMemcpyAsync(d_pts.p, pts, rec * n, cudaMemcpyHostToDevice, st));
+    int32_t ncell = 0;
+    VX_TRY(downsample_device(ctx, d_pts.p, n, voxel_size, mode, d_out.as<vx_point48>(), &ncell));
     VX_CUDA(cudaMemcpyAsync(out, d_out.p, sizeof(vx_point48) * ncell, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
     *out_n = ncell;
@@ -170,10 +191,9 @@ int downsample_cells(vx_ctx *ctx, const void *pts, size_t rec, int64_t n, double
   };
   const int status = body();
   cudaStreamSynchronize(st);
-  for (DevBuf *b : {&d_pts, &d_out, &d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad}) b->release();
+  d_pts.release(); d_out.release();
   return status;
 }
-
 }  // namespace
 
 extern "C" {

@@ -37,4 +37,8 @@ __host__ __device__ __forceinline__ void unpack_key(uint64_t k, int64_t &x, int6
   z = (int64_t)(k & 0x1fffff) - KEY_BIAS;
 }
 
+enum DsMode { DS_MEAN, DS_CLOSE, DS_PVEC };   // A2 down_sampling_voxel, A4 down_sampling_close, A3 down_sampling_pvec
+// down-sampling of device-resident points (vx_point48, or vx_point_var for DS_PVEC) into d_out (room for n records)
+int downsample_device(vx_ctx *ctx, const void *d_pts, int64_t n, double voxel_size, DsMode mode, vx_point48 *d_out, int32_t *ncell_out);
+
 }  // namespace vx
