@@ -245,6 +245,58 @@ def extra_benches(pkg, ctx):
                        "kernel_hbm_gbs": (96 * q.shape[0] + 408 * o["match_num"]) / (kms * 1e-3) / 1e9 if kms > 0 else None,
                        "what": "vx_lio_match_accumulate: one pass of voxelslam.cpp:1005-1050 over a ~60k-point sweep (synthetic layer-0 plane map)"}
     gm.free()
+    # --- C2-shaped local mapping: the device sliding-window map fed with ~60k-point sweeps (A5 -> A6 -> A9/A11 -> A12)
+    Wl = 10
+    Rm, pm = scene.arc_trajectory(Wl + 4, 5, step=0.5, yaw_step_deg=3.0)
+    mposes = pkg.as_poses((Rm, pm))
+    vm = pkg.VoxelMap(ctx, win_size=Wl, voxel_size=1.0, thre=(1, 1, 1, 1), max_layer=2)
+    fl = pkg.Factor(ctx, Wl)
+    ident = (np.eye(3)[None], np.zeros((1, 3)))
+    win = np.zeros(0, dtype=pkg.pose_dtype)
+    tt = {"front_end": [], "cut_voxel": [], "recut": [], "margi": []}
+    npts = 0
+    ctx.profile(True)
+    for i in range(Wl + 4):
+        xyz = scene.scan(rects, Rm[i], pm[i], scene.xt32_dirs(2000), rng, range_noise=0.01, blind=0.7).astype(np.float32)
+        t0 = time.perf_counter()
+        t1 = t0
+        win = np.concatenate([win, mposes[i:i + 1]])
+        vm.cut_voxel_xyz(xyz, ident, 0.01, 0.01, mposes[i:i + 1], cov, win.shape[0] - 1)
+        t2 = time.perf_counter()
+        vm.recut(win, fl)
+        t3 = time.perf_counter()
+        if i >= 4:      # skip the cold scans
+            tt["front_end"].append(t1 - t0); tt["cut_voxel"].append(t2 - t1); tt["recut"].append(t3 - t2); npts += xyz.shape[0]
+        if win.shape[0] >= Wl:
+            t4 = time.perf_counter()
+            vm.margi(win, fl); vm.shift_window(1); win = win[1:].copy()
+            tt["margi"].append(time.perf_counter() - t4)
+    prof = ctx.profile_read(); ctx.profile(False)
+    n_meas = len(tt["cut_voxel"])
+    med = lambda v: float(np.median(v)) if len(v) else None
+    kern = {k: {"ms_total": v[0], "launches": v[1]} for k, v in prof.items() if k.startswith("k_") and v[0] > 0}
+    out["local_map"] = {"points_per_scan": npts // max(n_meas, 1), "nodes": vm.num_nodes, "roots": vm.num_roots, "factor_voxels": fl.num_voxels,
+                        "ms_cut_voxel": 1e3 * med(tt["cut_voxel"]), "ms_recut_tras_opt": 1e3 * med(tt["recut"]),
+                        "ms_margi": 1e3 * med(tt["margi"]) if tt["margi"] else None,
+                        "cut_voxel_points_per_s": (npts / max(n_meas, 1)) / med(tt["cut_voxel"]),
+                        "kernel_ms_over_session": {k: round(v["ms_total"], 4) for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["ms_total"])[:8]},
+                        "what": "vx_map_cut_voxel_xyz (var_init + pvec_update + cut_voxel_multi from the raw scan), vx_map_recut (+tras_opt into the device factor), vx_map_margi per 64k-ray "
+                                "XT32 sweep, W=10, voxel 1 m, host buffers in (wall clock, median over the steady-state scans)"}
+    # --- B4: LiDAR-inertial LM on the factor the map just produced (W = 10), synthetic IMU
+    states, segs = synth.imu_trajectory(20241008 + 6, Wl, gyr_sigma=1e-3, acc_sigma=1e-2)
+    fli = synth.random_factor(20241008 + 7, 2000, Wl, poses=synth.states_poses(states), occupancy=0.7, min_frames=2)
+    f2 = pkg.Factor(ctx, Wl); f2.upload_dense(fli)
+    nz = pkg.imu_noise(0.01, 0.1, 1e-4, 1e-3)
+    imus = np.concatenate([pkg.imu_pre_new(sg, nz, states[k]["bg"], states[k]["ba"]) for k, sg in enumerate(segs)])
+    start = states.copy(); start["p"][1:] += rng.normal(0, 0.03, (Wl - 1, 3))
+    f2.ba_li(start, imus)
+    t0 = time.perf_counter()
+    for _ in range(5):
+        r = f2.ba_li(start, imus)
+    t = (time.perf_counter() - t0) / 5
+    out["li_ba"] = {"ms_per_damping_iter_call": 1e3 * t, "lm_iterations": len(r["accept"]), "voxels": 2000, "win_size": Wl,
+                    "what": "vx_ba_li (LI_BA_Optimizer::damping_iter, 3 LM iterations): device B1/B2 + host IMU factors and 150x150 LDL^T"}
+    f2.free(); fl.free(); vm.free()
     return out
 
 
@@ -415,7 +467,8 @@ def run_b200(args, rank, world, local_rank):
 
     if rank == 0 and world == 1 and not args.no_extras:
         extra["other_rows"] = extra_benches(pkg, ctx)
-    extra["fp64_peak_tflops"] = {"dfma": ctx.fp64_peak(0), "dmma": ctx.fp64_peak(1), "how": "vx_bench_fp64 (csrc/vx_peaks.cu), measured in this run"}
+    extra["fp64_peak_tflops"] = {"dfma": ctx.fp64_peak(0), "dmma": ctx.fp64_peak(1), "mixed_half_half": ctx.fp64_peak(2),
+                                 "how": "vx_bench_fp64 (csrc/vx_peaks.cu), measured in this run; mixed < either alone: DFMA and DMMA share the FP64 datapath"}
     roofline["fp64"]["peak_tflops"] = extra["fp64_peak_tflops"]["dfma"]
     roofline["fp64"]["frac"] = roofline["fp64"]["achieved_tflops"] / extra["fp64_peak_tflops"]["dfma"]
     if rank == 0:

@@ -76,7 +76,8 @@ int vx_ctx_profile_read(vx_ctx *ctx, char *names, size_t names_cap, double *ms, 
                         int max_entries, int *n_out);
 
 /* FP64 pipe peak of the device, measured in place (MEASURED_PEAKS.json has no FP64 figure):
- * mode 0 = DFMA on the CUDA cores, mode 1 = mma.sync m8n8k4 f64 on the tensor pipe.  TFLOP/s. */
+ * mode 0 = DFMA on the CUDA cores, mode 1 = mma.sync m8n8k4 f64 on the tensor pipe, mode 2 = half the warps of each
+ * (do the two share a datapath?).  TFLOP/s. */
 int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops);
 
 /* ---- B0: LidarFactor storage -------------------------------------------------------------- */
@@ -326,6 +327,10 @@ int vx_map_free(vx_map *map);
  * `ord` = the frame's position in the window (win_count - 1).  Keeps the ":2044-2045" quirk: when the scan touches fewer
  * root voxels than thread_num the roots are created / marked but no point is inserted. */
 int vx_map_cut_voxel(vx_ctx *ctx, vx_map *map, const vx_point_var *pvec, const double *pwld, int64_t n, int ord);
+/* The same insertion fed with the raw scan: var_init (voxelslam.cpp:1896), pvec_update (:1903) and cut_voxel_multi (:1917) run
+ * back to back on the device; 12 B/point cross PCIe instead of 120.  rot_var / tsl_var: x_curr.cov blocks (0,0), (3,3). */
+int vx_map_cut_voxel_xyz(vx_ctx *ctx, vx_map *map, const float *xyz, int64_t n, const vx_pose *ext, double dept_err, double beam_err,
+                         const vx_pose *x, const double *rot_var9, const double *tsl_var9, int ord);
 /* cut_voxel(feat_map, pvec, wdsize, jour)  voxel_map.hpp:2108-2152: already-world-frame points into pcr_fix / pcr_add only */
 int vx_map_cut_voxel_fix(vx_ctx *ctx, vx_map *map, const vx_point_var *pvec, int64_t n, double jour);
 /* multi_recut(surf_map_slide, win_count, x_buf, voxhess, sws)  voxelslam.cpp:1682-1737: OctoTree::recut on every root of the

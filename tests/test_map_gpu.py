@@ -34,8 +34,12 @@ def compare_maps(dev, ref, check_plane=True):
         assert bad.size == 0, "%s differs on %d nodes, first: dev %s ref %s" % (name, bad.size, d[bad[:1]], r[bad[:1]])
     for cl in ("pcr_add", "pcr_fix"):
         assert np.array_equal(d[cl]["N"], r[cl]["N"]), cl
-        for fld in ("P", "v"):
-            scale = np.maximum(np.abs(r[cl][fld]).max(axis=1, keepdims=True), 1e-300)
+        for fld, span in (("P", 15.0 ** 2), ("v", 15.0)):
+            # PointCluster::transform (tools.hpp:357-363) forms world moments as R P R^T + (Rv)p^T + p(Rv)^T + N p p^T: for a
+            # point near the world origin seen from 7 m away the terms are ~N*|p|^2 and cancel, so the rounding floor is
+            # relative to N * (scene extent)^2, not to the (possibly tiny) result
+            scale = np.maximum(np.abs(r[cl][fld]).max(axis=1, keepdims=True), r[cl]["N"][:, None] * span)
+            scale = np.maximum(scale, 1e-300)
             assert (np.abs(d[cl][fld] - r[cl][fld]) <= 1e-12 * scale).all(), (cl, fld)
     scale = np.maximum(np.abs(r["cov_add_trace"]), 1e-300)
     assert (np.abs(d["cov_add_trace"] - r["cov_add_trace"]) <= 1e-12 * scale).all()
@@ -280,3 +284,26 @@ def test_full_size_scan_properties(pkg, ctx):
             running = leaf_sum(st)
     assert m.num_nodes > m.num_roots
     f.free(); m.free()
+
+
+def test_raw_scan_insertion_matches_staged_path(pkg, ob, ctx):
+    # vx_map_cut_voxel_xyz (12 B/point in, var_init + pvec_update + cut_voxel_multi on the device) == the oracle session fed
+    # with the same raw scans: node set / membership / N exact, moments and cov_add to rounding
+    W = 6
+    dev = pkg.VoxelMap(ctx, win_size=W, voxel_size=1.0, thre=(1, 1, 1, 1), max_layer=2)
+    ref = ob.LocalMap(win_size=W, voxel_size=1.0, thre=(1, 1, 1, 1), max_layer=2, dept_err=0.02, beam_err=0.05)
+    f = pkg.Factor(ctx, W)
+    cov = ob.default_cov()
+    ident = (np.eye(3)[None], np.zeros((1, 3)))
+    win = np.zeros(0, dtype=pkg.pose_dtype)
+    for xyz, pose in _scans(W + 3, dirs=500, seed=21):
+        pv, pw = ref.insert(xyz, pose, cov)
+        win = np.concatenate([win, pkg.as_poses(pose)])
+        dev.cut_voxel_xyz(xyz, ident, 0.02, 0.05, pose, cov, win.shape[0] - 1)
+        compare_maps(dev.export(), ref.export_states(), check_plane=False)
+        ref.recut(); dev.recut(win, f)
+        compare_maps(dev.export(), ref.export_states())
+        if ref.margi():
+            dev.margi(win, f); dev.shift_window(1); win = win[1:].copy()
+        compare_maps(dev.export(), ref.export_states())
+    f.free(); dev.free()

@@ -323,6 +323,13 @@ class VoxelMap:
         pv = np.ascontiguousarray(pv, dtype=np.float64); pw = np.ascontiguousarray(pwld, dtype=np.float64)
         _chk(self.lib.vx_map_cut_voxel(self.ctx.h, self.h, _p(pv), _p(pw), C.c_int64(pv.shape[0]), C.c_int(ord_)))
 
+    def cut_voxel_xyz(self, xyz, ext, dept_err, beam_err, pose, cov, ord_):
+        """var_init + pvec_update + cut_voxel_multi on the device from the raw (n,3) float scan."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32); cov = np.asarray(cov, dtype=np.float64)
+        rv = np.ascontiguousarray(cov[0:3, 0:3].T); tv = np.ascontiguousarray(cov[3:6, 3:6].T)
+        _chk(self.lib.vx_map_cut_voxel_xyz(self.ctx.h, self.h, _p(xyz), C.c_int64(xyz.shape[0]), _p(as_poses(ext)), C.c_double(dept_err), C.c_double(beam_err),
+                                           _p(as_poses(pose)), _p(rv), _p(tv), C.c_int(ord_)))
+
     def cut_voxel_fix(self, pv, jour=0.0):
         pv = np.ascontiguousarray(pv, dtype=np.float64)
         _chk(self.lib.vx_map_cut_voxel_fix(self.ctx.h, self.h, _p(pv), C.c_int64(pv.shape[0]), C.c_double(jour)))

@@ -55,7 +55,9 @@ __global__ void __launch_bounds__(FE_THREADS) k_var_init(const float *__restrict
       for (int r = 0; r < 3; r++) var[c * 3 + r] = d[r] * (double)range_var * d[c] + (a1[r] * dir_var * a1[c] + a2[r] * dir_var * a2[c]);
     rot_sandwich(ext.R, var, wv);
     double *o = rec[threadIdx.x];
-    for (int r = 0; r < 3; r++) o[r] = ext.R[0 * 3 + r] * pb[0] + ext.R[1 * 3 + r] * pb[1] + ext.R[2 * 3 + r] * pb[2] + ext.p[r];
+    // the point decides voxel keys downstream: no FMA contraction, the reference's operation order
+    for (int r = 0; r < 3; r++)
+      o[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(ext.R[0 * 3 + r], pb[0]), __dmul_rn(ext.R[1 * 3 + r], pb[1])), __dmul_rn(ext.R[2 * 3 + r], pb[2])), ext.p[r]);
     for (int k = 0; k < 9; k++) o[3 + k] = wv[k];
   }
   __syncthreads();
@@ -89,7 +91,8 @@ __global__ void __launch_bounds__(FE_THREADS) k_pvec_update(const vx_point_var *
         const double hv = T[0 * 3 + r] * ph[0 * 3 + c] + T[1 * 3 + r] * ph[1 * 3 + c] + T[2 * 3 + r] * ph[2 * 3 + c];
         o[3 + c * 3 + r] = rv[c * 3 + r] + hv + tsl_var.m[r * 3 + c];
       }
-    for (int r = 0; r < 3; r++) w[r] = x.R[0 * 3 + r] * p[0] + x.R[1 * 3 + r] * p[1] + x.R[2 * 3 + r] * p[2] + x.p[r];
+    for (int r = 0; r < 3; r++)   // pwld feeds the key rule (A1): exact operation order, no contraction
+      w[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(x.R[0 * 3 + r], p[0]), __dmul_rn(x.R[1 * 3 + r], p[1])), __dmul_rn(x.R[2 * 3 + r], p[2])), x.p[r]);
   }
   __syncthreads();
   store_records(rec, out, base, n);

@@ -23,6 +23,7 @@
 #include "vx_math.cuh"
 #include "vx_planemap.cuh"
 #include "vx_voxelize.cuh"
+#include "vx_frontend.cuh"
 #include <cub/cub.cuh>
 #include <algorithm>
 
@@ -75,7 +76,7 @@ struct vx_map {
   DevBuf fix_pts, fix_leaf;
   int64_t n_fix = 0, cap_fix = 0;
   // work buffers
-  DevBuf w_key0, w_key1, w_val0, w_val1, w_flag, w_scan, w_seg, w_misc, w_cnt;
+  DevBuf w_key0, w_key1, w_val0, w_val1, w_flag, w_scan, w_seg, w_misc, w_cnt, w_part, w_pw, w_xyz;
   vx_planemap view;
 };
 
@@ -83,6 +84,7 @@ namespace {
 
 int grow_keep(vx_ctx *ctx, DevBuf &b, size_t used, size_t want) {
   if (want <= b.cap) return VX_OK;
+  if (used == 0) return b.reserve(want + want / 2);
   DevBuf nb;
   VX_TRY(nb.reserve(want));
   if (used) VX_CUDA(cudaMemcpyAsync(nb.p, b.p, used, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -374,98 +376,185 @@ struct AccArgs {
   int fix_novar;                    // push_fix_novar (no covariance term) instead of push_fix
 };
 
-// One warp per segment: every point of the segment is pushed into node seg_leaf[s] in sorted (= reference) order.
+// Pushing the sorted points into their target nodes, in two steps so that one huge leaf (a wall right in front of the
+// sensor collects thousands of points of a sweep) does not serialise the pass:
 //   window point: OctoTree::push (:1105-1143)  pcrs_local[mp[ord]] += local, pcr_add += world, cov_add += Bf_var(pv, pw)
 //   fixed point : push_fix (:1149-1162) / push_fix_novar (:1168-1178)   pcr_fix += p, pcr_add += p[, cov_add += Bf_var(pv, p)]
-// Lane l owns components l, l+32, l+64 of the 90 numbers {pcr_add P6 v3 | cov_add 81}; lanes 0..8 also own the 9 numbers
-// of the current run's target cluster (pcr_fix or one pcrs_local slot).  Accumulators START from the stored values, so
-// the additions happen in the reference's sequence.
-__global__ void __launch_bounds__(128) k_accumulate(const int32_t *__restrict__ sval, const int32_t *__restrict__ seg_start,
-                                                    const int32_t *__restrict__ seg_leaf, int nseg, AccArgs A, NodeMeta *__restrict__ meta,
-                                                    Mom *__restrict__ add, Mom *__restrict__ fix, Mom *__restrict__ loc, double *__restrict__ cov) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= nseg) return;
-  const int32_t leaf = seg_leaf[warp];
-  const int32_t b = seg_start[warp], e = seg_start[warp + 1];
-  double *addv = reinterpret_cast<double *>(&add[leaf]);      // 9 doubles then N
+// (1) k_acc_items: the sorted array is cut into ITEMS = runs of at most ACC_ITEM points of one segment and one source
+//     (pcr_fix or one window slot).  One warp per item: 32 points at a time are gathered into a shared-memory tile (all
+//     gathers in flight together); per point lanes 0..17 form Bi (6x3) and Bi*var once, then lane l adds its components
+//     l, l+32, l+64 of {pcr_add P6 v3 | cov_add 81} and lanes 0..8 the 9 numbers of the source cluster.  Sums run in scan
+//     order inside an item and are written as a 100-double partial.
+// (2) k_acc_final: one warp per segment adds the item partials, in order, onto the stored clusters / cov_add.
+// Everything is a fixed-order sum: reproducible bit for bit, within 1e-15 relative of a strictly sequential sum.
+constexpr int ACC_WARPS = 4;
+constexpr int ACC_ROW = 17;        // pnt 3 | var 9 | pw 3 | pad 2  (odd stride: conflict-free row reads)
+constexpr int ACC_ITEM = 128;      // points per item
+constexpr int ACC_PART = 100;      // pcr_add 9 | cov_add 81 | source cluster 9 | count
+
+__device__ __forceinline__ int slot_of(const AccArgs &A, int64_t g, int64_t &k) {
+  if (g < A.n_fix_range) { k = g; return -1; }
+  const int64_t gw = g - A.n_fix_range;
+  int slot = 0;
+  while (slot + 1 < A.ss.n && gw >= A.ss.beg[slot + 1]) slot++;
+  k = gw - A.ss.beg[slot];
+  return slot;
+}
+// item heads: segment start, source change, or every ACC_ITEM points of a segment
+__global__ void k_item_heads(const int32_t *__restrict__ sval, const int32_t *__restrict__ seg_incl, const int32_t *__restrict__ seg_start, int64_t n_valid,
+                             AccArgs A, int32_t *__restrict__ flag) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n_valid) return;
+  const int32_t s0 = seg_start[seg_incl[j] - 1];
+  int f = (j == s0 || ((j - s0) % ACC_ITEM) == 0) ? 1 : 0;
+  if (!f) {
+    int64_t k;
+    f = slot_of(A, sval[j], k) != slot_of(A, sval[j - 1], k) ? 1 : 0;
+  }
+  flag[j] = f;
+}
+__global__ void k_item_starts(const int32_t *__restrict__ flag, const int32_t *__restrict__ incl, int64_t n_valid, int32_t *__restrict__ item_start) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n_valid) return;
+  if (flag[j]) item_start[incl[j] - 1] = (int32_t)j;
+  if (j == n_valid - 1) item_start[incl[j]] = (int32_t)n_valid;
+}
+
+__global__ void __launch_bounds__(32 * ACC_WARPS) k_acc_items(const int32_t *__restrict__ sval, const int32_t *__restrict__ item_start, int nitems,
+                                                              const int32_t *__restrict__ seg_incl, const int32_t *__restrict__ seg_leaf, AccArgs A,
+                                                              double *__restrict__ part) {
+  __shared__ double tile_s[ACC_WARPS][32 * ACC_ROW];
+  __shared__ double bi_s[ACC_WARPS][2][36];      // [parity][Bi 18 | Bi*var 18]
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int item = blockIdx.x * ACC_WARPS + wib;
+  if (item >= nitems) return;
+  double *tile = tile_s[wib];
+  const int32_t b = item_start[item], e = item_start[item + 1];
+  const int32_t leaf = seg_leaf[seg_incl[b] - 1];
+  int64_t k0;
+  const int slot = slot_of(A, sval[b], k0);          // one source per item
+  double a[3] = {0.0, 0.0, 0.0}, run = 0.0;
+  int kind[3], i1[3], i2[3];     // kind 0: moment of pw, 1: 6x6 block (dot of two rows), 2: copy from Bi*var, 3: copy of var, 4: none
+#pragma unroll
+  for (int t = 0; t < 3; t++) {
+    const int c = lane + 32 * t;
+    i1[t] = c; i2[t] = 0;
+    if (c < 9) kind[t] = 0;
+    else if (c < 90) {
+      const int q = c - 9, r = q % 9, cc = q / 9;
+      if (r < 6 && cc < 6) { kind[t] = 1; i1[t] = 18 + r * 3; i2[t] = cc * 3; }
+      else if (r < 6) { kind[t] = 2; i1[t] = 18 + r * 3 + (cc - 6); }
+      else if (cc < 6) { kind[t] = 2; i1[t] = 18 + cc * 3 + (r - 6); }
+      else { kind[t] = 3; i1[t] = 3 + (cc - 6) * 3 + (r - 6); }
+    } else kind[t] = 4;
+  }
+  const bool with_cov = !(slot < 0 && A.fix_novar);
+  int par = 0;
+  for (int32_t base = b; base < e; base += 32) {
+    const int cnt = min(32, e - base);
+    __syncwarp();
+    if (lane < cnt) {                                   // gather: one point per lane
+      int64_t k;
+      const int64_t g = sval[base + lane];
+      slot_of(A, g, k);
+      const vx_point_var *pv;
+      double pw[3];
+      if (slot < 0) {
+        pv = A.fix_pts + k;
+        pw[0] = pv->pnt[0]; pw[1] = pv->pnt[1]; pw[2] = pv->pnt[2];
+        if (A.fix_leaf) A.fix_leaf[k] = leaf;          // the point now lives in `leaf`
+      } else {
+        pv = A.ss.pts[slot] + k;
+        A.ss.leaf[slot][k] = leaf;
+        if (A.pw_explicit) { pw[0] = A.pw_explicit[3 * k]; pw[1] = A.pw_explicit[3 * k + 1]; pw[2] = A.pw_explicit[3 * k + 2]; }
+        else {
+          const double *R = A.poses->R[slot], *t = A.poses->p[slot];
+#pragma unroll
+          for (int r = 0; r < 3; r++)
+            pw[r] = __dadd_rn(fma_off(fma_off(__dmul_rn(R[0 * 3 + r], pv->pnt[0]), R[1 * 3 + r], pv->pnt[1]), R[2 * 3 + r], pv->pnt[2]), t[r]);
+        }
+      }
+      double *row = tile + lane * ACC_ROW;
+#pragma unroll
+      for (int q = 0; q < 3; q++) row[q] = pv->pnt[q];
+#pragma unroll
+      for (int q = 0; q < 9; q++) row[3 + q] = pv->var[q];
+#pragma unroll
+      for (int q = 0; q < 3; q++) row[12 + q] = pw[q];
+    }
+    __syncwarp();
+    for (int q = 0; q < cnt; q++) {
+      const double *row = tile + q * ACC_ROW;
+      const double *pw = row + 12, *var = row + 3;
+      if (lane < 9) run = __dadd_rn(run, mom_entry(lane, slot < 0 ? pw : row));
+      double *bs = bi_s[wib][par];
+      if (with_cov && lane < 18) {                      // Bi(a, j) and (Bi * var)(a, k), one entry per lane
+        const int aa = lane / 3, j = lane - 3 * aa;
+        bs[lane] = bi_entry(aa, j, pw);
+        bs[18 + lane] = biup_entry(aa, j, var, pw);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < 3; t++) {
+        if (kind[t] == 0) a[t] = __dadd_rn(a[t], mom_entry(i1[t], pw));
+        else if (with_cov) {
+          if (kind[t] == 1) {
+            const double *u = bs + i1[t], *w = bs + i2[t];
+            a[t] = __dadd_rn(a[t], fma_off(fma_off(__dmul_rn(u[0], w[0]), u[1], w[1]), u[2], w[2]));
+          } else if (kind[t] == 2) a[t] = __dadd_rn(a[t], bs[i1[t]]);
+          else if (kind[t] == 3) a[t] = __dadd_rn(a[t], row[i1[t]]);
+        }
+      }
+      par ^= 1;                                          // the next point writes the other staging buffer
+    }
+  }
+  double *p = part + (int64_t)item * ACC_PART;
+#pragma unroll
+  for (int t = 0; t < 3; t++) if (lane + 32 * t < 90) p[lane + 32 * t] = a[t];
+  if (lane < 9) p[90 + lane] = run;
+  if (lane == 0) p[99] = (double)(e - b);
+}
+
+__global__ void __launch_bounds__(32 * ACC_WARPS) k_acc_final(const int32_t *__restrict__ sval, const int32_t *__restrict__ seg_start,
+                                                              const int32_t *__restrict__ seg_leaf, int nseg, const int32_t *__restrict__ item_incl,
+                                                              const int32_t *__restrict__ item_start, int nitems, const double *__restrict__ part, AccArgs A,
+                                                              NodeMeta *__restrict__ meta, Mom *__restrict__ add, Mom *__restrict__ fix, Mom *__restrict__ loc,
+                                                              double *__restrict__ cov) {
+  const int lane = threadIdx.x & 31;
+  const int seg = blockIdx.x * ACC_WARPS + (threadIdx.x >> 5);
+  if (seg >= nseg) return;
+  const int32_t leaf = seg_leaf[seg];
+  const int it0 = item_incl[seg_start[seg]] - 1;
+  const int it1 = seg + 1 < nseg ? item_incl[seg_start[seg + 1]] - 1 : nitems;
+  double *addv = reinterpret_cast<double *>(&add[leaf]);
   double *covv = cov + (int64_t)leaf * 81;
   double a[3];
-  int comp[3];
+#pragma unroll
+  for (int t = 0; t < 3; t++) { const int c = lane + 32 * t; a[t] = c < 9 ? addv[c] : (c < 90 ? covv[c - 9] : 0.0); }
+  int n_add = 0, n_win = 0;
+  for (int it = it0; it < it1; it++) {
+    const double *p = part + (int64_t)it * ACC_PART;
+#pragma unroll
+    for (int t = 0; t < 3; t++) if (lane + 32 * t < 90) a[t] = __dadd_rn(a[t], p[lane + 32 * t]);
+    int64_t k;
+    const int slot = slot_of(A, sval[item_start[it]], k);
+    const int n = (int)p[99];
+    Mom &tgt = slot < 0 ? fix[leaf] : loc[(int64_t)leaf * A.W + A.ss.phys[slot]];
+    if (lane < 9) { double *tv = reinterpret_cast<double *>(&tgt); tv[lane] = __dadd_rn(tv[lane], p[90 + lane]); }
+    if (lane == 0) tgt.N += n;
+    __syncwarp();
+    n_add += n;
+    if (slot >= 0) n_win += n;
+  }
 #pragma unroll
   for (int t = 0; t < 3; t++) {
-    comp[t] = lane + 32 * t;
-    a[t] = comp[t] < 9 ? addv[comp[t]] : (comp[t] < 90 ? covv[comp[t] - 9] : 0.0);
-  }
-  int run_slot = -2;              // -2 none, -1 pcr_fix, >= 0 window position i
-  double run = 0.0;
-  int run_n = 0, n_add = 0, n_win = 0;
-  auto flush = [&]() {
-    if (run_slot == -2) return;
-    Mom &tgt = run_slot < 0 ? fix[leaf] : loc[(int64_t)leaf * A.W + A.ss.phys[run_slot]];
-    if (lane < 9) reinterpret_cast<double *>(&tgt)[lane] = run;
-    if (lane == 0) tgt.N += run_n;
-  };
-  for (int32_t j = b; j < e; j++) {
-    const int64_t g = sval[j];
-    int slot = -1;
-    const vx_point_var *pv;
-    double pw[3];
-    if (g < A.n_fix_range) {
-      pv = A.fix_pts + g;
-      pw[0] = pv->pnt[0]; pw[1] = pv->pnt[1]; pw[2] = pv->pnt[2];
-    } else {
-      const int64_t gw = g - A.n_fix_range;
-      slot = 0;
-      while (slot + 1 < A.ss.n && gw >= A.ss.beg[slot + 1]) slot++;
-      const int64_t k = gw - A.ss.beg[slot];
-      pv = A.ss.pts[slot] + k;
-      if (A.pw_explicit) { pw[0] = A.pw_explicit[3 * k]; pw[1] = A.pw_explicit[3 * k + 1]; pw[2] = A.pw_explicit[3 * k + 2]; }
-      else {
-        const double *R = A.poses->R[slot], *t = A.poses->p[slot];
-#pragma unroll
-        for (int r = 0; r < 3; r++)
-          pw[r] = __dadd_rn(fma_off(fma_off(__dmul_rn(R[0 * 3 + r], pv->pnt[0]), R[1 * 3 + r], pv->pnt[1]), R[2 * 3 + r], pv->pnt[2]), t[r]);
-      }
-    }
-    if (slot != run_slot) {
-      flush();
-      run_slot = slot;
-      const Mom &tgt = slot < 0 ? fix[leaf] : loc[(int64_t)leaf * A.W + A.ss.phys[slot]];
-      run = lane < 9 ? reinterpret_cast<const double *>(&tgt)[lane] : 0.0;
-      run_n = 0;
-    }
-    if (lane < 9) run = __dadd_rn(run, mom_entry(lane, slot < 0 ? pw : pv->pnt));
-    run_n++;
-    n_add++;
-    if (slot >= 0) n_win++;
-    const bool with_cov = !(slot < 0 && A.fix_novar);
-#pragma unroll
-    for (int t = 0; t < 3; t++) {
-      const int c = comp[t];
-      if (c < 9) a[t] = __dadd_rn(a[t], mom_entry(c, pw));
-      else if (c < 90 && with_cov) { const int q = c - 9; a[t] = __dadd_rn(a[t], bf_entry(q % 9, q / 9, pv->var, pw)); }
-    }
-  }
-  flush();
-#pragma unroll
-  for (int t = 0; t < 3; t++) {
-    if (comp[t] < 9) addv[comp[t]] = a[t];
-    else if (comp[t] < 90) covv[comp[t] - 9] = a[t];
+    const int c = lane + 32 * t;
+    if (c < 9) addv[c] = a[t];
+    else if (c < 90) covv[c - 9] = a[t];
   }
   if (lane == 0) {
     add[leaf].N += n_add;
     if (n_win > 0) { meta[leaf].has_sw = 1; meta[leaf].isexist = 1; }   // push: sw allocated, isexist = true (:1108-1125)
-  }
-  // the points now live in `leaf`
-  for (int32_t j = b + lane; j < e; j += 32) {
-    const int64_t g = sval[j];
-    if (g < A.n_fix_range) { if (A.fix_leaf) A.fix_leaf[g] = leaf; }
-    else {
-      const int64_t gw = g - A.n_fix_range;
-      int slot = 0;
-      while (slot + 1 < A.ss.n && gw >= A.ss.beg[slot + 1]) slot++;
-      A.ss.leaf[slot][gw - A.ss.beg[slot]] = leaf;
-    }
   }
 }
 
@@ -579,9 +668,25 @@ int place_points(vx_map *m, const double *d_xyz, int stride, int64_t n, bool fix
 int launch_accumulate(vx_map *m, int nseg, const int32_t *seg_leaf, const AccArgs &A) {
   if (nseg == 0) return VX_OK;
   vx_ctx *ctx = m->ctx;
-  VX_KERNEL(ctx, "k_accumulate", k_accumulate<<<blocks_for((int64_t)nseg * 32, 128), 128, 0, ctx->stream>>>(m->w_val1.as<int32_t>(), m->w_seg.as<int32_t>(), seg_leaf, nseg, A,
-                                                                                                           m->meta.as<NodeMeta>(), m->add.as<Mom>(), m->fix.as<Mom>(),
-                                                                                                           m->loc.as<Mom>(), m->cov.as<double>()));
+  cudaStream_t st = ctx->stream;
+  // sorted layout at this point: w_val1 = point refs, w_seg = segment starts (nseg + 1), w_scan = inclusive segment id per position
+  int32_t n_valid = 0;
+  VX_TRY(read_i32(ctx, m->w_seg.as<int32_t>() + nseg, &n_valid));
+  if (n_valid == 0) return VX_OK;
+  int32_t *item_flag = m->w_flag.as<int32_t>();
+  int32_t *item_incl = reinterpret_cast<int32_t *>(m->w_key0.p);                // w_key0 is free once the sort is done
+  int32_t *item_start = item_incl + (n_valid + 2);
+  VX_KERNEL(ctx, "k_item_heads", k_item_heads<<<blocks_for(n_valid, 256), 256, 0, st>>>(m->w_val1.as<int32_t>(), m->w_scan.as<int32_t>(), m->w_seg.as<int32_t>(), n_valid, A, item_flag));
+  VX_TRY(scan_incl(m, item_flag, item_incl, n_valid));
+  int32_t nitems = 0;
+  VX_TRY(read_i32(ctx, item_incl + (n_valid - 1), &nitems));
+  VX_KERNEL(ctx, "k_item_starts", k_item_starts<<<blocks_for(n_valid, 256), 256, 0, st>>>(item_flag, item_incl, n_valid, item_start));
+  VX_TRY(m->w_part.reserve(sizeof(double) * ACC_PART * (size_t)nitems));
+  VX_KERNEL(ctx, "k_acc_items", k_acc_items<<<blocks_for(nitems, ACC_WARPS), 32 * ACC_WARPS, 0, st>>>(m->w_val1.as<int32_t>(), item_start, nitems, m->w_scan.as<int32_t>(), seg_leaf, A,
+                                                                                                   m->w_part.as<double>()));
+  VX_KERNEL(ctx, "k_acc_final", k_acc_final<<<blocks_for(nseg, ACC_WARPS), 32 * ACC_WARPS, 0, st>>>(m->w_val1.as<int32_t>(), m->w_seg.as<int32_t>(), seg_leaf, nseg, item_incl, item_start,
+                                                                                                 nitems, m->w_part.as<double>(), A, m->meta.as<NodeMeta>(), m->add.as<Mom>(),
+                                                                                                 m->fix.as<Mom>(), m->loc.as<Mom>(), m->cov.as<double>()));
   return VX_OK;
 }
 
@@ -1063,6 +1168,33 @@ int fix_append(vx_map *m, const vx_point_var *d_pts, const int32_t *d_lab, int64
 }
 }  // namespace
 
+// shared body of the two window-insertion entry points: `fill` puts the n pointVar records at d_pts and the world points at d_pw
+template <class Fill>
+static int cut_voxel_impl(vx_ctx *ctx, vx_map *m, int64_t n, int ord, Fill fill) {
+  cudaStream_t st = ctx->stream;
+  const int s = m->mp[ord];
+  const int64_t base = m->slot_n[s];
+  // the scan joins its physical slot (appended: a slot that multi_margi skipped keeps its stale points, voxelslam.cpp:1616-1617)
+  VX_TRY(grow_keep(ctx, m->slot_pts[s], sizeof(vx_point_var) * base, sizeof(vx_point_var) * (base + n)));
+  VX_TRY(grow_keep(ctx, m->slot_leaf[s], sizeof(int32_t) * base, sizeof(int32_t) * (base + n)));
+  vx_point_var *d_pts = m->slot_pts[s].as<vx_point_var>() + base;
+  int32_t *d_leaf = m->slot_leaf[s].as<int32_t>() + base;
+  VX_TRY(m->w_pw.reserve(sizeof(double) * 3 * n));
+  double *d_pw = m->w_pw.as<double>();
+  VX_TRY(fill(d_pts, d_pw));
+  VX_CUDA(cudaMemsetAsync(d_leaf, 0xff, sizeof(int32_t) * n, st));
+  int nroot = 0, nseg = 0; bool early = false;
+  VX_TRY(place_points(m, d_pw, 3, n, false, 0.0, m->prm.thread_num, &nroot, &nseg, &early));
+  if (early) return VX_OK;                     // voxel_map.hpp:2044-2045: nothing is inserted
+  AccArgs A;
+  std::memset(&A, 0, sizeof(A));
+  A.ss.n = 1; A.ss.pts[0] = d_pts; A.ss.leaf[0] = d_leaf; A.ss.beg[0] = 0; A.ss.beg[1] = n; A.ss.phys[0] = s;
+  A.n_fix_range = 0; A.pw_explicit = d_pw; A.W = m->W;
+  VX_TRY(launch_accumulate(m, nseg, misc_of(m, n).c, A));
+  m->slot_n[s] = base + n;
+  return VX_OK;
+}
+
 extern "C" {
 
 int vx_map_create(vx_ctx *ctx, const vx_map_params *params, vx_map **out) {
@@ -1084,7 +1216,7 @@ int vx_map_free(vx_map *m) {
   cudaSetDevice(m->ctx->device);
   cudaStreamSynchronize(m->ctx->stream);
   for (DevBuf *b : {&m->hkeys, &m->hvals, &m->nodes, &m->meta, &m->add, &m->fix, &m->loc, &m->cov, &m->eig, &m->flag_a, &m->flag_b, &m->fix_pts, &m->fix_leaf,
-                    &m->w_key0, &m->w_key1, &m->w_val0, &m->w_val1, &m->w_flag, &m->w_scan, &m->w_seg, &m->w_misc, &m->w_cnt})
+                    &m->w_key0, &m->w_key1, &m->w_val0, &m->w_val1, &m->w_flag, &m->w_scan, &m->w_seg, &m->w_misc, &m->w_cnt, &m->w_part, &m->w_pw, &m->w_xyz})
     b->release();
   for (auto &b : m->slot_pts) b.release();
   for (auto &b : m->slot_leaf) b.release();
@@ -1118,33 +1250,29 @@ int vx_map_cut_voxel(vx_ctx *ctx, vx_map *m, const vx_point_var *pvec, const dou
   VX_TRY(bind(ctx));
   if (n == 0) return VX_OK;
   cudaStream_t st = ctx->stream;
-  const int s = m->mp[ord];
-  const int64_t base = m->slot_n[s];
-  // the scan joins its physical slot (appended: a slot that multi_margi skipped keeps its stale points, voxelslam.cpp:1616-1617)
-  VX_TRY(grow_keep(ctx, m->slot_pts[s], sizeof(vx_point_var) * base, sizeof(vx_point_var) * (base + n)));
-  VX_TRY(grow_keep(ctx, m->slot_leaf[s], sizeof(int32_t) * base, sizeof(int32_t) * (base + n)));
-  vx_point_var *d_pts = m->slot_pts[s].as<vx_point_var>() + base;
-  int32_t *d_leaf = m->slot_leaf[s].as<int32_t>() + base;
-  DevBuf d_pw;
-  VX_TRY(d_pw.reserve(sizeof(double) * 3 * n));
-  auto body = [&]() -> int {
+  const int rc = cut_voxel_impl(ctx, m, n, ord, [&](vx_point_var *d_pts, double *d_pw) -> int {
     VX_CUDA(cudaMemcpyAsync(d_pts, pvec, sizeof(vx_point_var) * n, cudaMemcpyHostToDevice, st));
-    VX_CUDA(cudaMemcpyAsync(d_pw.p, pwld, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
-    VX_CUDA(cudaMemsetAsync(d_leaf, 0xff, sizeof(int32_t) * n, st));
-    int nroot = 0, nseg = 0; bool early = false;
-    VX_TRY(place_points(m, d_pw.as<double>(), 3, n, false, 0.0, m->prm.thread_num, &nroot, &nseg, &early));
-    if (early) return VX_OK;                     // voxel_map.hpp:2044-2045: nothing is inserted
-    AccArgs A;
-    std::memset(&A, 0, sizeof(A));
-    A.ss.n = 1; A.ss.pts[0] = d_pts; A.ss.leaf[0] = d_leaf; A.ss.beg[0] = 0; A.ss.beg[1] = n; A.ss.phys[0] = s;
-    A.n_fix_range = 0; A.pw_explicit = d_pw.as<double>(); A.W = m->W;
-    VX_TRY(launch_accumulate(m, nseg, misc_of(m, n).c, A));
-    m->slot_n[s] = base + n;
+    VX_CUDA(cudaMemcpyAsync(d_pw, pwld, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, st));
     return VX_OK;
-  };
-  const int rc = body();
+  });
   cudaStreamSynchronize(st);
-  d_pw.release();
+  return rc;
+}
+
+int vx_map_cut_voxel_xyz(vx_ctx *ctx, vx_map *m, const float *xyz, int64_t n, const vx_pose *ext, double dept_err, double beam_err, const vx_pose *x,
+                         const double *rot_var9, const double *tsl_var9, int ord) {
+  VX_ARG(ctx && m && m->ctx == ctx && n >= 0 && ord >= 0 && ord < m->W && ext && x && rot_var9 && tsl_var9 && (n == 0 || xyz));
+  VX_TRY(bind(ctx));
+  if (n == 0) return VX_OK;
+  cudaStream_t st = ctx->stream;
+  const int rc = cut_voxel_impl(ctx, m, n, ord, [&](vx_point_var *d_pts, double *d_pw) -> int {
+    VX_TRY(m->w_xyz.reserve(sizeof(float) * 3 * n));
+    VX_CUDA(cudaMemcpyAsync(m->w_xyz.p, xyz, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st));
+    VX_TRY(var_init_device(ctx, m->w_xyz.as<float>(), n, *ext, dept_err, beam_err, d_pts));        // voxelslam.cpp:1896
+    VX_TRY(pvec_update_device(ctx, d_pts, n, *x, rot_var9, tsl_var9, d_pts, d_pw));                 // voxelslam.cpp:1903
+    return VX_OK;
+  });
+  cudaStreamSynchronize(st);
   return rc;
 }
 

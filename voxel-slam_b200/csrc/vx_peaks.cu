@@ -39,11 +39,43 @@ __global__ void __launch_bounds__(256) k_peak_dmma(double *out, int iters, doubl
   for (int k = 0; k < 8; k++) s += c[k][0] + c[k][1];
   out[blockIdx.x * (size_t)blockDim.x + threadIdx.x] = s;
 }
+// mode 2: even warps run the DFMA body, odd warps the DMMA body, same iteration count: if the two instruction classes had
+// separate pipes the combined rate would approach the sum of modes 0 and 1; if they share the FP64 datapath it stays near one.
+__global__ void __launch_bounds__(256) k_peak_mixed(double *out, int iters, double a, double b) {
+  double r = 0.0;
+  if (((threadIdx.x >> 5) & 1) == 0) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 1
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+        x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+      }
+    }
+    r = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  } else {
+    double c[8][2];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { c[k][0] = threadIdx.x + k; c[k][1] = k; }
+#pragma unroll 1
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) dmma(c[k][0], c[k][1], a, b);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) r += c[k][0] + c[k][1];
+  }
+  out[blockIdx.x * (size_t)blockDim.x + threadIdx.x] = r;
+}
 }  // namespace
 
 extern "C" int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops) {
   VX_TRY(vx::bind(ctx));
-  VX_ARG(tflops != nullptr && (mode == 0 || mode == 1));
+  VX_ARG(tflops != nullptr && mode >= 0 && mode <= 2);
   const int blocks = ctx->sm_count * 8, threads = 256, iters = 4096;
   VX_TRY(ctx->scratch.reserve(sizeof(double) * (size_t)blocks * threads));
   cudaEvent_t e0, e1;
@@ -53,14 +85,17 @@ extern "C" int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops) {
   for (int rep = 0; rep < 4; rep++) {
     VX_CUDA(cudaEventRecord(e0, ctx->stream));
     if (mode == 0) k_peak_dfma<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch.as<double>(), iters, 0.999999, 1e-9);
-    else k_peak_dmma<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch.as<double>(), iters, 0.999999, 1e-9);
+    else if (mode == 1) k_peak_dmma<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch.as<double>(), iters, 0.999999, 1e-9);
+    else k_peak_mixed<<<blocks, threads, 0, ctx->stream>>>(ctx->scratch.as<double>(), iters, 0.999999, 1e-9);
     VX_LAUNCH_CHECK(ctx);
     VX_CUDA(cudaEventRecord(e1, ctx->stream));
     VX_CUDA(cudaEventSynchronize(e1));
     float ms = 0.f;
     VX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
     // mode 0: 64 FMA per thread-iteration = 128 flop; mode 1: 32 DMMA per warp-iteration x 512 flop
-    double flop = mode == 0 ? (double)blocks * threads * iters * 128.0 : (double)blocks * (threads / 32) * iters * 32.0 * 512.0;
+    // mode 2: half the warps of each kind
+    const double f0 = (double)blocks * threads * iters * 128.0, f1 = (double)blocks * (threads / 32) * iters * 32.0 * 512.0;
+    double flop = mode == 0 ? f0 : (mode == 1 ? f1 : 0.5 * (f0 + f1));
     double tf = flop / (ms * 1e-3) / 1e12;
     if (rep > 0 && tf > best) best = tf;
   }
