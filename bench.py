@@ -297,6 +297,32 @@ def extra_benches(pkg, ctx):
     out["li_ba"] = {"ms_per_damping_iter_call": 1e3 * t, "lm_iterations": len(r["accept"]), "voxels": 2000, "win_size": Wl,
                     "what": "vx_ba_li (LI_BA_Optimizer::damping_iter, 3 LM iterations): device B1/B2 + host IMU factors and 150x150 LDL^T"}
     f2.free(); fl.free(); vm.free()
+    # --- C4-top shaped: one window over W = 399 submaps (2394 unknowns): B1 through the generic pair-list path + the blocked
+    #     device LDL^T of the LM solve (voxel_map.hpp:457-458)
+    Wt, Vt = 399, 20000
+    top = synth.batched_factor_csr(20241008 + 8, 1, Vt, Wt, occupancy=4.0 / Wt, min_frames=2, pts_max=12)
+    ft = pkg.Factor(ctx, Wt); ft.upload_csr(top)
+    ft.residual(top["poses"])
+    Ht, Jt, ct = ft.hessian(top["poses"])
+    t0 = time.perf_counter()
+    for _ in range(3):
+        Ht, Jt, ct = ft.hessian(top["poses"])
+    t_h = (time.perf_counter() - t0) / 3
+    n_t = 6 * Wt
+    At = Ht.copy(); At[:6, :] = 0; At[:, :6] = 0; At[np.arange(6), np.arange(6)] = 1.0
+    At[np.arange(n_t), np.arange(n_t)] *= 1.01
+    bt = -Jt.copy(); bt[:6] = 0
+    xs = pkg.ldlt_solve(ctx, At, bt)
+    t0 = time.perf_counter()
+    xs = pkg.ldlt_solve(ctx, At, bt)
+    t_s = time.perf_counter() - t0
+    sym = np.tril(At) + np.tril(At, -1).T
+    out["top_level_gba"] = {"win_size": Wt, "unknowns": n_t, "voxels": Vt, "voxel_frames": ft.num_voxel_frames,
+                            "ms_hessian_e2e": 1e3 * t_h, "ms_ldlt_solve_e2e": 1e3 * t_s, "ldlt_gflops": (n_t ** 3 / 3) / t_s / 1e9,
+                            "solve_residual_rel": float(np.abs(sym @ xs - bt).max() / max(np.abs(bt).max(), 1e-300)),
+                            "what": "vx_factor_hessian at W=399 (45.8 MB Hess to the host) and vx_ldlt_solve of the gauge-fixed damped system "
+                                    "(H2D 45.8 MB, blocked device LDL^T, D2H, host substitution), wall clock"}
+    ft.free()
     return out
 
 

@@ -227,6 +227,11 @@ int vx_ba_li(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imus, doubl
 int vx_ba_li_gravity(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imus, double imu_coef, double *resis2,
                      double *hess_out, int max_iter, int *accept_trace, int *n_iters);
 
+/* (Hess + u*D).ldlt().solve(b) the way vx_ba_lidar solves large windows (>= 384 unknowns): Eigen's diagonal-pivot order from
+ * the input diagonal, blocked right-looking LDL^T of the permuted LOWER triangle on the device, substitution on the host.
+ * A: n x n column-major host matrix (only its lower triangle is read). */
+int vx_ldlt_solve(vx_ctx *ctx, const double *A, int n, const double *b, double *x);
+
 /* ---- C1h: VOXEL_SLAM::HBA_add_edge(p_xs, p_smps, gba_edges, maps, max_iter, thread_num, plptr)
  * voxelslam.cpp:2822-3015 (the session filter :2836-2857 stays with the caller: pass only connected frames).
  * For every window: up to max_iter outer iterations of {rebuild the GBA voxel map at the current poses,

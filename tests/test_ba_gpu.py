@@ -79,3 +79,37 @@ def test_ba_lidar_batched_windows(pkg, ob, ctx):
         assert rel(out["resis"][b], ref["resis"]) < 1e-8
         assert pose_err(out["poses"][b * W:(b + 1) * W], ref["poses"]) < 1e-8
     f.free()
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 64, 200, 777])
+def test_device_ldlt_matches_oracle(pkg, ob, ctx, n):
+    # the blocked device LDL^T (csrc/vx_ldlt.cu) against the oracle's sequential Eigen-style sweep, on a matrix that is NOT
+    # exactly symmetric (only the lower triangle may be read) with a diagonal that forces non-trivial pivot orders and ties
+    rng = np.random.Generator(np.random.PCG64(n))
+    M = rng.normal(size=(n, n + 3))
+    A = M @ M.T + np.diag(rng.uniform(0.1, 50.0, n))
+    if n > 4:
+        A[3, 3] = A[1, 1]                       # a tie on the diagonal: first index wins
+    A_low = A.copy()
+    A_bad = A.copy(); A_bad[np.triu_indices(n, 1)] += rng.normal(size=n * (n - 1) // 2)   # garbage above the diagonal
+    b = rng.normal(size=n)
+    want = ob.ldlt_solve(A_low, b)
+    got = pkg.ldlt_solve(ctx, A_bad, b)
+    assert np.abs(got - want).max() <= 1e-10 * np.abs(want).max()
+    sym = np.tril(A) + np.tril(A, -1).T
+    assert np.abs(sym @ got - b).max() <= 1e-9 * np.abs(b).max() * np.linalg.cond(sym) ** 0.5
+
+
+def test_ba_large_window_uses_device_solve(pkg, ob, ctx):
+    # W = 64 -> 384 unknowns: vx_ba_lidar factorises on the device; same LM trace and poses as the oracle
+    W, V = 64, 1500
+    fac = synth.random_factor(3100, V, W, occupancy=0.06, min_frames=2, pts_per_frame=(6, 20))
+    start = synth.perturb_poses(fac["poses"], 5, 0.003, 0.02)
+    of = ob.Factor(W); of.set_dense(fac)
+    f = pkg.Factor(ctx, W); f.upload_dense(fac)
+    of.residual(start); f.residual(start)
+    a = f.ba_lidar(start, max_iter=3, thd_num=2)
+    b = of.ba_lidar(start, max_iter=3, thd_num=2)
+    assert a["accept"][0] == b["accept"] and 1 in b["accept"]
+    assert np.abs(a["poses"]["R"] - b["poses"]["R"]).max() < 1e-8 and np.abs(a["poses"]["p"] - b["poses"]["p"]).max() < 1e-8
+    f.free()

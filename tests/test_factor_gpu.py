@@ -185,3 +185,27 @@ def test_upload_csr_validation_on_device(pkg, ctx):
     f.upload_csr(good)                                  # still usable afterwards
     assert np.isfinite(f.residual(good["poses"])).all()
     f.free()
+
+
+def test_top_level_window_regime(pkg, ob, ctx):
+    # C4-top: one problem over W ~ 399 submaps (voxelslam.cpp:3102-3127); every voxel is seen by a handful of frames
+    # (k << W), Hess is 2394 x 2394.  The generic pair-list path carries it (the fused small-window kernel is W <= 20).
+    W, V = 399, 900
+    fac = synth.random_factor(9001, V, W, occupancy=0.008, min_frames=2, pts_per_frame=(6, 20))
+    poses = synth.perturb_poses(fac["poses"], 11, 0.01, 0.03)
+    of = ob.Factor(W); of.set_dense(fac)
+    f = pkg.Factor(ctx, W); f.upload_dense(fac)
+    k = f.num_voxel_frames / V
+    assert 2 <= k < 8
+    rc, rg = of.residual(poses), f.residual(poses)
+    assert abs(rg - rc) <= 1e-9 * abs(rc)
+    Ho, Jo, co = of.hessian(poses)
+    H, J, c = f.hessian(poses)
+    assert H.shape == (6 * W, 6 * W)
+    assert abs(c - co) <= 1e-9 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+    # block sparsity: a frame pair without a common voxel has an exactly zero block
+    occ = fac["plvec"]["N"] != 0
+    common = (occ.T.astype(np.int32) @ occ.astype(np.int32)) > 0
+    Hb = np.abs(H.reshape(W, 6, W, 6)).max(axis=(1, 3))
+    assert not Hb[~common].any() and (Hb[common] > 0).all()
+    f.free()

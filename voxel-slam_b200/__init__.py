@@ -211,6 +211,14 @@ lio_state_dtype = np.dtype([("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8",
 assert map_node_dtype.itemsize == 408 and lio_state_dtype.itemsize == 8 * (21 + 225)
 
 
+def ldlt_solve(ctx, A, b):
+    """vx_ldlt_solve: Eigen-style LDL^T solve of the system defined by the LOWER triangle of A, factorised on the device."""
+    A = np.asarray(A, dtype=np.float64); n = A.shape[0]
+    Ac = np.ascontiguousarray(A.T); bb = np.ascontiguousarray(b, dtype=np.float64); x = np.zeros(n)
+    _chk(ctx.lib.vx_ldlt_solve(ctx.h, _p(Ac), C.c_int(n), _p(bb), _p(x)))
+    return x
+
+
 def var_init(ctx, xyz, ext, dept_err, beam_err):
     """calcBodyVar + var_init (voxelslam.hpp:180-234) on the device -> (n,12): pnt 3 + var 9 (col-major)."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32); n = xyz.shape[0]
