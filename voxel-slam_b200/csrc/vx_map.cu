@@ -420,6 +420,26 @@ __global__ void k_item_starts(const int32_t *__restrict__ flag, const int32_t *_
   if (j == n_valid - 1) item_start[incl[j]] = (int32_t)n_valid;
 }
 
+// Every accumulated number is  sum_{m<3} u_m * w_m  with u, w taken from the point's row {pnt 3 | var 9 | pw 3 | 1 | 0} or from
+// the staged {Bi 18 | Bi*var 18}: a 6x6 entry is a 3-term dot product, a copied entry is u*1 + 0*0 + 0*0 (exact), a moment is
+// pw_i*pw_j (or pw_k*1).  The operand indices are per-lane constants, so the inner loop has no divergent control flow.
+struct AccOp { int16_t u[3], w[3]; };     // index < 64: into the row, >= 64: into the staging buffer (index - 64)
+__device__ __forceinline__ AccOp acc_op_for(int c) {
+  constexpr int ONE = 15, ZERO = 16, PW = 12, VAR = 3, BI = 64, BIUP = 64 + 18;
+  AccOp o;
+  for (int m = 0; m < 3; m++) { o.u[m] = ZERO; o.w[m] = ZERO; }
+  if (c < 6) { const int ix[6][2] = {{0, 0}, {0, 1}, {0, 2}, {1, 1}, {1, 2}, {2, 2}}; o.u[0] = PW + ix[c][0]; o.w[0] = PW + ix[c][1]; }
+  else if (c < 9) { o.u[0] = PW + (c - 6); o.w[0] = ONE; }
+  else if (c < 90) {
+    const int q = c - 9, r = q % 9, cc = q / 9;
+    if (r < 6 && cc < 6) { for (int m = 0; m < 3; m++) { o.u[m] = BIUP + r * 3 + m; o.w[m] = BI + cc * 3 + m; } }
+    else if (r < 6) { o.u[0] = BIUP + r * 3 + (cc - 6); o.w[0] = ONE; }
+    else if (cc < 6) { o.u[0] = BIUP + cc * 3 + (r - 6); o.w[0] = ONE; }
+    else { o.u[0] = VAR + (cc - 6) * 3 + (r - 6); o.w[0] = ONE; }
+  }
+  return o;
+}
+
 __global__ void __launch_bounds__(32 * ACC_WARPS) k_acc_items(const int32_t *__restrict__ sval, const int32_t *__restrict__ item_start, int nitems,
                                                               const int32_t *__restrict__ seg_incl, const int32_t *__restrict__ seg_leaf, AccArgs A,
                                                               double *__restrict__ part) {
@@ -434,19 +454,21 @@ __global__ void __launch_bounds__(32 * ACC_WARPS) k_acc_items(const int32_t *__r
   int64_t k0;
   const int slot = slot_of(A, sval[b], k0);          // one source per item
   double a[3] = {0.0, 0.0, 0.0}, run = 0.0;
-  int kind[3], i1[3], i2[3];     // kind 0: moment of pw, 1: 6x6 block (dot of two rows), 2: copy from Bi*var, 3: copy of var, 4: none
+  AccOp op[3];
 #pragma unroll
-  for (int t = 0; t < 3; t++) {
-    const int c = lane + 32 * t;
-    i1[t] = c; i2[t] = 0;
-    if (c < 9) kind[t] = 0;
-    else if (c < 90) {
-      const int q = c - 9, r = q % 9, cc = q / 9;
-      if (r < 6 && cc < 6) { kind[t] = 1; i1[t] = 18 + r * 3; i2[t] = cc * 3; }
-      else if (r < 6) { kind[t] = 2; i1[t] = 18 + r * 3 + (cc - 6); }
-      else if (cc < 6) { kind[t] = 2; i1[t] = 18 + cc * 3 + (r - 6); }
-      else { kind[t] = 3; i1[t] = 3 + (cc - 6) * 3 + (r - 6); }
-    } else kind[t] = 4;
+  for (int t = 0; t < 3; t++) op[t] = acc_op_for(lane + 32 * t);
+  // source-cluster moment of lanes 0..8: local pnt for window points, world pnt (= pnt) for fixed points
+  const AccOp rop = acc_op_for(lane < 9 ? lane : 0);
+  const int roff = slot < 0 ? 0 : -12;                // window: read pnt (row[0..2]) instead of pw (row[12..14])
+  // staging roles of lanes 0..17: Bi(aa, j) = cf * pw[ix] and (Bi var)(aa, j) = sum_m Bi(aa, m) var(m, j)
+  const int aa = (lane < 18 ? lane : 0) / 3, jj = (lane < 18 ? lane : 0) % 3;
+  double cf[3]; int ix[3];
+#pragma unroll
+  for (int m = 0; m < 3; m++) {
+    // rows of Bi: 0:(2x,0,0) 1:(y,x,0) 2:(z,0,x) 3:(0,2y,0) 4:(0,z,y) 5:(0,0,2z)   (voxel_map.hpp:108-113)
+    const int code = aa * 3 + m;
+    cf[m] = (code == 0 || code == 10 || code == 17) ? 2.0 : ((code == 3 || code == 4 || code == 6 || code == 8 || code == 13 || code == 14) ? 1.0 : 0.0);
+    ix[m] = (code == 0 || code == 4 || code == 8) ? 0 : ((code == 3 || code == 10 || code == 14) ? 1 : 2);
   }
   const bool with_cov = !(slot < 0 && A.fix_novar);
   int par = 0;
@@ -481,28 +503,31 @@ __global__ void __launch_bounds__(32 * ACC_WARPS) k_acc_items(const int32_t *__r
       for (int q = 0; q < 9; q++) row[3 + q] = pv->var[q];
 #pragma unroll
       for (int q = 0; q < 3; q++) row[12 + q] = pw[q];
+      row[15] = 1.0; row[16] = 0.0;
     }
     __syncwarp();
     for (int q = 0; q < cnt; q++) {
       const double *row = tile + q * ACC_ROW;
-      const double *pw = row + 12, *var = row + 3;
-      if (lane < 9) run = __dadd_rn(run, mom_entry(lane, slot < 0 ? pw : row));
       double *bs = bi_s[wib][par];
-      if (with_cov && lane < 18) {                      // Bi(a, j) and (Bi * var)(a, k), one entry per lane
-        const int aa = lane / 3, j = lane - 3 * aa;
-        bs[lane] = bi_entry(aa, j, pw);
-        bs[18 + lane] = biup_entry(aa, j, var, pw);
+      if (with_cov && lane < 18) {
+        const double b0 = __dmul_rn(cf[0], row[12 + ix[0]]), b1 = __dmul_rn(cf[1], row[12 + ix[1]]), b2 = __dmul_rn(cf[2], row[12 + ix[2]]);
+        bs[lane] = jj == 0 ? b0 : (jj == 1 ? b1 : b2);
+        bs[18 + lane] = fma_off(fma_off(__dmul_rn(b0, row[3 + jj * 3 + 0]), b1, row[3 + jj * 3 + 1]), b2, row[3 + jj * 3 + 2]);
       }
+      if (lane < 9) run = __dadd_rn(run, __dmul_rn(row[rop.u[0] + roff], row[rop.w[0] == 15 ? 15 : rop.w[0] + roff]));
       __syncwarp();
 #pragma unroll
       for (int t = 0; t < 3; t++) {
-        if (kind[t] == 0) a[t] = __dadd_rn(a[t], mom_entry(i1[t], pw));
-        else if (with_cov) {
-          if (kind[t] == 1) {
-            const double *u = bs + i1[t], *w = bs + i2[t];
-            a[t] = __dadd_rn(a[t], fma_off(fma_off(__dmul_rn(u[0], w[0]), u[1], w[1]), u[2], w[2]));
-          } else if (kind[t] == 2) a[t] = __dadd_rn(a[t], bs[i1[t]]);
-          else if (kind[t] == 3) a[t] = __dadd_rn(a[t], row[i1[t]]);
+        if (t < 2 || lane < 26) {                       // components 0..89
+          if (with_cov || lane + 32 * t < 9) {
+            const double *pu0 = op[t].u[0] < 64 ? row + op[t].u[0] : bs + (op[t].u[0] - 64);
+            const double *pu1 = op[t].u[1] < 64 ? row + op[t].u[1] : bs + (op[t].u[1] - 64);
+            const double *pu2 = op[t].u[2] < 64 ? row + op[t].u[2] : bs + (op[t].u[2] - 64);
+            const double *pw0 = op[t].w[0] < 64 ? row + op[t].w[0] : bs + (op[t].w[0] - 64);
+            const double *pw1 = op[t].w[1] < 64 ? row + op[t].w[1] : bs + (op[t].w[1] - 64);
+            const double *pw2 = op[t].w[2] < 64 ? row + op[t].w[2] : bs + (op[t].w[2] - 64);
+            a[t] = __dadd_rn(a[t], fma_off(fma_off(__dmul_rn(*pu0, *pw0), *pu1, *pw1), *pu2, *pw2));
+          }
         }
       }
       par ^= 1;                                          // the next point writes the other staging buffer
