@@ -171,6 +171,15 @@ typedef struct vx_gba_params {
 int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
                  const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
 
+/* Multi-GPU voxelization (one exchange step): every rank keys its slice of points and routes each to the rank that owns its
+ * ROOT voxel, owner = mix64(packed root key) mod n_ranks, so that a root voxel — and therefore every (leaf, frame) cluster
+ * under it — lives on exactly one rank; sort / segment / moments / recut are then local and Hess is a sum over ranks.
+ * d_* are DEVICE pointers (the all-to-all between the two calls is NCCL's, on the same buffers); poses / cloud_off are host. */
+int vx_gba_point_owner(vx_ctx *ctx, const float *d_xyz, const int32_t *d_frame, int64_t n, const vx_pose *poses, int n_frames,
+                       double voxel_size, int n_ranks, int32_t *d_owner);
+int vx_gba_build_device(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                        const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
+
 /* ---- B3: Lidar_BA_Optimizer::damping_iter(x_stats, voxhess, hess*, resis, max_iter, is_display)
  * voxel_map.hpp:422-497.  Levenberg-Marquardt on 6W unknowns per window: u=0.01, v=2 (:427), *hess
  * snapshot before the gauge fix (:446), pose 0 fixed (:452-455), (Hess + u*diag(Hess)).ldlt().solve(-JacT)

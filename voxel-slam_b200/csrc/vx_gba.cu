@@ -542,3 +542,54 @@ extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_
   d_xyz.release(); d_coff.release();
   return s;
 }
+
+// ---- multi-GPU voxelization: key every point, route it to the rank that owns its ROOT voxel ----------
+#include "vx_planemap.cuh"   // mix64
+namespace {
+__global__ void k_point_owner(const float *__restrict__ xyz, const int32_t *__restrict__ frame, int64_t n, const double *__restrict__ poses, double vs,
+                              int n_ranks, int32_t *__restrict__ owner, int *__restrict__ bad) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const d3 w = world_of(poses + 12 * (int64_t)frame[i], (double)xyz[3 * i], (double)xyz[3 * i + 1], (double)xyz[3 * i + 2]);
+  uint64_t k;
+  if (!pack_key(key_axis_d(w.x, vs), key_axis_d(w.y, vs), key_axis_d(w.z, vs), k)) *bad = 1;
+  owner[i] = (int32_t)(mix64(k) % (uint64_t)n_ranks);
+}
+}  // namespace
+
+// All pointers except `poses` are DEVICE pointers (the exchange that follows is an NCCL all-to-all on those buffers).
+// owner[i] = mix64(packed root key of R_f p_i + t_f at `voxel_size`) mod n_ranks: every root voxel lives on exactly one rank.
+extern "C" int vx_gba_point_owner(vx_ctx *ctx, const float *d_xyz, const int32_t *d_frame, int64_t n, const vx_pose *poses, int n_frames,
+                                  double voxel_size, int n_ranks, int32_t *d_owner) {
+  VX_ARG(ctx && poses && n >= 0 && n_frames >= 1 && n_ranks >= 1 && voxel_size > 0 && (n == 0 || (d_xyz && d_frame && d_owner)));
+  VX_TRY(bind(ctx));
+  if (n == 0) return VX_OK;
+  VX_TRY(ctx->scratch.reserve(sizeof(double) * 12 * n_frames + 64));
+  double *d_poses = ctx->scratch.as<double>();
+  int *d_bad = reinterpret_cast<int *>(d_poses + 12 * (size_t)n_frames);
+  VX_CUDA(cudaMemcpyAsync(d_poses, poses, sizeof(vx_pose) * n_frames, cudaMemcpyHostToDevice, ctx->stream));
+  VX_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), ctx->stream));
+  VX_KERNEL(ctx, "k_point_owner", k_point_owner<<<blocks_for(n, 256), 256, 0, ctx->stream>>>(d_xyz, d_frame, n, d_poses, voxel_size, n_ranks, d_owner, d_bad));
+  int bad = 0;
+  VX_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (bad) { set_error("vx_gba_point_owner: a cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+  return VX_OK;
+}
+
+// vx_gba_build on DEVICE-resident clouds (d_xyz: float triples; cloud_off: HOST offsets, n_clouds + 1).
+extern "C" int vx_gba_build_device(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
+  VX_ARG(cloud_off != nullptr && n_clouds >= 1);
+  VX_TRY(bind(ctx));
+  DevBuf d_coff;
+  auto body = [&]() -> int {
+    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
+    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
+    return gba_build_impl(ctx, d_xyz, d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f);
+  };
+  const int s = body();
+  cudaStreamSynchronize(ctx->stream);
+  d_coff.release();
+  return s;
+}
