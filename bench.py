@@ -497,6 +497,19 @@ def run_b200(args, rank, world, local_rank):
                                  "how": "vx_bench_fp64 (csrc/vx_peaks.cu), measured in this run; mixed < either alone: DFMA and DMMA share the FP64 datapath"}
     roofline["fp64"]["peak_tflops"] = extra["fp64_peak_tflops"]["dfma"]
     roofline["fp64"]["frac"] = roofline["fp64"]["achieved_tflops"] / extra["fp64_peak_tflops"]["dfma"]
+    # Which ceiling binds?  B1's algorithmic intensity (flops / bytes of this workload) against the ridge of the measured peaks:
+    # above the ridge the FP64 datapath is the roofline (DFMA and the m8n8k4 DMMA share it, see fp64_peak_tflops), below it HBM.
+    intensity = flops / alg_bytes
+    ridge = extra["fp64_peak_tflops"]["dfma"] * 1e12 / (peak * 1e9)
+    hbm_view = {k: roofline[k] for k in ("achieved", "peak", "unit", "frac", "peak_source")}
+    roofline["intensity_flop_per_byte"] = intensity
+    roofline["ridge_flop_per_byte"] = ridge
+    if intensity > ridge:
+        roofline.update({"bound": "tensor", "achieved": roofline["fp64"]["achieved_tflops"], "peak": roofline["fp64"]["peak_tflops"], "unit": "TFLOP/s",
+                         "frac": roofline["fp64"]["frac"],
+                         "peak_source": "FP64 datapath peak measured in this run by vx_bench_fp64 (DFMA; the DMMA figure is within 9 % and the two share "
+                                        "the datapath); MEASURED_PEAKS.json carries no FP64 number",
+                         "hbm": hbm_view})
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
