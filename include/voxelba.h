@@ -79,6 +79,9 @@ int vx_ctx_profile_read(vx_ctx *ctx, char *names, size_t names_cap, double *ms, 
  * mode 0 = DFMA on the CUDA cores, mode 1 = mma.sync m8n8k4 f64 on the tensor pipe, mode 2 = half the warps of each
  * (do the two share a datapath?).  TFLOP/s. */
 int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops);
+/* One warp, `ilp` (1, 2, 4, 8) independent dependent chains of DFMA (mma = 0) or DMMA m8n8k4 (mma = 1): clock cycles per
+ * instruction issued; ilp = 1 is the dependent-issue latency that sizes the parallelism phase A of B1 needs. */
+int vx_bench_fp64_latency(vx_ctx *ctx, int mma, int ilp, double *cycles_per_instr);
 
 /* ---- B0: LidarFactor storage -------------------------------------------------------------- */
 /* LidarFactor::LidarFactor(int _w)  voxel_map.hpp:136.  `n_windows` > 1 makes a BATCH of

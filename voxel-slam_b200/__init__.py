@@ -101,6 +101,12 @@ class Context:
         _chk(self.lib.vx_bench_fp64(self.h, C.c_int(mode), C.byref(t)))
         return t.value
 
+    def fp64_latency(self, mma=0, ilp=1):
+        """Cycles per instruction of one warp running `ilp` independent dependent chains of DFMA / DMMA."""
+        t = C.c_double(0)
+        _chk(self.lib.vx_bench_fp64_latency(self.h, C.c_int(mma), C.c_int(ilp), C.byref(t)))
+        return t.value
+
     def profile(self, enable=True):
         """Start (and clear) / stop per-kernel CUDA-event timing of this context's launches."""
         _chk(self.lib.vx_ctx_profile(self.h, C.c_int(int(enable))))

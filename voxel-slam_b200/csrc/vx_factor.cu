@@ -40,7 +40,7 @@ int factor_alloc(vx_factor *f, int64_t V, int64_t nnz) {
   VX_TRY(f->mrg.reserve(sizeof(double) * 10 * std::max<int64_t>(V, 1)));
   VX_TRY(f->win.reserve(sizeof(int32_t) * std::max<int64_t>(V, 1)));
   VX_TRY(f->wv_off.reserve(sizeof(int32_t) * (f->n_win + 1)));
-  VX_TRY(f->cS.reserve(sizeof(double) * 3 * std::max<int64_t>(V, 1)));
+  VX_TRY(f->cS.reserve(sizeof(double) * 7 * std::max<int64_t>(V, 1)));
   VX_TRY(f->res_v.reserve(sizeof(double) * std::max<int64_t>(V, 1)));
   VX_TRY(f->G.reserve(sizeof(double) * 18 * std::max<int64_t>(nnz, 1)));
   VX_TRY(f->poses.reserve(sizeof(double) * 12 * F));
@@ -362,6 +362,39 @@ k_cost(const double *__restrict__ src, const double *__restrict__ coe, const int
   if (threadIdx.x == 0) cost[w] = sh[0];
 }
 
+// The fused small-window path wants every per-voxel division done once per voxel, not once per voxel-frame: this is k_cost
+// (window cost from the cached eigenvalues) that also writes, per voxel of [head, end),
+//   prep[0..2] = coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}   (voxel_map.hpp:198-201, :265-268)
+//   prep[3..5] = vBar = v / NN,  prep[6] = 1 / NN          (voxel_map.hpp:193-195)
+__global__ void __launch_bounds__(256)
+k_cost_prep(const double *__restrict__ lam, const double *__restrict__ coe, const double *__restrict__ mrg, const int32_t *__restrict__ wv_off,
+            double *__restrict__ cost, double *__restrict__ prep, int64_t V, int64_t head, int64_t end) {
+  __shared__ double sh[256];
+  const int w = blockIdx.x;
+  int64_t b = wv_off[w], e = wv_off[w + 1];
+  if (b < head) b = head;
+  if (e > end) e = end;
+  double acc = 0.0;
+  for (int64_t v = b + threadIdx.x; v < e; v += 256) {
+    const double l0 = lam[v], l1 = lam[V + v], l2 = lam[2 * V + v], c = coe[v], NN = mrg[9 * V + v];
+    acc += c * l0;
+    prep[v] = c * (2.0 / (l0 - l1));
+    prep[V + v] = c * (2.0 / (l0 - l2));
+    prep[2 * V + v] = c * (-2.0 / NN / NN);
+    prep[3 * V + v] = mrg[6 * V + v] / NN;
+    prep[4 * V + v] = mrg[7 * V + v] / NN;
+    prep[5 * V + v] = mrg[8 * V + v] / NN;
+    prep[6 * V + v] = 1.0 / NN;
+  }
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) cost[w] = sh[0];
+}
+
 // per voxel: cS = coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}   (voxel_map.hpp:198-201, :265-268)
 __global__ void k_voxel_prep(const double *__restrict__ lam, const double *__restrict__ mrg, const double *__restrict__ coe,
                              double *__restrict__ cS, int64_t V) {
@@ -430,7 +463,7 @@ k_diag(const int32_t *__restrict__ seg_frame, const int32_t *__restrict__ seg_be
     double NN = mrg[9 * V + v];
     d3 vbar = mk3(mrg[6 * V + v] / NN, mrg[7 * V + v] / NN, mrg[8 * V + v] / NN);
     VfTerms t;
-    vf_terms(R, p, P, vi, n, uk, u1, u2, vbar, NN, t);
+    vf_terms(R, p, P, vi, n, uk, u1, u2, vbar, 1.0 / NN, t);
     double *g = G + 18 * (int64_t)e;
 #pragma unroll
     for (int k = 0; k < 18; k += 2) *reinterpret_cast<double2 *>(g + k) = make_double2(t.g[k], t.g[k + 1]);
@@ -539,7 +572,13 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) 
   cudaStream_t st = ctx->stream;
   const size_t jl = (size_t)6 * f->W;
   bool fused = false;
-  if (f->V > 0 && f->nnz > 0 && !f->force_pairlist) VX_TRY(hessian_small(ctx, f, head, end, &fused));   // overwrites all of H, J
+  if (f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W)) {
+    // cost + the per-voxel divisions first, then the fused kernel (overwrites all of H, J)
+    VX_KERNEL(ctx, "k_cost_prep", k_cost_prep<<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->mrg.as<double>(), f->wv_off.as<int32_t>(),
+                                                                     f->cost_h.as<double>(), f->cS.as<double>(), f->V, head, end));
+    VX_TRY(hessian_small(ctx, f, head, end, &fused));
+    return VX_OK;
+  }
   if (!fused) {
     if (!f->plan_ready) VX_TRY(factor_build_plan(f));
     VX_CUDA(cudaMemsetAsync(f->H.p, 0, sizeof(double) * jl * jl * f->n_win, st));

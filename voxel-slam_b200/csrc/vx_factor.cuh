@@ -28,7 +28,7 @@ struct vx_factor {
   // evaluation state
   vx::DevBuf poses;                 // F x 12 doubles
   vx::DevBuf H, J, cost_h, cost_r;  // outputs
-  vx::DevBuf cS;                    // [3][V] coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}
+  vx::DevBuf cS;                    // [3][V] coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}; the fused path adds [3][V] vBar and [V] 1/NN
   vx::DevBuf res_v;                 // [V] coe * lambda_0
   vx::DevBuf G;                     // [nnz][18] per voxel-frame rows g1 g2 w
   // reduction plans (built on device at upload)
@@ -54,4 +54,5 @@ int factor_finish_upload(vx_factor *f);
 int factor_alloc(vx_factor *f, int64_t V, int64_t nnz);
 // Fused tensor-core path for small windows (vx_hess_small.cu); *handled=false when W has no instantiation.
 int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled);
+inline bool hessian_small_handles(int W) { return W == 10 || W == 20; }
 }  // namespace vx

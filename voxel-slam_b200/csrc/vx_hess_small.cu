@@ -40,7 +40,12 @@ template <int W, int NROLES> struct SmallCfg {
   static constexpr int NT = 32 * NROLES;                   // threads per CTA = voxel-frames per chunk
   static constexpr int STRIDE = NT + 1;                    // record NT is an all-zero record
   static constexpr int NDQ = (W * NF_E + NT - 1) / NT;     // (frame, component) sums owned per thread
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)ROWS * LD + (size_t)NF_E * STRIDE + ROWS) + sizeof(uint16_t) * (size_t)(CHV * W + 8);
+  // record table: per frame 24 entries (CHV = 21 chunk-local voxels, padded to whole 64-bit words) holding the record index of
+  // (frame, voxel) or NT = absent; one byte per entry when NT <= 128, two otherwise
+  static constexpr int RBYTES = NT <= 128 ? 1 : 2;
+  static constexpr int RB = 24 * RBYTES;                   // bytes per frame
+  static constexpr uint32_t RFILL = NT <= 128 ? (uint32_t)NT * 0x01010101u : (uint32_t)NT * 0x00010001u;
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)ROWS * LD + (size_t)NF_E * STRIDE + ROWS + 12 * W) + (size_t)W * RB + 16;
 };
 
 template <int NT8> struct TileTab8 {
@@ -121,23 +126,91 @@ __device__ __forceinline__ void role_store(const double (&C)[SmallCfg<W, NROLES>
     default: break;                                                     \
   }
 
+// Phase A of one voxel-frame: vf_terms (vx_terms.cuh) with every result stored where phases B / C read it, the common factors
+// coe * 2 / NN folded once (cs2) and nothing kept alive longer than needed.  g: panel rows 3lv..3lv+2 at columns 6fr..;
+// ee: this record's column of Es.
+template <int LD, int STRIDE>
+__device__ __forceinline__ void vf_emit(const rot &R, d3 p, const s33 &P, d3 v, double n, d3 uk, d3 u1, d3 u2, d3 vbar, double iNN,
+                                        double cc, double *__restrict__ g, double *__restrict__ ee) {
+  const double cs2 = cc * (2.0 * iNN);
+  const d3 a = rtmul(R, uk), b1 = rtmul(R, u1), b2 = rtmul(R, u2);
+  const d3 Pa = smul(P, a);
+  const d3 t = p - vbar;
+  const double c = dot(uk, t);
+  const d3 combo2 = axpy(n, t, rmul(R, v));
+  const d3 va = cross(v, a);                       // viRiTuk
+  const double c2uk = dot(combo2, uk);
+  // gradient coe * Auk^T uk (voxel_map.hpp:231-237) and half of its rotation part (the antisymmetric correction below)
+  const d3 gj = cs2 * axpy(c, va, cross(Pa, a));
+  const d3 hj = 0.5 * gj;
+  const double ct = cs2 * c2uk;
+  ee[24 * STRIDE] = gj.x; ee[25 * STRIDE] = gj.y; ee[26 * STRIDE] = gj.z;
+  ee[27 * STRIDE] = ct * uk.x; ee[28 * STRIDE] = ct * uk.y; ee[29 * STRIDE] = ct * uk.z;
+  g[2 * LD + 0] = va.x; g[2 * LD + 1] = va.y; g[2 * LD + 2] = va.z;
+  g[2 * LD + 3] = n * uk.x; g[2 * LD + 4] = n * uk.y; g[2 * LD + 5] = n * uk.z;
+  {
+    const d3 q = axpy(dot(t, u1), v, smul(P, b1));
+    const d3 gr = iNN * (cross(Pa, b1) - cross(a, q) + c * cross(v, b1));
+    const d3 gt = iNN * axpy(c2uk, u1, dot(combo2, u1) * uk);
+    g[0] = gr.x; g[1] = gr.y; g[2] = gr.z; g[3] = gt.x; g[4] = gt.y; g[5] = gt.z;
+  }
+  {
+    const d3 q = axpy(dot(t, u2), v, smul(P, b2));
+    const d3 gr = iNN * (cross(Pa, b2) - cross(a, q) + c * cross(v, b2));
+    const d3 gt = iNN * axpy(c2uk, u2, dot(combo2, u2) * uk);
+    g[LD + 0] = gr.x; g[LD + 1] = gr.y; g[LD + 2] = gr.z; g[LD + 3] = gt.x; g[LD + 4] = gt.y; g[LD + 5] = gt.z;
+  }
+  // diagonal-block corrections (vx_terms.cuh: E), times coe.  rot-rot: component cc*3 + r <-> E(r, cc)
+  {
+    const d3 q = axpy(c, v, Pa);
+    const double qa = dot(q, a);
+    const d3 p0 = mk3(P.xx, P.xy, P.xz), p1 = mk3(P.xy, P.yy, P.yz), p2 = mk3(P.xz, P.yz, P.zz);
+    const d3 c0 = cross(a, p0), c1 = cross(a, p1), c2 = cross(a, p2);
+    const d3 m0 = mk3(c0.x, c1.x, c2.x), m1 = mk3(c0.y, c1.y, c2.y), m2 = mk3(c0.z, c1.z, c2.z);
+    const d3 r0 = cross(m0, a), r1 = cross(m1, a), r2 = cross(m2, a);
+    ee[0 * STRIDE] = cs2 * (a.x * q.x - qa - r0.x);
+    ee[1 * STRIDE] = fma(cs2, a.y * q.x - r1.x, -hj.z);
+    ee[2 * STRIDE] = fma(cs2, a.z * q.x - r2.x, hj.y);
+    ee[3 * STRIDE] = fma(cs2, a.x * q.y - r0.y, hj.z);
+    ee[4 * STRIDE] = cs2 * (a.y * q.y - qa - r1.y);
+    ee[5 * STRIDE] = fma(cs2, a.z * q.y - r2.y, -hj.x);
+    ee[6 * STRIDE] = fma(cs2, a.x * q.z - r0.z, -hj.y);
+    ee[7 * STRIDE] = fma(cs2, a.y * q.z - r1.z, hj.x);
+    ee[8 * STRIDE] = cs2 * (a.z * q.z - qa - r2.z);
+  }
+  // rot-tra: component 9 + cc*3 + r <-> E(r, 3+cc) = (2/NN) va_r uk_cc
+  {
+    const d3 sva = cs2 * va;
+    ee[9 * STRIDE] = sva.x * uk.x;  ee[10 * STRIDE] = sva.y * uk.x; ee[11 * STRIDE] = sva.z * uk.x;
+    ee[12 * STRIDE] = sva.x * uk.y; ee[13 * STRIDE] = sva.y * uk.y; ee[14 * STRIDE] = sva.z * uk.y;
+    ee[15 * STRIDE] = sva.x * uk.z; ee[16 * STRIDE] = sva.y * uk.z; ee[17 * STRIDE] = sva.z * uk.z;
+  }
+  // tra-tra upper 00 01 02 11 12 22: (2/NN) n uk_r uk_c
+  {
+    const d3 su = (cs2 * n) * uk;
+    ee[18 * STRIDE] = su.x * uk.x; ee[19 * STRIDE] = su.x * uk.y; ee[20 * STRIDE] = su.x * uk.z;
+    ee[21 * STRIDE] = su.y * uk.y; ee[22 * STRIDE] = su.y * uk.z; ee[23 * STRIDE] = su.z * uk.z;
+  }
+}
+
 // One CTA per item.  item -> (window w, split s): voxels [lo, hi) = the s-th of `splits` equal parts of
 // [max(head, wv_off[w]), min(end, wv_off[w+1])).
 template <int W, int NROLES, int MINB>
 __global__ void __launch_bounds__(32 * NROLES, MINB)
-k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const int32_t *__restrict__ vox,
-             const double *__restrict__ mom, const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ lam,
-             const double *__restrict__ U, const double *__restrict__ mrg, const double *__restrict__ coe,
-             const int32_t *__restrict__ wv_off, const double *__restrict__ poses, double *__restrict__ part_t,
-             double *__restrict__ part_d, int64_t V, int64_t head, int64_t end, int splits) {
+k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const double *__restrict__ mom,
+             const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ prep, const double *__restrict__ U,
+             const double *__restrict__ coe, const int32_t *__restrict__ wv_off, const double *__restrict__ poses,
+             double *__restrict__ part_t, double *__restrict__ part_d, int64_t V, int64_t head, int64_t end, int splits) {
   using Cfg = SmallCfg<W, NROLES>;
-  constexpr int NT = Cfg::NT, STRIDE = Cfg::STRIDE, LD = Cfg::LD, T8 = Cfg::T8, TPR = Cfg::TPR, NDQ = Cfg::NDQ;
+  constexpr int NT = Cfg::NT, STRIDE = Cfg::STRIDE, LD = Cfg::LD, T8 = Cfg::T8, TPR = Cfg::TPR, NDQ = Cfg::NDQ, RB = Cfg::RB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *As = reinterpret_cast<double *>(smem_raw);        // [ROWS][LD] the chunk's panel of A
   double *Es = As + (size_t)ROWS * LD;                      // [NF_E][STRIDE] corrections + gradient per record
   double *Srow = Es + (size_t)NF_E * STRIDE;                // [ROWS] coe*{2/(l0-l1), 2/(l0-l2), -2/NN^2} per panel row
-  uint16_t *rec_s = reinterpret_cast<uint16_t *>(Srow + ROWS);  // [CHV][W] record of (voxel, frame), NT = absent
-  __shared__ int s_nv;
+  double *s_pose = Srow + ROWS;                             // [W][12] the window's poses
+  uint8_t *recb = reinterpret_cast<uint8_t *>(s_pose + 12 * W);  // [W][24] record of (frame, chunk-local voxel), NT = absent
+  __shared__ int s_off[CHV + 1];     // off[v0 + 1 + t] of the chunk
+  __shared__ uint8_t s_lv[NT];       // chunk-local voxel of each voxel-frame
 
   const int tid = threadIdx.x, lane = tid & 31, role = tid >> 5;
   const int item = blockIdx.x;
@@ -151,7 +224,8 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
     const int64_t a = lo + n * sp / splits, b = lo + n * (sp + 1) / splits;
     lo = a; hi = b;
   }
-  const double *ps_w = poses + 12 * (int64_t)w * W;
+  for (int k = tid; k < 12 * W; k += NT) s_pose[k] = poses[12 * (int64_t)w * W + k];
+  if (tid < NF_E) Es[tid * STRIDE + NT] = 0.0;   // the all-zero record
 
   double C[TPR][2];
 #pragma unroll
@@ -159,37 +233,41 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
   double dacc[NDQ];
 #pragma unroll
   for (int q = 0; q < NDQ; q++) dacc[q] = 0.0;
-  if (tid < NF_E) Es[tid * STRIDE + NT] = 0.0;   // the all-zero record
 
+  // chunk = the longest run of voxels from v0 with <= NT voxel-frames and <= CHV voxels.  The run of chunk n+1 is found
+  // while chunk n is processed (its offsets are loaded at the top of chunk n and consumed at the closing barrier).
   int64_t v0 = lo;
+  int32_t e0 = 0;
+  int nv = 0;
+  if (v0 < hi) {
+    e0 = off[v0];
+    const int64_t cand = v0 + 1 + tid;
+    bool ok = false;
+    if (tid < CHV && cand <= hi) { const int32_t o = off[cand]; ok = o - e0 <= NT; s_off[tid] = o; }
+    nv = __syncthreads_count(ok);
+  }
   while (v0 < hi) {
-    // ---- chunk = the longest run of voxels from v0 with <= NT voxel-frames and <= CHV voxels
-    const int32_t e0 = off[v0];
-    {
-      const int64_t cand = v0 + 1 + tid;
-      const bool ok = tid < CHV && cand <= hi && off[cand] - e0 <= NT;
-      const int nvv = __syncthreads_count(ok);
-      if (tid == 0) s_nv = nvv;
-    }
+    const int32_t e1 = s_off[nv - 1];
+    const int64_t v0n = v0 + nv, candn = v0n + 1 + tid;
+    int32_t on = 0;
+    if (tid < CHV && candn <= hi) on = off[candn];
     {
       double2 *z = reinterpret_cast<double2 *>(As);
       for (int k = tid; k < ROWS * LD / 2; k += NT) z[k] = make_double2(0.0, 0.0);
       if (tid < ROWS) Srow[tid] = 0.0;
-      for (int k = tid; k < CHV * W; k += NT) rec_s[k] = (uint16_t)NT;
+      for (int k = tid; k < W * RB / 4; k += NT) reinterpret_cast<uint32_t *>(recb)[k] = Cfg::RFILL;
+      if (tid < nv) {   // voxel tid of the chunk owns voxel-frames [off[v0+tid], off[v0+tid+1]) - e0
+        const int a = tid == 0 ? 0 : s_off[tid - 1] - e0, b = s_off[tid] - e0;
+        for (int j = a; j < b; j++) s_lv[j] = (uint8_t)tid;
+      }
     }
     __syncthreads();
-    const int nv = s_nv;
-    const int32_t e1 = off[v0 + nv];
-    // ---- phase A
+    // ---- phase A: one thread per voxel-frame
     const int32_t e = e0 + tid;
     if (e < e1) {
-      const int64_t v = vox[e];
-      const int lv = (int)(v - v0);
+      const int lv = s_lv[tid];
+      const int64_t v = v0 + lv;
       const int fr = frame[e] - w * W;
-      rec_s[lv * W + fr] = (uint16_t)tid;
-      const double *ps = ps_w + 12 * fr;
-      const rot R = load_rot(ps);
-      const d3 p = mk3(ps[9], ps[10], ps[11]);
       s33 P;
       P.xx = mom[0 * nnz + e]; P.xy = mom[1 * nnz + e]; P.xz = mom[2 * nnz + e];
       P.yy = mom[3 * nnz + e]; P.yz = mom[4 * nnz + e]; P.zz = mom[5 * nnz + e];
@@ -198,55 +276,52 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
       const d3 uk = mk3(U[0 * V + v], U[1 * V + v], U[2 * V + v]);
       const d3 u1 = mk3(U[3 * V + v], U[4 * V + v], U[5 * V + v]);
       const d3 u2 = mk3(U[6 * V + v], U[7 * V + v], U[8 * V + v]);
-      const double NN = mrg[9 * V + v];
-      const d3 vbar = mk3(mrg[6 * V + v] / NN, mrg[7 * V + v] / NN, mrg[8 * V + v] / NN);
+      const d3 vbar = mk3(prep[3 * V + v], prep[4 * V + v], prep[5 * V + v]);
+      const double iNN = prep[6 * V + v];
       const double c = coe[v];
-      if (e == off[v]) {   // first voxel-frame of the voxel also publishes the voxel's S (voxel_map.hpp:198-201, :265-268)
-        const double l0 = lam[v], l1 = lam[V + v], l2 = lam[2 * V + v];
-        Srow[3 * lv + 0] = c * (2.0 / (l0 - l1));
-        Srow[3 * lv + 1] = c * (2.0 / (l0 - l2));
-        Srow[3 * lv + 2] = c * (-2.0 / NN / NN);
-      }
-      VfTerms t;
-      vf_terms(R, p, P, vi, n, uk, u1, u2, vbar, NN, t);
-      double *g = As + (size_t)(3 * lv) * LD + 6 * fr;
-#pragma unroll
-      for (int m = 0; m < 3; m++)
-#pragma unroll
-        for (int r = 0; r < 6; r++) g[m * LD + r] = t.g[m * 6 + r];
-      double *ee = Es + tid;
-#pragma unroll
-      for (int cc = 0; cc < 3; cc++)
-#pragma unroll
-        for (int r = 0; r < 3; r++) {
-          ee[(cc * 3 + r) * STRIDE] = c * t.E[cc * 6 + r];              // rot-rot (r, cc)
-          ee[(9 + cc * 3 + r) * STRIDE] = c * t.E[(3 + cc) * 6 + r];    // rot-tra (r, 3+cc) == (3+cc, r)
-        }
-      ee[18 * STRIDE] = c * t.E[3 * 6 + 3]; ee[19 * STRIDE] = c * t.E[4 * 6 + 3]; ee[20 * STRIDE] = c * t.E[5 * 6 + 3];
-      ee[21 * STRIDE] = c * t.E[4 * 6 + 4]; ee[22 * STRIDE] = c * t.E[5 * 6 + 4]; ee[23 * STRIDE] = c * t.E[5 * 6 + 5];
-#pragma unroll
-      for (int r = 0; r < 6; r++) ee[(24 + r) * STRIDE] = c * t.jj[r];
+      const double S0 = prep[v], S1 = prep[V + v], S2 = prep[2 * V + v];
+      const double *ps = s_pose + 12 * fr;
+      const rot R = load_rot(ps);
+      const d3 p = mk3(ps[9], ps[10], ps[11]);
+      if (Cfg::RBYTES == 1) recb[fr * RB + lv] = (uint8_t)tid;
+      else reinterpret_cast<uint16_t *>(recb)[fr * 24 + lv] = (uint16_t)tid;
+      // every voxel-frame of the voxel publishes the voxel's S (identical values; voxel_map.hpp:198-201, :265-268)
+      Srow[3 * lv + 0] = S0; Srow[3 * lv + 1] = S1; Srow[3 * lv + 2] = S2;
+      vf_emit<LD, STRIDE>(R, p, P, vi, n, uk, u1, u2, vbar, iNN, c, As + (size_t)(3 * lv) * LD + 6 * fr, Es + tid);
     }
     __syncthreads();
     // ---- phase B: tensor-core SYRK of the panel, one role per warp
     const int nks = (3 * nv + 3) >> 2;
     VX_ROLE_SWITCH(role, role_chunk, C, As, Srow, nks, lane)
-    // ---- phase C: per-frame corrections + gradient, fixed owner threads, voxel order
+    // ---- phase C: per-frame corrections + gradient.  The owner thread of (frame, component) reads the frame's CHV record
+    //      bytes (absent -> the zero record) and adds the records in four interleaved chains.
 #pragma unroll
     for (int q = 0; q < NDQ; q++) {
       const int id = tid + q * NT;
       if (id < W * NF_E) {
         const int fr = id / NF_E, comp = id - fr * NF_E;
         const double *src = Es + comp * STRIDE;
-        const uint16_t *rp = rec_s + fr;
-        double acc = dacc[q];
-#pragma unroll 4
-        for (int lv = 0; lv < nv; lv++) acc += src[rp[lv * W]];   // absent frames read the zero record
-        dacc[q] = acc;
+        const unsigned long long *rw = reinterpret_cast<const unsigned long long *>(recb + fr * RB);
+        constexpr int EPW = 8 / Cfg::RBYTES, NWD = 24 / EPW;     // entries per word, words per frame
+        unsigned long long wd[NWD];
+#pragma unroll
+        for (int k = 0; k < NWD; k++) wd[k] = rw[k];
+        double sacc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < CHV; k++) {
+          const unsigned idx = (unsigned)(wd[k / EPW] >> (8 * Cfg::RBYTES * (k % EPW))) & (Cfg::RBYTES == 1 ? 0xffu : 0xffffu);
+          sacc[k & 3] += src[idx];
+        }
+        dacc[q] += (sacc[0] + sacc[1]) + (sacc[2] + sacc[3]);
       }
     }
-    __syncthreads();
-    v0 += nv;
+    // ---- close the chunk and fix the next one (s_off was last read before the previous barrier)
+    {
+      bool ok = false;
+      if (tid < CHV && candn <= hi) { ok = on - e1 <= NT; s_off[tid] = on; }
+      nv = __syncthreads_count(ok);
+      v0 = v0n; e0 = e1;
+    }
   }
   // ---- item partials
   double *pt = part_t + (size_t)item * T8 * 64;
@@ -315,6 +390,7 @@ __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ pa
   }
 }
 
+
 template <int W, int NROLES, int MINB>
 int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   using Cfg = SmallCfg<W, NROLES>;
@@ -337,8 +413,8 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
     attr_set = true;
   }
   VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES, MINB><<<(unsigned)items, Cfg::NT, Cfg::SMEM, st>>>(
-      f->off.as<int32_t>(), f->frame.as<int32_t>(), f->vox.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
-      f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
+      f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
+      f->cS.as<double>(), f->U.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
       f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits));
   VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<f->n_win, 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
                                                                                f->H.as<double>(), f->J.as<double>(), splits));

@@ -71,7 +71,57 @@ __global__ void __launch_bounds__(256) k_peak_mixed(double *out, int iters, doub
   }
   out[blockIdx.x * (size_t)blockDim.x + threadIdx.x] = r;
 }
+// modes 16 + ilp (ilp = 1, 2, 4, 8): ONE warp, `ilp` independent dependent-DFMA chains; returns cycles per DFMA issued
+// (ilp = 1: the dependent-issue latency of the FP64 pipe).  modes 32 + ilp: the same for DMMA chains.
+template <int ILP, bool MMA>
+__global__ void k_latency(double *out, long long *cyc, int iters, double a, double b) {
+  double x[8][2];
+#pragma unroll
+  for (int k = 0; k < 8; k++) { x[k][0] = threadIdx.x + k; x[k][1] = k; }
+  const long long t0 = clock64();
+#pragma unroll 1
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+#pragma unroll
+      for (int k = 0; k < ILP; k++) {
+        if (MMA) dmma(x[k][0], x[k][1], a, b);
+        else x[k][0] = fma(x[k][0], a, b);
+      }
+    }
+  }
+  const long long t1 = clock64();
+  double s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) s += x[k][0] + x[k][1];
+  out[threadIdx.x] = s;
+  if (threadIdx.x == 0) *cyc = t1 - t0;
+}
 }  // namespace
+
+extern "C" int vx_bench_fp64_latency(vx_ctx *ctx, int mma, int ilp, double *cycles_per_instr) {
+  VX_TRY(vx::bind(ctx));
+  VX_ARG(cycles_per_instr != nullptr && (ilp == 1 || ilp == 2 || ilp == 4 || ilp == 8));
+  const int iters = 2048;
+  VX_TRY(ctx->scratch.reserve(sizeof(double) * 64));
+  double *out = ctx->scratch.as<double>();
+  long long *cyc = reinterpret_cast<long long *>(out + 32);
+  for (int rep = 0; rep < 2; rep++) {
+#define VX_LAT(I)                                                                                         \
+    if (ilp == I) {                                                                                       \
+      if (mma) k_latency<I, true><<<1, 32, 0, ctx->stream>>>(out, cyc, iters, 0.999999, 1e-9);            \
+      else k_latency<I, false><<<1, 32, 0, ctx->stream>>>(out, cyc, iters, 0.999999, 1e-9);               \
+    }
+    VX_LAT(1) VX_LAT(2) VX_LAT(4) VX_LAT(8)
+#undef VX_LAT
+    VX_LAUNCH_CHECK(ctx);
+    VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  }
+  long long h = 0;
+  VX_CUDA(cudaMemcpy(&h, cyc, sizeof(h), cudaMemcpyDeviceToHost));
+  *cycles_per_instr = (double)h / ((double)iters * 8 * ilp);
+  return VX_OK;
+}
 
 extern "C" int vx_bench_fp64(vx_ctx *ctx, int mode, double *tflops) {
   VX_TRY(vx::bind(ctx));

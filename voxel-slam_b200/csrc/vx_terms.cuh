@@ -14,8 +14,7 @@ struct VfTerms {
 
 // All per-voxel-frame quantities of voxel_map.hpp:203-252 in closed form (see file header).
 __device__ __forceinline__ void vf_terms(const rot &R, d3 p, const s33 &P, d3 v, double n, d3 uk, d3 u1, d3 u2, d3 vbar,
-                                         double NN, VfTerms &o) {
-  const double iNN = 1.0 / NN;
+                                         double iNN /* 1 / NN */, VfTerms &o) {
   d3 a = rtmul(R, uk), b1 = rtmul(R, u1), b2 = rtmul(R, u2);
   d3 Pa = smul(P, a);
   d3 t = p - vbar;
