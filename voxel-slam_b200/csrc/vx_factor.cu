@@ -26,7 +26,7 @@ using namespace vx;
 namespace vx {
 
 int factor_alloc(vx_factor *f, int64_t V, int64_t nnz) {
-  f->V = V; f->nnz = nnz; f->plan_ready = false;
+  f->V = V; f->nnz = nnz; f->plan_ready = false; f->prep_lo = f->prep_hi = 0;
   const int F = f->F();
   VX_TRY(f->off.reserve(sizeof(int32_t) * (V + 1)));
   VX_TRY(f->frame.reserve(sizeof(int32_t) * std::max<int64_t>(nnz, 1)));
@@ -135,7 +135,7 @@ static int scan_i32(vx_ctx *ctx, const int32_t *in, int32_t *out, int64_t n) {
 int factor_finish_upload(vx_factor *f) {
   vx_ctx *ctx = f->ctx;
   VX_TRY(bind(ctx));
-  f->plan_ready = false;
+  f->plan_ready = false; f->prep_lo = f->prep_hi = 0;
   f->n_pairs = f->n_tiles = f->n_dseg = f->n_oseg = 0;
   if (f->V == 0 || f->nnz == 0) { f->plan_ready = true; return VX_OK; }
   k_fill_vox<<<blocks_for(f->V, 256), 256, 0, ctx->stream>>>(f->off.as<int32_t>(), f->vox.as<int32_t>(), f->V);
@@ -149,7 +149,7 @@ int factor_build_plan(vx_factor *f) {
   cudaStream_t st = ctx->stream;
   const int64_t V = f->V, nnz = f->nnz;
   const int F = f->F();
-  f->plan_ready = false;
+  f->plan_ready = false; f->prep_lo = f->prep_hi = 0;
   f->n_pairs = f->n_tiles = f->n_dseg = f->n_oseg = 0;
   if (V == 0 || nnz == 0) { f->plan_ready = true; return VX_OK; }
   VX_ARG(nnz < (int64_t)1 << 31);
@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(RES_THREADS)
 k_residual(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const double *__restrict__ mom,
            const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ fix, const double *__restrict__ coe,
            const double *__restrict__ poses, double *__restrict__ lam, double *__restrict__ U, double *__restrict__ mrg,
-           double *__restrict__ res_v, int64_t V, int64_t head, int64_t end) {
+           double *__restrict__ res_v, double *__restrict__ prep, int64_t V, int64_t head, int64_t end) {
   int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (v >= V || v < head || v >= end) return;
   s33 P;
@@ -328,7 +328,6 @@ k_residual(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, c
   s33 C;
   C.xx = P.xx / N - vb.x * vb.x; C.xy = P.xy / N - vb.x * vb.y; C.xz = P.xz / N - vb.x * vb.z;
   C.yy = P.yy / N - vb.y * vb.y; C.yz = P.yz / N - vb.y * vb.z; C.zz = P.zz / N - vb.z * vb.z;
-  (void)invN;
   double l[3], u[9];
   eig3_jacobi(C, l, u);
   lam[0 * V + v] = l[0]; lam[1 * V + v] = l[1]; lam[2 * V + v] = l[2];
@@ -338,7 +337,14 @@ k_residual(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, c
   mrg[3 * V + v] = P.yy; mrg[4 * V + v] = P.yz; mrg[5 * V + v] = P.zz;
   mrg[6 * V + v] = sv.x; mrg[7 * V + v] = sv.y; mrg[8 * V + v] = sv.z;
   mrg[9 * V + v] = N;
-  res_v[v] = coe[v] * l[0];
+  const double cf = coe[v];
+  res_v[v] = cf * l[0];
+  // the divisions the next acc_evaluate2 needs per voxel (k_cost_prep below states them)
+  prep[v] = cf * (2.0 / (l[0] - l[1]));
+  prep[V + v] = cf * (2.0 / (l[0] - l[2]));
+  prep[2 * V + v] = cf * (-2.0 / N / N);
+  prep[3 * V + v] = vb.x; prep[4 * V + v] = vb.y; prep[5 * V + v] = vb.z;
+  prep[6 * V + v] = invN;
 }
 
 // cost[w] = sum over voxels of window w (restricted to [head,end)) of coe*lambda_0, fixed-shape tree.
@@ -366,16 +372,16 @@ k_cost(const double *__restrict__ src, const double *__restrict__ coe, const int
 // (window cost from the cached eigenvalues) that also writes, per voxel of [head, end),
 //   prep[0..2] = coe * {2/(l0-l1), 2/(l0-l2), -2/NN^2}   (voxel_map.hpp:198-201, :265-268)
 //   prep[3..5] = vBar = v / NN,  prep[6] = 1 / NN          (voxel_map.hpp:193-195)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_cost_prep(const double *__restrict__ lam, const double *__restrict__ coe, const double *__restrict__ mrg, const int32_t *__restrict__ wv_off,
             double *__restrict__ cost, double *__restrict__ prep, int64_t V, int64_t head, int64_t end) {
-  __shared__ double sh[256];
+  __shared__ double sh[1024];
   const int w = blockIdx.x;
   int64_t b = wv_off[w], e = wv_off[w + 1];
   if (b < head) b = head;
   if (e > end) e = end;
   double acc = 0.0;
-  for (int64_t v = b + threadIdx.x; v < e; v += 256) {
+  for (int64_t v = b + threadIdx.x; v < e; v += 1024) {
     const double l0 = lam[v], l1 = lam[V + v], l2 = lam[2 * V + v], c = coe[v], NN = mrg[9 * V + v];
     acc += c * l0;
     prep[v] = c * (2.0 / (l0 - l1));
@@ -388,7 +394,7 @@ k_cost_prep(const double *__restrict__ lam, const double *__restrict__ coe, cons
   }
   sh[threadIdx.x] = acc;
   __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
+  for (int s = 512; s > 0; s >>= 1) {
     if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
     __syncthreads();
   }
@@ -562,7 +568,8 @@ static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end)
     VX_KERNEL(ctx, "k_residual", k_residual<<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>(
         f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(),
         f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(),
-        f->res_v.as<double>(), f->V, head, end));
+        f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end));
+    f->prep_lo = std::max<int64_t>(head, 0); f->prep_hi = std::min<int64_t>(end, f->V);
   }
   VX_KERNEL(ctx, "k_cost", k_cost<false><<<f->n_win, 256, 0, st>>>(f->res_v.as<double>(), nullptr, f->wv_off.as<int32_t>(), f->cost_r.as<double>(), head, end));
   return VX_OK;
@@ -573,9 +580,15 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) 
   const size_t jl = (size_t)6 * f->W;
   bool fused = false;
   if (f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W)) {
-    // cost + the per-voxel divisions first, then the fused kernel (overwrites all of H, J)
-    VX_KERNEL(ctx, "k_cost_prep", k_cost_prep<<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->mrg.as<double>(), f->wv_off.as<int32_t>(),
-                                                                     f->cost_h.as<double>(), f->cS.as<double>(), f->V, head, end));
+    // cost (+ the per-voxel divisions unless the last residual pass left them), then the fused kernel (overwrites all of H, J)
+    const int64_t lo = std::max<int64_t>(head, 0), hi = std::min<int64_t>(end, f->V);
+    if (f->prep_lo <= lo && hi <= f->prep_hi) {
+      VX_KERNEL(ctx, "k_cost", k_cost<true><<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(), f->cost_h.as<double>(), head, end));
+    } else {
+      VX_KERNEL(ctx, "k_cost_prep", k_cost_prep<<<f->n_win, 1024, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->mrg.as<double>(), f->wv_off.as<int32_t>(),
+                                                                       f->cost_h.as<double>(), f->cS.as<double>(), f->V, head, end));
+      f->prep_lo = lo; f->prep_hi = hi;
+    }
     VX_TRY(hessian_small(ctx, f, head, end, &fused));
     return VX_OK;
   }

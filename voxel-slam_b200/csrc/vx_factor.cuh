@@ -33,6 +33,9 @@ struct vx_factor {
   vx::DevBuf G;                     // [nnz][18] per voxel-frame rows g1 g2 w
   // reduction plans (built on device at upload)
   bool plan_ready = false;
+  // voxel range whose division planes cS[3..6] (and cS[0..2]) match the cache lam / mrg / coe: written by k_residual with the
+  // cache, rebuilt by k_cost_prep when an evaluation finds its range uncovered.  Every other writer of the cache empties it.
+  int64_t prep_lo = 0, prep_hi = 0;
   vx::DevBuf fm_order, fm_off;                          // frame-major order of voxel-frames
   vx::DevBuf dseg_frame, dseg_beg, dseg_end, dseg_off;  // diagonal-tile segments
   vx::DevBuf pair_ab;                                   // packed (a<<32 | b), sorted by tile

@@ -340,21 +340,16 @@ template <int W, int NT8>
 __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ part_t, const double *__restrict__ part_d,
                                                    double *__restrict__ H, double *__restrict__ J, int splits) {
   constexpr int T = W * (W + 1) / 2, T8 = NT8 * (NT8 + 1) / 2;
-  __shared__ unsigned char ti[T], tj[T];
-  if (threadIdx.x == 0) {
-    int t = 0;
-    for (int a = 0; a < W; a++)
-      for (int b = a; b < W; b++) { ti[t] = (unsigned char)a; tj[t] = (unsigned char)b; t++; }
-  }
-  __syncthreads();
   const int w = blockIdx.x;
   const int64_t jl = 6 * W;
   double *Hw = H + (size_t)w * jl * jl;
   const double *pt = part_t + (size_t)w * splits * T8 * 64;
   const double *pd = part_d + (size_t)w * splits * W * NF_E;
-  for (int idx = threadIdx.x; idx < T * 36; idx += blockDim.x) {
+  for (int idx = blockIdx.y * blockDim.x + threadIdx.x; idx < T * 36; idx += blockDim.x * gridDim.y) {
     const int t = idx / 36, x = idx - t * 36;
-    const int i = ti[t], j = tj[t];
+    int i = 0, rem = t;                      // t-th upper block (i, j), row-major
+    while (rem >= W - i) { rem -= W - i; i++; }
+    const int j = i + rem;
     const int r = x % 6, c = x / 6;
     // element (R, Cc) of the symmetric rank-3 sum; only upper 8x8 tiles are stored
     int R = 6 * i + r, Cc = 6 * j + c;
@@ -382,6 +377,7 @@ __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ pa
       Hw[(6 * i + r) * jl + (6 * j + c)] = s;
     }
   }
+  if (blockIdx.y != 0) return;
   for (int idx = threadIdx.x; idx < 6 * W; idx += blockDim.x) {
     const int i = idx / 6, r = idx - i * 6;
     double g = 0.0;
@@ -398,11 +394,15 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   // items: enough CTAs to fill the machine several times over, but >= ~96 voxels per item
   int splits = 1;
   {
-    const int64_t want_items = (int64_t)ctx->sm_count * 8;
+    // ~3.6 items per resident CTA slot (3 CTAs per SM): measured best on the bench workload (splits 3 -> 4: -7 %), the last
+    // round of CTAs then ends nearly together
+    const int64_t want_items = (int64_t)(ctx->sm_count * 3 * 3.6);
     const int64_t vox_per_win = std::max<int64_t>(1, f->V / f->n_win);
-    int64_t s = (want_items + f->n_win - 1) / f->n_win;
+    int64_t s = (want_items + f->n_win / 2) / f->n_win;
     s = std::min<int64_t>(s, std::max<int64_t>(1, vox_per_win / 96));
     splits = (int)std::max<int64_t>(1, s);
+    static const int forced = getenv("VX_HS_SPLITS") ? atoi(getenv("VX_HS_SPLITS")) : 0;
+    if (forced > 0) splits = forced;
   }
   const int64_t items = (int64_t)f->n_win * splits;
   VX_TRY(f->part_t.reserve(sizeof(double) * items * Cfg::T8 * 64));
@@ -416,7 +416,7 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
       f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
       f->cS.as<double>(), f->U.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
       f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits));
-  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<f->n_win, 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
+  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<dim3(f->n_win, 4), 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
                                                                                f->H.as<double>(), f->J.as<double>(), splits));
   return VX_OK;
 }
