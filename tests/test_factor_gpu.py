@@ -78,9 +78,10 @@ def test_hessian_parity(pkg, ob, ctx, V, W, occ):
     f.free(); g.free()
 
 
-def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx):
+@pytest.mark.parametrize("W", [8, 10])
+def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx, W):
     # stateful cache semantics: B1 reads what the LAST B2 wrote
-    V, W = 800, 8
+    V = 800
     fac = synth.random_factor(301, V, W)
     p1 = synth.perturb_poses(fac["poses"], 1, 0.02, 0.05)
     of = ob.Factor(W); of.set_dense(fac)
@@ -89,6 +90,23 @@ def test_hessian_after_residual_uses_refreshed_cache(pkg, ob, ctx):
     Ho, Jo, co = of.hessian(p1)
     H, J, c = f.hessian(p1)
     assert abs(c - co) <= 1e-9 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9
+    f.free()
+
+
+def test_partial_residual_then_full_hessian(pkg, ob, ctx):
+    # the fused W = 10 path keeps per-voxel division planes next to the cache: a residual pass over PART of the voxels
+    # refreshes them for that part only, and a Hessian over a wider range must rebuild them from the (mixed) cache
+    V, W = 900, 10
+    fac = synth.random_factor(311, V, W)
+    p1 = synth.perturb_poses(fac["poses"], 2, 0.02, 0.05)
+    of = ob.Factor(W); of.set_dense(fac)
+    f = pkg.Factor(ctx, W); f.upload_dense(fac)
+    for head, end in [(0, 450), (200, 700)]:
+        of.residual(p1, head, end); f.residual(p1, head, end)
+        for h2, e2 in [(0, V), (head, end), (head + 10, end - 10)]:
+            Ho, Jo, co = of.hessian(p1, h2, e2)
+            H, J, c = f.hessian(p1, h2, e2)
+            assert abs(c - co) <= 1e-9 * abs(co) and rel(J, Jo) < 1e-9 and rel(H, Ho) < 1e-9, (head, end, h2, e2)
     f.free()
 
 

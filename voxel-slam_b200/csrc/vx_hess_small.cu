@@ -45,7 +45,8 @@ template <int W, int NROLES> struct SmallCfg {
   static constexpr int RBYTES = NT <= 128 ? 1 : 2;
   static constexpr int RB = 24 * RBYTES;                   // bytes per frame
   static constexpr uint32_t RFILL = NT <= 128 ? (uint32_t)NT * 0x01010101u : (uint32_t)NT * 0x00010001u;
-  static constexpr size_t SMEM = sizeof(double) * ((size_t)ROWS * LD + (size_t)NF_E * STRIDE + ROWS + 12 * W) + (size_t)W * RB + 16;
+  static constexpr int NVF = 17;                            // per-voxel fields staged per chunk: U 9 | S 3, vBar 3, 1/NN | coe
+  static constexpr size_t SMEM = sizeof(double) * ((size_t)ROWS * LD + (size_t)NF_E * STRIDE + ROWS + 12 * W + NVF * CHV) + (size_t)W * RB + 16;
 };
 
 template <int NT8> struct TileTab8 {
@@ -193,6 +194,32 @@ __device__ __forceinline__ void vf_emit(const rot &R, d3 p, const s33 &P, d3 v, 
   }
 }
 
+// per-voxel-frame operands of phase A (76 B of the cluster record)
+struct VfRow {
+  s33 P; d3 vi; int32_t cnt, frame;
+  __device__ __forceinline__ void load(const int32_t *__restrict__ frame_, const double *__restrict__ mom, const int32_t *__restrict__ cnt_,
+                                       int64_t nnz, int64_t e) {
+    frame = frame_[e]; cnt = cnt_[e];
+    P.xx = mom[0 * nnz + e]; P.xy = mom[1 * nnz + e]; P.xz = mom[2 * nnz + e];
+    P.yy = mom[3 * nnz + e]; P.yz = mom[4 * nnz + e]; P.zz = mom[5 * nnz + e];
+    vi = mk3(mom[6 * nnz + e], mom[7 * nnz + e], mom[8 * nnz + e]);
+  }
+};
+
+// cp.async the NVF per-voxel fields of voxels [vbeg, vbeg + CHV) (clamped to the last voxel) into s_vox[NVF][CHV]
+template <int NVF, int NT>
+__device__ __forceinline__ void stage_voxels(double *s_vox, const double *__restrict__ U, const double *__restrict__ prep,
+                                             const double *__restrict__ coe, int64_t V, int64_t vbeg, int tid) {
+  for (int idx = tid; idx < NVF * CHV; idx += NT) {
+    const int fld = idx / CHV, j = idx - fld * CHV;
+    const double *base = fld < 9 ? U + (int64_t)fld * V : (fld < 16 ? prep + (int64_t)(fld - 9) * V : coe);
+    int64_t v = vbeg + j;
+    if (v >= V) v = V - 1;
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(s_vox + idx);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(base + v) : "memory");
+  }
+}
+
 // One CTA per item.  item -> (window w, split s): voxels [lo, hi) = the s-th of `splits` equal parts of
 // [max(head, wv_off[w]), min(end, wv_off[w+1])).
 template <int W, int NROLES, int MINB>
@@ -208,7 +235,8 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
   double *Es = As + (size_t)ROWS * LD;                      // [NF_E][STRIDE] corrections + gradient per record
   double *Srow = Es + (size_t)NF_E * STRIDE;                // [ROWS] coe*{2/(l0-l1), 2/(l0-l2), -2/NN^2} per panel row
   double *s_pose = Srow + ROWS;                             // [W][12] the window's poses
-  uint8_t *recb = reinterpret_cast<uint8_t *>(s_pose + 12 * W);  // [W][24] record of (frame, chunk-local voxel), NT = absent
+  double *s_vox = s_pose + 12 * W;                          // [NVF][CHV] per-voxel operands of the chunk (cp.async, one chunk ahead)
+  uint8_t *recb = reinterpret_cast<uint8_t *>(s_vox + Cfg::NVF * CHV);  // [W][24] record of (frame, chunk-local voxel), NT = absent
   __shared__ int s_off[CHV + 1];     // off[v0 + 1 + t] of the chunk
   __shared__ uint8_t s_lv[NT];       // chunk-local voxel of each voxel-frame
 
@@ -234,16 +262,22 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
 #pragma unroll
   for (int q = 0; q < NDQ; q++) dacc[q] = 0.0;
 
-  // chunk = the longest run of voxels from v0 with <= NT voxel-frames and <= CHV voxels.  The run of chunk n+1 is found
-  // while chunk n is processed (its offsets are loaded at the top of chunk n and consumed at the closing barrier).
+  // chunk = the longest run of voxels from v0 with <= NT voxel-frames and <= CHV voxels.  Everything chunk n+1 needs is on its
+  // way while chunk n is multiplied: its voxel run (offsets loaded at the top of chunk n, counted at the closing barrier), its
+  // per-voxel-frame operands (registers pf, issued after phase A) and its per-voxel operands (cp.async into s_vox, ditto) —
+  // rows e1.. and voxels v0+nv.. follow the chunk contiguously in every field array.
   int64_t v0 = lo;
   int32_t e0 = 0;
   int nv = 0;
+  const int32_t e_last = off[hi] - 1;        // last voxel-frame of the item (clamp for look-ahead rows)
+  VfRow pf;
   if (v0 < hi) {
     e0 = off[v0];
     const int64_t cand = v0 + 1 + tid;
     bool ok = false;
     if (tid < CHV && cand <= hi) { const int32_t o = off[cand]; ok = o - e0 <= NT; s_off[tid] = o; }
+    pf.load(frame, mom, cnt, nnz, min(e0 + tid, e_last));
+    stage_voxels<Cfg::NVF, NT>(s_vox, U, prep, coe, V, v0, tid);
     nv = __syncthreads_count(ok);
   }
   while (v0 < hi) {
@@ -261,35 +295,35 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
         for (int j = a; j < b; j++) s_lv[j] = (uint8_t)tid;
       }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
     // ---- phase A: one thread per voxel-frame
     const int32_t e = e0 + tid;
     if (e < e1) {
       const int lv = s_lv[tid];
-      const int64_t v = v0 + lv;
-      const int fr = frame[e] - w * W;
-      s33 P;
-      P.xx = mom[0 * nnz + e]; P.xy = mom[1 * nnz + e]; P.xz = mom[2 * nnz + e];
-      P.yy = mom[3 * nnz + e]; P.yz = mom[4 * nnz + e]; P.zz = mom[5 * nnz + e];
-      const d3 vi = mk3(mom[6 * nnz + e], mom[7 * nnz + e], mom[8 * nnz + e]);
-      const double n = (double)cnt[e];
-      const d3 uk = mk3(U[0 * V + v], U[1 * V + v], U[2 * V + v]);
-      const d3 u1 = mk3(U[3 * V + v], U[4 * V + v], U[5 * V + v]);
-      const d3 u2 = mk3(U[6 * V + v], U[7 * V + v], U[8 * V + v]);
-      const d3 vbar = mk3(prep[3 * V + v], prep[4 * V + v], prep[5 * V + v]);
-      const double iNN = prep[6 * V + v];
-      const double c = coe[v];
-      const double S0 = prep[v], S1 = prep[V + v], S2 = prep[2 * V + v];
+      const int fr = pf.frame - w * W;
+      const double *sv = s_vox + lv;
+      const d3 uk = mk3(sv[0 * CHV], sv[1 * CHV], sv[2 * CHV]);
+      const d3 u1 = mk3(sv[3 * CHV], sv[4 * CHV], sv[5 * CHV]);
+      const d3 u2 = mk3(sv[6 * CHV], sv[7 * CHV], sv[8 * CHV]);
+      const d3 vbar = mk3(sv[12 * CHV], sv[13 * CHV], sv[14 * CHV]);
+      const double iNN = sv[15 * CHV];
+      const double c = sv[16 * CHV];
       const double *ps = s_pose + 12 * fr;
       const rot R = load_rot(ps);
       const d3 p = mk3(ps[9], ps[10], ps[11]);
       if (Cfg::RBYTES == 1) recb[fr * RB + lv] = (uint8_t)tid;
       else reinterpret_cast<uint16_t *>(recb)[fr * 24 + lv] = (uint16_t)tid;
       // every voxel-frame of the voxel publishes the voxel's S (identical values; voxel_map.hpp:198-201, :265-268)
-      Srow[3 * lv + 0] = S0; Srow[3 * lv + 1] = S1; Srow[3 * lv + 2] = S2;
-      vf_emit<LD, STRIDE>(R, p, P, vi, n, uk, u1, u2, vbar, iNN, c, As + (size_t)(3 * lv) * LD + 6 * fr, Es + tid);
+      Srow[3 * lv + 0] = sv[9 * CHV]; Srow[3 * lv + 1] = sv[10 * CHV]; Srow[3 * lv + 2] = sv[11 * CHV];
+      vf_emit<LD, STRIDE>(R, p, pf.P, pf.vi, (double)pf.cnt, uk, u1, u2, vbar, iNN, c, As + (size_t)(3 * lv) * LD + 6 * fr, Es + tid);
     }
     __syncthreads();
+    // ---- look ahead: operands of chunk n+1
+    if (v0n < hi) {
+      pf.load(frame, mom, cnt, nnz, min(e1 + tid, e_last));
+      stage_voxels<Cfg::NVF, NT>(s_vox, U, prep, coe, V, v0n, tid);
+    }
     // ---- phase B: tensor-core SYRK of the panel, one role per warp
     const int nks = (3 * nv + 3) >> 2;
     VX_ROLE_SWITCH(role, role_chunk, C, As, Srow, nks, lane)
