@@ -62,6 +62,9 @@ struct ProfSpan { const char *name; cudaEvent_t a, b; };
 struct vx_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;   // device->host copies of finished window groups while later groups are evaluated
+  cudaEvent_t group_ev[8] = {};
+  cudaEvent_t copy_done = nullptr;
   int sm_count = 148;
   int64_t launches = 0;
   bool profiling = false;

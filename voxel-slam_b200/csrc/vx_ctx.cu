@@ -33,6 +33,9 @@ int vx_ctx_create(int device, vx_ctx **out) {
   VX_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   VX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  VX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  for (auto &e : c->group_ev) VX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  VX_CUDA(cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming));
   c->pinned_cap = 1 << 16;
   VX_CUDA(cudaMallocHost(&c->pinned, c->pinned_cap));
   *out = c;
@@ -43,6 +46,9 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   if (!ctx) return VX_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+  if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+  for (auto &e : ctx->group_ev) if (e) cudaEventDestroy(e);
+  if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
   for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
   ctx->scratch.release();
   ctx->scratch2.release();

@@ -17,6 +17,7 @@
 #include "vx_terms.cuh"
 #include <cub/cub.cuh>
 #include <algorithm>
+#include <cstdlib>
 
 using namespace vx;
 
@@ -575,7 +576,10 @@ static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end)
   return VX_OK;
 }
 
-static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
+// host destinations of a grouped evaluation (vx_factor_hessian on a batched factor)
+struct GroupOut { double *Hess, *JacT; int groups; };
+
+static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, const GroupOut *group_out = nullptr) {
   cudaStream_t st = ctx->stream;
   const size_t jl = (size_t)6 * f->W;
   bool fused = false;
@@ -589,7 +593,29 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) 
                                                                        f->cost_h.as<double>(), f->cS.as<double>(), f->V, head, end));
       f->prep_lo = lo; f->prep_hi = hi;
     }
-    VX_TRY(hessian_small(ctx, f, head, end, &fused));
+    if (!group_out) {
+      VX_TRY(hessian_small(ctx, f, head, end, &fused));
+      return VX_OK;
+    }
+    // host output of a batch: evaluate the windows in groups and copy each finished group out on the copy stream while the
+    // next one is evaluated (the 11.7 MB of Hess at the bench workload take as long over PCIe as two thirds of the kernel)
+    const size_t jl6 = (size_t)6 * f->W;
+    const int G = group_out->groups;
+    VX_CUDA(cudaEventRecord(ctx->copy_done, ctx->copy_stream));          // order behind whatever the copy stream still holds
+    VX_CUDA(cudaStreamWaitEvent(st, ctx->copy_done, 0));
+    for (int gi = 0; gi < G; gi++) {
+      const int w_lo = (int)((int64_t)f->n_win * gi / G), w_hi = (int)((int64_t)f->n_win * (gi + 1) / G);
+      if (w_hi <= w_lo) continue;
+      VX_TRY(hessian_small(ctx, f, head, end, &fused, w_lo, w_hi));
+      VX_CUDA(cudaEventRecord(ctx->group_ev[gi], st));
+      VX_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->group_ev[gi], 0));
+      if (group_out->Hess) VX_CUDA(cudaMemcpyAsync(group_out->Hess + (size_t)w_lo * jl6 * jl6, f->H.as<double>() + (size_t)w_lo * jl6 * jl6,
+                                                   sizeof(double) * jl6 * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, ctx->copy_stream));
+      if (group_out->JacT) VX_CUDA(cudaMemcpyAsync(group_out->JacT + (size_t)w_lo * jl6, f->J.as<double>() + (size_t)w_lo * jl6,
+                                                   sizeof(double) * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    }
+    VX_CUDA(cudaEventRecord(ctx->copy_done, ctx->copy_stream));
+    VX_CUDA(cudaStreamWaitEvent(st, ctx->copy_done, 0));                 // the main stream is complete when the copies are
     return VX_OK;
   }
   if (!fused) {
@@ -924,11 +950,19 @@ int vx_factor_device_buffers(vx_factor *f, void **Hess, void **JacT, void **cost
 int vx_factor_hessian(vx_ctx *ctx, vx_factor *f, const vx_pose *poses, int64_t head, int64_t end, double *Hess, double *JacT, double *residual) {
   VX_ARG(f != nullptr && poses != nullptr);
   VX_TRY(vx_factor_set_poses(ctx, f, poses));
-  VX_TRY(vx_factor_hessian_async(ctx, f, head, end));
   const size_t jl = (size_t)6 * f->W;
   cudaStream_t st = ctx->stream;
-  if (Hess) VX_CUDA(cudaMemcpyAsync(Hess, f->H.p, sizeof(double) * jl * jl * f->n_win, cudaMemcpyDeviceToHost, st));
-  if (JacT) VX_CUDA(cudaMemcpyAsync(JacT, f->J.p, sizeof(double) * jl * f->n_win, cudaMemcpyDeviceToHost, st));
+  const bool grouped = f->n_win >= 32 && (Hess || JacT) && f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W);
+  if (grouped) {
+    static const int groups = getenv("VX_HESS_GROUPS") ? std::max(1, std::min(8, atoi(getenv("VX_HESS_GROUPS")))) : 4;
+    GroupOut go{Hess, JacT, groups};
+    clamp_range(f, head, end);
+    VX_TRY(launch_hessian(ctx, f, head, end, &go));
+  } else {
+    VX_TRY(vx_factor_hessian_async(ctx, f, head, end));
+    if (Hess) VX_CUDA(cudaMemcpyAsync(Hess, f->H.p, sizeof(double) * jl * jl * f->n_win, cudaMemcpyDeviceToHost, st));
+    if (JacT) VX_CUDA(cudaMemcpyAsync(JacT, f->J.p, sizeof(double) * jl * f->n_win, cudaMemcpyDeviceToHost, st));
+  }
   if (residual) VX_CUDA(cudaMemcpyAsync(residual, f->cost_h.p, sizeof(double) * f->n_win, cudaMemcpyDeviceToHost, st));
   VX_CUDA(cudaStreamSynchronize(st));
   return VX_OK;

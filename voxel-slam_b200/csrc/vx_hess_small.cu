@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(32 * NROLES, MINB)
 k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const double *__restrict__ mom,
              const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ prep, const double *__restrict__ U,
              const double *__restrict__ coe, const int32_t *__restrict__ wv_off, const double *__restrict__ poses,
-             double *__restrict__ part_t, double *__restrict__ part_d, int64_t V, int64_t head, int64_t end, int splits) {
+             double *__restrict__ part_t, double *__restrict__ part_d, int64_t V, int64_t head, int64_t end, int splits, int w_base) {
   using Cfg = SmallCfg<W, NROLES>;
   constexpr int NT = Cfg::NT, STRIDE = Cfg::STRIDE, LD = Cfg::LD, T8 = Cfg::T8, TPR = Cfg::TPR, NDQ = Cfg::NDQ, RB = Cfg::RB;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -241,7 +241,7 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
   __shared__ uint8_t s_lv[NT];       // chunk-local voxel of each voxel-frame
 
   const int tid = threadIdx.x, lane = tid & 31, role = tid >> 5;
-  const int item = blockIdx.x;
+  const int item = w_base * splits + blockIdx.x;
   const int w = item / splits, sp = item - w * splits;
   int64_t lo = wv_off[w], hi = wv_off[w + 1];
   if (lo < head) lo = head;
@@ -372,9 +372,9 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
 // blocks, voxel_map.hpp:279-281) and JacT.  One CTA per window.
 template <int W, int NT8>
 __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ part_t, const double *__restrict__ part_d,
-                                                   double *__restrict__ H, double *__restrict__ J, int splits) {
+                                                   double *__restrict__ H, double *__restrict__ J, int splits, int w_base) {
   constexpr int T = W * (W + 1) / 2, T8 = NT8 * (NT8 + 1) / 2;
-  const int w = blockIdx.x;
+  const int w = w_base + blockIdx.x;
   const int64_t jl = 6 * W;
   double *Hw = H + (size_t)w * jl * jl;
   const double *pt = part_t + (size_t)w * splits * T8 * 64;
@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ pa
 
 
 template <int W, int NROLES, int MINB>
-int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
+int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo, int w_hi) {
   using Cfg = SmallCfg<W, NROLES>;
   cudaStream_t st = ctx->stream;
   // items: enough CTAs to fill the machine several times over, but >= ~96 voxels per item
@@ -438,7 +438,7 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
     static const int forced = getenv("VX_HS_SPLITS") ? atoi(getenv("VX_HS_SPLITS")) : 0;
     if (forced > 0) splits = forced;
   }
-  const int64_t items = (int64_t)f->n_win * splits;
+  const int64_t items = (int64_t)f->n_win * splits;     // partials are indexed by the global item
   VX_TRY(f->part_t.reserve(sizeof(double) * items * Cfg::T8 * 64));
   VX_TRY(f->part_d.reserve(sizeof(double) * items * W * NF_E));
   static bool attr_set = false;
@@ -446,29 +446,32 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
     VX_CUDA(cudaFuncSetAttribute(k_hess_small<W, NROLES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
     attr_set = true;
   }
-  VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES, MINB><<<(unsigned)items, Cfg::NT, Cfg::SMEM, st>>>(
+  VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES, MINB><<<(unsigned)((w_hi - w_lo) * splits), Cfg::NT, Cfg::SMEM, st>>>(
       f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
       f->cS.as<double>(), f->U.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
-      f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits));
-  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<dim3(f->n_win, 4), 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
-                                                                               f->H.as<double>(), f->J.as<double>(), splits));
+      f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits, w_lo));
+  VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<dim3(w_hi - w_lo, 4), 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
+                                                                                   f->H.as<double>(), f->J.as<double>(), splits, w_lo));
   return VX_OK;
 }
 
 }  // namespace
 
 namespace vx {
-// Returns VX_OK and sets *handled when W has a fused instantiation.  Hess/JacT are fully overwritten.
-int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled) {
+// Returns VX_OK and sets *handled when W has a fused instantiation.  Hess/JacT of windows [w_lo, w_hi) (all when w_hi < 0) are
+// fully overwritten.
+int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled, int w_lo, int w_hi) {
   *handled = true;
+  if (w_hi < 0) { w_lo = 0; w_hi = f->n_win; }
+  if (w_hi <= w_lo) return VX_OK;
   switch (f->W) {
     case 10: {
       static const int minb = getenv("VX_HS_MINB") ? atoi(getenv("VX_HS_MINB")) : 3;
-      if (minb == 4) return launch_small<10, 4, 4>(ctx, f, head, end);
-      if (minb == 2) return launch_small<10, 4, 2>(ctx, f, head, end);
-      return launch_small<10, 4, 3>(ctx, f, head, end);
+      if (minb == 4) return launch_small<10, 4, 4>(ctx, f, head, end, w_lo, w_hi);
+      if (minb == 2) return launch_small<10, 4, 2>(ctx, f, head, end, w_lo, w_hi);
+      return launch_small<10, 4, 3>(ctx, f, head, end, w_lo, w_hi);
     }
-    case 20: return launch_small<20, 8, 1>(ctx, f, head, end);
+    case 20: return launch_small<20, 8, 1>(ctx, f, head, end, w_lo, w_hi);
     default: *handled = false; return VX_OK;
   }
 }
