@@ -69,11 +69,19 @@ __host__ __device__ __forceinline__ s33 rprt(const rot &R, const s33 &P) {
 __host__ __device__ __forceinline__ void jacobi_rot(double &app, double &aqq, double &apq, double &arp, double &arq,
                                            double &v0p, double &v0q, double &v1p, double &v1q, double &v2p, double &v2q) {
   if (apq == 0.0) return;
-  double theta = (aqq - app) / (2.0 * apq);
-  double t = 1.0 / (fabs(theta) + sqrt(fma(theta, theta, 1.0)));
-  t = theta < 0.0 ? -t : t;
-  double c = 1.0 / sqrt(fma(t, t, 1.0));
-  double s = t * c;
+  // Rotation angle phi with tan(2 phi) = 2 apq / (aqq - app) =: b / d, |phi| <= pi/4 (the smaller root t = tan phi of
+  // t^2 + 2 t d / b - 1 = 0), from the double angle: cos(2 phi) = |d| / r, r = sqrt(d^2 + b^2), c^2 = (1 + cos 2phi) / 2,
+  // s = sin(2 phi) / (2 c), t = s / c.  Two rsqrt and no division or square root per rotation: the batched solve is bound by
+  // FP64 issue slots, and rsqrt is the cheapest of the three (MUFU.RSQ64H + Newton steps, <= 1 ulp).
+  const double d = aqq - app, b2 = 2.0 * apq;
+  const double h = fma(d, d, b2 * b2);
+  if (h < 1e-290) { apq = 0.0; return; }   // |apq| and |d| below 1e-145 of the matrix scale
+  const double rs = rsqrt(h);
+  const double cc = fma(0.5 * fabs(d), rs, 0.5);      // c^2 in [1/2, 1]
+  const double q = rsqrt(cc);                          // 1 / c
+  const double c = cc * q;
+  const double s = (d < 0.0 ? -b2 : b2) * rs * (0.5 * q);
+  const double t = s * q;
   app = fma(-t, apq, app);
   aqq = fma(t, apq, aqq);
   apq = 0.0;
