@@ -64,6 +64,20 @@ __host__ __device__ __forceinline__ s33 rprt(const rot &R, const s33 &P) {
   return o;
 }
 
+// 1 / sqrt(x) for normal, positive x (the two call sites below guarantee it): MUFU.RSQ64H (2^-22.9) and one third-order
+// step y (1 + e/2 + 3 e^2 / 8), e = 1 - x y^2, which leaves ~2^-68 before rounding.  The library rsqrt() wraps the same seed
+// in special-case handling (zero, denormal, infinity, NaN: a branch and a slow-path call per use) that this solve never needs.
+__host__ __device__ __forceinline__ double rsqrt_pos(double x) {
+#ifdef __CUDA_ARCH__
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-(x * y), y, 1.0);
+  return fma(y, e * fma(0.375, e, 0.5), y);
+#else
+  return 1.0 / sqrt(x);
+#endif
+}
+
 // One Jacobi rotation annihilating a_pq of a symmetric 3x3 held in scalars; V accumulates columns.
 // app,aqq,apq: the 2x2 pivot block; arp,arq: the remaining row's couplings; vXp,vXq: columns p,q of V.
 __host__ __device__ __forceinline__ void jacobi_rot(double &app, double &aqq, double &apq, double &arp, double &arq,
@@ -72,13 +86,13 @@ __host__ __device__ __forceinline__ void jacobi_rot(double &app, double &aqq, do
   // Rotation angle phi with tan(2 phi) = 2 apq / (aqq - app) =: b / d, |phi| <= pi/4 (the smaller root t = tan phi of
   // t^2 + 2 t d / b - 1 = 0), from the double angle: cos(2 phi) = |d| / r, r = sqrt(d^2 + b^2), c^2 = (1 + cos 2phi) / 2,
   // s = sin(2 phi) / (2 c), t = s / c.  Two rsqrt and no division or square root per rotation: the batched solve is bound by
-  // FP64 issue slots, and rsqrt is the cheapest of the three (MUFU.RSQ64H + Newton steps, <= 1 ulp).
+  // FP64 issue slots, and rsqrt is the cheapest of the three (rsqrt_pos above).
   const double d = aqq - app, b2 = 2.0 * apq;
   const double h = fma(d, d, b2 * b2);
   if (h < 1e-290) { apq = 0.0; return; }   // |apq| and |d| below 1e-145 of the matrix scale
-  const double rs = rsqrt(h);
+  const double rs = rsqrt_pos(h);
   const double cc = fma(0.5 * fabs(d), rs, 0.5);      // c^2 in [1/2, 1]
-  const double q = rsqrt(cc);                          // 1 / c
+  const double q = rsqrt_pos(cc);                      // 1 / c
   const double c = cc * q;
   const double s = (d < 0.0 ? -b2 : b2) * rs * (0.5 * q);
   const double t = s * q;
@@ -104,16 +118,20 @@ __host__ __device__ inline void eig3_jacobi(const s33 &A, double lam[3], double 
   double inv = 1.0 / scale;
   double a00 = A.xx * inv, a11 = A.yy * inv, a22 = A.zz * inv, a01 = A.xy * inv, a02 = A.xz * inv, a12 = A.yz * inv;
   double v00 = 1, v01 = 0, v02 = 0, v10 = 0, v11 = 1, v12 = 0, v20 = 0, v21 = 0, v22 = 1;
+  // Plane covariances take 3-4 sweeps (never fewer than 2): the first three run without the convergence test, which costs
+  // nearly as much as a rotation; a rotation of an already diagonal pair returns at once.
 #pragma unroll 1
   for (int sweep = 0; sweep < 12; sweep++) {
-    double off = fabs(a01) + fabs(a02) + fabs(a12);
-    if (off <= 1e-300) break;
-    // converged when every off-diagonal is negligible against its two diagonal neighbours
-    const double eps = 1.1102230246251565e-16;
-    bool c01 = fabs(a01) <= eps * 0.125 * fmin(fabs(a00), fabs(a11)) || a01 == 0.0;
-    bool c02 = fabs(a02) <= eps * 0.125 * fmin(fabs(a00), fabs(a22)) || a02 == 0.0;
-    bool c12 = fabs(a12) <= eps * 0.125 * fmin(fabs(a11), fabs(a22)) || a12 == 0.0;
-    if (c01 && c02 && c12) break;
+    if (sweep >= 3) {
+      double off = fabs(a01) + fabs(a02) + fabs(a12);
+      if (off <= 1e-300) break;
+      // converged when every off-diagonal is negligible against its two diagonal neighbours
+      const double eps = 1.1102230246251565e-16;
+      bool c01 = fabs(a01) <= eps * 0.125 * fmin(fabs(a00), fabs(a11)) || a01 == 0.0;
+      bool c02 = fabs(a02) <= eps * 0.125 * fmin(fabs(a00), fabs(a22)) || a02 == 0.0;
+      bool c12 = fabs(a12) <= eps * 0.125 * fmin(fabs(a11), fabs(a22)) || a12 == 0.0;
+      if (c01 && c02 && c12) break;
+    }
     // (p,q) = (0,1): remaining index r = 2 couples through a02 (r,p) and a12 (r,q)
     jacobi_rot(a00, a11, a01, a02, a12, v00, v01, v10, v11, v20, v21);
     // (0,2): r = 1 couples through a01 (r,p) and a12 (r,q)
