@@ -62,9 +62,11 @@ struct ProfSpan { const char *name; cudaEvent_t a, b; };
 struct vx_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t copy_stream = nullptr;   // device->host copies of finished window groups while later groups are evaluated
+  // vx_factor_hessian on a batched factor: window groups are evaluated on their own streams (the CTAs of a later group fill
+  // the SM slots an earlier one leaves idle) and each group's Hess/JacT go to the host behind its last kernel
+  cudaStream_t group_stream[8] = {};
   cudaEvent_t group_ev[8] = {};
-  cudaEvent_t copy_done = nullptr;
+  cudaEvent_t fork_ev = nullptr;
   int sm_count = 148;
   int64_t launches = 0;
   bool profiling = false;

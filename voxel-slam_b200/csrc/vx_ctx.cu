@@ -1,4 +1,5 @@
 // vx_ctx.cu — context, error text, version.
+#include <algorithm>
 #include "vx_common.cuh"
 
 namespace vx {
@@ -33,9 +34,15 @@ int vx_ctx_create(int device, vx_ctx **out) {
   VX_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   VX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  VX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  {
+    // earlier groups get the higher priority: the block scheduler then drains them first, so their copies start early
+    int least = 0, greatest = 0;
+    VX_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    for (int g = 0; g < 8; g++)
+      VX_CUDA(cudaStreamCreateWithPriority(&c->group_stream[g], cudaStreamNonBlocking, std::min(least, greatest + g)));
+  }
   for (auto &e : c->group_ev) VX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  VX_CUDA(cudaEventCreateWithFlags(&c->copy_done, cudaEventDisableTiming));
+  VX_CUDA(cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
   c->pinned_cap = 1 << 16;
   VX_CUDA(cudaMallocHost(&c->pinned, c->pinned_cap));
   *out = c;
@@ -46,9 +53,9 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   if (!ctx) return VX_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
-  if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+  for (auto &g : ctx->group_stream) if (g) { cudaStreamSynchronize(g); cudaStreamDestroy(g); }
   for (auto &e : ctx->group_ev) if (e) cudaEventDestroy(e);
-  if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
+  if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
   for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
   ctx->scratch.release();
   ctx->scratch2.release();

@@ -597,25 +597,32 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, 
       VX_TRY(hessian_small(ctx, f, head, end, &fused));
       return VX_OK;
     }
-    // host output of a batch: evaluate the windows in groups and copy each finished group out on the copy stream while the
-    // next one is evaluated (the 11.7 MB of Hess at the bench workload take as long over PCIe as two thirds of the kernel)
+    // host output of a batch: the windows are evaluated in groups, each on its own stream with its Hess/JacT copy behind its
+    // last kernel.  The 11.7 MB of Hess at the bench workload take as long over PCIe as two thirds of the evaluation; with
+    // concurrent groups the kernels keep the SMs as full as one launch would (a later group's CTAs take the slots an earlier
+    // one's last wave leaves idle) and only the last group's copy is exposed.  The group streams carry descending priorities
+    // (vx_ctx.cu): without them the block scheduler interleaves the groups, all finish together and no copy starts early
+    // (measured: 0.61 ms without priorities, 0.48 ms with, 0.557 ms for groups run back to back on one stream).  Groups that
+    // shrink towards the end (4 4 4 4 4 3 2 1) did not help: 0.49 ms.
     const size_t jl6 = (size_t)6 * f->W;
     const int G = group_out->groups;
-    VX_CUDA(cudaEventRecord(ctx->copy_done, ctx->copy_stream));          // order behind whatever the copy stream still holds
-    VX_CUDA(cudaStreamWaitEvent(st, ctx->copy_done, 0));
+    VX_CUDA(cudaEventRecord(ctx->fork_ev, st));
     for (int gi = 0; gi < G; gi++) {
       const int w_lo = (int)((int64_t)f->n_win * gi / G), w_hi = (int)((int64_t)f->n_win * (gi + 1) / G);
       if (w_hi <= w_lo) continue;
-      VX_TRY(hessian_small(ctx, f, head, end, &fused, w_lo, w_hi));
-      VX_CUDA(cudaEventRecord(ctx->group_ev[gi], st));
-      VX_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->group_ev[gi], 0));
+      cudaStream_t gs = ctx->group_stream[gi];
+      VX_CUDA(cudaStreamWaitEvent(gs, ctx->fork_ev, 0));
+      ctx->stream = gs;                                   // hessian_small launches (and times) on the context stream
+      const int rc = hessian_small(ctx, f, head, end, &fused, w_lo, w_hi);
+      ctx->stream = st;
+      VX_TRY(rc);
       if (group_out->Hess) VX_CUDA(cudaMemcpyAsync(group_out->Hess + (size_t)w_lo * jl6 * jl6, f->H.as<double>() + (size_t)w_lo * jl6 * jl6,
-                                                   sizeof(double) * jl6 * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, ctx->copy_stream));
+                                                   sizeof(double) * jl6 * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, gs));
       if (group_out->JacT) VX_CUDA(cudaMemcpyAsync(group_out->JacT + (size_t)w_lo * jl6, f->J.as<double>() + (size_t)w_lo * jl6,
-                                                   sizeof(double) * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, ctx->copy_stream));
+                                                   sizeof(double) * jl6 * (w_hi - w_lo), cudaMemcpyDeviceToHost, gs));
+      VX_CUDA(cudaEventRecord(ctx->group_ev[gi], gs));
+      VX_CUDA(cudaStreamWaitEvent(st, ctx->group_ev[gi], 0));   // the main stream is complete when every group is
     }
-    VX_CUDA(cudaEventRecord(ctx->copy_done, ctx->copy_stream));
-    VX_CUDA(cudaStreamWaitEvent(st, ctx->copy_done, 0));                 // the main stream is complete when the copies are
     return VX_OK;
   }
   if (!fused) {
@@ -954,7 +961,7 @@ int vx_factor_hessian(vx_ctx *ctx, vx_factor *f, const vx_pose *poses, int64_t h
   cudaStream_t st = ctx->stream;
   const bool grouped = f->n_win >= 32 && (Hess || JacT) && f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W);
   if (grouped) {
-    static const int groups = getenv("VX_HESS_GROUPS") ? std::max(1, std::min(8, atoi(getenv("VX_HESS_GROUPS")))) : 4;
+    static const int groups = getenv("VX_HESS_GROUPS") ? std::max(1, std::min(8, atoi(getenv("VX_HESS_GROUPS")))) : 8;
     GroupOut go{Hess, JacT, groups};
     clamp_range(f, head, end);
     VX_TRY(launch_hessian(ctx, f, head, end, &go));
