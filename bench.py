@@ -245,7 +245,39 @@ def extra_benches(pkg, ctx):
                        "kernel_ms": kms, "points_per_s_kernel": q.shape[0] / (kms * 1e-3) if kms > 0 else None,
                        "kernel_hbm_gbs": (96 * q.shape[0] + 408 * o["match_num"]) / (kms * 1e-3) / 1e9 if kms > 0 else None,
                        "what": "vx_lio_match_accumulate: one pass of voxelslam.cpp:1005-1050 over a ~60k-point sweep (synthetic layer-0 plane map)"}
+    # the call the LIO loop makes per sweep (voxelslam.cpp:962-1098): raw float xyz in (12 B/point), var_init on the device,
+    # up to 4 match/update iterations, state + covariance out
+    q32 = q.astype(np.float32)
+    ext = (np.eye(3)[None], np.zeros((1, 3)))
+    se = gm.lio_state_estimation(q32, R0[0], p0[0], cov, xyz_ext=(ext, 0.01, 0.01))
+    t0 = time.perf_counter()
+    for _ in range(10):
+        se = gm.lio_state_estimation(q32, R0[0], p0[0], cov, xyz_ext=(ext, 0.01, 0.01))
+    t = (time.perf_counter() - t0) / 10
+    out["lio_state_estimation"] = {"ms_e2e": 1e3 * t, "points": int(q.shape[0]), "iterations": int(se["iters"]),
+                                   "points_per_s_e2e": q.shape[0] / t, "point_iterations_per_s_e2e": q.shape[0] * se["iters"] / t,
+                                   "h2d_bytes": int(q32.nbytes),
+                                   "what": "vx_lio_state_estimation_xyz: whole ESIKF update of one ~60k-point sweep, host scan in, host state out (wall clock)"}
     gm.free()
+    # the reference's CPU path for the same update (oracle restatement, one thread as in the reference's LIO loop), on a map
+    # the oracle builds from the same sweeps
+    try:
+        import oracle_bind as ob
+        rng2 = np.random.Generator(np.random.PCG64(20241008 + 5))
+        om = ob.LocalMap(win_size=10, voxel_size=1.0, thre=(1, 1, 1, 1), dept_err=0.01, beam_err=0.01)
+        for i in range(10):
+            om.push(scene.scan(rects, Rl[i], pl[i], scene.xt32_dirs(700), rng2, range_noise=0.01, blind=0.7), (Rl[i:i + 1], pl[i:i + 1]), ob.default_cov())
+        opv = ob.var_init(q, 0.01, 0.01)
+        best = 1e30
+        for _ in range(3):
+            t0 = time.perf_counter()
+            oref = om.lio_state_estimation(opv, R0[0], p0[0], ob.default_cov())
+            best = min(best, time.perf_counter() - t0)
+        out["lio_state_estimation"]["cpu_baseline"] = {"ms": 1e3 * best, "iterations": int(oref["iters"]), "points_per_s": q.shape[0] / best,
+                                                       "point_iterations_per_s": q.shape[0] * oref["iters"] / best, "cores": 1, "kind": "port",
+                                                       "sample": "the same sweep, oracle lio_state_estimation on an oracle-built map of the same 10 sweeps, best of 3"}
+    except Exception as e:  # the CPU leg is a reported baseline only
+        out["lio_state_estimation"]["cpu_baseline"] = {"error": str(e)[:200]}
     # --- C2-shaped local mapping: the device sliding-window map fed with ~60k-point sweeps (A5 -> A6 -> A9/A11 -> A12)
     Wl = 10
     Rm, pm = scene.arc_trajectory(Wl + 4, 5, step=0.5, yaw_step_deg=3.0)
@@ -410,7 +442,11 @@ def run_b200(args, rank, world, local_rank):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = alg_bytes / (pass_ms * 1e-3) / 1e9
     flops = algorithmic_flops(fac)
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of k_hess_small from the committed ncu --set full capture of this workload
+                # (profiles/r01j_k_hess_small_ncu.txt: 249.29 + 22.36 MB); only valid for the default workload size
+                "traffic": 271650048 if (args.windows, args.voxels_per_window) == (N_WINDOWS, VOX_PER_WIN) else None,
+                "traffic_source": "profiles/r01j_k_hess_small_ncu.txt (ncu --set full, one launch of k_hess_small)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
                 "kernel": "whole acc_evaluate2 pass (sum of its kernels' event times); top kernel = " + top,
                 "algorithmic_bytes_per_step": alg_bytes, "kernels": kern,

@@ -1,8 +1,80 @@
 // vx_ctx.cu — context, error text, version.
 #include <algorithm>
+#include <mutex>
 #include "vx_common.cuh"
 
 namespace vx {
+// ---- cache of freed device blocks (see DevBuf, vx_common.cuh) ---------------------------------------------------
+namespace {
+struct FreeBlock { void *p; size_t bytes; int device; };
+std::mutex g_cache_mu;
+std::vector<FreeBlock> g_cache;
+size_t g_cache_bytes = 0;
+constexpr size_t CACHE_MAX_BYTES = (size_t)8 << 30;   // retained at most; beyond it blocks go back to the driver
+constexpr size_t CACHE_MAX_BLOCKS = 256;
+}  // namespace
+
+void *cached_malloc(size_t bytes, size_t *got) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    int best = -1;
+    for (int i = 0; i < (int)g_cache.size(); i++) {
+      const FreeBlock &b = g_cache[i];
+      if (b.device != dev || b.bytes < bytes || b.bytes > 2 * bytes + 4096) continue;   // best fit, at most 2x oversized
+      if (best < 0 || b.bytes < g_cache[best].bytes) best = i;
+    }
+    if (best >= 0) {
+      FreeBlock b = g_cache[best];
+      g_cache.erase(g_cache.begin() + best);
+      g_cache_bytes -= b.bytes;
+      *got = b.bytes;
+      return b.p;
+    }
+  }
+  void *p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    cached_trim(dev);                                   // out of memory: give the cached blocks back and try once more
+    if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+  }
+  *got = bytes;
+  return p;
+}
+
+void cached_free(void *p, size_t bytes) {
+  if (!p) return;
+  cudaPointerAttributes at;
+  int dev = 0;
+  if (cudaPointerGetAttributes(&at, p) == cudaSuccess) dev = at.device; else { cudaGetLastError(); cudaGetDevice(&dev); }
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    if (g_cache_bytes + bytes <= CACHE_MAX_BYTES && g_cache.size() < CACHE_MAX_BLOCKS) {
+      g_cache.push_back({p, bytes, dev});
+      g_cache_bytes += bytes;
+      return;
+    }
+  }
+  cudaFree(p);
+}
+
+void cached_trim(int device) {
+  std::vector<FreeBlock> out;
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (size_t i = 0; i < g_cache.size();) {
+      if (g_cache[i].device == device) { out.push_back(g_cache[i]); g_cache_bytes -= g_cache[i].bytes; g_cache.erase(g_cache.begin() + i); }
+      else i++;
+    }
+  }
+  int cur = 0;
+  cudaGetDevice(&cur);
+  if (!out.empty()) cudaSetDevice(device);
+  for (auto &b : out) cudaFree(b.p);
+  if (!out.empty()) cudaSetDevice(cur);
+}
+
 static thread_local char g_err[512] = "";
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -60,6 +132,7 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   ctx->scratch.release();
   ctx->scratch2.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  vx::cached_trim(ctx->device);
   delete ctx;
   return VX_OK;
 }

@@ -231,8 +231,11 @@ int lio_pass_device(vx_ctx *ctx, vx_planemap *map, const vx_point_var *d_pts, in
   VX_KERNEL(ctx, "k_lio_pass", k_lio_pass<<<nblocks, LIO_THREADS, 0, ctx->stream>>>(d_pts, n, X, map->hkeys.as<uint64_t>(), map->hvals.as<int32_t>(), map->hmask,
                                                                                    map->nodes.as<vx_map_node>(), map->voxel_size, d_cache, d_flags, partial));
   VX_KERNEL(ctx, "k_lio_fin", k_lio_fin<<<NACC, 256, 0, ctx->stream>>>(partial, nblocks, fin));
-  VX_CUDA(cudaMemcpyAsync(out34, fin, sizeof(double) * NACC, cudaMemcpyDeviceToHost, ctx->stream));
+  // through the context's pinned staging area: a copy into pageable memory is staged by the driver and costs a second wait
+  static_assert(sizeof(double) * NACC <= (1 << 16), "pinned staging area too small");
+  VX_CUDA(cudaMemcpyAsync(ctx->pinned, fin, sizeof(double) * NACC, cudaMemcpyDeviceToHost, ctx->stream));
   VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  memcpy(out34, ctx->pinned, sizeof(double) * NACC);
   return VX_OK;
 }
 void unpack_acc(const double *a, double *HTH36, double *HTz6, double *nnt9, int32_t *match_num) {
