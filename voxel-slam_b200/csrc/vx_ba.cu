@@ -1,8 +1,9 @@
 // vx_ba.cu — Lidar_BA_Optimizer::damping_iter (voxel_map.hpp:422-497) over the device LidarFactor.
 //
-// The LM control flow, the gauge fix, the (6W x 6W) LDL^T solve and the pose retraction run on the
-// host (W <= 20: 60..120 unknowns, microseconds); acc_evaluate2 / evaluate_only_residual run on the
-// device.  A factor created with n_windows > 1 is a BATCH of independent problems (bottom-level GBA
+// acc_evaluate2 / evaluate_only_residual run on the device; so do the gauge fix and the (6W x 6W) LDL^T solve of every
+// window with up to 128 unknowns (k_lm_solve below: W <= 21, i.e. every local BA and every bottom-level GBA window).  The
+// LM control flow and the pose retraction (6W numbers per window) stay on the host.  Larger systems (top-level GBA) take
+// the host sweep or the blocked device factorisation of vx_ldlt.cu.  A factor created with n_windows > 1 is a BATCH of independent problems (bottom-level GBA
 // windows, voxelslam.cpp:3096): every window keeps its own damping state (u, v), accept/reject
 // sequence and stop test, and each device pass evaluates all windows at once.
 #include "vx_factor.cuh"
@@ -31,6 +32,145 @@ void retract_rot(const double *R, const double *w, double *out) {
   }
   for (int c = 0; c < 3; c++)
     for (int r = 0; r < 3; r++) out[c * 3 + r] = R[0 * 3 + r] * E[c * 3 + 0] + R[1 * 3 + r] * E[c * 3 + 1] + R[2 * 3 + r] * E[c * 3 + 2];
+}
+
+
+// ---- batched LM step on the device (6W <= LM_MAXN unknowns per window) ------------------------------------------
+// One CTA per window, the system in shared memory, one thread per row.  The arithmetic is the host sweep's
+// (hm::ldlt_lower_solve, vx_hostmat.hpp: Eigen's unblocked diagonal-pivot LDL^T on the lower triangle) operation for
+// operation — explicit round-to-nearest multiplies and adds, no FMA contraction, sums in the same order — so dx, and with
+// it every accept / reject decision of the LM loop, is bitwise what the host solve gives.  What it removes is the traffic:
+// the 6W x 6W Hessians stay in HBM (11.7 MB per LM iteration at 399 windows), only dx and q1 (6W + 1 doubles per window)
+// cross PCIe, and 399 solves run side by side instead of one after another on a host core.
+constexpr int LM_MAXN = 128;
+
+// windows with mask[w] != 0 take the new evaluation; the others keep their old Hess / JacT (voxel_map.hpp:486-489)
+__global__ void k_lm_keep(const double *__restrict__ H, const double *__restrict__ J, double *__restrict__ Hk, double *__restrict__ Jk,
+                          const int32_t *__restrict__ mask, int n) {
+  const int w = blockIdx.x;
+  if (!mask[w]) return;
+  const size_t nn = (size_t)n * n;
+  const double2 *src = reinterpret_cast<const double2 *>(H + nn * w);
+  double2 *dst = reinterpret_cast<double2 *>(Hk + nn * w);
+  for (size_t k = threadIdx.x; k < nn / 2; k += blockDim.x) dst[k] = src[k];
+  for (int k = threadIdx.x; k < n; k += blockDim.x) Jk[(size_t)n * w + k] = J[(size_t)n * w + k];
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT)
+k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const double *__restrict__ u_w, const int32_t *__restrict__ act,
+           int n, double *__restrict__ dx, double *__restrict__ q1) {
+  extern __shared__ double lm_sm[];
+  double *A = lm_sm;                 // [n][n] column-major, lower triangle used
+  double *tmp = A + (size_t)n * n;   // [n]
+  double *x = tmp + n;               // [n]
+  double *D = x + n;                 // [n]
+  double *Jg = D + n;                // [n]
+  __shared__ int s_tr[LM_MAXN];
+  __shared__ double s_rv[NT / 32];
+  __shared__ int s_ri[NT / 32];
+  const int w = blockIdx.x, t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  if (!act[w]) return;
+  const double u = u_w[w];
+#define LM_AT(r, c) A[(size_t)(c) * n + (r)]
+  // gauge: pose 0 fixed (voxel_map.hpp:452-455)
+  for (int idx = t; idx < n * n; idx += NT) {
+    const int c = idx / n, r = idx - c * n;
+    double v = Hk[(size_t)n * n * w + idx];
+    if (r < 6 || c < 6) v = r == c ? 1.0 : 0.0;
+    A[idx] = v;
+  }
+  __syncthreads();
+  if (t < n) {
+    D[t] = LM_AT(t, t);
+    Jg[t] = t < 6 ? 0.0 : Jk[(size_t)n * w + t];
+  }
+  __syncthreads();
+  if (t < n) {
+    LM_AT(t, t) = __dadd_rn(LM_AT(t, t), __dmul_rn(u, D[t]));
+    x[t] = -Jg[t];
+  }
+  __syncthreads();
+  for (int k = 0; k < n; k++) {
+    // pivot: first index of the largest |diagonal| in [k, n); comparisons with NaN are false, as on the host
+    {
+      double bv = -1.0; int bi = n;
+      if (t >= k && t < n) { const double v = fabs(LM_AT(t, t)); if (v == v) { bv = v; bi = t; } }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_down_sync(0xffffffffu, bv, o);
+        const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+      }
+      if (lane == 0) { s_rv[wp] = bv; s_ri[wp] = bi; }
+      __syncthreads();
+      if (t == 0) {
+        double v = s_rv[0]; int i = s_ri[0];
+        for (int q = 1; q < NT / 32; q++) if (s_rv[q] > v || (s_rv[q] == v && s_ri[q] < i)) { v = s_rv[q]; i = s_ri[q]; }
+        const double dk = fabs(LM_AT(k, k));
+        if (!(dk == dk) || i >= n) i = k;      // NaN on the diagonal at k: the host keeps k
+        s_tr[k] = i;
+      }
+      __syncthreads();
+    }
+    const int big = s_tr[k];
+    if (big != k) {   // symmetric interchange restricted to the lower triangle
+      if (t < k) { const double a = LM_AT(k, t); LM_AT(k, t) = LM_AT(big, t); LM_AT(big, t) = a; }
+      else if (t > big && t < n) { const double a = LM_AT(t, k); LM_AT(t, k) = LM_AT(t, big); LM_AT(t, big) = a; }
+      else if (t > k && t < big) { const double a = LM_AT(t, k); LM_AT(t, k) = LM_AT(big, t); LM_AT(big, t) = a; }
+      else if (t == k) { const double a = LM_AT(k, k); LM_AT(k, k) = LM_AT(big, big); LM_AT(big, big) = a; }
+      __syncthreads();
+    }
+    if (k > 0) {
+      if (t < k) tmp[t] = __dmul_rn(LM_AT(t, t), LM_AT(k, t));
+      __syncthreads();
+      if (t == k) {
+        double acc = 0.0;
+        for (int j = 0; j < k; j++) acc = __dadd_rn(acc, __dmul_rn(LM_AT(k, j), tmp[j]));
+        LM_AT(k, k) = __dadd_rn(LM_AT(k, k), -acc);
+      } else if (t > k && t < n) {
+        double a = LM_AT(t, k);
+        for (int j = 0; j < k; j++) {
+          const double tj = tmp[j];
+          if (tj == 0.0) continue;
+          a = __dadd_rn(a, -__dmul_rn(LM_AT(t, j), tj));
+        }
+        LM_AT(t, k) = a;
+      }
+      __syncthreads();
+    }
+    const double akk = LM_AT(k, k);
+    if (fabs(akk) > 0.0 && t > k && t < n) LM_AT(t, k) = LM_AT(t, k) / akk;
+    __syncthreads();
+  }
+  // solve: P, L, D, L^T, P^T
+  if (t == 0) for (int k = 0; k < n; k++) if (s_tr[k] != k) { const double a = x[k]; x[k] = x[s_tr[k]]; x[s_tr[k]] = a; }
+  __syncthreads();
+  for (int j = 0; j < n; j++) {
+    const double xj = x[j];
+    if (xj != 0.0 && t > j && t < n) x[t] = __dadd_rn(x[t], -__dmul_rn(LM_AT(t, j), xj));
+    __syncthreads();
+  }
+  if (t < n) {
+    const double tol = 1.0 / 1.7976931348623157e308;
+    x[t] = fabs(LM_AT(t, t)) > tol ? x[t] / LM_AT(t, t) : 0.0;
+  }
+  __syncthreads();
+  if (t == 0) {
+    for (int j = n - 1; j >= 0; j--) {
+      double s = x[j];
+      for (int i = j + 1; i < n; i++) s = __dadd_rn(s, -__dmul_rn(LM_AT(i, j), x[i]));
+      x[j] = s;
+    }
+    for (int k = n - 1; k >= 0; k--) if (s_tr[k] != k) { const double a = x[k]; x[k] = x[s_tr[k]]; x[s_tr[k]] = a; }
+    // q1 = 0.5 dx^T (u D dx - JacT)   (voxel_map.hpp:470)
+    double q = 0.0;
+    for (int r = 0; r < n; r++) q = __dadd_rn(q, __dmul_rn(x[r], __dadd_rn(__dmul_rn(__dmul_rn(u, D[r]), x[r]), -Jg[r])));
+    q1[w] = 0.5 * q;
+  }
+  __syncthreads();
+  if (t < n) dx[(size_t)n * w + t] = x[t];
+#undef LM_AT
 }
 
 }  // namespace
@@ -62,7 +202,8 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   }
   static const int ldlt_device_min = [] { const char *e = std::getenv("VX_LDLT_DEVICE_MIN"); return e ? std::atoi(e) : 384; }();
   const size_t hsz = (size_t)jl * jl;
-  std::vector<double> Hess(hsz * NW), JacT((size_t)jl * NW), Hnew(hsz * NW), Jnew((size_t)jl * NW), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
+  const bool host_mats = !(jl <= LM_MAXN && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr);
+  std::vector<double> Hess(host_mats ? hsz * NW : 0), JacT(host_mats ? (size_t)jl * NW : 0), Hnew(Hess.size()), Jnew(JacT.size()), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
   std::vector<double> u(NW, 0.01), v(NW, 2.0), A(hsz), dxi(jl), D(jl), nb(jl), tmp, q1s(NW, 0.0);
   std::vector<char> calc(NW, 1), active(NW, 1), conv(NW, 1);
   std::vector<int> iters(NW, 0), tr;
@@ -71,11 +212,38 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   if (resis) std::fill(resis, resis + 2 * (size_t)NW, 0.0);
   for (int w = 0; w < NW; w++) if (few[w]) { active[w] = 0; conv[w] = 0; }
 
+  // device LM step (k_lm_keep / k_lm_solve): Hess and JacT never leave the device
+  const bool dev = jl <= LM_MAXN && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr;
+  std::vector<int32_t> mask(NW);
+  std::vector<double> dx_all;
+  cudaStream_t st = ctx->stream;
+  if (dev) {
+    VX_TRY(f->lm_H.reserve(sizeof(double) * hsz * NW)); VX_TRY(f->lm_J.reserve(sizeof(double) * jl * NW));
+    VX_TRY(f->lm_dx.reserve(sizeof(double) * jl * NW)); VX_TRY(f->lm_q1.reserve(sizeof(double) * NW));
+    VX_TRY(f->lm_u.reserve(sizeof(double) * NW)); VX_TRY(f->lm_mask.reserve(sizeof(int32_t) * NW));
+    dx_all.resize((size_t)jl * NW);
+    const size_t smem = sizeof(double) * ((size_t)jl * jl + 4 * jl);
+    if (jl <= 64) VX_CUDA(cudaFuncSetAttribute(k_lm_solve<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else VX_CUDA(cudaFuncSetAttribute(k_lm_solve<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  bool evaluated = false;
+
   for (int it = 0; it < max_iter; it++) {
     bool any_active = false, any_calc = false;
     for (int w = 0; w < NW; w++) { any_active |= active[w] != 0; any_calc |= (active[w] && calc[w]); }
     if (!any_active) break;
-    if (any_calc) {
+    if (any_calc && dev) {
+      VX_TRY(vx_factor_set_poses(ctx, f, x.data()));
+      VX_TRY(vx_factor_hessian_async(ctx, f, 0, -1));
+      for (int w = 0; w < NW; w++) mask[w] = active[w] && calc[w];
+      VX_CUDA(cudaMemcpyAsync(f->lm_mask.p, mask.data(), sizeof(int32_t) * NW, cudaMemcpyHostToDevice, st));
+      VX_KERNEL(ctx, "k_lm_keep", k_lm_keep<<<NW, 256, 0, st>>>(f->H.as<double>(), f->J.as<double>(), f->lm_H.as<double>(), f->lm_J.as<double>(),
+                                                              f->lm_mask.as<int32_t>(), jl));
+      VX_CUDA(cudaMemcpyAsync(r_new.data(), f->cost_h.p, sizeof(double) * NW, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+      for (int w = 0; w < NW; w++) if (mask[w]) r1[w] = r_new[w];
+      evaluated = true;
+    } else if (any_calc) {
       VX_TRY(vx_factor_hessian(ctx, f, x.data(), 0, -1, Hnew.data(), Jnew.data(), r_new.data()));
       for (int w = 0; w < NW; w++)
         if (active[w] && calc[w]) {
@@ -85,30 +253,51 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
           if (hess_out) std::copy(Hnew.begin() + hsz * w, Hnew.begin() + hsz * (w + 1), hess_out + hsz * w);   // *hess = Hess, before the gauge fix (:446)
         }
     }
+    if (dev) {
+      for (int w = 0; w < NW; w++) mask[w] = active[w];
+      VX_CUDA(cudaMemcpyAsync(f->lm_mask.p, mask.data(), sizeof(int32_t) * NW, cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemcpyAsync(f->lm_u.p, u.data(), sizeof(double) * NW, cudaMemcpyHostToDevice, st));
+      const size_t smem = sizeof(double) * ((size_t)jl * jl + 4 * jl);
+      if (jl <= 64) {
+        VX_KERNEL(ctx, "k_lm_solve", k_lm_solve<64><<<NW, 64, smem, st>>>(f->lm_H.as<double>(), f->lm_J.as<double>(), f->lm_u.as<double>(),
+                                                                        f->lm_mask.as<int32_t>(), jl, f->lm_dx.as<double>(), f->lm_q1.as<double>()));
+      } else {
+        VX_KERNEL(ctx, "k_lm_solve", k_lm_solve<128><<<NW, 128, smem, st>>>(f->lm_H.as<double>(), f->lm_J.as<double>(), f->lm_u.as<double>(),
+                                                                          f->lm_mask.as<int32_t>(), jl, f->lm_dx.as<double>(), f->lm_q1.as<double>()));
+      }
+      VX_CUDA(cudaMemcpyAsync(dx_all.data(), f->lm_dx.p, sizeof(double) * jl * NW, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaMemcpyAsync(q1s.data(), f->lm_q1.p, sizeof(double) * NW, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+    }
     for (int w = 0; w < NW; w++) {
       if (!active[w]) continue;
       if (it == 0 && resis) resis[2 * w] = r1[w];
-      double *H = Hess.data() + hsz * w, *J = JacT.data() + (size_t)jl * w;
-      // gauge: pose 0 fixed (voxel_map.hpp:452-455)
-      for (int c = 0; c < jl; c++) for (int r = 0; r < 6; r++) H[(size_t)c * jl + r] = 0.0;
-      for (int c = 0; c < 6; c++) for (int r = 0; r < jl; r++) H[(size_t)c * jl + r] = 0.0;
-      for (int r = 0; r < 6; r++) { H[(size_t)r * jl + r] = 1.0; J[r] = 0.0; }
-      for (int r = 0; r < jl; r++) D[r] = H[(size_t)r * jl + r];
-      std::copy(H, H + hsz, A.begin());
-      for (int r = 0; r < jl; r++) { A[(size_t)r * jl + r] += u[w] * D[r]; nb[r] = -J[r]; }
-      // small windows: the host sweep (microseconds); the top-level GBA window (W ~ 399, 2394 unknowns, 4.6 GFLOP) goes to
-      // the blocked device factorisation (vx_ldlt.cu)
-      if (jl >= ldlt_device_min) VX_TRY(ldlt_lower_solve_device(ctx, A.data(), jl, nb.data(), dxi.data()));
-      else hm::ldlt_lower_solve(A.data(), jl, nb.data(), dxi.data(), tr, tmp);
+      const double *dxw = dxi.data();
+      if (dev) {
+        dxw = dx_all.data() + (size_t)jl * w;
+      } else {
+        double *H = Hess.data() + hsz * w, *J = JacT.data() + (size_t)jl * w;
+        // gauge: pose 0 fixed (voxel_map.hpp:452-455)
+        for (int c = 0; c < jl; c++) for (int r = 0; r < 6; r++) H[(size_t)c * jl + r] = 0.0;
+        for (int c = 0; c < 6; c++) for (int r = 0; r < jl; r++) H[(size_t)c * jl + r] = 0.0;
+        for (int r = 0; r < 6; r++) { H[(size_t)r * jl + r] = 1.0; J[r] = 0.0; }
+        for (int r = 0; r < jl; r++) D[r] = H[(size_t)r * jl + r];
+        std::copy(H, H + hsz, A.begin());
+        for (int r = 0; r < jl; r++) { A[(size_t)r * jl + r] += u[w] * D[r]; nb[r] = -J[r]; }
+        // the host sweep, or for the top-level GBA window (W ~ 399, 2394 unknowns, 4.6 GFLOP) the blocked device
+        // factorisation (vx_ldlt.cu)
+        if (jl >= ldlt_device_min) VX_TRY(ldlt_lower_solve_device(ctx, A.data(), jl, nb.data(), dxi.data()));
+        else hm::ldlt_lower_solve(A.data(), jl, nb.data(), dxi.data(), tr, tmp);
+        double q1 = 0.0;
+        for (int r = 0; r < jl; r++) q1 += dxi[r] * (u[w] * D[r] * dxi[r] - J[r]);
+        q1s[w] = 0.5 * q1;
+      }
       for (int j = 0; j < W; j++) {
         const vx_pose &s = x[(size_t)w * W + j];
         vx_pose &d = xt[(size_t)w * W + j];
-        retract_rot(s.R, &dxi[6 * j], d.R);
-        for (int k = 0; k < 3; k++) d.p[k] = s.p[k] + dxi[6 * j + 3 + k];
+        retract_rot(s.R, &dxw[6 * j], d.R);
+        for (int k = 0; k < 3; k++) d.p[k] = s.p[k] + dxw[6 * j + 3 + k];
       }
-      double q1 = 0.0;
-      for (int r = 0; r < jl; r++) q1 += dxi[r] * (u[w] * D[r] * dxi[r] - J[r]);
-      q1s[w] = 0.5 * q1;
     }
     VX_TRY(vx_factor_residual(ctx, f, xt.data(), 0, -1, r_new.data()));
     for (int w = 0; w < NW; w++) {
@@ -138,6 +327,11 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       }
     }
     // windows that stopped keep the cache of their LAST trial (voxel_map.hpp:317-319): pin xt to it
+  }
+  if (dev && hess_out && evaluated) {   // *hess = Hess of the last accepted evaluation, before the gauge fix (:446)
+    VX_CUDA(cudaMemcpyAsync(hess_out, f->lm_H.p, sizeof(double) * hsz * NW, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    for (int w = 0; w < NW; w++) if (few[w]) std::fill(hess_out + hsz * w, hess_out + hsz * (w + 1), 0.0);
   }
   for (int w = 0; w < NW; w++) {
     if (resis) resis[2 * w + 1] = r2[w];

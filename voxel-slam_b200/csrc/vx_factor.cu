@@ -802,7 +802,8 @@ int vx_factor_free(vx_factor *f) {
   vx::DevBuf *all[] = {&f->off, &f->frame, &f->vox, &f->mom, &f->cnt, &f->fix, &f->coe, &f->lam, &f->U, &f->mrg, &f->win, &f->wv_off,
                        &f->poses, &f->H, &f->J, &f->cost_h, &f->cost_r, &f->cS, &f->res_v, &f->G, &f->fm_order, &f->fm_off,
                        &f->dseg_frame, &f->dseg_beg, &f->dseg_end, &f->dseg_off, &f->pair_ab, &f->tile_key, &f->tile_off,
-                       &f->oseg_tile, &f->oseg_beg, &f->oseg_end, &f->oseg_off, &f->dpart, &f->opart, &f->part_t, &f->part_d};
+                       &f->oseg_tile, &f->oseg_beg, &f->oseg_end, &f->oseg_off, &f->dpart, &f->opart, &f->part_t, &f->part_d,
+                       &f->lm_H, &f->lm_J, &f->lm_dx, &f->lm_q1, &f->lm_u, &f->lm_mask};
   for (auto *b : all) b->release();
   delete f;
   return VX_OK;

@@ -43,6 +43,7 @@ struct vx_factor {
   vx::DevBuf oseg_tile, oseg_beg, oseg_end, oseg_off;   // off-diagonal tile segments
   vx::DevBuf dpart, opart;                              // per-segment partial sums
   vx::DevBuf part_t, part_d;                            // fused small-window path: per-item tile / diagonal partials
+  vx::DevBuf lm_H, lm_J, lm_dx, lm_q1, lm_u, lm_mask;   // vx_ba_lidar: Hess / JacT each window last accepted, step, damping, masks
   int64_t n_pairs = 0, n_tiles = 0, n_dseg = 0, n_oseg = 0;
   int seg_len = 1024;
   bool force_pairlist = false;   // tests: evaluate through the generic pair-list path even when a fused one exists
