@@ -13,6 +13,7 @@
 //   4. one warp per segment: scan-local and world moments (P, v, N)
 //   5. per node: merged world cluster, 3x3 eigen-solve, plane / accept / subdivide flags, top-down liveness
 //   6. accepted planes -> voxels (ordered by position), segments -> (voxel, frame) clusters -> device LidarFactor
+#include <cstdlib>
 #include "vx_factor.cuh"
 #include "vx_math.cuh"
 #include "vx_voxelize.cuh"
@@ -115,25 +116,28 @@ __global__ void k_starts(const int32_t *__restrict__ flag, const int32_t *__rest
   if (i == n - 1) start[incl[i]] = (int32_t)n;
 }
 
-// 4. one warp per segment = (finest leaf, frame): scan-local moments (what LidarFactor stores per
+// 4. GL lanes per segment = (finest leaf, frame): scan-local moments (what LidarFactor stores per
 // voxel-frame, loop_refine.hpp:382-385) and world moments (pcr_add, loop_refine.hpp:320).
 // seg planes: [0..8] local P6 v3, [9..17] world P6 v3, all [19][nseg]; N in segN.
+// A finest leaf (voxel_size / 2^max_layer) holds a handful of points of one scan, so a whole warp per segment spends its
+// time in the 18-value reduction with 27 idle lanes: GL = 4 (measured on the 128-window bench input: 32 lanes 3.20 ms, 16: 1.66, 8: 0.96, 4: 0.67, 2: 0.60).
+template <int GL>
 __global__ void __launch_bounds__(256)
 k_seg_moments(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
               const int64_t *__restrict__ inst_off, const double *__restrict__ poses, const int32_t *__restrict__ sidx,
               const uint32_t *__restrict__ k1, const int32_t *__restrict__ seg_start, int64_t nseg, double *__restrict__ segm,
               int32_t *__restrict__ segN, int32_t *__restrict__ segF) {
-  const int64_t s = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (s >= nseg) return;
-  const int32_t b = seg_start[s], e = seg_start[s + 1];
-  const int g = (int)(k1[b] & ((1u << FRAME_BITS) - 1u));
+  const int64_t s = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / GL;
+  const int lane = threadIdx.x & (GL - 1);
+  const bool on = s < nseg;                       // every lane stays for the shuffles
+  const int32_t b = on ? seg_start[s] : 0, e = on ? seg_start[s + 1] : 0;
+  const int g = on ? (int)(k1[b] & ((1u << FRAME_BITS) - 1u)) : 0;
   const double *ps = poses + 12 * (int64_t)g;
-  const int64_t base = cloud_off[frame_cloud[g]] - inst_off[g];
+  const int64_t base = on ? cloud_off[frame_cloud[g]] - inst_off[g] : 0;
   double a[18];
 #pragma unroll
   for (int k = 0; k < 18; k++) a[k] = 0.0;
-  for (int32_t i = b + lane; i < e; i += 32) {
+  for (int32_t i = b + lane; i < e; i += GL) {
     const int64_t pt = base + sidx[i];
     const double lx = (double)xyz[3 * pt], ly = (double)xyz[3 * pt + 1], lz = (double)xyz[3 * pt + 2];
     const d3 w = world_of(ps, lx, ly, lz);
@@ -146,10 +150,10 @@ k_seg_moments(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_o
   for (int k = 0; k < 18; k++) {
     double x = a[k];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
-    if (lane == 0) segm[(size_t)k * nseg + s] = x;
+    for (int o = GL / 2; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o, GL);
+    if (on && lane == 0) segm[(size_t)k * nseg + s] = x;
   }
-  if (lane == 0) { segN[s] = e - b; segF[s] = g; }
+  if (on && lane == 0) { segN[s] = e - b; segF[s] = g; }
 }
 
 // 5a. per node of one layer: merged world cluster over its segments (in order), frame span, eigen-solve, flags
@@ -440,9 +444,15 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   // ---- 4. segment moments
   DevBuf &segm = T.make(), &segN = T.make(), &segF = T.make();
   VX_TRY(segm.reserve(sizeof(double) * 18 * (size_t)nseg)); VX_TRY(segN.reserve(4 * (size_t)nseg)); VX_TRY(segF.reserve(4 * (size_t)nseg));
-  VX_KERNEL(ctx, "k_seg_moments", k_seg_moments<<<blocks_for((int64_t)nseg * 32, 256), 256, 0, st>>>(
-      d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg,
-      segm.as<double>(), segN.as<int32_t>(), segF.as<int32_t>()));
+  {
+    static const int gl = getenv("VX_SEG_LANES") ? atoi(getenv("VX_SEG_LANES")) : 4;
+#define VX_SEG_LAUNCH(GL)                                                                                                                    \
+    VX_KERNEL(ctx, "k_seg_moments", k_seg_moments<GL><<<blocks_for((int64_t)nseg * GL, 256), 256, 0, st>>>(                                    \
+        d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg, \
+        segm.as<double>(), segN.as<int32_t>(), segF.as<int32_t>()))
+    if (gl == 32) { VX_SEG_LAUNCH(32); } else if (gl == 16) { VX_SEG_LAUNCH(16); } else if (gl == 8) { VX_SEG_LAUNCH(8); } else if (gl == 2) { VX_SEG_LAUNCH(2); } else { VX_SEG_LAUNCH(4); }
+#undef VX_SEG_LAUNCH
+  }
 
   // ---- 5. node statistics, decisions, liveness (top-down), emission marks
   DevBuf *nodeS[MAXL + 1], *nodeE[MAXL + 1], *nflag[MAXL + 1], *nfs[MAXL + 1];
