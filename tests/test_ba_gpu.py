@@ -113,3 +113,25 @@ def test_ba_large_window_uses_device_solve(pkg, ob, ctx):
     assert a["accept"][0] == b["accept"] and 1 in b["accept"]
     assert np.abs(a["poses"]["R"] - b["poses"]["R"]).max() < 1e-8 and np.abs(a["poses"]["p"] - b["poses"]["p"]).max() < 1e-8
     f.free()
+
+
+@pytest.mark.parametrize("V,W,occ,iters", [(1200, 10, 0.7, 4), (500, 20, 0.5, 4), (300, 21, 0.6, 3), (400, 4, 0.9, 5)])
+def test_device_lm_step_is_the_host_sweep(pkg, ctx, V, W, occ, iters, monkeypatch):
+    # k_lm_solve (gauge fix, damped LDL^T on the lower triangle, q1: csrc/vx_ba.cu) restates hm::ldlt_lower_solve operation for
+    # operation: poses, Hess snapshot, costs, flags and the accept trace must be the same BYTES as with the host sweep
+    # (VX_LM_HOST=1), including W = 20 / 21 (120 / 126 unknowns: the 128-thread instantiation, > 48 KB of shared memory).
+    fac = synth.random_factor(4100 + V, V, W, occupancy=occ, min_frames=2)
+    start = synth.perturb_poses(fac["poses"], 5, 0.01, 0.05)
+    outs = []
+    for host in (False, True):
+        if host:
+            monkeypatch.setenv("VX_LM_HOST", "1")
+        else:
+            monkeypatch.delenv("VX_LM_HOST", raising=False)
+        f = pkg.Factor(ctx, W); f.upload_dense(fac); f.residual(start)
+        outs.append(f.ba_lidar(start, max_iter=iters, thd_num=2))
+        f.free()
+    dev, hst = outs
+    assert 1 in dev["accept"][0]
+    for k in dev:
+        assert np.ascontiguousarray(dev[k]).tobytes() == np.ascontiguousarray(hst[k]).tobytes(), k
