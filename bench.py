@@ -19,6 +19,8 @@ windows are independent); rank r evaluates its own 2,000-keyframe j
 itself needs Eigen/PCL/ROS/GTSAM and cannot be built here: DESIGN.md "Oracle").
 """
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -575,10 +577,28 @@ def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        run_reference(args, rank, world)
-    else:
-        run_b200(args, rank, world, local_rank)
+    # stdout carries exactly ONE JSON line: libraries that write to file descriptor 1 themselves (NCCL prints its version
+    # banner there) are pointed at stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            if args.impl == "reference":
+                run_reference(args, rank, world)
+            else:
+                run_b200(args, rank, world, local_rank)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    lines = [ln for ln in buf.getvalue().splitlines() if ln.strip()]
+    for ln in lines:
+        if ln.lstrip().startswith("{"):
+            print(ln, flush=True)
+        else:
+            print(ln, file=sys.stderr, flush=True)
 
 
 if __name__ == "__main__":
