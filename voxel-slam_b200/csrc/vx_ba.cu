@@ -50,10 +50,15 @@ __global__ void k_lm_keep(const double *__restrict__ H, const double *__restrict
   const int w = blockIdx.x;
   if (!mask[w]) return;
   const size_t nn = (size_t)n * n;
-  const double2 *src = reinterpret_cast<const double2 *>(H + nn * w);
-  double2 *dst = reinterpret_cast<double2 *>(Hk + nn * w);
-  for (size_t k = threadIdx.x; k < nn / 2; k += blockDim.x) dst[k] = src[k];
-  for (int k = threadIdx.x; k < n; k += blockDim.x) Jk[(size_t)n * w + k] = J[(size_t)n * w + k];
+  const size_t t0 = blockIdx.y * (size_t)blockDim.x + threadIdx.x, step = (size_t)gridDim.y * blockDim.x;
+  if (nn % 2 == 0) {
+    const double2 *src = reinterpret_cast<const double2 *>(H + nn * w);
+    double2 *dst = reinterpret_cast<double2 *>(Hk + nn * w);
+    for (size_t k = t0; k < nn / 2; k += step) dst[k] = src[k];
+  } else {
+    for (size_t k = t0; k < nn; k += step) Hk[nn * w + k] = H[nn * w + k];
+  }
+  for (size_t k = t0; k < (size_t)n; k += step) Jk[(size_t)n * w + k] = J[(size_t)n * w + k];
 }
 
 template <int NT>
@@ -177,6 +182,7 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
 
 namespace vx {
 int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b, double *x);   // vx_ldlt.cu
+int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1);   // vx_ldlt.cu
 // win_status (optional, n_windows): when given, a window with fewer voxels than thd_num is flagged
 // VX_ERR_TOO_FEW and left untouched instead of failing the whole batch.
 int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
@@ -202,18 +208,21 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   }
   static const int ldlt_device_min = [] { const char *e = std::getenv("VX_LDLT_DEVICE_MIN"); return e ? std::atoi(e) : 384; }();
   const size_t hsz = (size_t)jl * jl;
-  const bool host_mats = !(jl <= LM_MAXN && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr);
+  // device LM step: k_lm_keep + k_lm_solve for windows of up to LM_MAXN unknowns, the blocked factorisation of vx_ldlt.cu from
+  // ldlt_device_min unknowns on (top-level GBA); Hess and JacT never leave the device.  In between (129...383 unknowns) and
+  // under VX_LM_HOST the host sweep.
+  const bool small = jl <= LM_MAXN;
+  const bool dev = (small || jl >= ldlt_device_min) && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr;
+  const bool host_mats = !dev;
   std::vector<double> Hess(host_mats ? hsz * NW : 0), JacT(host_mats ? (size_t)jl * NW : 0), Hnew(Hess.size()), Jnew(JacT.size()), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
   std::vector<double> u(NW, 0.01), v(NW, 2.0), A(hsz), dxi(jl), D(jl), nb(jl), tmp, q1s(NW, 0.0);
   std::vector<char> calc(NW, 1), active(NW, 1), conv(NW, 1);
   std::vector<int> iters(NW, 0), tr;
   std::vector<vx_pose> x(poses, poses + F), xt(poses, poses + F);
-  if (hess_out) std::fill(hess_out, hess_out + hsz * NW, 0.0);
+  if (hess_out && (!dev || max_iter == 0)) std::fill(hess_out, hess_out + hsz * NW, 0.0);   // the device path writes it whole at the end
   if (resis) std::fill(resis, resis + 2 * (size_t)NW, 0.0);
   for (int w = 0; w < NW; w++) if (few[w]) { active[w] = 0; conv[w] = 0; }
 
-  // device LM step (k_lm_keep / k_lm_solve): Hess and JacT never leave the device
-  const bool dev = jl <= LM_MAXN && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr;
   std::vector<int32_t> mask(NW);
   std::vector<double> dx_all;
   cudaStream_t st = ctx->stream;
@@ -223,7 +232,8 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
     VX_TRY(f->lm_u.reserve(sizeof(double) * NW)); VX_TRY(f->lm_mask.reserve(sizeof(int32_t) * NW));
     dx_all.resize((size_t)jl * NW);
     const size_t smem = sizeof(double) * ((size_t)jl * jl + 4 * jl);
-    if (jl <= 64) VX_CUDA(cudaFuncSetAttribute(k_lm_solve<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (!small) {}
+    else if (jl <= 64) VX_CUDA(cudaFuncSetAttribute(k_lm_solve<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     else VX_CUDA(cudaFuncSetAttribute(k_lm_solve<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   bool evaluated = false;
@@ -237,7 +247,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       VX_TRY(vx_factor_hessian_async(ctx, f, 0, -1));
       for (int w = 0; w < NW; w++) mask[w] = active[w] && calc[w];
       VX_CUDA(cudaMemcpyAsync(f->lm_mask.p, mask.data(), sizeof(int32_t) * NW, cudaMemcpyHostToDevice, st));
-      VX_KERNEL(ctx, "k_lm_keep", k_lm_keep<<<NW, 256, 0, st>>>(f->H.as<double>(), f->J.as<double>(), f->lm_H.as<double>(), f->lm_J.as<double>(),
+      VX_KERNEL(ctx, "k_lm_keep", k_lm_keep<<<dim3(NW, (unsigned)std::max<size_t>(1, std::min<size_t>(hsz / 4096, 1024))), 256, 0, st>>>(f->H.as<double>(), f->J.as<double>(), f->lm_H.as<double>(), f->lm_J.as<double>(),
                                                               f->lm_mask.as<int32_t>(), jl));
       VX_CUDA(cudaMemcpyAsync(r_new.data(), f->cost_h.p, sizeof(double) * NW, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaStreamSynchronize(st));
@@ -253,7 +263,12 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
           if (hess_out) std::copy(Hnew.begin() + hsz * w, Hnew.begin() + hsz * (w + 1), hess_out + hsz * w);   // *hess = Hess, before the gauge fix (:446)
         }
     }
-    if (dev) {
+    if (dev && !small) {
+      for (int w = 0; w < NW; w++)
+        if (active[w])
+          VX_TRY(lm_solve_large_device(ctx, f->lm_H.as<double>() + hsz * w, f->lm_J.as<double>() + (size_t)jl * w, u[w], jl,
+                                       dx_all.data() + (size_t)jl * w, &q1s[w]));
+    } else if (dev) {
       for (int w = 0; w < NW; w++) mask[w] = active[w];
       VX_CUDA(cudaMemcpyAsync(f->lm_mask.p, mask.data(), sizeof(int32_t) * NW, cudaMemcpyHostToDevice, st));
       VX_CUDA(cudaMemcpyAsync(f->lm_u.p, u.data(), sizeof(double) * NW, cudaMemcpyHostToDevice, st));
@@ -332,6 +347,8 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
     VX_CUDA(cudaMemcpyAsync(hess_out, f->lm_H.p, sizeof(double) * hsz * NW, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
     for (int w = 0; w < NW; w++) if (few[w]) std::fill(hess_out + hsz * w, hess_out + hsz * (w + 1), 0.0);
+  } else if (dev && hess_out && max_iter > 0) {
+    std::fill(hess_out, hess_out + hsz * NW, 0.0);
   }
   for (int w = 0; w < NW; w++) {
     if (resis) resis[2 * w + 1] = r2[w];
