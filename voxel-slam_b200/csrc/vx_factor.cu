@@ -586,15 +586,15 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, 
   if (f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W)) {
     // cost (+ the per-voxel divisions unless the last residual pass left them), then the fused kernel (overwrites all of H, J)
     const int64_t lo = std::max<int64_t>(head, 0), hi = std::min<int64_t>(end, f->V);
-    if (f->prep_lo <= lo && hi <= f->prep_hi) {
-      VX_KERNEL(ctx, "k_cost", k_cost<true><<<f->n_win, 256, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(), f->cost_h.as<double>(), head, end));
-    } else {
+    // covered: the cost comes out of the finaliser (k_fin_small, same sums as k_cost); uncovered: k_cost_prep writes both
+    const bool covered = f->prep_lo <= lo && hi <= f->prep_hi;
+    if (!covered) {
       VX_KERNEL(ctx, "k_cost_prep", k_cost_prep<<<f->n_win, 1024, 0, st>>>(f->lam.as<double>(), f->coe.as<double>(), f->mrg.as<double>(), f->wv_off.as<int32_t>(),
                                                                        f->cost_h.as<double>(), f->cS.as<double>(), f->V, head, end));
       f->prep_lo = lo; f->prep_hi = hi;
     }
     if (!group_out) {
-      VX_TRY(hessian_small(ctx, f, head, end, &fused));
+      VX_TRY(hessian_small(ctx, f, head, end, &fused, 0, -1, covered));
       return VX_OK;
     }
     // host output of a batch: the windows are evaluated in groups, each on its own stream with its Hess/JacT copy behind its
@@ -613,7 +613,7 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, 
       cudaStream_t gs = ctx->group_stream[gi];
       VX_CUDA(cudaStreamWaitEvent(gs, ctx->fork_ev, 0));
       ctx->stream = gs;                                   // hessian_small launches (and times) on the context stream
-      const int rc = hessian_small(ctx, f, head, end, &fused, w_lo, w_hi);
+      const int rc = hessian_small(ctx, f, head, end, &fused, w_lo, w_hi, covered);
       ctx->stream = st;
       VX_TRY(rc);
       if (group_out->Hess) VX_CUDA(cudaMemcpyAsync(group_out->Hess + (size_t)w_lo * jl6 * jl6, f->H.as<double>() + (size_t)w_lo * jl6 * jl6,

@@ -370,9 +370,13 @@ k_hess_small(const int32_t *__restrict__ off, const int32_t *__restrict__ frame,
 
 // Adds the items of each window in ascending order and writes Hess (upper blocks + mirrored lower
 // blocks, voxel_map.hpp:279-281) and JacT.  One CTA per window.
+// When `cost` is given, the y == 1 CTA of a window also reduces the window's cost sum coe * lambda_0 over [head, end) — the same
+// 256-thread strided sums and tree as k_cost (vx_factor.cu), so the value is bitwise k_cost's — which saves that launch.
 template <int W, int NT8>
 __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ part_t, const double *__restrict__ part_d,
-                                                   double *__restrict__ H, double *__restrict__ J, int splits, int w_base) {
+                                                   double *__restrict__ H, double *__restrict__ J, int splits, int w_base,
+                                                   const double *__restrict__ lam, const double *__restrict__ coe,
+                                                   const int32_t *__restrict__ wv_off, double *__restrict__ cost, int64_t head, int64_t end) {
   constexpr int T = W * (W + 1) / 2, T8 = NT8 * (NT8 + 1) / 2;
   const int w = w_base + blockIdx.x;
   const int64_t jl = 6 * W;
@@ -411,6 +415,21 @@ __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ pa
       Hw[(6 * i + r) * jl + (6 * j + c)] = s;
     }
   }
+  if (blockIdx.y == 1 && cost != nullptr) {
+    __shared__ double sh[256];
+    int64_t b = wv_off[w], e = wv_off[w + 1];
+    if (b < head) b = head;
+    if (e > end) e = end;
+    double acc = 0.0;
+    for (int64_t v = b + threadIdx.x; v < e; v += 256) acc += coe[v] * lam[v];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) cost[w] = sh[0];
+  }
   if (blockIdx.y != 0) return;
   for (int idx = threadIdx.x; idx < 6 * W; idx += blockDim.x) {
     const int i = idx / 6, r = idx - i * 6;
@@ -422,7 +441,7 @@ __global__ void __launch_bounds__(256) k_fin_small(const double *__restrict__ pa
 
 
 template <int W, int NROLES, int MINB>
-int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo, int w_hi) {
+int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo, int w_hi, bool with_cost) {
   using Cfg = SmallCfg<W, NROLES>;
   cudaStream_t st = ctx->stream;
   // items: enough CTAs to fill the machine several times over, but >= ~96 voxels per item
@@ -451,7 +470,9 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo,
       f->cS.as<double>(), f->U.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
       f->poses.as<double>(), f->part_t.as<double>(), f->part_d.as<double>(), f->V, head, end, splits, w_lo));
   VX_KERNEL(ctx, "k_fin_small", k_fin_small<W, Cfg::NT8><<<dim3(w_hi - w_lo, 4), 256, 0, st>>>(f->part_t.as<double>(), f->part_d.as<double>(),
-                                                                                   f->H.as<double>(), f->J.as<double>(), splits, w_lo));
+                                                                                   f->H.as<double>(), f->J.as<double>(), splits, w_lo,
+                                                                                   f->lam.as<double>(), f->coe.as<double>(), f->wv_off.as<int32_t>(),
+                                                                                   with_cost ? f->cost_h.as<double>() : nullptr, head, end));
   return VX_OK;
 }
 
@@ -460,18 +481,18 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo,
 namespace vx {
 // Returns VX_OK and sets *handled when W has a fused instantiation.  Hess/JacT of windows [w_lo, w_hi) (all when w_hi < 0) are
 // fully overwritten.
-int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled, int w_lo, int w_hi) {
+int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled, int w_lo, int w_hi, bool with_cost) {
   *handled = true;
   if (w_hi < 0) { w_lo = 0; w_hi = f->n_win; }
   if (w_hi <= w_lo) return VX_OK;
   switch (f->W) {
     case 10: {
       static const int minb = getenv("VX_HS_MINB") ? atoi(getenv("VX_HS_MINB")) : 3;
-      if (minb == 4) return launch_small<10, 4, 4>(ctx, f, head, end, w_lo, w_hi);
-      if (minb == 2) return launch_small<10, 4, 2>(ctx, f, head, end, w_lo, w_hi);
-      return launch_small<10, 4, 3>(ctx, f, head, end, w_lo, w_hi);
+      if (minb == 4) return launch_small<10, 4, 4>(ctx, f, head, end, w_lo, w_hi, with_cost);
+      if (minb == 2) return launch_small<10, 4, 2>(ctx, f, head, end, w_lo, w_hi, with_cost);
+      return launch_small<10, 4, 3>(ctx, f, head, end, w_lo, w_hi, with_cost);
     }
-    case 20: return launch_small<20, 8, 1>(ctx, f, head, end, w_lo, w_hi);
+    case 20: return launch_small<20, 8, 1>(ctx, f, head, end, w_lo, w_hi, with_cost);
     default: *handled = false; return VX_OK;
   }
 }
