@@ -240,9 +240,19 @@ int vx_ba_li_gravity(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imu
                      double *hess_out, int max_iter, int *accept_trace, int *n_iters);
 
 /* (Hess + u*D).ldlt().solve(b) the way vx_ba_lidar solves large windows (>= 384 unknowns): Eigen's diagonal-pivot order from
- * the input diagonal, blocked right-looking LDL^T of the permuted LOWER triangle on the device, substitution on the host.
+ * the input diagonal, blocked right-looking LDL^T of the permuted LOWER triangle and the substitution on the device.
  * A: n x n column-major host matrix (only its lower triangle is read). */
 int vx_ldlt_solve(vx_ctx *ctx, const double *A, int n, const double *b, double *x);
+
+/* ---- bool icp_normal(pl_src, pl_tar, pose, icp_eigval)   loop_refine.hpp:47-145
+ * Point-to-plane ICP with normal-compatibility gates, the geometric check of a loop-closure candidate.  src / tar: n x 3 float
+ * points and n x 3 float normals (PointXYZINormal's x,y,z / normal_x,y,z).  pose (R, p) is the reference's pair<Vector3d,
+ * Matrix3d>, updated in place.  Nearest neighbour = exact 1-NN under FLANN's float squared distance (lowest target index on
+ * ties).  *accepted = the reference's return value (smallest eigenvalue of sum n n^T > icp_eigval and converged).
+ * match_nums20 / resis20: per-iteration match count and 0.5 * sum r^2 (<= 20 entries, may be NULL); eig3: ascending. */
+int vx_icp_normal(vx_ctx *ctx, const float *src_xyz, const float *src_nrm, int64_t ns, const float *tar_xyz, const float *tar_nrm,
+                  int64_t nt, vx_pose *pose, double icp_eigval, int32_t *accepted, int32_t *iters, int32_t *match_nums20,
+                  double *resis20, double *eig3, int32_t *is_converge);
 
 /* ---- C1h: VOXEL_SLAM::HBA_add_edge(p_xs, p_smps, gba_edges, maps, max_iter, thread_num, plptr)
  * voxelslam.cpp:2822-3015 (the session filter :2836-2857 stays with the caller: pass only connected frames).

@@ -8,6 +8,7 @@
 #include "octree.hpp"
 #include "gba.hpp"
 #include "lio.hpp"
+#include "icp.hpp"
 #include <chrono>
 
 using namespace orc;
@@ -586,6 +587,23 @@ void orc_ba_li(void *h, oc_imu_state *xs, oc_imu_pre *pres, double imu_coef, int
   if (resis2 && resis.size() >= 2) { resis2[0] = resis[0]; resis2[1] = resis[1]; }
   if (n_trace) *n_trace = (int)trace.size();
   if (accept_trace) for (size_t i = 0; i < trace.size(); i++) accept_trace[i] = trace[i];
+}
+
+// icp_normal (loop_refine.hpp:47-145).  pose: R (column-major 9) + p (3), in/out.  match_nums / resis: up to 20 entries.
+int orc_icp_normal(const float *src_xyz, const float *src_nrm, int ns, const float *tar_xyz, const float *tar_nrm, int nt, oc_pose *pose,
+                   double icp_eigval, int *iters, int *match_nums, double *resis, double *eig3, int *is_converge) {
+  M3 R; V3 p;
+  for (int k = 0; k < 9; k++) R[k] = pose->R[k];
+  for (int k = 0; k < 3; k++) p[k] = pose->p[k];
+  IcpTrace tr;
+  const bool ok = icp_normal(src_xyz, src_nrm, ns, tar_xyz, tar_nrm, nt, p, R, icp_eigval, &tr);
+  for (int k = 0; k < 9; k++) pose->R[k] = R[k];
+  for (int k = 0; k < 3; k++) pose->p[k] = p[k];
+  if (iters) *iters = tr.iters;
+  for (int k = 0; k < tr.iters; k++) { if (match_nums) match_nums[k] = tr.match_num[k]; if (resis) resis[k] = tr.resi[k]; }
+  if (eig3) for (int k = 0; k < 3; k++) eig3[k] = tr.eig[k];
+  if (is_converge) *is_converge = tr.is_converge;
+  return ok ? 1 : 0;
 }
 
 double orc_now() {

@@ -291,6 +291,20 @@ map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("
 assert map_node_dtype.itemsize == 408
 
 
+def icp_normal(src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
+    """orc_icp_normal: the oracle's icp_normal (loop_refine.hpp:47-145), brute-force nearest neighbour."""
+    sx = np.ascontiguousarray(src_xyz, dtype=np.float32); sn = np.ascontiguousarray(src_nrm, dtype=np.float32)
+    tx = np.ascontiguousarray(tar_xyz, dtype=np.float32); tn = np.ascontiguousarray(tar_nrm, dtype=np.float32)
+    ps = as_poses((np.asarray(pose[0], dtype=np.float64)[None], np.asarray(pose[1], dtype=np.float64)[None])).copy()
+    it = C.c_int(0); conv = C.c_int(0)
+    mn = np.zeros(20, dtype=np.int32); rs = np.zeros(20); eig = np.zeros(3)
+    f = lib().orc_icp_normal; f.restype = C.c_int
+    ok = f(_p(sx), _p(sn), C.c_int(sx.shape[0]), _p(tx), _p(tn), C.c_int(tx.shape[0]), _p(ps), C.c_double(icp_eigval),
+           C.byref(it), _p(mn), _p(rs), _p(eig), C.byref(conv))
+    return dict(ok=bool(ok), R=ps["R"][0].reshape(3, 3).T.copy(), p=ps["p"][0].copy(), iters=it.value, match_nums=mn[:it.value].tolist(),
+                resis=rs[:it.value].copy(), eig=eig, is_converge=conv.value)
+
+
 def var_init(xyz, dept_err, beam_err):
     """calcBodyVar + var_init (voxelslam.hpp:180-234), identity extrinsic -> (n,12): pnt 3 + var 9 (col-major)."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32)

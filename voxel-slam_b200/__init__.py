@@ -225,6 +225,19 @@ def ldlt_solve(ctx, A, b):
     return x
 
 
+def icp_normal(ctx, src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
+    """icp_normal (loop_refine.hpp:47-145).  pose = (R (3,3), p (3,)); returns dict(ok, R, p, iters, match_nums, resis, eig, is_converge)."""
+    sx = np.ascontiguousarray(src_xyz, dtype=np.float32); sn = np.ascontiguousarray(src_nrm, dtype=np.float32)
+    tx = np.ascontiguousarray(tar_xyz, dtype=np.float32); tn = np.ascontiguousarray(tar_nrm, dtype=np.float32)
+    ps = as_poses((np.asarray(pose[0], dtype=np.float64)[None], np.asarray(pose[1], dtype=np.float64)[None])).copy()
+    ok = C.c_int32(0); it = C.c_int32(0); conv = C.c_int32(0)
+    mn = np.zeros(20, dtype=np.int32); rs = np.zeros(20); eig = np.zeros(3)
+    _chk(ctx.lib.vx_icp_normal(ctx.h, _p(sx), _p(sn), C.c_int64(sx.shape[0]), _p(tx), _p(tn), C.c_int64(tx.shape[0]), _p(ps), C.c_double(icp_eigval),
+                               C.byref(ok), C.byref(it), _p(mn), _p(rs), _p(eig), C.byref(conv)))
+    return dict(ok=bool(ok.value), R=ps["R"][0].reshape(3, 3).T.copy(), p=ps["p"][0].copy(), iters=it.value, match_nums=mn[:it.value].tolist(),
+                resis=rs[:it.value].copy(), eig=eig, is_converge=conv.value)
+
+
 def var_init(ctx, xyz, ext, dept_err, beam_err):
     """calcBodyVar + var_init (voxelslam.hpp:180-234) on the device -> (n,12): pnt 3 + var 9 (col-major)."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32); n = xyz.shape[0]
