@@ -244,6 +244,32 @@ int vx_ba_li_gravity(vx_ctx *ctx, vx_factor *f, vx_imu_state *x, vx_imu_pre *imu
  * A: n x n column-major host matrix (only its lower triangle is read). */
 int vx_ldlt_solve(vx_ctx *ctx, const double *A, int n, const double *b, double *x);
 
+/* ---- stored sessions (host code, no device needed) and the keyframe assembly ----------------------
+ * One scan of alidarState.txt: IMUST t, p, R (column-major), v, bg, ba, g and ScanPose::v6 (voxelslam.cpp:181-204). */
+typedef struct vx_scan_state { double t, p[3], R[9], v[3], bg[3], ba[3], g[3], v6[6]; } vx_scan_state;
+/* Eigen's Quaterniond::matrix() and Quaterniond(Matrix3d) as the formats use them; q = x y z w. */
+void vx_quat_to_R(const double *q_xyzw, double *R9);
+void vx_R_to_quat(const double *R9, double *q_xyzw);
+/* FileReaderWriter::save_pose voxelslam.cpp:181-204 (the caller keeps the reference's "fewer than 100 scans: no file" rule) */
+int vx_session_write_lidarstate(const char *path, const vx_scan_state *xs, int64_t n);
+/* read_lidarstate voxelslam.hpp:268-306: 8, 20 or 26 single-space separated numbers per line; *n = scans in the file */
+int vx_session_read_lidarstate(const char *path, vx_scan_state *out, int64_t cap, int64_t *n);
+/* FileReaderWriter::save_pcd voxelslam.cpp:166-179: PCD v0.7, DATA binary, FIELDS x y z intensity; xyzi: n x 4 floats */
+int vx_session_write_pcd_xyzi(const char *path, const float *xyzi, int64_t n);
+/* pcl::io::loadPCDFile into PointXYZI (voxelslam.cpp:340): fields by name, DATA ascii | binary; *n = points in the file */
+int vx_session_read_pcd_xyzi(const char *path, float *xyzi, int64_t cap, int64_t *n);
+/* vx_pgo_edge is declared further down */
+struct vx_pgo_edge;
+/* FileReaderWriter::pgo_edges_io voxelslam.cpp:207-279, write (io = 1) and read (io = 0) sides */
+int vx_session_write_edges(const char *path, const char *const *fnames, int n_names, const struct vx_pgo_edge *edges, int64_t n, const char *absent);
+int vx_session_read_edges(const char *path, const char *const *fnames, int n_names, const char *bagname, struct vx_pgo_edge *edges, int64_t cap,
+                          int64_t *n, char *absent_buf, int64_t absent_cap, int64_t *absent_len);
+/* Keyframe assembly of a stored session (voxelslam.cpp:345-378; online twin :2355-2385): the `win` scans (cloud_off[win + 1]
+ * offsets into xyz) moved into the frame of the LAST scan's pose, then down_sampling_voxel(pl_lc, voxel_size / 10), on the device.
+ * out: cells in ascending packed-key order; *n_out = cells. */
+int vx_keyframe_assemble(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int win, const vx_pose *poses, double voxel_size,
+                         vx_point48 *out, int64_t out_cap, int64_t *n_out);
+
 /* ---- bool icp_normal(pl_src, pl_tar, pose, icp_eigval)   loop_refine.hpp:47-145
  * Point-to-plane ICP with normal-compatibility gates, the geometric check of a loop-closure candidate.  src / tar: n x 3 float
  * points and n x 3 float normals (PointXYZINormal's x,y,z / normal_x,y,z).  pose (R, p) is the reference's pair<Vector3d,

@@ -9,6 +9,7 @@
 #include "gba.hpp"
 #include "lio.hpp"
 #include "icp.hpp"
+#include "session.hpp"
 #include <chrono>
 
 using namespace orc;
@@ -604,6 +605,46 @@ int orc_icp_normal(const float *src_xyz, const float *src_nrm, int ns, const flo
   if (eig3) for (int k = 0; k < 3; k++) eig3[k] = tr.eig[k];
   if (is_converge) *is_converge = tr.is_converge;
   return ok ? 1 : 0;
+}
+
+// ---- stored sessions ------------------------------------------------------------------------
+struct oc_scan_state { double t, p[3], R[9], v[3], bg[3], ba[3], g[3], v6[6]; };
+static_assert(sizeof(oc_scan_state) == sizeof(ScanState), "scan state layout");
+
+int orc_write_lidarstate(const char *path, const oc_scan_state *xs, int64_t n) {
+  std::vector<ScanState> v(n);
+  if (n) std::memcpy(v.data(), xs, sizeof(ScanState) * n);
+  return write_lidarstate(path, v) ? 0 : -1;
+}
+int orc_read_lidarstate(const char *path, oc_scan_state *out, int64_t cap, int64_t *n) {
+  std::vector<ScanState> v;
+  if (!read_lidarstate(path, v)) return -1;
+  *n = (int64_t)v.size();
+  if ((int64_t)v.size() > cap) return -2;
+  if (!v.empty()) std::memcpy(out, v.data(), sizeof(ScanState) * v.size());
+  return 0;
+}
+int orc_write_pcd_xyzi(const char *path, const float *xyzi, int64_t n) { return write_pcd_xyzi(path, xyzi, n) ? 0 : -1; }
+int orc_write_edges(const char *path, const char *const *n1, const char *const *n2, const int32_t *id1, const int32_t *id2, const double *tra3,
+                    const double *quat4, int64_t n) {
+  std::vector<EdgeLine> es(n);
+  for (int64_t i = 0; i < n; i++) {
+    es[i].n1 = n1[i]; es[i].n2 = n2[i]; es[i].id1 = id1[i]; es[i].id2 = id2[i];
+    for (int k = 0; k < 3; k++) es[i].tra[k] = tra3[3 * i + k];
+    for (int k = 0; k < 4; k++) es[i].q[k] = quat4[4 * i + k];
+  }
+  return write_edges(path, es) ? 0 : -1;
+}
+void orc_quat_to_R(const double *q_xyzw, double *R9) { quat_to_R(q_xyzw[3], q_xyzw[0], q_xyzw[1], q_xyzw[2], R9); }
+void orc_R_to_quat(const double *R9, double *q_xyzw) { R_to_quat(R9, q_xyzw); }
+// voxelslam.cpp:345-378; out: capacity = total number of points
+void orc_keyframe_assemble(const float *xyz, const int64_t *cloud_off, int win, const oc_pose *poses, double voxel_size, PointXYZIN *out, int64_t *n_out) {
+  std::vector<IMUST> xs = poses_in(poses, win);
+  std::vector<const float *> ptr(win); std::vector<int64_t> n(win);
+  for (int j = 0; j < win; j++) { ptr[j] = xyz + 3 * cloud_off[j]; n[j] = cloud_off[j + 1] - cloud_off[j]; }
+  std::vector<PointXYZIN> pl = keyframe_assemble(ptr, n, xs, voxel_size);
+  for (size_t k = 0; k < pl.size(); k++) out[k] = pl[k];
+  *n_out = (int64_t)pl.size();
 }
 
 double orc_now() {

@@ -291,6 +291,16 @@ map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("
 assert map_node_dtype.itemsize == 408
 
 
+def keyframe_assemble(clouds, poses, voxel_size):
+    """orc_keyframe_assemble: voxelslam.cpp:345-378 (scans into the frame of the last one, down_sampling_voxel(voxel_size / 10))."""
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses)
+    out = np.zeros(max(int(off[-1]), 1), dtype=point48_dtype); n = C.c_int64(0)
+    lib().orc_keyframe_assemble(_p(xyz), _p(off), C.c_int(len(clouds)), _p(ps), C.c_double(voxel_size), _p(out), C.byref(n))
+    return out[:n.value].copy()
+
+
 def icp_normal(src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
     """orc_icp_normal: the oracle's icp_normal (loop_refine.hpp:47-145), brute-force nearest neighbour."""
     sx = np.ascontiguousarray(src_xyz, dtype=np.float32); sn = np.ascontiguousarray(src_nrm, dtype=np.float32)

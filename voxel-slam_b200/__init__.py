@@ -225,6 +225,69 @@ def ldlt_solve(ctx, A, b):
     return x
 
 
+# ---- stored sessions: host-side formats, no device needed ------------------------------------
+scan_state_dtype = np.dtype([("t", "<f8"), ("p", "<f8", (3,)), ("R", "<f8", (9,)), ("v", "<f8", (3,)), ("bg", "<f8", (3,)), ("ba", "<f8", (3,)),
+                             ("g", "<f8", (3,)), ("v6", "<f8", (6,))])
+pgo_edge_dtype = np.dtype([("m1", "<i4"), ("m2", "<i4"), ("id1", "<i4"), ("id2", "<i4"), ("rot", "<f8", (9,)), ("tra", "<f8", (3,)), ("cov", "<f8", (6,))])
+assert scan_state_dtype.itemsize == 8 * 31 and pgo_edge_dtype.itemsize == 16 + 8 * 18
+
+
+def _chk_host(lib, rc):
+    if rc != 0:
+        raise VxError(rc, lib.vx_last_error().decode())
+
+
+def write_lidarstate(path, states):
+    lib = load_library(); st = np.ascontiguousarray(states, dtype=scan_state_dtype)
+    _chk_host(lib, lib.vx_session_write_lidarstate(path.encode(), _p(st), C.c_int64(st.shape[0])))
+
+
+def read_lidarstate(path, cap=1 << 20):
+    lib = load_library(); out = np.zeros(cap, dtype=scan_state_dtype); n = C.c_int64(0)
+    _chk_host(lib, lib.vx_session_read_lidarstate(path.encode(), _p(out), C.c_int64(cap), C.byref(n)))
+    return out[:n.value].copy()
+
+
+def write_pcd_xyzi(path, xyzi):
+    lib = load_library(); a = np.ascontiguousarray(xyzi, dtype=np.float32).reshape(-1, 4)
+    _chk_host(lib, lib.vx_session_write_pcd_xyzi(path.encode(), _p(a), C.c_int64(a.shape[0])))
+
+
+def read_pcd_xyzi(path, cap=1 << 22):
+    lib = load_library(); out = np.zeros((cap, 4), dtype=np.float32); n = C.c_int64(0)
+    _chk_host(lib, lib.vx_session_read_pcd_xyzi(path.encode(), _p(out), C.c_int64(cap), C.byref(n)))
+    return out[:n.value].copy()
+
+
+def _names(fnames):
+    arr = (C.c_char_p * max(len(fnames), 1))(*[f.encode() for f in fnames])
+    return arr
+
+
+def write_edges(path, fnames, edges, absent=None):
+    lib = load_library(); e = np.ascontiguousarray(edges, dtype=pgo_edge_dtype)
+    _chk_host(lib, lib.vx_session_write_edges(path.encode(), _names(fnames), C.c_int(len(fnames)), _p(e), C.c_int64(e.shape[0]),
+                                              None if absent is None else absent.encode()))
+
+
+def read_edges(path, fnames, bagname, cap=1 << 16):
+    lib = load_library(); out = np.zeros(cap, dtype=pgo_edge_dtype); n = C.c_int64(0)
+    buf = C.create_string_buffer(1 << 20); blen = C.c_int64(0)
+    _chk_host(lib, lib.vx_session_read_edges(path.encode(), _names(fnames), C.c_int(len(fnames)), None if bagname is None else bagname.encode(),
+                                             _p(out), C.c_int64(cap), C.byref(n), buf, C.c_int64(len(buf)), C.byref(blen)))
+    return out[:n.value].copy(), buf.value.decode()
+
+
+def keyframe_assemble(ctx, clouds, poses, voxel_size):
+    """voxelslam.cpp:345-378: the scans of one keyframe into the frame of the last scan, down_sampling_voxel(voxel_size / 10)."""
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    ps = as_poses(poses); cap = int(off[-1])
+    out = np.zeros(max(cap, 1), dtype=point48_dtype); n = C.c_int64(0)
+    _chk(ctx.lib.vx_keyframe_assemble(ctx.h, _p(xyz), _p(off), C.c_int(len(clouds)), _p(ps), C.c_double(voxel_size), _p(out), C.c_int64(cap), C.byref(n)))
+    return out[:n.value].copy()
+
+
 def icp_normal(ctx, src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
     """icp_normal (loop_refine.hpp:47-145).  pose = (R (3,3), p (3,)); returns dict(ok, R, p, iters, match_nums, resis, eig, is_converge)."""
     sx = np.ascontiguousarray(src_xyz, dtype=np.float32); sn = np.ascontiguousarray(src_nrm, dtype=np.float32)

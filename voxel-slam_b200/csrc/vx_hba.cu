@@ -166,6 +166,38 @@ __global__ void k_merge_transform(const float *__restrict__ xyz, int64_t beg, in
 }
 }  // namespace
 
+// Clouds cidx[0..W) moved into the frame of pose `ref` (dp = x_ref.R^T (x_i.p - x_ref.p), dR = x_ref.R^T x_i.R, v3 = dR v3 + dp
+// in doubles, narrowed to float), intensity = mp[i], then down_sampling_voxel(leaf).  Result: ncell records in d_out.
+static int assemble_window(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, const int *cidx, const vx_pose *xs, const int32_t *mp,
+                           int W, int ref, double leaf, DevBuf &d_in, DevBuf &d_out, int32_t *ncell) {
+  cudaStream_t st = ctx->stream;
+  int64_t total = 0;
+  for (int i = 0; i < W; i++) total += cloud_off[cidx[i] + 1] - cloud_off[cidx[i]];
+  *ncell = 0;
+  if (total == 0) return VX_OK;
+  VX_TRY(d_in.reserve(sizeof(vx_point48) * total)); VX_TRY(d_out.reserve(sizeof(vx_point48) * total));
+  const vx_pose &xc = xs[ref];
+  int64_t at = 0;
+  for (int i = 0; i < W; i++) {
+    const int c = cidx[i];
+    const int64_t n = cloud_off[c + 1] - cloud_off[c];
+    if (n == 0) continue;
+    const vx_pose &xi = xs[i];
+    RelPose rp;
+    // R column-major: R(r,c) = R[c*3+r]
+    double d[3] = {xi.p[0] - xc.p[0], xi.p[1] - xc.p[1], xi.p[2] - xc.p[2]};
+    for (int r = 0; r < 3; r++) {
+      double sacc = 0; for (int k = 0; k < 3; k++) sacc += xc.R[r * 3 + k] * d[k];
+      rp.dp[r] = sacc;
+      for (int cc = 0; cc < 3; cc++) { double t = 0; for (int k = 0; k < 3; k++) t += xc.R[r * 3 + k] * xi.R[cc * 3 + k]; rp.dR[r * 3 + cc] = t; }
+    }
+    rp.mp = (float)(mp ? mp[i] : 0);
+    VX_KERNEL(ctx, "k_merge_transform", k_merge_transform<<<blocks_for(n, 256), 256, 0, st>>>(d_xyz, cloud_off[c], n, rp, d_in.as<vx_point48>() + at));
+    at += n;
+  }
+  return downsample_device(ctx, d_in.p, total, leaf, DS_MEAN, d_out.as<vx_point48>(), ncell);
+}
+
 extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
                                    const int32_t *frame_mp, const vx_pose *poses, int W, int n_windows, double voxel_size, vx_point48 *out,
                                    int64_t out_cap, int64_t *win_off) {
@@ -181,31 +213,13 @@ extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t 
     int64_t written = 0;
     win_off[0] = 0;
     for (int w = 0; w < n_windows; w++) {
-      int64_t total = 0;
-      for (int i = 0; i < W; i++) { const int c = frame_cloud ? frame_cloud[w * W + i] : w * W + i; VX_ARG(c >= 0 && c < n_clouds); total += cloud_off[c + 1] - cloud_off[c]; }
-      if (total > 0) {
-        VX_TRY(d_in.reserve(sizeof(vx_point48) * total)); VX_TRY(d_out.reserve(sizeof(vx_point48) * total));
-        const vx_pose &xc = poses[(size_t)w * W];
-        int64_t at = 0;
-        for (int i = 0; i < W; i++) {
-          const int g = w * W + i, c = frame_cloud ? frame_cloud[g] : g;
-          const int64_t n = cloud_off[c + 1] - cloud_off[c];
-          if (n == 0) continue;
-          const vx_pose &xi = poses[g];
-          RelPose rp;
-          // dp = xc.R^T (xs[i].p - xc.p), dR = xc.R^T xs[i].R   (:2958-2959); R column-major: R(r,c) = R[c*3+r]
-          double d[3] = {xi.p[0] - xc.p[0], xi.p[1] - xc.p[1], xi.p[2] - xc.p[2]};
-          for (int r = 0; r < 3; r++) {
-            double s = 0; for (int k = 0; k < 3; k++) s += xc.R[r * 3 + k] * d[k];
-            rp.dp[r] = s;
-            for (int cc = 0; cc < 3; cc++) { double t = 0; for (int k = 0; k < 3; k++) t += xc.R[r * 3 + k] * xi.R[cc * 3 + k]; rp.dR[r * 3 + cc] = t; }
-          }
-          rp.mp = (float)(frame_mp ? frame_mp[g] : 0);
-          VX_KERNEL(ctx, "k_merge_transform", k_merge_transform<<<blocks_for(n, 256), 256, 0, st>>>(d_xyz.as<float>(), cloud_off[c], n, rp, d_in.as<vx_point48>() + at));
-          at += n;
-        }
-        int32_t ncell = 0;
-        VX_TRY(downsample_device(ctx, d_in.p, total, voxel_size / 8, DS_MEAN, d_out.as<vx_point48>(), &ncell));   // :2978
+      std::vector<int> cidx(W);
+      for (int i = 0; i < W; i++) { const int c = frame_cloud ? frame_cloud[w * W + i] : w * W + i; VX_ARG(c >= 0 && c < n_clouds); cidx[i] = c; }
+      int32_t ncell = 0;
+      // every keyframe cloud into the frame of keyframe 0 (:2958-2969), down_sampling_voxel(pl, voxel_size / 8) (:2978)
+      VX_TRY(assemble_window(ctx, d_xyz.as<float>(), cloud_off, cidx.data(), poses + (size_t)w * W, frame_mp ? frame_mp + (size_t)w * W : nullptr, W, 0,
+                             voxel_size / 8, d_in, d_out, &ncell));
+      if (ncell > 0) {
         if (written + ncell > out_cap) { set_error("vx_hba_merge_clouds: output capacity %lld too small", (long long)out_cap); return VX_ERR_ARG; }
         VX_CUDA(cudaMemcpyAsync(out + written, d_out.p, sizeof(vx_point48) * ncell, cudaMemcpyDeviceToHost, st));
         written += ncell;
@@ -213,6 +227,36 @@ extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t 
       win_off[w + 1] = written;
     }
     VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  d_xyz.release(); d_in.release(); d_out.release();
+  return rc;
+}
+
+// Keyframe assembly of a stored session (voxelslam.cpp:345-378; the online twin :2355-2385 uses the same relative poses): the
+// `win` scans of a keyframe moved into the frame of the LAST scan's pose, then down_sampling_voxel(pl_lc, voxel_size / 10).
+extern "C" int vx_keyframe_assemble(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int win, const vx_pose *poses, double voxel_size,
+                                    vx_point48 *out, int64_t out_cap, int64_t *n_out) {
+  VX_ARG(ctx && cloud_off && poses && n_out && win >= 1 && voxel_size > 0 && out_cap >= 0);
+  VX_TRY(bind(ctx));
+  const int64_t NP = cloud_off[win];
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  cudaStream_t st = ctx->stream;
+  DevBuf d_xyz, d_in, d_out;
+  *n_out = 0;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, st));
+    std::vector<int> cidx(win);
+    for (int i = 0; i < win; i++) cidx[i] = i;
+    int32_t ncell = 0;
+    VX_TRY(assemble_window(ctx, d_xyz.as<float>(), cloud_off, cidx.data(), poses, nullptr, win, win - 1, voxel_size / 10, d_in, d_out, &ncell));
+    if (ncell > out_cap) { set_error("vx_keyframe_assemble: output capacity %lld too small for %d cells", (long long)out_cap, ncell); return VX_ERR_ARG; }
+    if (ncell > 0) VX_CUDA(cudaMemcpyAsync(out, d_out.p, sizeof(vx_point48) * ncell, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    *n_out = ncell;
     return VX_OK;
   };
   const int rc = body();
