@@ -280,6 +280,14 @@ int vx_icp_normal(vx_ctx *ctx, const float *src_xyz, const float *src_nrm, int64
                   int64_t nt, vx_pose *pose, double icp_eigval, int32_t *accepted, int32_t *iters, int32_t *match_nums20,
                   double *resis20, double *eig3, int32_t *is_converge);
 
+/* STDescManager::init_voxel_map + BTCOctoTree::init_plane + STDescManager::get_plane (BTC.cpp:279-334, :90-143): the plane cloud
+ * the loop-closure thread hands to icp_normal.  xyz: n x 3 floats.  A voxel (BTC's own key rule: double quotient, truncated)
+ * with more than init_num points whose smallest covariance eigenvalue is below plane_thre yields one PointXYZINormal (center,
+ * normal; the sign of the normal is as arbitrary as Eigen::EigenSolver's).  aux (may be NULL): per plane center 3 | normal 3 |
+ * min_eigen_value | radius | d | points_size (BTCPlane).  Planes in ascending voxel-key order (the reference: hash-map order). */
+int vx_btc_plane_cloud(vx_ctx *ctx, const float *xyz, int64_t n, double voxel_size, double plane_thre, int init_num, vx_point48 *out,
+                       double *aux, int64_t out_cap, int64_t *n_out);
+
 /* ---- C1h: VOXEL_SLAM::HBA_add_edge(p_xs, p_smps, gba_edges, maps, max_iter, thread_num, plptr)
  * voxelslam.cpp:2822-3015 (the session filter :2836-2857 stays with the caller: pass only connected frames).
  * For every window: up to max_iter outer iterations of {rebuild the GBA voxel map at the current poses,

@@ -10,6 +10,7 @@
 #include "lio.hpp"
 #include "icp.hpp"
 #include "session.hpp"
+#include "btc.hpp"
 #include <chrono>
 
 using namespace orc;
@@ -645,6 +646,13 @@ void orc_keyframe_assemble(const float *xyz, const int64_t *cloud_off, int win, 
   std::vector<PointXYZIN> pl = keyframe_assemble(ptr, n, xs, voxel_size);
   for (size_t k = 0; k < pl.size(); k++) out[k] = pl[k];
   *n_out = (int64_t)pl.size();
+}
+
+// BTC plane voxels (BTC.cpp:279-334): out = 10 doubles per plane (center 3 | normal 3 | min_eigen_value | radius | d | points_size)
+void orc_btc_plane_cloud(const float *xyz, int64_t n, double voxel_size, double plane_thre, int init_num, double *out, int64_t cap, int64_t *n_out) {
+  std::vector<BtcPlane> pl = btc_plane_cloud(xyz, n, voxel_size, plane_thre, init_num);
+  *n_out = (int64_t)pl.size();
+  for (size_t k = 0; k < pl.size() && (int64_t)k < cap; k++) std::memcpy(out + 10 * k, &pl[k], sizeof(BtcPlane));
 }
 
 double orc_now() {

@@ -291,6 +291,14 @@ map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("
 assert map_node_dtype.itemsize == 408
 
 
+def btc_plane_cloud(xyz, voxel_size, plane_thre, init_num):
+    """orc_btc_plane_cloud (BTC.cpp:279-334) -> (m, 10): center 3 | normal 3 | min_eigen_value | radius | d | points_size."""
+    a = np.ascontiguousarray(xyz, dtype=np.float32); cap = max(a.shape[0], 1)
+    out = np.zeros((cap, 10)); n = C.c_int64(0)
+    lib().orc_btc_plane_cloud(_p(a), C.c_int64(a.shape[0]), C.c_double(voxel_size), C.c_double(plane_thre), C.c_int(init_num), _p(out), C.c_int64(cap), C.byref(n))
+    return out[:n.value].copy()
+
+
 def keyframe_assemble(clouds, poses, voxel_size):
     """orc_keyframe_assemble: voxelslam.cpp:345-378 (scans into the frame of the last one, down_sampling_voxel(voxel_size / 10))."""
     xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)

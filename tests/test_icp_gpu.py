@@ -78,3 +78,49 @@ def test_icp_normal_edge_cases(pkg, ob, ctx):
     out = pkg.icp_normal(ctx, src, sn, tar2, tn2, I, 0.1)
     assert out["match_nums"] == ref["match_nums"] and out["iters"] == ref["iters"]
     assert np.abs(out["p"] - ref["p"]).max() < 1e-9
+
+
+# ---- BTC plane voxels (BTC.cpp:279-334): the plane cloud icp_normal is fed with ------------------------------------
+def _world_cloud(seed, frames, pts):
+    import scene
+    clouds, (R, p) = scene.config1(seed=seed, W=frames, pts_per_scan=pts)
+    return np.concatenate([c @ R[i].T + p[i] for i, c in enumerate(clouds)]).astype(np.float32), clouds, (R, p)
+
+
+@pytest.mark.parametrize("seed,voxel", [(31, 1.0), (32, 0.5), (33, 2.0)])
+def test_btc_plane_cloud_matches_oracle(pkg, ob, ctx, seed, voxel):
+    xyz, _, _ = _world_cloud(seed, 6, 8000)
+    xyz[:50] *= -1.0                                     # negative coordinates: the "-1.0 on the double quotient" branch
+    thre = float(np.float32(0.01))                       # config_setting_.plane_detection_thre_ is a float (BTC.h:29)
+    ref = ob.btc_plane_cloud(xyz, voxel, thre, 10)
+    pts, aux = pkg.btc_plane_cloud(ctx, xyz, voxel, thre, 10)
+    assert ref.shape[0] > 30 and aux.shape == ref.shape  # same voxels pass N > 10 and lambda_min < thre, in the same (key) order
+    assert np.array_equal(aux[:, :3], ref[:, :3]) and np.array_equal(aux[:, 9], ref[:, 9])     # centers: same sums, bit for bit
+    sgn = np.sign(np.sum(aux[:, 3:6] * ref[:, 3:6], axis=1, keepdims=True))                   # eigenvector sign is unspecified
+    assert np.abs(aux[:, 3:6] * sgn - ref[:, 3:6]).max() < 1e-7      # lambda_0 vs lambda_1 gaps of ~1e-3 amplify eps
+    assert np.abs(aux[:, 6] - ref[:, 6]).max() <= 1e-12 * np.abs(ref[:, 7] ** 2).max()
+    assert np.abs(aux[:, 7] - ref[:, 7]).max() < 1e-12 and np.abs(aux[:, 8] * sgn[:, 0] - ref[:, 8]).max() < 1e-6
+    assert np.array_equal(pts["x"], aux[:, 0].astype(np.float32)) and np.array_equal(pts["normal_z"], aux[:, 5].astype(np.float32))
+    assert pkg.btc_plane_cloud(ctx, xyz[:0], voxel, thre, 10)[0].shape[0] == 0
+    assert pkg.btc_plane_cloud(ctx, xyz[:10], voxel, thre, 10)[0].shape[0] == 0        # no voxel with more than 10 points
+
+
+def test_loop_closure_geometry_chain(pkg, ob, ctx):
+    # keyframe clouds -> BTC plane clouds -> icp_normal, device against oracle end to end (voxelslam.cpp:2434)
+    xyz_a, _, _ = _world_cloud(41, 6, 8000)
+    xyz_b, _, _ = _world_cloud(42, 6, 8000)             # another sample of the same room
+    Rt, pt = synth.random_poses(9, 1, rot_sigma=0.2, tra_sigma=1.0); Rt, pt = Rt[0], pt[0]
+    src_local = ((xyz_b.astype(np.float64) - pt) @ Rt).astype(np.float32)
+    thre = float(np.float32(0.01))
+    pa, _ = pkg.btc_plane_cloud(ctx, xyz_a, 1.0, thre, 10)
+    pb, _ = pkg.btc_plane_cloud(ctx, src_local, 1.0, thre, 10)
+    assert pa.shape[0] > 50 and pb.shape[0] > 50
+    f3 = lambda a, names: np.stack([a[n] for n in names], axis=1)
+    tar, tn = f3(pa, "xyz"), f3(pa, ("normal_x", "normal_y", "normal_z"))
+    src, sn = f3(pb, "xyz"), f3(pb, ("normal_x", "normal_y", "normal_z"))
+    R0, p0 = synth.perturb_poses((Rt[None], pt[None]), 3, 0.02, 0.1, fix_first=False)
+    ref = ob.icp_normal(src, sn, tar, tn, (R0[0], p0[0]), 0.1)
+    out = pkg.icp_normal(ctx, src, sn, tar, tn, (R0[0], p0[0]), 0.1)
+    assert ref["match_nums"][0] > 20
+    assert out["match_nums"] == ref["match_nums"] and out["iters"] == ref["iters"] and out["ok"] == ref["ok"]
+    assert np.abs(out["R"] - ref["R"]).max() < 1e-9 and np.abs(out["p"] - ref["p"]).max() < 1e-9

@@ -288,6 +288,15 @@ def keyframe_assemble(ctx, clouds, poses, voxel_size):
     return out[:n.value].copy()
 
 
+def btc_plane_cloud(ctx, xyz, voxel_size=1.0, plane_thre=float(np.float32(0.01)), init_num=10):
+    """STDescManager::init_voxel_map + get_plane (BTC.cpp:279-334) -> (planes as point48, aux (m, 10))."""
+    a = np.ascontiguousarray(xyz, dtype=np.float32); cap = max(a.shape[0], 1)
+    out = np.zeros(cap, dtype=point48_dtype); aux = np.zeros((cap, 10)); n = C.c_int64(0)
+    _chk(ctx.lib.vx_btc_plane_cloud(ctx.h, _p(a), C.c_int64(a.shape[0]), C.c_double(voxel_size), C.c_double(plane_thre), C.c_int(init_num), _p(out), _p(aux),
+                                    C.c_int64(cap), C.byref(n)))
+    return out[:n.value].copy(), aux[:n.value].copy()
+
+
 def icp_normal(ctx, src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
     """icp_normal (loop_refine.hpp:47-145).  pose = (R (3,3), p (3,)); returns dict(ok, R, p, iters, match_nums, resis, eig, is_converge)."""
     sx = np.ascontiguousarray(src_xyz, dtype=np.float32); sn = np.ascontiguousarray(src_nrm, dtype=np.float32)

@@ -8,6 +8,7 @@
 //   vx_downsample_close   tools.hpp:240-302 (A4): the input point nearest the float cell centroid.
 //   vx_downsample_pvec    voxel_map.hpp:39-81 (A3): running double mean of point and covariance, diag(var) out.
 #include "vx_voxelize.cuh"
+#include "vx_math.cuh"
 #include <cub/cub.cuh>
 
 using namespace vx;
@@ -118,6 +119,70 @@ __global__ void k_ds_pvec(const vx_point_var *__restrict__ pts, const int32_t *_
   ap.normal_x = (float)m[3]; ap.normal_y = (float)m[4]; ap.normal_z = (float)m[5]; ap._p1 = 0.0f;
   ap.intensity = 0.0f; ap.curvature = 0.0f; ap._p2 = ap._p3 = 0.0f;
   out[c] = ap;
+}
+
+// ---- BTC plane voxels (BTC.cpp:279-334, :96-143) -----------------------------------------------
+// STDescManager::init_voxel_map's key rule is NOT the map's: the quotient stays a double (p / voxel_size, minus 1.0 when
+// negative) and is truncated to int64 (BTC.cpp:288-296).
+__global__ void k_btc_key(const float *__restrict__ xyz, int64_t n, double vs, uint64_t *__restrict__ keys, int32_t *__restrict__ idx, int *__restrict__ bad) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int64_t c[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    double loc = __ddiv_rn((double)xyz[3 * i + j], vs);
+    if (loc < 0) loc = __dadd_rn(loc, -1.0);
+    c[j] = (int64_t)loc;
+  }
+  uint64_t k;
+  if (!pack_key(c[0], c[1], c[2], k)) *bad = 1;
+  keys[i] = k;
+  idx[i] = (int32_t)i;
+}
+// One thread per voxel: BTCOctoTree::init_octo_tree / init_plane (BTC.cpp:90-143) with the sums in insertion order; a plane
+// voxel becomes the PointXYZINormal of STDescManager::get_plane (:322-334): center, normal of the smallest eigenvalue.
+__global__ void k_btc_plane(const float *__restrict__ xyz, const int32_t *__restrict__ idx, const int32_t *__restrict__ start, int64_t ncell,
+                            int init_num, double thre, vx_point48 *__restrict__ out, double *__restrict__ aux, int32_t *__restrict__ flag) {
+  int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= ncell) return;
+  const int32_t b = start[c], e = start[c + 1];
+  flag[c] = 0;
+  if (e - b <= init_num) return;                       // voxel_points_.size() > voxel_init_num_ (:91)
+  double S[6] = {0, 0, 0, 0, 0, 0}, m[3] = {0, 0, 0};
+  for (int32_t k = b; k < e; k++) {
+    const float *q = xyz + 3 * (int64_t)idx[k];
+    const double x = (double)q[0], y = (double)q[1], z = (double)q[2];
+    S[0] = __dadd_rn(S[0], __dmul_rn(x, x)); S[1] = __dadd_rn(S[1], __dmul_rn(x, y)); S[2] = __dadd_rn(S[2], __dmul_rn(x, z));
+    S[3] = __dadd_rn(S[3], __dmul_rn(y, y)); S[4] = __dadd_rn(S[4], __dmul_rn(y, z)); S[5] = __dadd_rn(S[5], __dmul_rn(z, z));
+    m[0] = __dadd_rn(m[0], x); m[1] = __dadd_rn(m[1], y); m[2] = __dadd_rn(m[2], z);
+  }
+  const double N = (double)(e - b);
+  const double cx = __ddiv_rn(m[0], N), cy = __ddiv_rn(m[1], N), cz = __ddiv_rn(m[2], N);
+  s33 C;
+  C.xx = __dadd_rn(__ddiv_rn(S[0], N), -__dmul_rn(cx, cx)); C.xy = __dadd_rn(__ddiv_rn(S[1], N), -__dmul_rn(cx, cy));
+  C.xz = __dadd_rn(__ddiv_rn(S[2], N), -__dmul_rn(cx, cz)); C.yy = __dadd_rn(__ddiv_rn(S[3], N), -__dmul_rn(cy, cy));
+  C.yz = __dadd_rn(__ddiv_rn(S[4], N), -__dmul_rn(cy, cz)); C.zz = __dadd_rn(__ddiv_rn(S[5], N), -__dmul_rn(cz, cz));
+  double lam[3], U[9];
+  eig3_jacobi(C, lam, U);                              // ascending: lam[0] = evalsReal(evalsMin), lam[2] = evalsReal(evalsMax)
+  if (!(lam[0] < thre)) return;
+  vx_point48 pi;
+  pi.x = (float)cx; pi.y = (float)cy; pi.z = (float)cz; pi._p0 = 1.0f;
+  pi.normal_x = (float)U[0]; pi.normal_y = (float)U[1]; pi.normal_z = (float)U[2]; pi._p1 = 0.0f;
+  pi.intensity = 0.0f; pi.curvature = 0.0f; pi._p2 = pi._p3 = 0.0f;
+  out[c] = pi;
+  // BTCPlane's doubles for callers that want them: center 3 | normal 3 | min_eigen_value | radius | d | points_size
+  double *a = aux + 10 * c;
+  a[0] = cx; a[1] = cy; a[2] = cz; a[3] = U[0]; a[4] = U[1]; a[5] = U[2]; a[6] = lam[0]; a[7] = sqrt(lam[2]);
+  a[8] = -__dadd_rn(__dadd_rn(__dmul_rn(U[0], cx), __dmul_rn(U[1], cy)), __dmul_rn(U[2], cz)); a[9] = N;
+  flag[c] = 1;
+}
+__global__ void k_btc_compact(const vx_point48 *__restrict__ in, const double *__restrict__ aux_in, const int32_t *__restrict__ flag,
+                              const int32_t *__restrict__ incl, int64_t ncell, vx_point48 *__restrict__ out, double *__restrict__ aux_out) {
+  int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= ncell || !flag[c]) return;
+  const int32_t o = incl[c] - 1;
+  out[o] = in[c];
+  for (int k = 0; k < 10; k++) aux_out[10 * (int64_t)o + k] = aux_in[10 * c + k];
 }
 
 }  // namespace
@@ -237,6 +302,64 @@ int vx_downsample_close(vx_ctx *ctx, const vx_point48 *pts, int64_t n, double vo
 int vx_downsample_pvec(vx_ctx *ctx, const vx_point_var *pvec, int64_t n, double voxel_size, vx_point48 *out, int64_t *out_n) {
   VX_ARG(n >= 0 && out_n != nullptr && voxel_size > 0 && (n == 0 || (pvec && out)));
   return downsample_cells(ctx, pvec, sizeof(vx_point_var), n, voxel_size, DS_PVEC, out, out_n);
+}
+
+// STDescManager::init_voxel_map + get_plane (BTC.cpp:279-334): the plane cloud icp_normal works on.  xyz: n x 3 floats
+// (PointXYZI x,y,z).  out / aux (10 doubles per plane, may be NULL): planes in ascending voxel-key order.
+int vx_btc_plane_cloud(vx_ctx *ctx, const float *xyz, int64_t n, double voxel_size, double plane_thre, int init_num, vx_point48 *out,
+                       double *aux, int64_t out_cap, int64_t *n_out) {
+  VX_ARG(ctx && n_out && n >= 0 && voxel_size > 0 && out_cap >= 0 && (n == 0 || xyz) && n < ((int64_t)1 << 31));
+  VX_TRY(bind(ctx));
+  *n_out = 0;
+  if (n == 0) return VX_OK;
+  cudaStream_t st = ctx->stream;
+  DevBuf d_xyz, d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad, d_pl, d_aux, d_pf, d_pi, d_out, d_aout;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(12 * n)); VX_TRY(d_k0.reserve(8 * n)); VX_TRY(d_k1.reserve(8 * n)); VX_TRY(d_i0.reserve(4 * n)); VX_TRY(d_i1.reserve(4 * n));
+    VX_TRY(d_flag.reserve(4 * n)); VX_TRY(d_incl.reserve(4 * n)); VX_TRY(d_start.reserve(4 * (n + 1))); VX_TRY(d_bad.reserve(4));
+    VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, 12 * n, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
+    VX_KERNEL(ctx, "k_btc_key", k_btc_key<<<blocks_for(n, 256), 256, 0, st>>>(d_xyz.as<float>(), n, voxel_size, d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
+    size_t tb = 0;
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)n, 0, 63, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)n, 0, 63, st));
+    VX_KERNEL(ctx, "k_head_flags", k_head_flags<<<blocks_for(n, 256), 256, 0, st>>>(d_k1.as<uint64_t>(), n, d_flag.as<int32_t>()));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tb, d_flag.as<int32_t>(), d_incl.as<int32_t>(), (int)n, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(ctx->scratch.p, tb, d_flag.as<int32_t>(), d_incl.as<int32_t>(), (int)n, st));
+    ctx->launches += 6;
+    VX_KERNEL(ctx, "k_cell_starts", k_cell_starts<<<blocks_for(n, 256), 256, 0, st>>>(d_flag.as<int32_t>(), d_incl.as<int32_t>(), n, d_start.as<int32_t>()));
+    int32_t ncell = 0; int bad = 0;
+    VX_CUDA(cudaMemcpyAsync(&ncell, d_incl.as<int32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (bad) { set_error("vx_btc_plane_cloud: a cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+    VX_TRY(d_pl.reserve(sizeof(vx_point48) * ncell)); VX_TRY(d_aux.reserve(80 * (size_t)ncell)); VX_TRY(d_pf.reserve(4 * (size_t)ncell)); VX_TRY(d_pi.reserve(4 * (size_t)ncell));
+    VX_KERNEL(ctx, "k_btc_plane", k_btc_plane<<<blocks_for(ncell, 128), 128, 0, st>>>(d_xyz.as<float>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, init_num,
+                                                                                    plane_thre, d_pl.as<vx_point48>(), d_aux.as<double>(), d_pf.as<int32_t>()));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tb, d_pf.as<int32_t>(), d_pi.as<int32_t>(), ncell, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(ctx->scratch.p, tb, d_pf.as<int32_t>(), d_pi.as<int32_t>(), ncell, st));
+    ctx->launches += 1;
+    int32_t np = 0;
+    VX_CUDA(cudaMemcpyAsync(&np, d_pi.as<int32_t>() + (ncell - 1), 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    *n_out = np;
+    if (np > out_cap) { set_error("vx_btc_plane_cloud: %d planes, capacity %lld", np, (long long)out_cap); return VX_ERR_ARG; }
+    if (np == 0) return VX_OK;
+    VX_TRY(d_out.reserve(sizeof(vx_point48) * np)); VX_TRY(d_aout.reserve(80 * (size_t)np));
+    VX_KERNEL(ctx, "k_btc_compact", k_btc_compact<<<blocks_for(ncell, 256), 256, 0, st>>>(d_pl.as<vx_point48>(), d_aux.as<double>(), d_pf.as<int32_t>(), d_pi.as<int32_t>(),
+                                                                                        ncell, d_out.as<vx_point48>(), d_aout.as<double>()));
+    if (out) VX_CUDA(cudaMemcpyAsync(out, d_out.p, sizeof(vx_point48) * np, cudaMemcpyDeviceToHost, st));
+    if (aux) VX_CUDA(cudaMemcpyAsync(aux, d_aout.p, 80 * (size_t)np, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int status = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : {&d_xyz, &d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad, &d_pl, &d_aux, &d_pf, &d_pi, &d_out, &d_aout}) b->release();
+  return status;
 }
 
 }  // extern "C"
