@@ -456,9 +456,9 @@ def run_b200(args, rank, world, local_rank):
     flops = algorithmic_flops(fac)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of k_hess_small from the committed ncu --set full capture of this workload
-                # (profiles/r01j_k_hess_small_ncu.txt: 249.29 + 22.36 MB); only valid for the default workload size
-                "traffic": 271650048 if (args.windows, args.voxels_per_window) == (N_WINDOWS, VOX_PER_WIN) else None,
-                "traffic_source": "profiles/r01j_k_hess_small_ncu.txt (ncu --set full, one launch of k_hess_small)",
+                # (profiles/r01m_k_hess_small_ncu.txt: 249.45 + 24.55 MB); only valid for the default workload size
+                "traffic": 274003968 if (args.windows, args.voxels_per_window) == (N_WINDOWS, VOX_PER_WIN) else None,
+                "traffic_source": "profiles/r01m_k_hess_small_ncu.txt (ncu --set full, one launch of k_hess_small)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
                 "kernel": "whole acc_evaluate2 pass (sum of its kernels' event times); top kernel = " + top,
                 "algorithmic_bytes_per_step": alg_bytes, "kernels": kern,
