@@ -596,11 +596,19 @@ class Factor:
         _chk(self.lib.vx_factor_residual(self.ctx.h, self.h, _p(ps), C.c_int64(head), C.c_int64(end), _p(c)))
         return float(c[0]) if self.n_win == 1 else c
 
-    def ba_lidar(self, poses, max_iter=3, thd_num=2):
-        """Lidar_BA_Optimizer::damping_iter (voxel_map.hpp:422-497) on every window of the factor."""
+    def ba_lidar(self, poses, max_iter=3, thd_num=2, hess_buf=None):
+        """Lidar_BA_Optimizer::damping_iter (voxel_map.hpp:422-497) on every window of the factor.  hess_buf: optional
+        C-contiguous float64 array (n_win, 6W, 6W) to receive the Hessian snapshots (the reference's MatrixXd *hess is the
+        caller's too); a fresh one costs a page fault per 4 KB, 30 ms at W = 399."""
         ps = as_poses(poses).copy()
         jl = 6 * self.W
-        hess = np.zeros((self.n_win, jl, jl)); resis = np.zeros((self.n_win, 2))
+        if hess_buf is None:
+            hess = np.zeros((self.n_win, jl, jl))
+        else:
+            hess = hess_buf
+            if hess.shape != (self.n_win, jl, jl) or hess.dtype != np.float64 or not hess.flags.c_contiguous:
+                raise ValueError("hess_buf must be a C-contiguous float64 array of shape (%d, %d, %d)" % (self.n_win, jl, jl))
+        resis = np.zeros((self.n_win, 2))
         conv = np.zeros(self.n_win, dtype=np.int32); trace = np.full((self.n_win, max(max_iter, 1)), -1, dtype=np.int32)
         nit = np.zeros(self.n_win, dtype=np.int32)
         _chk(self.lib.vx_ba_lidar(self.ctx.h, self.h, _p(ps), _p(hess), _p(resis), C.c_int(max_iter), C.c_int(thd_num),

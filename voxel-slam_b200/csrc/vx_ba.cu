@@ -215,7 +215,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   const bool dev = (small || jl >= ldlt_device_min) && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr;
   const bool host_mats = !dev;
   std::vector<double> Hess(host_mats ? hsz * NW : 0), JacT(host_mats ? (size_t)jl * NW : 0), Hnew(Hess.size()), Jnew(JacT.size()), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
-  std::vector<double> u(NW, 0.01), v(NW, 2.0), A(hsz), dxi(jl), D(jl), nb(jl), tmp, q1s(NW, 0.0);
+  std::vector<double> u(NW, 0.01), v(NW, 2.0), A(host_mats ? hsz : 0), dxi(jl), D(jl), nb(jl), tmp, q1s(NW, 0.0);
   std::vector<char> calc(NW, 1), active(NW, 1), conv(NW, 1);
   std::vector<int> iters(NW, 0), tr;
   std::vector<vx_pose> x(poses, poses + F), xt(poses, poses + F);

@@ -83,6 +83,12 @@ struct vx_ctx {
   vx::DevBuf scratch;        // CUB temp storage and short-lived work arrays
   vx::DevBuf scratch2;
   void *pinned = nullptr;    // small pinned staging area for scalar read-backs
+  // vx_ldlt.cu: factored diagonal blocks + the captured panel sweep (replayed while n and the buffers stay the same)
+  vx::DevBuf ldlt_side, ldlt_mat;
+  cudaGraphExec_t ldlt_exec = nullptr;
+  int ldlt_n = 0;
+  int64_t ldlt_launches = 0;
+  double *ldlt_B = nullptr, *ldlt_F = nullptr;
   size_t pinned_cap = 0;
 };
 

@@ -131,6 +131,9 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
   ctx->scratch.release();
   ctx->scratch2.release();
+  if (ctx->ldlt_exec) cudaGraphExecDestroy(ctx->ldlt_exec);
+  ctx->ldlt_side.release();
+  ctx->ldlt_mat.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   vx::cached_trim(ctx->device);
   delete ctx;

@@ -9,15 +9,18 @@
 //   host    pivot sequence from the diagonal (n^2/2 comparisons), exactly Eigen's transposition rule
 //   k_permute_lower   B(i,j) = A(max(p_i,p_j), min(p_i,p_j)), i >= j  — only the LOWER triangle of the (not exactly
 //                     symmetric) input is ever read, as Eigen does
-//   per 32-column panel: k_ldlt_diag (1 CTA: the 32x32 diagonal block), k_ldlt_rows (one thread per row below it),
+//   per 32-column panel: k_ldlt_panel (the 32x32 diagonal block in one warp's registers + one warp per row below it),
 //                        k_ldlt_trailing (64x64 tiles of the trailing lower triangle -= L21 D L21^T)
-//   k_ldlt_substitute  forward / diagonal / backward substitution, one CTA, the vector in shared memory, 32-column panels
+//   substitution: forward + diagonal ride in k_ldlt_panel; backward = k_ldlt_back, one multi-CTA launch per panel
 //   The factor never leaves the device; vx_ba_lidar hands over the device Hessian (gauge fix and damping applied while it is
 //   permuted, k_permute_gauged), so per LM iteration 4 n doubles cross PCIe instead of 4 n^2.
 // Sums are re-associated relative to the sequential sweep; results agree to rounding (tests: dxi <= 1e-9 relative,
 // identical LM accept/reject traces).
 #include "vx_common.cuh"
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <limits>
 #include <vector>
 #include <algorithm>
@@ -37,72 +40,124 @@ __global__ void k_permute_lower(const double *__restrict__ A, int n, const int32
   B[(size_t)j * n + i] = A[(size_t)c * n + r];
 }
 
-// diagonal block [c0, c0+nb): in-place L11 (unit lower, strictly-lower part stored) and D (diagonal).  Right-looking with one
-// thread per entry: column k is scaled by its pivot, then every remaining entry takes its rank-1 update — 3 barriers per
-// column instead of a dependent chain of k multiply-adds on 32 threads (25 us -> 5 us per panel).
-__global__ void __launch_bounds__(NB * NB) k_ldlt_diag(double *__restrict__ B, int n, int c0, int nb) {
-  __shared__ double S[NB][NB + 1];
-  const int i = threadIdx.x % NB, j = threadIdx.x / NB;
-  const bool in = i < nb && j < nb && i >= j;
-  if (in) S[i][j] = B[(size_t)(c0 + j) * n + c0 + i];
-  __syncthreads();
-  for (int k = 0; k < nb; k++) {
-    const double d = S[k][k];
-    __syncthreads();
-    if (j == k && i > k && i < nb && fabs(d) > 0.0) S[i][k] /= d;
-    __syncthreads();
-    if (in && j > k) S[i][j] -= S[i][k] * d * S[j][k];
-    __syncthreads();
-  }
-  if (in) B[(size_t)(c0 + j) * n + c0 + i] = S[i][j];
-}
-
-// rows below the diagonal block: L21(r,j) = (A(r,j) - sum_{t<j} L21(r,t) D_t L11(j,t)) / D_j.  One warp per row, lane = column
-// of the panel: column j is final once the updates of columns < j have been applied, its value is broadcast and the lanes to its
-// right take their update — 32 short steps instead of one thread walking a 496-term triangle (19 us -> 3 us per panel).  A CTA
-// moves a 32-row tile through shared memory so that the global accesses stay coalesced along the rows.
-__global__ void __launch_bounds__(NB * 32) k_ldlt_rows(double *__restrict__ B, int n, int c0, int nb) {
+// Panel [c0, c0+nb): the 32x32 diagonal block is factorised by warp 0 of EVERY CTA (lane = row, right-looking, operands by
+// shuffle: no barrier per column, and one launch fewer per panel than a separate diagonal kernel), then the CTA's 32 rows below the block follow: L21(r,j) = (A(r,j) - sum_{t<j} L21(r,t) D_t L11(j,t)) / D_j,
+// one warp per row, lane = column of the panel; column j is final once the updates of columns < j have been applied, its value
+// is broadcast and the lanes to its right take their update.  The factored diagonal block goes to the side array
+// F[panel][col][row] (CTA 0), NOT back into B: the other CTAs of the launch are still reading the unfactored block from B.
+constexpr int PR = 16;     // rows below the diagonal block per CTA of k_ldlt_panel
+__global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb, double *__restrict__ x,
+                                                       double *__restrict__ z) {
   __shared__ double L11[NB][NB + 1];
-  __shared__ double D[NB];
-  __shared__ double T[32][NB + 1];    // [row in tile][column of the panel]
-  const int tx = threadIdx.x % 32, ty = threadIdx.x / 32;
-  {
-    const int i = tx, j = ty;
-    if (i < nb && j < nb && i >= j) { const double v = B[(size_t)(c0 + j) * n + c0 + i]; if (i == j) D[i] = v; else L11[i][j] = v; }
+  __shared__ double D[NB], Y[NB];
+  __shared__ double T[PR][NB + 1];    // [row in tile][column of the panel]
+  const int tid = threadIdx.x, tx = tid % 32, ty = tid / 32;
+  for (int e = tid; e < NB * NB; e += PR * 32) {
+    const int i = e % NB, j = e / NB;
+    L11[i][j] = (i < nb && j < nb && i >= j) ? B[(size_t)(c0 + j) * n + c0 + i] : 0.0;
   }
-  const int r0 = c0 + nb + blockIdx.x * 32;
-  if (ty < nb && r0 + tx < n) T[tx][ty] = B[(size_t)(c0 + ty) * n + r0 + tx];
+  const int r0 = c0 + nb + blockIdx.x * PR;
+  for (int e = tid; e < PR * NB; e += PR * 32) {
+    const int row = e % PR, col = e / PR;
+    if (col < nb && r0 + row < n) T[row][col] = B[(size_t)(c0 + col) * n + r0 + row];
+  }
   __syncthreads();
+  // the diagonal block, 8 columns at a time: warp 0 (lane = row) takes the 8 columns through all rows with the 8 entries of its
+  // row in registers (28 rank-1 steps, unrolled; operands by shuffle), then every thread applies the rank-8 update to what is
+  // left of the block.  Straight-line code for all 496 steps is instruction-fetch bound (each CTA runs it once), a rolled
+  // 32-column loop is a chain of 496 dependent shared-memory round trips; this form has 32 divisions + 8 barriers on its chain.
+  for (int kb = 0; kb < NB; kb += 8) {
+    if (ty == 0) {
+      const int r = kb + tx;             // rows kb .. NB-1
+      double a[8];
+#pragma unroll
+      for (int c = 0; c < 8; c++) a[c] = r < NB ? L11[r][kb + c] : 0.0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const double d = __shfl_sync(0xffffffffu, a[k], k);
+        double l = a[k];
+        if (fabs(d) > 0.0) l /= d;
+        if (tx > k) a[k] = l;
+        const double ld = l * d;
+#pragma unroll
+        for (int j = k + 1; j < 8; j++) {
+          const double ljk = __shfl_sync(0xffffffffu, l, j);
+          if (tx >= j) a[j] -= ld * ljk;
+        }
+      }
+      if (r < NB) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) if (tx >= c) L11[r][kb + c] = a[c];
+      }
+    }
+    __syncthreads();
+    const int m = NB - kb - 8;           // rows / columns left
+    for (int e = tid; e < m * m; e += PR * 32) {
+      const int i = kb + 8 + e % m, j = kb + 8 + e / m;
+      if (i >= j) {
+        double acc = L11[i][j];
+#pragma unroll
+        for (int c = 0; c < 8; c++) acc -= L11[i][kb + c] * L11[kb + c][kb + c] * L11[j][kb + c];
+        L11[i][j] = acc;
+      }
+    }
+    __syncthreads();
+  }
+  if (ty == 0) {
+    D[tx] = L11[tx][tx];
+    __syncwarp();
+    // forward substitution rides along: y_p = L11^-1 x_p (x_p already carries the updates of the panels to the left)
+    double xi = tx < nb ? x[c0 + tx] : 0.0;
+    for (int t = 0; t < nb; t++) {
+      const double xt = __shfl_sync(0xffffffffu, xi, t);
+      if (tx > t && tx < nb) xi -= L11[tx][t] * xt;
+    }
+    Y[tx] = xi;
+    if (blockIdx.x == 0 && tx < nb) {       // z = D^-1 L^-1 x, Eigen's rule for tiny pivots (LDLT::_solve_impl)
+      const double tol = 1.0 / 1.7976931348623157e308;
+      const double d = D[tx];
+      z[c0 + tx] = fabs(d) > tol ? xi / d : 0.0;
+    }
+  }
+  __syncthreads();
+  if (blockIdx.x == 0)
+    for (int e = tid; e < NB * NB; e += PR * 32) F[(size_t)(c0 / NB) * NB * NB + e] = L11[e % NB][e / NB];
   {
     const int row = ty, lane = tx;      // warp ty <-> row r0 + ty
     if (r0 + row < n) {
       double a = lane < nb ? T[row][lane] : 0.0;
-      for (int j = 0; j < nb; j++) {
-        double l = __shfl_sync(0xffffffffu, a, j);
-        const double dj = D[j];
-        if (fabs(dj) > 0.0) l /= dj;
-        if (lane == j) a = l;
-        else if (lane > j && lane < nb) a -= l * dj * L11[lane][j];
+      for (int j = 0; j < nb; j++) {       // lanes right of j take L(r,j) D_j L11(lane,j) = (entry before its division) * L11(lane,j):
+        const double pj = __shfl_sync(0xffffffffu, a, j);      // the division stays off the dependent chain
+        if (lane > j && lane < nb) a -= pj * L11[lane][j];
       }
-      if (lane < nb) T[row][lane] = a;
+      if (lane < nb) { const double dj = D[lane]; if (fabs(dj) > 0.0) a /= dj; T[row][lane] = a; }
+      double sx = lane < nb ? a * Y[lane] : 0.0;       // x_r -= L21(r,:) y_p
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sx += __shfl_xor_sync(0xffffffffu, sx, o);
+      if (lane == 0) x[r0 + row] -= sx;
     }
   }
   __syncthreads();
-  if (ty < nb && r0 + tx < n) B[(size_t)(c0 + ty) * n + r0 + tx] = T[tx][ty];
+  for (int e = tid; e < PR * NB; e += PR * 32) {
+    const int row = e % PR, col = e / PR;
+    if (col < nb && r0 + row < n) B[(size_t)(c0 + col) * n + r0 + row] = T[row][col];
+  }
 }
 
 // trailing update of the lower triangle: C(I,J) -= L(I,:) D L(J,:)^T over the panel's nb columns
-__global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, int n, int c0, int nb) {
+__global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, const double *__restrict__ F, int n, int c0, int nb) {
   const int t0 = c0 + nb;
-  const int bi = blockIdx.x, bj = blockIdx.y;
-  if (bj > bi) return;
+  int bi = (int)((sqrtf(8.0f * (float)blockIdx.x + 1.0f) - 1.0f) * 0.5f);      // lower-triangular tiles only: blockIdx.x = bi (bi + 1) / 2 + bj
+  while (bi * (bi + 1) / 2 > (int)blockIdx.x) bi--;
+  while ((bi + 1) * (bi + 2) / 2 <= (int)blockIdx.x) bi++;
+  const int bj = (int)blockIdx.x - bi * (bi + 1) / 2;
   __shared__ double Li[NB][TR + 1], Lj[NB][TR + 1];    // [t][row]; Lj pre-scaled by D_t
   const int r0 = t0 + bi * TR, q0 = t0 + bj * TR;
   for (int k = threadIdx.x; k < NB * TR; k += blockDim.x) {
     const int rr = k % TR, t = k / TR;
     double a = 0.0, b = 0.0;
     if (t < nb) {
-      const double d = B[(size_t)(c0 + t) * n + c0 + t];
+      const double d = F[(size_t)(c0 / NB) * NB * NB + t * NB + t];
       if (r0 + rr < n) a = B[(size_t)(c0 + t) * n + r0 + rr];
       if (q0 + rr < n) b = B[(size_t)(c0 + t) * n + q0 + rr] * d;
     }
@@ -154,97 +209,73 @@ __global__ void k_permute_gauged(const double *__restrict__ H, int n, const int3
   B[(size_t)j * n + i] = v;
 }
 
-// x <- L^-T D^-1 L^-1 x on the factor in B (unit lower L below the diagonal, D on it).  One CTA of 1024 threads, x in shared
-// memory; per 32-column panel the diagonal block is solved by warp 0 (shuffles) and the rest is a panel-wide update (forward:
-// one thread per row, 32 independent loads in flight; backward: one warp per column, coalesced dot products).
-__global__ void __launch_bounds__(1024) k_ldlt_substitute(const double *__restrict__ B, int n, double *__restrict__ x) {
-  extern __shared__ double xs[];
+// Backward substitution, one launch per panel from the last to the first: every CTA solves the panel's 32 unknowns
+// L11^T x_p = z_p in warp 0 (shuffles; z_p already carries the updates of the panels to the right), CTA 0 stores them, and each
+// warp then takes BC columns i < c0 of the factor: z_i -= L(c0.., i)^T x_p, lane = row of the panel (256 contiguous bytes per
+// column).  x_p goes to its own array: the other CTAs of the launch are still reading z_p.
+constexpr int BC = 4;
+__global__ void __launch_bounds__(256) k_ldlt_back(const double *__restrict__ B, const double *__restrict__ F, int n, int c0, int nb, double *__restrict__ z,
+                                                   double *__restrict__ xo) {
   __shared__ double L11[NB][NB + 1];
-  __shared__ double part[NB];
+  __shared__ double X[NB];
   const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
-  for (int i = tid; i < n; i += 1024) xs[i] = x[i];
+  for (int e = tid; e < NB * NB; e += 256) L11[e % NB][e / NB] = F[(size_t)(c0 / NB) * NB * NB + e];
   __syncthreads();
-  for (int c0 = 0; c0 < n; c0 += NB) {
-    const int nb = min(NB, n - c0);
-    { const int i = tid % NB, j = tid / NB; if (i < nb && j < nb && i > j) L11[i][j] = B[(size_t)(c0 + j) * n + c0 + i]; }
-    __syncthreads();
-    if (wp == 0) {
-      double xi = lane < nb ? xs[c0 + lane] : 0.0;
-      for (int t = 0; t < nb; t++) {
-        const double xt = __shfl_sync(0xffffffffu, xi, t);
-        if (lane > t && lane < nb) xi -= L11[lane][t] * xt;
-      }
-      if (lane < nb) xs[c0 + lane] = xi;
+  if (wp == 0) {
+    double xj = lane < nb ? z[c0 + lane] : 0.0;
+    for (int t = nb - 1; t >= 0; t--) {
+      const double xt = __shfl_sync(0xffffffffu, xj, t);
+      if (lane < t) xj -= L11[t][lane] * xt;
     }
-    __syncthreads();
-    for (int r = c0 + nb + tid; r < n; r += 1024) {
-      double acc = xs[r];
-#pragma unroll 8
-      for (int t = 0; t < nb; t++) acc -= B[(size_t)(c0 + t) * n + r] * xs[c0 + t];
-      xs[r] = acc;
-    }
-    __syncthreads();
-  }
-  {
-    const double tol = 1.0 / 1.7976931348623157e308;
-    for (int i = tid; i < n; i += 1024) { const double d = B[(size_t)i * n + i]; xs[i] = fabs(d) > tol ? xs[i] / d : 0.0; }
+    X[lane] = xj;
+    if (blockIdx.x == 0 && lane < nb) xo[c0 + lane] = xj;
   }
   __syncthreads();
-  for (int c0 = ((n - 1) / NB) * NB; c0 >= 0; c0 -= NB) {
-    const int nb = min(NB, n - c0);
-    { const int i = tid % NB, j = tid / NB; if (i < nb && j < nb && i > j) L11[i][j] = B[(size_t)(c0 + j) * n + c0 + i]; }
-    if (wp < nb) {
-      const double *col = B + (size_t)(c0 + wp) * n;
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-      int i = c0 + nb + lane;
-      for (; i + 96 < n; i += 128) { s0 += col[i] * xs[i]; s1 += col[i + 32] * xs[i + 32]; s2 += col[i + 64] * xs[i + 64]; s3 += col[i + 96] * xs[i + 96]; }
-      for (; i < n; i += 32) s0 += col[i] * xs[i];
-      double sacc = (s0 + s1) + (s2 + s3);
+  const double xr = lane < nb ? X[lane] : 0.0;
+  const int i0 = (blockIdx.x * 8 + wp) * BC;
+  double v[BC];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) sacc += __shfl_down_sync(0xffffffffu, sacc, o);
-      if (lane == 0) part[wp] = sacc;
-    }
-    __syncthreads();
-    if (wp == 0) {
-      double xj = lane < nb ? xs[c0 + lane] - part[lane] : 0.0;
-      for (int t = nb - 1; t >= 0; t--) {
-        const double xt = __shfl_sync(0xffffffffu, xj, t);
-        if (lane < t) xj -= L11[t][lane] * xt;
-      }
-      if (lane < nb) xs[c0 + lane] = xj;
-    }
-    __syncthreads();
+  for (int q = 0; q < BC; q++) v[q] = (i0 + q < c0 && lane < nb) ? B[(size_t)(i0 + q) * n + c0 + lane] * xr : 0.0;
+#pragma unroll
+  for (int q = 0; q < BC; q++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    if (lane == 0 && i0 + q < c0) z[i0 + q] -= v[q];
   }
-  for (int i = tid; i < n; i += 1024) x[i] = xs[i];
 }
 
 }  // namespace
 
 namespace vx {
 
-// Eigen's pivot rule on the damped diagonal d (non-negative): at step k the largest d_i, i >= k, first index on ties; the swap
-// moves the displaced entry to the winner's old position.  pos[k] = original index that ends up at position k, tr[k] = the
-// transposition of step k.  With distinct values the order is simply "descending" and the transpositions follow from an
-// index map in O(n log n); ties take the literal O(n^2) selection.
+// Eigen's pivot rule on the damped diagonal d (non-negative): at step k the largest d_i among the positions i >= k, the first
+// POSITION on ties; the swap moves the displaced entry to the winner's old position.  pos[k] = original index that ends up at
+// position k, tr[k] = the transposition of step k.  Evaluated in O(n log n): entries sorted by value; within a run of equal
+// values the members are taken in the order of their positions when the run starts — a member still waiting is never the one
+// displaced (the displaced entry sits at position k, the smallest position left: were it a member it would be the winner),
+// so those positions stay put while the run is consumed.  (The gauge rows make ties the rule, not the exception: six 1 + u.)
+// NaN on the diagonal: the literal O(n^2) selection.
 static void pivot_order(std::vector<double> d, std::vector<int32_t> &pos, std::vector<int32_t> &tr) {
   const int n = (int)d.size();
   pos.resize(n); tr.resize(n);
-  std::vector<int32_t> ord(n);
-  for (int i = 0; i < n; i++) ord[i] = i;
-  bool distinct = true;
-  for (int i = 0; i < n; i++) if (!(d[i] == d[i])) distinct = false;    // NaN: no ordering to sort by
-  if (distinct)
+  bool ordered = true;
+  for (int i = 0; i < n; i++) if (!(d[i] == d[i])) ordered = false;
+  if (ordered) {
+    std::vector<int32_t> ord(n), at(n), where(n);   // at[p] = original index now at position p; where[i] = position of index i
+    for (int i = 0; i < n; i++) { ord[i] = i; at[i] = i; where[i] = i; }
     std::sort(ord.begin(), ord.end(), [&](int a, int b) { return d[a] > d[b] || (d[a] == d[b] && a < b); });
-  for (int k = 0; distinct && k + 1 < n; k++) if (!(d[ord[k]] > d[ord[k + 1]])) distinct = false;   // ties: the literal rule
-  if (distinct) {
-    std::vector<int32_t> at(n), where(n);   // at[p] = original index now at position p; where[i] = position of original index i
-    for (int i = 0; i < n; i++) { at[i] = i; where[i] = i; }
-    for (int k = 0; k < n; k++) {
-      const int win = ord[k], big = where[win];
-      tr[k] = big;
-      if (big != k) { const int lose = at[k]; at[k] = win; at[big] = lose; where[win] = k; where[lose] = big; }
+    int k = 0;
+    while (k < n) {
+      int e = k + 1;
+      while (e < n && d[ord[e]] == d[ord[k]]) e++;
+      if (e - k > 1) std::sort(ord.begin() + k, ord.begin() + e, [&](int a, int b) { return where[a] < where[b]; });
+      for (; k < e; k++) {
+        const int win = ord[k], big = where[win];
+        tr[k] = big;
+        if (big != k) { const int lose = at[k]; at[k] = win; at[big] = lose; where[win] = k; where[lose] = big; }
+      }
     }
-    for (int k = 0; k < n; k++) pos[k] = at[k];
+    for (int i = 0; i < n; i++) pos[i] = at[i];
     return;
   }
   for (int i = 0; i < n; i++) pos[i] = i;
@@ -256,28 +287,60 @@ static void pivot_order(std::vector<double> d, std::vector<int32_t> &pos, std::v
   }
 }
 
-// blocked factorisation of the permuted lower triangle in dB, then x <- (L D L^T)^-1 x on the device; x: host, n doubles
-static int factor_and_substitute(vx_ctx *ctx, double *dB, int n, double *x) {
+// the sweep: panel + trailing update per 32-column panel, left to right (the forward substitution rides in the panel kernel),
+// then the backward substitution right to left: 3 launches per panel, 224 at n = 2394
+static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx, double *dz, double *dxo) {
   cudaStream_t st = ctx->stream;
   for (int c0 = 0; c0 < n; c0 += NB) {
     const int nb = std::min(NB, n - c0);
-    VX_KERNEL(ctx, "k_ldlt_diag", k_ldlt_diag<<<1, NB * NB, 0, st>>>(dB, n, c0, nb));
     const int below = n - c0 - nb;
+    VX_KERNEL(ctx, "k_ldlt_panel", k_ldlt_panel<<<std::max(1, blocks_for(below, PR)), PR * 32, 0, st>>>(dB, dF, n, c0, nb, dx, dz));
     if (below > 0) {
-      VX_KERNEL(ctx, "k_ldlt_rows", k_ldlt_rows<<<blocks_for(below, 32), NB * 32, 0, st>>>(dB, n, c0, nb));
       const int nt = (below + TR - 1) / TR;
-      VX_KERNEL(ctx, "k_ldlt_trailing", k_ldlt_trailing<<<dim3(nt, nt), 256, 0, st>>>(dB, n, c0, nb));
+      VX_KERNEL(ctx, "k_ldlt_trailing", k_ldlt_trailing<<<nt * (nt + 1) / 2, 256, 0, st>>>(dB, dF, n, c0, nb));
     }
   }
-  VX_TRY(ctx->scratch2.reserve(sizeof(double) * n));
-  double *dx = ctx->scratch2.as<double>();
+  for (int c0 = ((n - 1) / NB) * NB; c0 >= 0; c0 -= NB) {
+    const int nb = std::min(NB, n - c0);
+    VX_KERNEL(ctx, "k_ldlt_back", k_ldlt_back<<<std::max(1, blocks_for(c0, 8 * BC)), 256, 0, st>>>(dB, dF, n, c0, nb, dz, dxo));
+  }
+  return VX_OK;
+}
+
+// blocked factorisation of the permuted lower triangle in dB and x <- (L D L^T)^-1 x on the device; x: host, n doubles.
+// The sweep is launch-bound towards its end (the trailing matrix shrinks to a few tiles), so it is captured once per (n, buffers)
+// into a CUDA graph and replayed; under the kernel profiler the launches are issued one by one so that they can be timed.
+static int factor_and_substitute(vx_ctx *ctx, double *dB, int n, double *x) {
+  cudaStream_t st = ctx->stream;
+  const int np = (n + NB - 1) / NB;
+  VX_TRY(ctx->ldlt_side.reserve(sizeof(double) * ((size_t)NB * NB * np + 3 * (size_t)n)));
+  double *dF = ctx->ldlt_side.as<double>();
+  double *dx = dF + (size_t)NB * NB * np, *dz = dx + n, *dxo = dz + n;
   VX_CUDA(cudaMemcpyAsync(dx, x, sizeof(double) * n, cudaMemcpyHostToDevice, st));
-  const size_t smem = sizeof(double) * n;
-  VX_ARG(smem <= 200 * 1024);     // 25600 unknowns
-  static size_t attr = 0;
-  if (smem > 48 * 1024 && smem > attr) { VX_CUDA(cudaFuncSetAttribute(k_ldlt_substitute, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem; }
-  VX_KERNEL(ctx, "k_ldlt_substitute", k_ldlt_substitute<<<1, 1024, smem, st>>>(dB, n, dx));
-  VX_CUDA(cudaMemcpyAsync(x, dx, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+  static const bool use_graph = std::getenv("VX_LDLT_NO_GRAPH") == nullptr;
+  if (ctx->profiling || !use_graph) {
+    VX_TRY(enqueue_sweep(ctx, dB, dF, n, dx, dz, dxo));
+  } else {
+    if (!ctx->ldlt_exec || ctx->ldlt_n != n || ctx->ldlt_B != dB || ctx->ldlt_F != dF) {
+      if (ctx->ldlt_exec) { cudaGraphExecDestroy(ctx->ldlt_exec); ctx->ldlt_exec = nullptr; }
+      cudaGraph_t g = nullptr;
+      const int64_t before = ctx->launches;
+      VX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      const int rc = enqueue_sweep(ctx, dB, dF, n, dx, dz, dxo);
+      const cudaError_t ce = cudaStreamEndCapture(st, &g);
+      ctx->ldlt_launches = ctx->launches - before;
+      ctx->launches = before;
+      if (rc != VX_OK) { if (g) cudaGraphDestroy(g); return rc; }
+      VX_CUDA(ce);
+      const cudaError_t ci = cudaGraphInstantiate(&ctx->ldlt_exec, g, 0);
+      cudaGraphDestroy(g);
+      VX_CUDA(ci);
+      ctx->ldlt_n = n; ctx->ldlt_B = dB; ctx->ldlt_F = dF;
+    }
+    VX_CUDA(cudaGraphLaunch(ctx->ldlt_exec, st));
+    ctx->launches += ctx->ldlt_launches;
+  }
+  VX_CUDA(cudaMemcpyAsync(x, dxo, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
   VX_CUDA(cudaStreamSynchronize(st));
   return VX_OK;
 }
@@ -291,7 +354,8 @@ int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b
   for (int i = 0; i < n; i++) d[i] = std::fabs(A[(size_t)i * n + i]);
   pivot_order(d, pos, tr);
   const size_t bytes = sizeof(double) * (size_t)n * n;
-  DevBuf dA, dB, dP;
+  DevBuf dA, dP;
+  DevBuf &dB = ctx->ldlt_mat;       // kept across calls: the captured sweep is replayed while its address stays
   for (int i = 0; i < n; i++) x[i] = b[i];
   for (int k = 0; k < n; k++) if (tr[k] != k) std::swap(x[k], x[tr[k]]);
   auto body = [&]() -> int {
@@ -303,7 +367,7 @@ int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b
   };
   const int rc = body();
   cudaStreamSynchronize(st);
-  dA.release(); dB.release(); dP.release();
+  dA.release(); dP.release();
   VX_TRY(rc);
   for (int k = n - 1; k >= 0; k--) if (tr[k] != k) std::swap(x[k], x[tr[k]]);
   return VX_OK;
@@ -316,25 +380,33 @@ int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, doubl
   cudaStream_t st = ctx->stream;
   std::vector<double> D(n), J(n), d(n);
   std::vector<int32_t> pos, tr;
-  DevBuf dB, dP, dD;
+  DevBuf dP, dD;
+  DevBuf &dB = ctx->ldlt_mat;
   auto body = [&]() -> int {
     VX_TRY(dB.reserve(sizeof(double) * (size_t)n * n)); VX_TRY(dP.reserve(sizeof(int32_t) * n)); VX_TRY(dD.reserve(sizeof(double) * n));
+    auto T0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char *w) { if (getenv("VX_LDLT_TIMING")) { cudaStreamSynchronize(st); auto t = std::chrono::steady_clock::now(); fprintf(stderr, "[ldlt] %s %.3f ms\n", w, std::chrono::duration<double, std::milli>(t - T0).count()); T0 = t; } };
     VX_KERNEL(ctx, "k_diag_gauged", k_diag_gauged<<<blocks_for(n, 256), 256, 0, st>>>(dH, n, dD.as<double>()));
     VX_CUDA(cudaMemcpyAsync(D.data(), dD.p, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaMemcpyAsync(J.data(), dJ, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
     for (int r = 0; r < 6 && r < n; r++) J[r] = 0.0;
     for (int r = 0; r < n; r++) d[r] = std::fabs(D[r] + u * D[r]);
+    lap("diag");
     pivot_order(d, pos, tr);
+    lap("pivot");
     for (int i = 0; i < n; i++) dx[i] = -J[i];
     for (int k = 0; k < n; k++) if (tr[k] != k) std::swap(dx[k], dx[tr[k]]);
     VX_CUDA(cudaMemcpyAsync(dP.p, pos.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
     VX_KERNEL(ctx, "k_permute_gauged", k_permute_gauged<<<dim3(blocks_for(n, 128), n), 128, 0, st>>>(dH, n, dP.as<int32_t>(), u, dB.as<double>()));
-    return factor_and_substitute(ctx, dB.as<double>(), n, dx);
+    lap("permute");
+    const int r = factor_and_substitute(ctx, dB.as<double>(), n, dx);
+    lap("factor");
+    return r;
   };
   const int rc = body();
   cudaStreamSynchronize(st);
-  dB.release(); dP.release(); dD.release();
+  dP.release(); dD.release();
   VX_TRY(rc);
   for (int k = n - 1; k >= 0; k--) if (tr[k] != k) std::swap(dx[k], dx[tr[k]]);
   double q = 0.0;
