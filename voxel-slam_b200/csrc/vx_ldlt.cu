@@ -9,8 +9,9 @@
 //   host    pivot sequence from the diagonal (n^2/2 comparisons), exactly Eigen's transposition rule
 //   k_permute_lower   B(i,j) = A(max(p_i,p_j), min(p_i,p_j)), i >= j  — only the LOWER triangle of the (not exactly
 //                     symmetric) input is ever read, as Eigen does
-//   per 32-column panel: k_ldlt_panel (the 32x32 diagonal block in one warp's registers + one warp per row below it),
-//                        k_ldlt_trailing (64x64 tiles of the trailing lower triangle -= L21 D L21^T)
+//   per 32-column panel: k_ldlt_panel (one warp per row below the diagonal block),
+//                        k_ldlt_trailing (64x64 tiles of the trailing lower triangle -= L21 D L21^T; tile (0,0) goes on to
+//                        factor the next panel's 32x32 diagonal block, so that step is off the panel's dependent chain)
 //   substitution: forward + diagonal ride in k_ldlt_panel; backward = k_ldlt_back, one multi-CTA launch per panel
 //   The factor never leaves the device; vx_ba_lidar hands over the device Hessian (gauge fix and damping applied while it is
 //   permuted, k_permute_gauged), so per LM iteration 4 n doubles cross PCIe instead of 4 n^2.
@@ -40,32 +41,24 @@ __global__ void k_permute_lower(const double *__restrict__ A, int n, const int32
   B[(size_t)j * n + i] = A[(size_t)c * n + r];
 }
 
-// Panel [c0, c0+nb): the 32x32 diagonal block is factorised by warp 0 of EVERY CTA (lane = row, right-looking, operands by
-// shuffle: no barrier per column, and one launch fewer per panel than a separate diagonal kernel), then the CTA's 32 rows below the block follow: L21(r,j) = (A(r,j) - sum_{t<j} L21(r,t) D_t L11(j,t)) / D_j,
-// one warp per row, lane = column of the panel; column j is final once the updates of columns < j have been applied, its value
-// is broadcast and the lanes to its right take their update.  The factored diagonal block goes to the side array
-// F[panel][col][row] (CTA 0), NOT back into B: the other CTAs of the launch are still reading the unfactored block from B.
-constexpr int PR = 16;     // rows below the diagonal block per CTA of k_ldlt_panel
-__global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb, double *__restrict__ x,
-                                                       double *__restrict__ z) {
-  __shared__ double L11[NB][NB + 1];
-  __shared__ double D[NB], Y[NB];
-  __shared__ double T[PR][NB + 1];    // [row in tile][column of the panel]
-  const int tid = threadIdx.x, tx = tid % 32, ty = tid / 32;
-  for (int e = tid; e < NB * NB; e += PR * 32) {
-    const int i = e % NB, j = e / NB;
-    L11[i][j] = (i < nb && j < nb && i >= j) ? B[(size_t)(c0 + j) * n + c0 + i] : 0.0;
-  }
-  const int r0 = c0 + nb + blockIdx.x * PR;
-  for (int e = tid; e < PR * NB; e += PR * 32) {
-    const int row = e % PR, col = e / PR;
-    if (col < nb && r0 + row < n) T[row][col] = B[(size_t)(c0 + col) * n + r0 + row];
-  }
-  __syncthreads();
-  // the diagonal block, 8 columns at a time: warp 0 (lane = row) takes the 8 columns through all rows with the 8 entries of its
-  // row in registers (28 rank-1 steps, unrolled; operands by shuffle), then every thread applies the rank-8 update to what is
-  // left of the block.  Straight-line code for all 496 steps is instruction-fetch bound (each CTA runs it once), a rolled
-  // 32-column loop is a chain of 496 dependent shared-memory round trips; this form has 32 divisions + 8 barriers on its chain.
+// In-place L11 (unit lower, strictly-lower part) and D (diagonal) of a 32x32 block in shared memory (zero-padded lower triangle),
+// NT threads, 8 columns at a time: warp 0 (lane = row) takes the 8 columns through all rows with the 8 entries of its row in
+// registers (28 rank-1 steps, unrolled; operands by shuffle), then every thread applies the rank-8 update to what is left of
+// the block.  Straight-line code for all 496 steps is instruction-fetch bound (a CTA runs it once), a rolled 32-column loop is a
+// chain of 496 dependent shared-memory round trips; this form has 32 divisions + 8 barriers on its chain.
+// 1/d for a normal-range d: hardware seed (rcp.approx.ftz.f64, ~20 bits) + two Newton steps, relative error ~1e-16 (not the
+// correctly rounded quotient: the factor agrees with the sequential sweep to rounding, as the re-associated sums already do)
+__device__ __forceinline__ double rcp_newton(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  r = fma(fma(-d, r, 1.0), r, r);
+  r = fma(fma(-d, r, 1.0), r, r);
+  return r;
+}
+
+template <int NT>
+__device__ __forceinline__ void ldlt_diag_block(double (*L11)[NB + 1], int tid) {
+  const int tx = tid % 32, ty = tid / 32;
   for (int kb = 0; kb < NB; kb += 8) {
     if (ty == 0) {
       const int r = kb + tx;             // rows kb .. NB-1
@@ -76,7 +69,9 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
       for (int k = 0; k < 8; k++) {
         const double d = __shfl_sync(0xffffffffu, a[k], k);
         double l = a[k];
-        if (fabs(d) > 0.0) l /= d;
+        const double ad = fabs(d);
+        if (ad > 1e-290 && ad < 1e290) l *= rcp_newton(d);       // the 32 pivots are the block's dependent chain: ~55 cycles, not ~300
+        else if (ad > 0.0) l /= d;
         if (tx > k) a[k] = l;
         const double ld = l * d;
 #pragma unroll
@@ -92,7 +87,7 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
     }
     __syncthreads();
     const int m = NB - kb - 8;           // rows / columns left
-    for (int e = tid; e < m * m; e += PR * 32) {
+    for (int e = tid; e < m * m; e += NT) {
       const int i = kb + 8 + e % m, j = kb + 8 + e / m;
       if (i >= j) {
         double acc = L11[i][j];
@@ -103,6 +98,38 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
     }
     __syncthreads();
   }
+}
+
+// the first diagonal block; the others are factored by tile (0,0) of the trailing update that completes them
+__global__ void __launch_bounds__(256) k_ldlt_diag0(const double *__restrict__ B, double *__restrict__ F, int n, int nb) {
+  __shared__ double L11[NB][NB + 1];
+  for (int e = threadIdx.x; e < NB * NB; e += 256) {
+    const int i = e % NB, j = e / NB;
+    L11[i][j] = (i < nb && j < nb && i >= j) ? B[(size_t)j * n + i] : 0.0;
+  }
+  __syncthreads();
+  ldlt_diag_block<256>(L11, threadIdx.x);
+  for (int e = threadIdx.x; e < NB * NB; e += 256) F[e] = L11[e % NB][e / NB];
+}
+
+// Panel [c0, c0+nb): the rows below the (already factored, F[panel][col][row]) diagonal block:
+// L21(r,j) = (A(r,j) - sum_{t<j} L21(r,t) D_t L11(j,t)) / D_j, one warp per row, lane = column of the panel; the entry of column
+// j BEFORE its division is L21(r,j) D_j, so it is broadcast as it stands and the lanes to its right take their update — the
+// division stays off the dependent chain.  The forward substitution rides along.
+constexpr int PR = 16;     // rows per CTA
+__global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, const double *__restrict__ F, int n, int c0, int nb, double *__restrict__ x,
+                                                       double *__restrict__ z) {
+  __shared__ double L11[NB][NB + 1];
+  __shared__ double D[NB], Y[NB];
+  __shared__ double T[PR][NB + 1];    // [row in tile][column of the panel]
+  const int tid = threadIdx.x, tx = tid % 32, ty = tid / 32;
+  for (int e = tid; e < NB * NB; e += PR * 32) L11[e % NB][e / NB] = F[(size_t)(c0 / NB) * NB * NB + e];
+  const int r0 = c0 + nb + blockIdx.x * PR;
+  for (int e = tid; e < PR * NB; e += PR * 32) {
+    const int row = e % PR, col = e / PR;
+    if (col < nb && r0 + row < n) T[row][col] = B[(size_t)(c0 + col) * n + r0 + row];
+  }
+  __syncthreads();
   if (ty == 0) {
     D[tx] = L11[tx][tx];
     __syncwarp();
@@ -120,8 +147,6 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
     }
   }
   __syncthreads();
-  if (blockIdx.x == 0)
-    for (int e = tid; e < NB * NB; e += PR * 32) F[(size_t)(c0 / NB) * NB * NB + e] = L11[e % NB][e / NB];
   {
     const int row = ty, lane = tx;      // warp ty <-> row r0 + ty
     if (r0 + row < n) {
@@ -145,7 +170,7 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
 }
 
 // trailing update of the lower triangle: C(I,J) -= L(I,:) D L(J,:)^T over the panel's nb columns
-__global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, const double *__restrict__ F, int n, int c0, int nb) {
+__global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb) {
   const int t0 = c0 + nb;
   int bi = (int)((sqrtf(8.0f * (float)blockIdx.x + 1.0f) - 1.0f) * 0.5f);      // lower-triangular tiles only: blockIdx.x = bi (bi + 1) / 2 + bj
   while (bi * (bi + 1) / 2 > (int)blockIdx.x) bi--;
@@ -153,18 +178,30 @@ __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, c
   const int bj = (int)blockIdx.x - bi * (bi + 1) / 2;
   __shared__ double Li[NB][TR + 1], Lj[NB][TR + 1];    // [t][row]; Lj pre-scaled by D_t
   const int r0 = t0 + bi * TR, q0 = t0 + bj * TR;
-  for (int k = threadIdx.x; k < NB * TR; k += blockDim.x) {
-    const int rr = k % TR, t = k / TR;
-    double a = 0.0, b = 0.0;
-    if (t < nb) {
-      const double d = F[(size_t)(c0 / NB) * NB * NB + t * NB + t];
-      if (r0 + rr < n) a = B[(size_t)(c0 + t) * n + r0 + rr];
-      if (q0 + rr < n) b = B[(size_t)(c0 + t) * n + q0 + rr] * d;
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;     // 16 x 16 threads, 4 x 4 outputs each
+  // every global load of the tile is issued before anything waits: the C entries first (used last), then the two L strips
+  double cc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+      const int r = r0 + tx + 16 * a, c = q0 + ty + 16 * b;
+      cc[a][b] = (r < n && c < n && r >= c) ? B[(size_t)c * n + r] : 0.0;
     }
-    Li[t][rr] = a; Lj[t][rr] = b;
+  double la[NB * TR / 256], lb[NB * TR / 256];
+#pragma unroll
+  for (int q = 0; q < NB * TR / 256; q++) {
+    const int k = threadIdx.x + 256 * q;
+    const int rr = k % TR, t = k / TR;
+    la[q] = (t < nb && r0 + rr < n) ? B[(size_t)(c0 + t) * n + r0 + rr] : 0.0;
+    lb[q] = (t < nb && q0 + rr < n) ? B[(size_t)(c0 + t) * n + q0 + rr] * F[(size_t)(c0 / NB) * NB * NB + t * NB + t] : 0.0;
+  }
+#pragma unroll
+  for (int q = 0; q < NB * TR / 256; q++) {
+    const int k = threadIdx.x + 256 * q;
+    Li[k / TR][k % TR] = la[q]; Lj[k / TR][k % TR] = lb[q];
   }
   __syncthreads();
-  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;     // 16 x 16 threads, 4 x 4 outputs each
   double acc[4][4];
 #pragma unroll
   for (int a = 0; a < 4; a++)
@@ -185,8 +222,22 @@ __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, c
 #pragma unroll
     for (int b = 0; b < 4; b++) {
       const int r = r0 + tx + 16 * a, c = q0 + ty + 16 * b;
-      if (r < n && c < n && r >= c) B[(size_t)c * n + r] -= acc[a][b];
+      if (r < n && c < n && r >= c) B[(size_t)c * n + r] = cc[a][b] - acc[a][b];
     }
+  if (bi == 0 && bj == 0) {               // this tile completes the next panel's diagonal block: factor it here, off the panel's chain
+    __syncthreads();                      // everybody is done with Li / Lj
+    double (*L11)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(&Li[0][0]);
+#pragma unroll
+    for (int a = 0; a < 2; a++)
+#pragma unroll
+      for (int b = 0; b < 2; b++) {
+        const int i = tx + 16 * a, j = ty + 16 * b;
+        L11[i][j] = (t0 + i < n && t0 + j < n && i >= j) ? cc[a][b] - acc[a][b] : 0.0;
+      }
+    __syncthreads();
+    ldlt_diag_block<256>(L11, threadIdx.x);
+    for (int e = threadIdx.x; e < NB * NB; e += 256) F[(size_t)(t0 / NB) * NB * NB + e] = L11[e % NB][e / NB];
+  }
 }
 
 
@@ -288,9 +339,10 @@ static void pivot_order(std::vector<double> d, std::vector<int32_t> &pos, std::v
 }
 
 // the sweep: panel + trailing update per 32-column panel, left to right (the forward substitution rides in the panel kernel),
-// then the backward substitution right to left: 3 launches per panel, 224 at n = 2394
+// then the backward substitution right to left: 3 launches per panel, 225 at n = 2394
 static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx, double *dz, double *dxo) {
   cudaStream_t st = ctx->stream;
+  VX_KERNEL(ctx, "k_ldlt_diag0", k_ldlt_diag0<<<1, 256, 0, st>>>(dB, dF, n, std::min(NB, n)));
   for (int c0 = 0; c0 < n; c0 += NB) {
     const int nb = std::min(NB, n - c0);
     const int below = n - c0 - nb;
