@@ -100,6 +100,26 @@ def test_device_ldlt_matches_oracle(pkg, ob, ctx, n):
     assert np.abs(sym @ got - b).max() <= 1e-9 * np.abs(b).max() * np.linalg.cond(sym) ** 0.5
 
 
+@pytest.mark.parametrize("n", [70, 300])
+def test_device_ldlt_tied_pivots(pkg, ob, ctx, n):
+    # runs of equal diagonal entries (the six gauge rows 1 + u of the LM system are such a run): Eigen takes the first POSITION
+    # among equals at every step, and positions move with the swaps; the O(n log n) pivot order of vx_ldlt.cu must reproduce it.
+    # A is diagonally dominant with well separated groups, so a different order among equals changes the answer beyond rounding
+    # only through the permutation bookkeeping (x comes back un-permuted) - which is exactly what is being checked.
+    rng = np.random.Generator(np.random.PCG64(1000 + n))
+    M = rng.normal(size=(n, n)) * 0.05
+    A = M @ M.T
+    levels = rng.choice([1.01, 3.0, 3.0, 7.5, 20.0], size=n)
+    levels[:6] = 1.01
+    A[np.arange(n), np.arange(n)] = levels            # exact ties, many per level, scattered positions
+    b = rng.normal(size=n)
+    want = ob.ldlt_solve(A, b)
+    got = pkg.ldlt_solve(ctx, A, b)
+    assert np.abs(got - want).max() <= 1e-11 * np.abs(want).max()
+    sym = np.tril(A) + np.tril(A, -1).T
+    assert np.abs(sym @ got - b).max() <= 1e-10 * np.abs(b).max()
+
+
 def test_ba_large_window_uses_device_solve(pkg, ob, ctx):
     # W = 64 -> 384 unknowns: vx_ba_lidar factorises on the device; same LM trace and poses as the oracle
     W, V = 64, 1500
