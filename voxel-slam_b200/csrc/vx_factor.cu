@@ -523,6 +523,56 @@ k_offdiag(const int32_t *__restrict__ seg_beg, const int32_t *__restrict__ seg_e
   block_reduce_store<36, DIAG_THREADS>(acc, sh, opart + 36 * (int64_t)s);
 }
 
+// The same for SPARSE tile lists (top-level GBA: W ~ 399, ~4 frames per voxel -> 1-2 pairs per tile, tens of thousands of
+// tiles): one WARP per segment, 8 segments per CTA, no shared memory or barrier; the shuffle tree is only as deep as the
+// segment is long (lanes past its end hold exact zeros, so the result equals the full tree's).  A CTA per 1-pair segment spent
+// its time being scheduled: 0.56 ms per evaluation at 82 k voxel-frames.
+__global__ void __launch_bounds__(256)
+k_offdiag_warp(const int32_t *__restrict__ seg_beg, const int32_t *__restrict__ seg_end, const int64_t *__restrict__ pair_ab,
+               const int32_t *__restrict__ vox, const double *__restrict__ cS, const double *__restrict__ G,
+               double *__restrict__ opart, int64_t V, int64_t head, int64_t end, int64_t n_seg) {
+  const int64_t s = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (s >= n_seg) return;
+  const int32_t beg = seg_beg[s], fin = seg_end[s];
+  double acc[36];
+#pragma unroll
+  for (int k = 0; k < 36; k++) acc[k] = 0.0;
+  for (int32_t x = beg + lane; x < fin; x += 32) {
+    const int64_t ab = pair_ab[x];
+    const int32_t a = (int32_t)(ab >> 32), b = (int32_t)(ab & 0xffffffff);
+    const int64_t v = vox[a];
+    if (v < head || v >= end) continue;
+    double ga[18], gb[18];
+    const double2 *pa = reinterpret_cast<const double2 *>(G + 18 * (int64_t)a);
+    const double2 *pb = reinterpret_cast<const double2 *>(G + 18 * (int64_t)b);
+#pragma unroll
+    for (int k = 0; k < 9; k++) { double2 t = pa[k]; ga[2 * k] = t.x; ga[2 * k + 1] = t.y; }
+#pragma unroll
+    for (int k = 0; k < 9; k++) { double2 t = pb[k]; gb[2 * k] = t.x; gb[2 * k + 1] = t.y; }
+    const double s1 = cS[v], s2 = cS[V + v], s3 = cS[2 * V + v];
+#pragma unroll
+    for (int cc = 0; cc < 6; cc++) {
+      const double x1 = s1 * gb[cc], x2 = s2 * gb[6 + cc], x3 = s3 * gb[12 + cc];
+#pragma unroll
+      for (int r = 0; r < 6; r++)
+        acc[cc * 6 + r] += fma(ga[r], x1, fma(ga[6 + r], x2, ga[12 + r] * x3));
+    }
+  }
+  const int len = fin - beg;
+  for (int o = 16; o > 0; o >>= 1) {
+    if (o < len) {                        // warp-uniform
+#pragma unroll
+      for (int k = 0; k < 36; k++) acc[k] += __shfl_down_sync(0xffffffffu, acc[k], o);
+    }
+  }
+  if (lane == 0) {
+    double2 *out = reinterpret_cast<double2 *>(opart + 36 * s);
+#pragma unroll
+    for (int k = 0; k < 18; k++) out[k] = make_double2(acc[2 * k], acc[2 * k + 1]);
+  }
+}
+
 // second pass: add segment partials of each frame in ascending order; write H(i,i) and JacT(i)
 __global__ void k_fin_diag(const int32_t *__restrict__ dseg_off, const double *__restrict__ dpart, double *__restrict__ H,
                            double *__restrict__ J, int W) {
@@ -641,9 +691,14 @@ static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, 
       VX_KERNEL(ctx, "k_fin_diag", k_fin_diag<<<f->F(), 64, 0, st>>>(f->dseg_off.as<int32_t>(), f->dpart.as<double>(), f->H.as<double>(), f->J.as<double>(), f->W));
     }
     if (f->n_oseg > 0) {
-      VX_KERNEL(ctx, "k_offdiag", k_offdiag<<<(int)f->n_oseg, DIAG_THREADS, 0, st>>>(
-          f->oseg_beg.as<int32_t>(), f->oseg_end.as<int32_t>(), f->pair_ab.as<int64_t>(), f->vox.as<int32_t>(),
-          f->cS.as<double>(), f->G.as<double>(), f->opart.as<double>(), f->V, head, end));
+      if (f->n_pairs < 32 * f->n_oseg)     // short segments on average: a warp each
+        VX_KERNEL(ctx, "k_offdiag_warp", k_offdiag_warp<<<blocks_for(f->n_oseg, 8), 256, 0, st>>>(
+            f->oseg_beg.as<int32_t>(), f->oseg_end.as<int32_t>(), f->pair_ab.as<int64_t>(), f->vox.as<int32_t>(),
+            f->cS.as<double>(), f->G.as<double>(), f->opart.as<double>(), f->V, head, end, f->n_oseg));
+      else
+        VX_KERNEL(ctx, "k_offdiag", k_offdiag<<<(int)f->n_oseg, DIAG_THREADS, 0, st>>>(
+            f->oseg_beg.as<int32_t>(), f->oseg_end.as<int32_t>(), f->pair_ab.as<int64_t>(), f->vox.as<int32_t>(),
+            f->cS.as<double>(), f->G.as<double>(), f->opart.as<double>(), f->V, head, end));
       VX_KERNEL(ctx, "k_fin_off", k_fin_off<<<(int)f->n_tiles, 64, 0, st>>>(f->tile_key.as<int64_t>(), f->oseg_off.as<int32_t>(), f->opart.as<double>(),
                                              f->H.as<double>(), f->W, f->F()));
     }
