@@ -72,8 +72,7 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
   double *D = x + n;                 // [n]
   double *Jg = D + n;                // [n]
   __shared__ int s_tr[LM_MAXN];
-  __shared__ double s_rv[NT / 32];
-  __shared__ int s_ri[NT / 32];
+  __shared__ double s_d[LM_MAXN];
   const int w = blockIdx.x, t = threadIdx.x, lane = t & 31, wp = t >> 5;
   if (!act[w]) return;
   const double u = u_w[w];
@@ -96,28 +95,34 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
     x[t] = -Jg[t];
   }
   __syncthreads();
-  for (int k = 0; k < n; k++) {
-    // pivot: first index of the largest |diagonal| in [k, n); comparisons with NaN are false, as on the host
-    {
+  // Pivot sequence up front.  The sweep is left-looking: when step k picks its pivot the diagonal entries at positions >= k
+  // still hold their input values (moved only by the earlier interchanges), so the whole sequence is a function of the input
+  // diagonal — one warp runs the host's selection (first index of the largest |diagonal| in (k, n) if it beats |A(k,k)|;
+  // comparisons with NaN are false) on a copy of the diagonal instead of two CTA barriers inside every column step.
+  if (t < n) s_d[t] = fabs(LM_AT(t, t));
+  __syncthreads();
+  if (wp == 0) {
+    for (int k = 0; k < n; k++) {
       double bv = -1.0; int bi = n;
-      if (t >= k && t < n) { const double v = fabs(LM_AT(t, t)); if (v == v) { bv = v; bi = t; } }
+      for (int i = k + 1 + lane; i < n; i += 32) { const double v = s_d[i]; if (v > bv) { bv = v; bi = i; } }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        const double ov = __shfl_down_sync(0xffffffffu, bv, o);
-        const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
         if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
       }
-      if (lane == 0) { s_rv[wp] = bv; s_ri[wp] = bi; }
-      __syncthreads();
-      if (t == 0) {
-        double v = s_rv[0]; int i = s_ri[0];
-        for (int q = 1; q < NT / 32; q++) if (s_rv[q] > v || (s_rv[q] == v && s_ri[q] < i)) { v = s_rv[q]; i = s_ri[q]; }
-        const double dk = fabs(LM_AT(k, k));
-        if (!(dk == dk) || i >= n) i = k;      // NaN on the diagonal at k: the host keeps k
-        s_tr[k] = i;
+      const double dk = s_d[k];
+      const int big = bv > dk ? bi : k;
+      __syncwarp();
+      if (lane == 0) {
+        s_tr[k] = big;
+        if (big != k) { s_d[k] = s_d[big]; s_d[big] = dk; }
       }
-      __syncthreads();
+      __syncwarp();
     }
+  }
+  __syncthreads();
+  for (int k = 0; k < n; k++) {
     const int big = s_tr[k];
     if (big != k) {   // symmetric interchange restricted to the lower triangle
       if (t < k) { const double a = LM_AT(k, t); LM_AT(k, t) = LM_AT(big, t); LM_AT(big, t) = a; }
@@ -129,16 +134,20 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
     if (k > 0) {
       if (t < k) tmp[t] = __dmul_rn(LM_AT(t, t), LM_AT(k, t));
       __syncthreads();
+      // only the running sum is a dependent chain: loads and products are independent, so the loops are unrolled and the host's
+      // "skip a zero tmp[j]" is a select, not a branch (a - 0 would turn a = -0 into +0)
       if (t == k) {
         double acc = 0.0;
+#pragma unroll 4
         for (int j = 0; j < k; j++) acc = __dadd_rn(acc, __dmul_rn(LM_AT(k, j), tmp[j]));
         LM_AT(k, k) = __dadd_rn(LM_AT(k, k), -acc);
       } else if (t > k && t < n) {
         double a = LM_AT(t, k);
+#pragma unroll 4
         for (int j = 0; j < k; j++) {
           const double tj = tmp[j];
-          if (tj == 0.0) continue;
-          a = __dadd_rn(a, -__dmul_rn(LM_AT(t, j), tj));
+          const double na = __dadd_rn(a, -__dmul_rn(LM_AT(t, j), tj));
+          a = tj == 0.0 ? a : na;
         }
         LM_AT(t, k) = a;
       }
@@ -164,6 +173,7 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
   if (t == 0) {
     for (int j = n - 1; j >= 0; j--) {
       double s = x[j];
+#pragma unroll 4
       for (int i = j + 1; i < n; i++) s = __dadd_rn(s, -__dmul_rn(LM_AT(i, j), x[i]));
       x[j] = s;
     }
