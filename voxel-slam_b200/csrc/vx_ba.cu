@@ -100,18 +100,24 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
   }
   __syncthreads();
   // the host's selection: first index of the largest |diagonal| in (k, n) if it beats |A(k,k)|; comparisons with NaN are false
+  // (keys: the bit pattern of a non-negative double orders like the value; +1 keeps 0 for "no candidate / NaN"; the warp maximum
+  // is three redux.sync — high word, low word among the high-word winners, then the smallest index among the winners)
   if (wp == 0) {
     for (int k = 0; k < n; k++) {
-      double bv = -1.0; int bi = n;
-      for (int i = k + 1 + lane; i < n; i += 32) { const double v = s_d[i]; if (v > bv) { bv = v; bi = i; } }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+      unsigned long long key = 0ull; int bi = n;
+      for (int i = k + 1 + lane; i < n; i += 32) {
+        const double v = s_d[i];
+        const unsigned long long kv = v == v ? (unsigned long long)__double_as_longlong(v) + 1ull : 0ull;
+        if (kv > key) { key = kv; bi = i; }
       }
+      const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+      const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+      const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+      const int best = (int)__reduce_min_sync(0xffffffffu, (hi == mhi && lo == mlo && key != 0ull) ? (unsigned)bi : (unsigned)n);
       const double dk = s_d[k];
-      const int big = bv > dk ? bi : k;
+      const unsigned long long kk = dk == dk ? (unsigned long long)__double_as_longlong(dk) + 1ull : ~0ull;   // NaN at k: keep k
+      const unsigned long long mk = ((unsigned long long)mhi << 32) | mlo;
+      const int big = (mk > kk && best < n) ? best : k;
       __syncwarp();
       if (lane == 0 && big != k) {
         s_d[k] = s_d[big]; s_d[big] = dk;
@@ -187,15 +193,20 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
     x[t] = fabs(LM_AT(t, t)) > tol ? x[t] / LM_AT(t, t) : 0.0;
   }
   __syncthreads();
-  if (t == 0) {
-    for (int j = n - 1; j >= 0; j--) {
-      double s = x[j];
+  // backward: x_j - sum_{i>j} L(i,j) x_i with i ascending is one dependent chain of n(n-1)/2 additions whatever is done; the
+  // products are not on it — as soon as x_i is final the rows above park L(i,j) x_i in the unused upper triangle (A(j,i)),
+  // and the chain of row i-1 only adds
+  for (int i = n - 1; i >= 1; i--) {
+    if (t < i) LM_AT(t, i) = __dmul_rn(LM_AT(i, t), x[i]);
+    __syncthreads();
+    if (t == 0) {
+      double s = x[i - 1];
 #pragma unroll 4
-      for (int i = j + 1; i < n; i++) s = __dadd_rn(s, -__dmul_rn(LM_AT(i, j), x[i]));
-      x[j] = s;
+      for (int ii = i; ii < n; ii++) s = __dadd_rn(s, -LM_AT(i - 1, ii));
+      x[i - 1] = s;
     }
+    __syncthreads();
   }
-  __syncthreads();
   if (t < n) wv[s_pos[t]] = x[t];        // back to input order
   __syncthreads();
   if (t == 0) {
