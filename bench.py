@@ -375,6 +375,19 @@ def extra_benches(pkg, ctx):
                                     "returns the 45.8 MB Hessian snapshot); vx_factor_hessian alone with the 45.8 MB Hess to the host; vx_ldlt_solve of "
                                     "the gauge-fixed damped system from a HOST matrix (H2D 45.8 MB + the same device solve), wall clock; ms_per_later_lm_iteration = "
                                     "(call with max_iter 3 - call with max_iter 1) / 2: pivot order + permutation + graph-replayed factorisation + substitutions + B2"}
+    # the reference's CPU path for the LM solve of that window: Eigen's unblocked diagonal-pivot LDL^T (oracle restatement, one
+    # thread as in the reference: voxel_map.hpp:457-458 runs on the optimizer's own thread), once; also the parity check
+    try:
+        import oracle_bind as ob
+        t0 = time.perf_counter()
+        xo = ob.ldlt_solve(At, bt)
+        t_cpu = time.perf_counter() - t0
+        out["top_level_gba"]["cpu_baseline"] = {"ms_ldlt_solve": 1e3 * t_cpu, "gflops": (n_t ** 3 / 3) / t_cpu / 1e9, "cores": 1, "kind": "port",
+                                                "device_vs_cpu_rel": float(np.abs(xs - xo).max() / max(np.abs(xo).max(), 1e-300)),
+                                                "sample": "one (Hess + u D).ldlt().solve(-JacT) of the same 2394-unknown system (the device "
+                                                          "iteration above also contains the B2 pass and the retraction)"}
+    except Exception as e:  # the CPU leg is a reported baseline only
+        out["top_level_gba"]["cpu_baseline"] = {"error": str(e)[:200]}
     ft.free()
     return out
 
