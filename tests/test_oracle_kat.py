@@ -163,3 +163,62 @@ def test_thread_split_matches_single_range(ob):
     H5, J5, r5 = f.divide_thread(poses, thd_num=5, use_threads=True)
     assert np.max(np.abs(H1 - H5)) < 1e-12 * np.max(np.abs(H1))
     assert abs(r1 - r5) < 1e-12 * abs(r1)
+
+
+def test_btc_plane_cloud_vs_numpy(ob):
+    # independent numpy restatement of BTC.cpp:279-334 / :90-143 on a small cloud: key rule (double quotient, -1 when negative,
+    # truncation), per-voxel mean / covariance / eigh, plane when N > init_num and lambda_min < thre, std::map key order
+    rng = np.random.Generator(np.random.PCG64(77))
+    n0 = np.array([0.3, -0.5, 0.81]); n0 /= np.linalg.norm(n0)
+    a = rng.uniform(-3.0, 3.0, size=(6000, 2))
+    e1 = np.cross(n0, [1.0, 0, 0]); e1 /= np.linalg.norm(e1); e2 = np.cross(n0, e1)
+    plane = a[:, :1] * e1 + a[:, 1:] * e2 + rng.normal(size=(6000, 1)) * 0.01 * n0
+    clutter = rng.uniform(4.0, 7.0, size=(3000, 3))            # dense non-planar voxels: must be rejected by the eigenvalue test
+    xyz = np.concatenate([plane, clutter]).astype(np.float32)
+    thre = float(np.float32(0.01))
+    out = ob.btc_plane_cloud(xyz, 1.0, thre, 10)
+    q = xyz.astype(np.float64) / 1.0
+    q[q < 0] -= 1.0
+    keys = np.trunc(q).astype(np.int64)
+    want = []
+    for key in sorted({tuple(k) for k in keys}):
+        m = np.all(keys == np.array(key), axis=1)
+        pts = xyz[m].astype(np.float64)
+        if pts.shape[0] <= 10:
+            continue
+        c = pts.mean(axis=0)
+        cov = pts.T @ pts / pts.shape[0] - np.outer(c, c)
+        w, U = np.linalg.eigh(cov)
+        if w[0] < thre:
+            want.append((c, U[:, 0], w[0], pts.shape[0]))
+    assert len(want) > 20 and out.shape[0] == len(want)
+    for row, (c, nrm, w0, cnt) in zip(out, want):
+        assert np.abs(row[:3] - c).max() < 1e-12 and int(row[9]) == cnt
+        assert abs(row[6] - w0) < 1e-12
+        if w0 < 1e-3:        # a clean plane voxel: the normal is well conditioned
+            assert min(np.abs(row[3:6] - nrm).max(), np.abs(row[3:6] + nrm).max()) < 1e-8
+    clean = out[out[:, 6] < 3e-4]
+    assert clean.shape[0] > 10 and np.all(np.abs(np.abs(clean[:, 3:6] @ n0) - 1.0) < 2e-2)   # planted normal recovered (border voxels hold few points)
+
+
+def test_icp_normal_recovers_planted_pose(ob):
+    # three orthogonal walls sampled on a jittered grid with exact normals; the source is the target moved by a known small
+    # transform: icp_normal must bring it back, converge within its 20 iterations and accept (eigenvalue gate on sum n n^T)
+    rng = np.random.Generator(np.random.PCG64(5))
+    g = np.stack(np.meshgrid(np.arange(0.0, 10.0, 0.5), np.arange(0.0, 10.0, 0.5), indexing="ij"), -1).reshape(-1, 2)
+    g = g + rng.uniform(-0.05, 0.05, size=g.shape)
+    z = np.zeros((g.shape[0], 1))
+    walls = [np.hstack([g, z]), np.hstack([g[:, :1], z, g[:, 1:]]), np.hstack([z, g])]
+    nrms = [np.tile([0, 0, 1.0], (g.shape[0], 1)), np.tile([0, 1.0, 0], (g.shape[0], 1)), np.tile([1.0, 0, 0], (g.shape[0], 1))]
+    tar = np.concatenate(walls).astype(np.float32); tn = np.concatenate(nrms).astype(np.float32)
+    Rt, pt = synth.random_poses(3, 1, rot_sigma=0.03, tra_sigma=0.15)
+    Rt, pt = Rt[0], pt[0]
+    src = ((tar.astype(np.float64) - pt) @ Rt).astype(np.float32)       # R^T (x - p): local frame of the source
+    sn = (tn.astype(np.float64) @ Rt).astype(np.float32)
+    out = ob.icp_normal(src, sn, tar, tn, (np.eye(3), np.zeros(3)), 0.1)
+    assert out["ok"] and out["is_converge"] == 1 and out["iters"] <= 20
+    assert out["match_nums"][-1] > 0.8 * src.shape[0]
+    assert np.abs(out["R"] - Rt).max() < 2e-3 and np.abs(out["p"] - pt).max() < 2e-2
+    # an empty target can never be accepted
+    bad = ob.icp_normal(src, sn, tar[:0], tn[:0], (np.eye(3), np.zeros(3)), 0.1)
+    assert not bad["ok"]
