@@ -290,7 +290,8 @@ constexpr int RES_THREADS = 128;
 
 // B2: one thread per voxel.  sig = fix + sum_i transform(cluster_i, pose_i) (tools.hpp:357-363),
 // eigen-solve of sig.P/N - vbar vbar^T (voxel_map.hpp:312), cache write-back (voxel_map.hpp:317-319).
-__global__ void __launch_bounds__(RES_THREADS)
+template <int MINB>
+__global__ void __launch_bounds__(RES_THREADS, MINB)
 k_residual(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const double *__restrict__ mom,
            const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ fix, const double *__restrict__ coe,
            const double *__restrict__ poses, double *__restrict__ lam, double *__restrict__ U, double *__restrict__ mrg,
@@ -616,10 +617,15 @@ __global__ void k_fin_off(const int64_t *__restrict__ tile_key, const int32_t *_
 static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   cudaStream_t st = ctx->stream;
   if (f->V > 0) {
-    VX_KERNEL(ctx, "k_residual", k_residual<<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>(
-        f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(),
-        f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(),
-        f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end));
+    static const int res_minb = [] { const char *e = std::getenv("VX_RES_MINB"); return e ? std::atoi(e) : 0; }();
+#define VX_RES_LAUNCH(MB) VX_KERNEL(ctx, "k_residual", k_residual<MB><<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>( \
+        f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(), \
+        f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), \
+        f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end))
+    if (res_minb >= 8) VX_RES_LAUNCH(8);
+    else if (res_minb >= 6) VX_RES_LAUNCH(6);
+    else VX_RES_LAUNCH(0);
+#undef VX_RES_LAUNCH
     f->prep_lo = std::max<int64_t>(head, 0); f->prep_hi = std::min<int64_t>(end, f->V);
   }
   VX_KERNEL(ctx, "k_cost", k_cost<false><<<f->n_win, 256, 0, st>>>(f->res_v.as<double>(), nullptr, f->wv_off.as<int32_t>(), f->cost_r.as<double>(), head, end));
