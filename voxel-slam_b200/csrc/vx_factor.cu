@@ -617,12 +617,13 @@ __global__ void k_fin_off(const int64_t *__restrict__ tile_key, const int32_t *_
 static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   cudaStream_t st = ctx->stream;
   if (f->V > 0) {
-    static const int res_minb = [] { const char *e = std::getenv("VX_RES_MINB"); return e ? std::atoi(e) : 0; }();
+    static const int res_minb = [] { const char *e = std::getenv("VX_RES_MINB"); return e ? std::atoi(e) : 6; }();   // 80 registers, 24 warps per SM: measured best
 #define VX_RES_LAUNCH(MB) VX_KERNEL(ctx, "k_residual", k_residual<MB><<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>( \
         f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(), \
         f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), \
         f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end))
     if (res_minb >= 8) VX_RES_LAUNCH(8);
+    else if (res_minb >= 7) VX_RES_LAUNCH(7);
     else if (res_minb >= 6) VX_RES_LAUNCH(6);
     else VX_RES_LAUNCH(0);
 #undef VX_RES_LAUNCH
