@@ -196,13 +196,13 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
   // backward: x_j - sum_{i>j} L(i,j) x_i with i ascending is one dependent chain of n(n-1)/2 additions whatever is done; the
   // products are not on it — as soon as x_i is final the rows above park L(i,j) x_i in the unused upper triangle (A(j,i)),
   // and the chain of row i-1 only adds
+  // (one barrier per row: the chain of row i-1 forms its newest term L(i,i-1) x_i itself while the other threads park theirs)
   for (int i = n - 1; i >= 1; i--) {
-    if (t < i) LM_AT(t, i) = __dmul_rn(LM_AT(i, t), x[i]);
-    __syncthreads();
+    if (t >= 1 && t <= i - 1) LM_AT(t - 1, i) = __dmul_rn(LM_AT(i, t - 1), x[i]);      // rows 0 .. i-2, by threads 1 .. i-1
     if (t == 0) {
-      double s = x[i - 1];
+      double s = __dadd_rn(x[i - 1], -__dmul_rn(LM_AT(i, i - 1), x[i]));
 #pragma unroll 4
-      for (int ii = i; ii < n; ii++) s = __dadd_rn(s, -LM_AT(i - 1, ii));
+      for (int ii = i + 1; ii < n; ii++) s = __dadd_rn(s, -LM_AT(i - 1, ii));
       x[i - 1] = s;
     }
     __syncthreads();
