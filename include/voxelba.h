@@ -30,8 +30,10 @@ extern "C" {
 #define VX_ERR_TOO_FEW (-3)   /* reference: printf("Too Less Voxel"); exit(0)   voxel_map.hpp:399-403 */
 #define VX_ERR_OPT_STATE (-4) /* reference: printf("Error: opt_state"); exit(0)  voxel_map.hpp:1488-1492 */
 #define VX_ERR_NOMEM (-5)
+#define VX_ERR_NCCL (-6)      /* NCCL missing or a collective failed (multi-GPU entry points only) */
 
 typedef struct vx_ctx vx_ctx;       /* one per host thread: device, stream, scratch */
+typedef struct vx_comm vx_comm;     /* one per (process, GPU): NCCL communicator over the GPUs that share a problem */
 typedef struct vx_factor vx_factor; /* class LidarFactor (a.k.a. VOX_HESS), voxel_map.hpp:124-339 */
 
 /* class PointCluster {Matrix3d P; Vector3d v; int N;}  tools.hpp:304-310 (104 bytes, 8-aligned) */
@@ -183,6 +185,38 @@ int vx_gba_point_owner(vx_ctx *ctx, const float *d_xyz, const int32_t *d_frame, 
 int vx_gba_build_device(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
                         const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
 
+/* ---- multi-GPU: one process per GPU, NCCL over NVLink / NVSwitch ------------------------------------------
+ * The reference parallelises acc_evaluate2 / evaluate_only_residual over host threads and adds the per-thread partial
+ * Hess / JacT / residual (voxel_map.hpp:373-386); across GPUs the same sum is ONE all-reduce of
+ * [lower triangle of Hess | 15 W upper entries of the diagonal blocks | JacT | cost] per evaluation.  Voxelization across GPUs
+ * is one exchange: each point goes to the rank that owns its ROOT voxel (vx_gba_build_sharded).
+ * Bootstrap: rank 0 calls vx_comm_unique_id and hands the 128 bytes to the other ranks by whatever the host program has
+ * (MPI_Bcast, a file, torch.distributed's store); every rank then calls vx_comm_create on its own context.  NCCL is bound at
+ * run time (libnccl.so.2), so single-GPU use needs no NCCL at all. */
+#define VX_COMM_ID_BYTES 128
+int vx_comm_unique_id(void *id128);                                               /* ncclGetUniqueId */
+int vx_comm_create(vx_ctx *ctx, const void *id128, int rank, int n_ranks, vx_comm **out);   /* ncclCommInitRank; n_ranks == 1 needs no id */
+int vx_comm_free(vx_comm *comm);
+int vx_comm_rank(const vx_comm *comm);
+int vx_comm_size(const vx_comm *comm);
+int vx_comm_nccl_version(void);                                                   /* 0 when NCCL is unavailable */
+int vx_comm_allreduce_f64(vx_comm *comm, void *d_buf, int64_t n);                 /* in-place SUM of n device doubles, async on the ctx stream */
+/* bytes all-reduced / exchanged point-to-point and collectives issued on this communicator so far (bench.py reports them) */
+int vx_comm_stats(const vx_comm *comm, int64_t *bytes_allreduced, int64_t *bytes_exchanged, int64_t *n_collectives);
+
+/* OctreeGBA::cut_voxel + OctreeGBA_multi_recut (loop_refine.hpp:446-537) with the ROOT voxels partitioned over the ranks:
+ * xyz / cloud_off describe THIS rank's clouds (host), cloud c being the points of global frame cloud_frame[c] (one frame per
+ * cloud); poses holds ALL F = n_windows * W frames of `f` on every rank.  Each point is keyed at its pose, routed to
+ * owner = mix64(packed root key) mod n_ranks by a stable bucket partition + one grouped ncclSend/ncclRecv round (16 B/point),
+ * and the receiver builds the LidarFactor of the root voxels it owns: per (leaf, frame) moments are bitwise the single-GPU
+ * ones; Hess / JacT / cost of the whole problem are sums over ranks (vx_ba_lidar_sharded).  *n_points_owned: points received. */
+int vx_gba_build_sharded(vx_ctx *ctx, vx_comm *comm, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *cloud_frame,
+                         const vx_pose *poses, const vx_gba_params *params, vx_factor *f, int64_t *n_points_owned);
+/* vx_ba_lidar on a factor whose voxels are sharded over the ranks (voxel_map.hpp:422-497 with the thread sum :382-384 taken
+ * across GPUs): every rank passes the same poses and gets the same result; the LM solve is replicated. */
+int vx_ba_lidar_sharded(vx_ctx *ctx, vx_comm *comm, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
+                        int *converged, int *accept_trace, int *n_iters);
+
 /* ---- B3: Lidar_BA_Optimizer::damping_iter(x_stats, voxhess, hess*, resis, max_iter, is_display)
  * voxel_map.hpp:422-497.  Levenberg-Marquardt on 6W unknowns per window: u=0.01, v=2 (:427), *hess
  * snapshot before the gauge fix (:446), pose 0 fixed (:452-455), (Hess + u*diag(Hess)).ldlt().solve(-JacT)
@@ -323,6 +357,47 @@ int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int
 int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
                         const int32_t *frame_mp, const vx_pose *poses, int W, int n_windows, double voxel_size, vx_point48 *out,
                         int64_t out_cap, int64_t *win_off);
+
+/* ---- C2h: the bottom-up schedule of VOXEL_SLAM::thd_globalmapping (voxelslam.cpp:3018-3141) --------------------------------
+ * Keyframes arrive session by session; a bottom window opens every `mgsize` keyframes and holds `wdsize` of them (:3033-3034,
+ * :3076-3082, :3135-3138).  When a session ends (:3127-3133) or the global pass fires (:3054-3058) the keyframes still in the
+ * local queue (mgsize .. wdsize-1 of them) form one more, shorter window.  session_sizes: keyframes per session.
+ * Outputs (cap entries each): window w covers keyframes [win_start[w], win_start[w] + win_size[w]) of session win_session[w]
+ * (win_start counts inside the session). */
+int vx_hba_schedule(const int32_t *session_sizes, int n_sessions, int wdsize, int mgsize, int32_t *win_session, int32_t *win_start,
+                    int32_t *win_size, int cap, int32_t *n_windows);
+
+/* The whole hierarchical global BA of thd_globalmapping for stored sessions, bottom level + top level (voxelslam.cpp:3084-3127):
+ *   bottom  every window of the schedule through HBA_add_edge(xs = Keyframe::x0, max_iter = bottom_max_iter (1), thread_num = 2,
+ *           plptr) -> edges `edges1` (gba_edges1) and one submap per window: pose Keyframe::x0 of its first keyframe, id / mp of
+ *           that keyframe, cloud = the window's keyframe clouds merged with the optimized poses, down-sampled at voxel_size / 8
+ *           (:3094-3099, :2954-2985)
+ *   top     HBA_add_edge over all submaps whose session is in cnct_map (:2836-2857) with xs = kf_x of the submap's keyframe
+ *           (multimap_scanPoses[mp][id]->x, :3110), max_iter = total_max_iter, thread_num = 5 -> edges `edges2` (gba_edges2)
+ * With a communicator the bottom windows are block-distributed over the ranks (independent problems, no collective; edges are
+ * gathered), the submap clouds stay on the GPU that made them, and the top level is voxel-sharded: points exchanged by
+ * root-voxel owner at every outer iteration, [Hess | JacT | cost] all-reduced per evaluation, LM solve replicated.
+ * Every rank passes the SAME host inputs and receives the SAME outputs.
+ *   xyz / cloud_off     all keyframe clouds (local frame, float triples), n_kf + 1 offsets
+ *   kf_session          session (Keyframe::mp) of every keyframe, ascending; kf_id: Keyframe::id
+ *   kf_x0 / kf_x        Keyframe::x0 and the current scan pose of the keyframe's id (kf_x == NULL: x0)
+ *   edges1 / edges2     capacity cap1 / cap2 edges; *n1 / *n2 written
+ *   top_poses / top_kf  optimized pose and first keyframe of every top-level frame (n_top written; capacity = number of windows)
+ *   stats (16 doubles, may be NULL): [0] windows, [1] top-level frames, [2] voxel-frames through acc_evaluate2 in all LM passes
+ *           (this rank), [3..8] ms upload / bottom / merge / gather / top / total, [9] points in the top-level map,
+ *           [10] bottom voxel-frame evaluations, [11] top voxel-frame evaluations (this rank) */
+typedef struct vx_hba_global_params {
+  vx_hba_params hba;
+  int32_t wdsize, mgsize;            /* 10, 5     voxelslam.cpp:3033-3034 */
+  int32_t bottom_max_iter;           /* 1         :3096 */
+  int32_t bottom_thread_num;         /* 2         :3096 */
+  int32_t total_max_iter;            /* GBA/total_max_iter :3025 */
+  int32_t top_thread_num;            /* 5         :3035 */
+} vx_hba_global_params;
+int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const int64_t *cloud_off, int n_kf, const int32_t *kf_session,
+                  const int32_t *kf_id, const vx_pose *kf_x0, const vx_pose *kf_x, const int32_t *cnct_map, int n_cnct,
+                  const vx_hba_global_params *prm, vx_pgo_edge *edges1, int64_t cap1, int64_t *n1, vx_pgo_edge *edges2, int64_t cap2,
+                  int64_t *n2, vx_pose *top_poses, int32_t *top_kf, int32_t *n_top, double *stats);
 
 /* ---- D1 / D2: LIO ESIKF point-to-plane update -----------------------------------------------------------
  * The voxel map as OctoTree::match reads it (voxel_map.hpp:1649-1721), flattened by the caller: one record per

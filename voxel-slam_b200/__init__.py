@@ -24,7 +24,7 @@ point48_dtype = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("_p0", "<f4
 assert gba_params_dtype.itemsize == 56 and point48_dtype.itemsize == 48
 
 VX_OK = 0
-ERR_NAMES = {-1: "VX_ERR_CUDA", -2: "VX_ERR_ARG", -3: "VX_ERR_TOO_FEW", -4: "VX_ERR_OPT_STATE", -5: "VX_ERR_NOMEM"}
+ERR_NAMES = {-1: "VX_ERR_CUDA", -2: "VX_ERR_ARG", -3: "VX_ERR_TOO_FEW", -4: "VX_ERR_OPT_STATE", -5: "VX_ERR_NOMEM", -6: "VX_ERR_NCCL"}
 
 
 class VxError(RuntimeError):
@@ -210,6 +210,116 @@ def hba_merge_clouds(ctx, clouds, poses, W, n_windows, voxel_size, frame_cloud=N
                                      C.c_double(voxel_size), _p(out), C.c_int64(cap), _p(wo)))
     return [out[wo[b]:wo[b + 1]].copy() for b in range(n_windows)]
 
+
+
+# ---- multi-GPU (vx_comm_*) and the two-level hierarchical GBA ----------------------------------------------------------------
+hba_global_params_dtype = np.dtype([("hba", hba_params_dtype), ("wdsize", "<i4"), ("mgsize", "<i4"), ("bottom_max_iter", "<i4"),
+                                    ("bottom_thread_num", "<i4"), ("total_max_iter", "<i4"), ("top_thread_num", "<i4")])
+assert hba_global_params_dtype.itemsize == 104 + 24
+
+
+def comm_unique_id():
+    """128-byte NCCL id (rank 0 creates it, the other ranks receive it through the host program's own channel)."""
+    buf = np.zeros(128, dtype=np.uint8)
+    _chk(load_library().vx_comm_unique_id(_p(buf)))
+    return buf
+
+
+class Comm:
+    """vx_comm: NCCL communicator of the library, one per (process, GPU)."""
+
+    def __init__(self, ctx, uid, rank, world):
+        self.ctx = ctx
+        h = C.c_void_p()
+        uid = None if uid is None else np.ascontiguousarray(uid, dtype=np.uint8)
+        _chk(ctx.lib.vx_comm_create(ctx.h, _p(uid), C.c_int(rank), C.c_int(world), C.byref(h)))
+        self.h = h
+        self.rank, self.world = rank, world
+
+    @classmethod
+    def from_torch(cls, ctx, group=None):
+        """Bootstrap over an initialised torch.distributed process group (any backend): rank 0's id is broadcast."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        obj = [comm_unique_id().tobytes() if rank == 0 else None]
+        if world > 1:
+            dist.broadcast_object_list(obj, src=0, group=group)
+        return cls(ctx, np.frombuffer(obj[0], dtype=np.uint8), rank, world)
+
+    def stats(self):
+        a, b, c = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+        _chk(self.ctx.lib.vx_comm_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"bytes_allreduced": a.value, "bytes_exchanged": b.value, "collectives": c.value}
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.vx_comm_free(self.h)
+            self.h = None
+
+
+def hba_schedule(session_sizes, wdsize=10, mgsize=5):
+    """vx_hba_schedule: the bottom windows of thd_globalmapping -> (session, start, size) int32 arrays."""
+    ss = np.ascontiguousarray(session_sizes, dtype=np.int32)
+    n = C.c_int32(0)
+    lib = load_library()
+    _chk(lib.vx_hba_schedule(_p(ss), C.c_int(ss.size), C.c_int(wdsize), C.c_int(mgsize), None, None, None, C.c_int(0), C.byref(n)))
+    a = np.zeros(n.value, dtype=np.int32); b = np.zeros(n.value, dtype=np.int32); c = np.zeros(n.value, dtype=np.int32)
+    _chk(lib.vx_hba_schedule(_p(ss), C.c_int(ss.size), C.c_int(wdsize), C.c_int(mgsize), _p(a), _p(b), _p(c), C.c_int(n.value), C.byref(n)))
+    return a, b, c
+
+
+def hba_global_params(local, gba, max_layer, total_max_iter=1, wdsize=10, mgsize=5, bottom_max_iter=1, bottom_thread_num=2, top_thread_num=5):
+    prm = np.zeros(1, dtype=hba_global_params_dtype)
+    h = prm["hba"]
+    h["gba"]["voxel_size"] = gba[0]; h["gba"]["min_eigen_value"] = gba[1]; h["gba"]["eigen_value_array"] = gba[2]; h["gba"]["max_layer"] = max_layer
+    h["voxel_size"] = local[0]; h["min_eigen_value"] = local[1]; h["plane_eigen_value_thre"] = local[2]
+    prm["wdsize"] = wdsize; prm["mgsize"] = mgsize; prm["bottom_max_iter"] = bottom_max_iter; prm["bottom_thread_num"] = bottom_thread_num
+    prm["total_max_iter"] = total_max_iter; prm["top_thread_num"] = top_thread_num
+    return prm
+
+
+class HbaGlobalJob:
+    """Host buffers of one vx_hba_global call, prepared once (bench.py times run() only)."""
+
+    def __init__(self, xyz, off, kf_session, kf_x0, prm, kf_x=None, kf_id=None, cnct_map=None):
+        self.xyz = xyz if (isinstance(xyz, np.ndarray) and xyz.dtype == np.float32 and xyz.flags.c_contiguous) else np.ascontiguousarray(xyz, dtype=np.float32)
+        self.off = np.ascontiguousarray(off, dtype=np.int64)
+        self.n_kf = self.off.size - 1
+        self.sess = np.ascontiguousarray(kf_session, dtype=np.int32)
+        self.x0 = as_poses(kf_x0)
+        self.x = None if kf_x is None else as_poses(kf_x)
+        self.ids = None if kf_id is None else np.ascontiguousarray(kf_id, dtype=np.int32)
+        self.cnct = None if cnct_map is None else np.ascontiguousarray(cnct_map, dtype=np.int32)
+        self.prm = prm
+        sizes = np.bincount(self.sess)
+        ws, wst, wsz = hba_schedule(sizes, int(prm["wdsize"][0]), int(prm["mgsize"][0]))
+        self.n_windows = ws.size
+        wd = int(prm["wdsize"][0])
+        self.cap1 = self.n_windows * wd * (wd - 1) // 2
+        self.cap2 = self.n_windows * (self.n_windows - 1) // 2
+        self.e1 = np.zeros(max(self.cap1, 1), dtype=edge_dtype); self.e2 = np.zeros(max(self.cap2, 1), dtype=edge_dtype)
+        self.tp = np.zeros(self.n_windows, dtype=pose_dtype); self.tk = np.zeros(self.n_windows, dtype=np.int32)
+        self.stats = np.zeros(16)
+
+    def run(self, ctx, comm=None):
+        n1, n2, nt = C.c_int64(0), C.c_int64(0), C.c_int32(0)
+        _chk(ctx.lib.vx_hba_global(ctx.h, comm.h if comm is not None else None, _p(self.xyz), _p(self.off), C.c_int(self.n_kf), _p(self.sess), _p(self.ids),
+                                   _p(self.x0), _p(self.x), _p(self.cnct), C.c_int(0 if self.cnct is None else self.cnct.size), _p(self.prm),
+                                   _p(self.e1), C.c_int64(self.cap1), C.byref(n1), _p(self.e2), C.c_int64(self.cap2), C.byref(n2), _p(self.tp), _p(self.tk),
+                                   C.byref(nt), _p(self.stats)))
+        st = self.stats
+        return dict(edges1=self.e1[:n1.value], edges2=self.e2[:n2.value], top_poses=self.tp[:nt.value], top_kf=self.tk[:nt.value],
+                    stats=dict(windows=int(st[0]), top_frames=int(st[1]), voxel_frame_evals=int(st[2]), ms_upload=st[3], ms_bottom=st[4], ms_merge=st[5],
+                               ms_gather=st[6], ms_top=st[7], ms_total=st[8], top_points=int(st[9]), vf_evals_bottom=int(st[10]), vf_evals_top=int(st[11])))
+
+
+def hba_global(ctx, clouds, kf_session, kf_x0, local, gba, max_layer, total_max_iter=1, kf_x=None, kf_id=None, cnct_map=None, comm=None, **kw):
+    """vx_hba_global: bottom windows -> submaps -> top-level HBA_add_edge (voxelslam.cpp:3018-3141)."""
+    xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32)
+    off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+    job = HbaGlobalJob(xyz, off, kf_session, kf_x0, hba_global_params(local, gba, max_layer, total_max_iter, **kw), kf_x, kf_id, cnct_map)
+    return job.run(ctx, comm)
 
 map_node_dtype = np.dtype([("center", "<f8", (3,)), ("quater_length", "<f4"), ("octo_state", "<i4"), ("child", "<i4", (8,)), ("is_plane", "<i4"),
                            ("radius", "<f4"), ("p_center", "<f8", (3,)), ("p_normal", "<f8", (3,)), ("plane_var", "<f8", (36,))])
@@ -633,6 +743,27 @@ class Factor:
         return dict(states=x, imus=pr, hess=hess.T.copy(), resis=resis, accept=trace[:nit[0]].tolist())
 
     # device-resident path
+    def gba_build_sharded(self, comm, clouds, cloud_frame, poses, voxel_size, min_eigen_value, eig_array, max_layer):
+        """vx_gba_build_sharded: this rank's clouds (cloud c = frame cloud_frame[c]); poses = ALL frames.  -> points owned."""
+        xyz = np.ascontiguousarray(np.concatenate(clouds), dtype=np.float32) if len(clouds) else np.zeros((0, 3), dtype=np.float32)
+        off = np.zeros(len(clouds) + 1, dtype=np.int64); off[1:] = np.cumsum([c.shape[0] for c in clouds])
+        cf = np.ascontiguousarray(cloud_frame, dtype=np.int32)
+        prm = np.zeros(1, dtype=gba_params_dtype)
+        prm["voxel_size"] = voxel_size; prm["min_eigen_value"] = min_eigen_value; prm["eigen_value_array"] = eig_array; prm["max_layer"] = max_layer
+        ps = as_poses(poses)
+        n = C.c_int64(0)
+        _chk(self.lib.vx_gba_build_sharded(self.ctx.h, comm.h, _p(xyz), _p(off), C.c_int(len(clouds)), _p(cf), _p(ps), _p(prm), self.h, C.byref(n)))
+        return n.value
+
+    def ba_lidar_sharded(self, comm, poses, max_iter=3, thd_num=2):
+        ps = as_poses(poses).copy()
+        NW, W = self.n_win, self.W
+        jl = 6 * W
+        hess = np.zeros((NW, jl, jl)); resis = np.zeros((NW, 2)); conv = np.zeros(NW, dtype=np.int32)
+        tr = np.full((NW, max(max_iter, 1)), -1, dtype=np.int32); it = np.zeros(NW, dtype=np.int32)
+        _chk(self.lib.vx_ba_lidar_sharded(self.ctx.h, comm.h, self.h, _p(ps), _p(hess), _p(resis), C.c_int(max_iter), C.c_int(thd_num), _p(conv), _p(tr), _p(it)))
+        return dict(poses=ps, hess=np.transpose(hess, (0, 2, 1)), resis=resis, converged=conv, accept=[tr[w, :it[w]].tolist() for w in range(NW)], iters=it)
+
     def set_poses(self, poses):
         self._poses_keep = as_poses(poses)
         _chk(self.lib.vx_factor_set_poses(self.ctx.h, self.h, _p(self._poses_keep)))

@@ -7,6 +7,7 @@
 // windows, voxelslam.cpp:3096): every window keeps its own damping state (u, v), accept/reject
 // sequence and stop test, and each device pass evaluates all windows at once.
 #include "vx_factor.cuh"
+#include "vx_comm.cuh"
 #include "vx_hostmat.hpp"
 #include <cmath>
 #include <limits>
@@ -219,18 +220,79 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
 #undef LM_AT
 }
 
+// ---- voxel-sharded evaluation: [lower triangle of Hess | JacT | cost] of every window, packed for ONE all-reduce ------------
+// (the reference adds its per-thread partial Hess / JacT / residual the same way, voxel_map.hpp:382-384).  Hess is symmetric
+// block-wise (acc_evaluate2 mirrors the upper blocks, :279-281) except for the antisymmetric -0.5*hat(jjt) term inside the
+// diagonal blocks (:242), so the lower triangle alone is not the matrix: the strict upper part of each 6x6 DIAGONAL block
+// travels too (15 numbers per frame).  Packed length per window: n(n+1)/2 + 15 W + n + 1.
+__device__ __forceinline__ int64_t tri_col_start(int64_t c, int64_t n) { return c * n - c * (c - 1) / 2; }   // packed lower triangle, column-major
+__global__ void k_pack_eval(const double *__restrict__ H, const double *__restrict__ J, const double *__restrict__ cost, int n, int64_t plen,
+                            double *__restrict__ pack) {
+  const int w = blockIdx.y;
+  const double *Hw = H + (size_t)n * n * w;
+  double *pw = pack + plen * w;
+  const int64_t ntri = (int64_t)n * (n + 1) / 2;
+  const int c = blockIdx.x;                       // one CTA per column
+  if (c < n) {
+    const int64_t cs = tri_col_start(c, n);
+    for (int r = c + threadIdx.x; r < n; r += blockDim.x) pw[cs + (r - c)] = Hw[(size_t)c * n + r];
+    // strict upper part of the diagonal 6x6 block: rows 6i .. c-1 of column c
+    const int i = c / 6, cc = c % 6;
+    if ((int)threadIdx.x < cc) pw[ntri + 15 * i + cc * (cc - 1) / 2 + threadIdx.x] = Hw[(size_t)c * n + 6 * i + threadIdx.x];
+    if (threadIdx.x == 0) pw[ntri + 15 * (n / 6) + c] = J[(size_t)n * w + c];
+    if (c == 0 && threadIdx.x == 0) pw[ntri + 15 * (n / 6) + n] = cost[w];
+  }
+}
+__global__ void k_unpack_eval(const double *__restrict__ pack, int n, int64_t plen, double *__restrict__ H, double *__restrict__ J, double *__restrict__ cost) {
+  const int w = blockIdx.y;
+  double *Hw = H + (size_t)n * n * w;
+  const double *pw = pack + plen * w;
+  const int64_t ntri = (int64_t)n * (n + 1) / 2;
+  const int c = blockIdx.x;
+  if (c < n) {
+    const int64_t cs = tri_col_start(c, n);
+    const int dlim = 6 * (c / 6) + 6;               // rows below the diagonal block are mirrored into the upper triangle
+    for (int r = c + threadIdx.x; r < n; r += blockDim.x) {
+      const double v = pw[cs + (r - c)];
+      Hw[(size_t)c * n + r] = v;
+      if (r >= dlim) Hw[(size_t)r * n + c] = v;
+    }
+    const int i = c / 6, cc = c % 6;
+    if ((int)threadIdx.x < cc) Hw[(size_t)c * n + 6 * i + threadIdx.x] = pw[ntri + 15 * i + cc * (cc - 1) / 2 + threadIdx.x];
+    if (threadIdx.x == 0) J[(size_t)n * w + c] = pw[ntri + 15 * (n / 6) + c];
+    if (c == 0 && threadIdx.x == 0) cost[w] = pw[ntri + 15 * (n / 6) + n];
+  }
+}
+
 }  // namespace
 
 namespace vx {
+// Sum of the evaluation a voxel-sharded factor just produced (f->H, f->J, f->cost_h) over the ranks of `comm`, in place.
+int allreduce_evaluation(vx_ctx *ctx, vx_comm *comm, vx_factor *f) {
+  if (!comm || comm->size == 1) return VX_OK;
+  const int n = 6 * f->W, NW = f->n_win;
+  const int64_t plen = (int64_t)n * (n + 1) / 2 + 15 * f->W + n + 1;
+  VX_TRY(comm->pack.reserve(sizeof(double) * (size_t)plen * NW));
+  cudaStream_t st = ctx->stream;
+  VX_KERNEL(ctx, "k_pack_eval", k_pack_eval<<<dim3(n, NW), 128, 0, st>>>(f->H.as<double>(), f->J.as<double>(), f->cost_h.as<double>(), n, plen, comm->pack.as<double>()));
+  VX_TRY(comm_allreduce_f64(comm, comm->pack.as<double>(), plen * NW));
+  VX_KERNEL(ctx, "k_unpack_eval", k_unpack_eval<<<dim3(n, NW), 128, 0, st>>>(comm->pack.as<double>(), n, plen, f->H.as<double>(), f->J.as<double>(), f->cost_h.as<double>()));
+  return VX_OK;
+}
+
 int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b, double *x);   // vx_ldlt.cu
 int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1);   // vx_ldlt.cu
 // win_status (optional, n_windows): when given, a window with fewer voxels than thd_num is flagged
 // VX_ERR_TOO_FEW and left untouched instead of failing the whole batch.
+// comm (optional): the factor holds only this rank's voxels of every window; Hess / JacT / cost are all-reduced after each
+// evaluation, the LM step is replicated (every rank sees bitwise the same sums, so every rank takes the same decisions).
 int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
-                  int *converged, int *accept_trace, int *n_iters, int *win_status) {
+                  int *converged, int *accept_trace, int *n_iters, int *win_status, vx_comm *comm) {
   VX_ARG(f != nullptr && poses != nullptr && max_iter >= 0);
   VX_TRY(bind(ctx));
   const int W = f->W, NW = f->n_win, jl = 6 * W, F = W * NW;
+  const bool sharded = comm != nullptr && comm->size > 1;
+  int64_t Vglobal = f->V;
   std::vector<char> few;
   // Lidar_BA_Optimizer::only_residual exits the process when a problem has fewer voxels than threads
   // (voxel_map.hpp:399-403); the drop-in reports it instead.
@@ -238,11 +300,22 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
     std::vector<int32_t> wv(NW + 1);
     VX_CUDA(cudaMemcpyAsync(wv.data(), f->wv_off.p, sizeof(int32_t) * (NW + 1), cudaMemcpyDeviceToHost, ctx->stream));
     VX_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::vector<int64_t> nv(NW + 1);
+    for (int w = 0; w < NW; w++) nv[w] = f->V > 0 ? wv[w + 1] - wv[w] : 0;
+    nv[NW] = f->V;
+    if (sharded) {   // voxel counts of the whole problem
+      VX_TRY(comm->counts.reserve(8 * (size_t)(NW + 1)));
+      VX_CUDA(cudaMemcpyAsync(comm->counts.p, nv.data(), 8 * (size_t)(NW + 1), cudaMemcpyHostToDevice, ctx->stream));
+      VX_TRY(comm_allreduce_i64(comm, comm->counts.as<int64_t>(), NW + 1));
+      VX_CUDA(cudaMemcpyAsync(nv.data(), comm->counts.p, 8 * (size_t)(NW + 1), cudaMemcpyDeviceToHost, ctx->stream));
+      VX_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    Vglobal = nv[NW];
     few.assign(NW, 0);
     for (int w = 0; w < NW; w++) {
       if (win_status) win_status[w] = VX_OK;
-      if (wv[w + 1] - wv[w] < thd_num) {
-        if (!win_status) { set_error("Too Less Voxel: window %d has %d voxels < thd_num %d", w, wv[w + 1] - wv[w], thd_num); return VX_ERR_TOO_FEW; }
+      if (nv[w] < thd_num) {
+        if (!win_status) { set_error("Too Less Voxel: window %d has %lld voxels < thd_num %d", w, (long long)nv[w], thd_num); return VX_ERR_TOO_FEW; }
         win_status[w] = VX_ERR_TOO_FEW; few[w] = 1;
       }
     }
@@ -253,7 +326,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   // ldlt_device_min unknowns on (top-level GBA); Hess and JacT never leave the device.  In between (129...383 unknowns) and
   // under VX_LM_HOST the host sweep.
   const bool small = jl <= LM_MAXN;
-  const bool dev = (small || jl >= ldlt_device_min) && f->V > 0 && f->nnz > 0 && getenv("VX_LM_HOST") == nullptr;
+  const bool dev = (small || jl >= ldlt_device_min || sharded) && Vglobal > 0 && (sharded || f->nnz > 0) && getenv("VX_LM_HOST") == nullptr;
   const bool host_mats = !dev;
   std::vector<double> Hess(host_mats ? hsz * NW : 0), JacT(host_mats ? (size_t)jl * NW : 0), Hnew(Hess.size()), Jnew(JacT.size()), r_new(NW), r1(NW, 0.0), r2(NW, 0.0);
   std::vector<double> u(NW, 0.01), v(NW, 2.0), A(host_mats ? hsz : 0), dxi(jl), D(jl), nb(jl), tmp, q1s(NW, 0.0);
@@ -286,6 +359,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
     if (any_calc && dev) {
       VX_TRY(vx_factor_set_poses(ctx, f, x.data()));
       VX_TRY(vx_factor_hessian_async(ctx, f, 0, -1));
+      VX_TRY(allreduce_evaluation(ctx, comm, f));
       for (int w = 0; w < NW; w++) mask[w] = active[w] && calc[w];
       VX_CUDA(cudaMemcpyAsync(f->lm_mask.p, mask.data(), sizeof(int32_t) * NW, cudaMemcpyHostToDevice, st));
       VX_KERNEL(ctx, "k_lm_keep", k_lm_keep<<<dim3(NW, (unsigned)std::max<size_t>(1, std::min<size_t>(hsz / 4096, 1024))), 256, 0, st>>>(f->H.as<double>(), f->J.as<double>(), f->lm_H.as<double>(), f->lm_J.as<double>(),
@@ -355,7 +429,15 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
         for (int k = 0; k < 3; k++) d.p[k] = s.p[k] + dxw[6 * j + 3 + k];
       }
     }
-    VX_TRY(vx_factor_residual(ctx, f, xt.data(), 0, -1, r_new.data()));
+    if (sharded) {
+      VX_TRY(vx_factor_set_poses(ctx, f, xt.data()));
+      VX_TRY(vx_factor_residual_async(ctx, f, 0, -1));
+      VX_TRY(comm_allreduce_f64(comm, f->cost_r.as<double>(), NW));
+      VX_CUDA(cudaMemcpyAsync(r_new.data(), f->cost_r.p, sizeof(double) * NW, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+    } else {
+      VX_TRY(vx_factor_residual(ctx, f, xt.data(), 0, -1, r_new.data()));
+    }
     for (int w = 0; w < NW; w++) {
       if (!active[w]) continue;
       r2[w] = r_new[w];
@@ -403,5 +485,14 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
 
 extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
                            int *converged, int *accept_trace, int *n_iters) {
-  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr);
+  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, nullptr);
+}
+
+// Lidar_BA_Optimizer::damping_iter on a factor whose voxels are sharded over the ranks of `comm` (each rank's `f` holds the
+// voxels it owns, e.g. from vx_gba_build_sharded): one all-reduce of [Hess | JacT | cost] per evaluation — the sum the reference
+// takes over its worker threads (voxel_map.hpp:382-384) — and one of the cost per trial step; every rank returns the same result.
+extern "C" int vx_ba_lidar_sharded(vx_ctx *ctx, vx_comm *comm, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter,
+                                   int thd_num, int *converged, int *accept_trace, int *n_iters) {
+  VX_ARG(comm != nullptr && comm->ctx == ctx);
+  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, comm);
 }

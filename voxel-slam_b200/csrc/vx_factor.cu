@@ -616,6 +616,7 @@ __global__ void k_fin_off(const int64_t *__restrict__ tile_key, const int32_t *_
 // ----------------------------------------------------------------------------------------------
 static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end) {
   cudaStream_t st = ctx->stream;
+  f->n_res_evals++;
   if (f->V > 0) {
     static const int res_minb = [] { const char *e = std::getenv("VX_RES_MINB"); return e ? std::atoi(e) : 6; }();   // 80 registers, 24 warps per SM: measured best
 #define VX_RES_LAUNCH(MB) VX_KERNEL(ctx, "k_residual", k_residual<MB><<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>( \
@@ -638,6 +639,7 @@ struct GroupOut { double *Hess, *JacT; int groups; };
 
 static int launch_hessian(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, const GroupOut *group_out = nullptr) {
   cudaStream_t st = ctx->stream;
+  f->n_hess_evals++;
   const size_t jl = (size_t)6 * f->W;
   bool fused = false;
   if (f->V > 0 && f->nnz > 0 && !f->force_pairlist && hessian_small_handles(f->W)) {

@@ -46,6 +46,7 @@ struct vx_factor {
   vx::DevBuf lm_H, lm_J, lm_dx, lm_q1, lm_u, lm_mask;   // vx_ba_lidar: Hess / JacT each window last accepted, step, damping, masks
   int64_t n_pairs = 0, n_tiles = 0, n_dseg = 0, n_oseg = 0;
   int seg_len = 1024;
+  int64_t n_hess_evals = 0, n_res_evals = 0;   // acc_evaluate2 / evaluate_only_residual passes launched on this factor
   bool force_pairlist = false;   // tests: evaluate through the generic pair-list path even when a fused one exists
 };
 

@@ -50,12 +50,14 @@ __device__ __forceinline__ int frame_of(const int64_t *__restrict__ inst_off, in
 
 // 1. keys
 __global__ void k_gba_point(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
-                            const int64_t *__restrict__ inst_off, int F, const double *__restrict__ poses, GbaP prm, int64_t NI,
-                            uint32_t *__restrict__ key1, uint64_t *__restrict__ key2, int32_t *__restrict__ idx, int *__restrict__ bad) {
+                            const int64_t *__restrict__ inst_off, const int32_t *__restrict__ pt_frame, int F, const double *__restrict__ poses, GbaP prm,
+                            int64_t NI, uint32_t *__restrict__ key1, uint64_t *__restrict__ key2, int32_t *__restrict__ idx, int *__restrict__ bad) {
   const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (j >= NI) return;
-  const int g = frame_of(inst_off, F, j);
-  const int64_t pt = cloud_off[frame_cloud[g]] + (j - inst_off[g]);
+  // cloud mode: instance j is a point of the cloud of frame g; explicit mode (pt_frame, the routed points of a sharded
+  // build): instance j is point j and carries its frame
+  const int g = pt_frame ? pt_frame[j] : frame_of(inst_off, F, j);
+  const int64_t pt = pt_frame ? j : cloud_off[frame_cloud[g]] + (j - inst_off[g]);
   const double lx = (double)xyz[3 * pt], ly = (double)xyz[3 * pt + 1], lz = (double)xyz[3 * pt + 2];
   const d3 w = world_of(poses + 12 * (int64_t)g, lx, ly, lz);
   const int64_t kx = key_axis_d(w.x, prm.vs), ky = key_axis_d(w.y, prm.vs), kz = key_axis_d(w.z, prm.vs);
@@ -124,7 +126,7 @@ __global__ void k_starts(const int32_t *__restrict__ flag, const int32_t *__rest
 template <int GL>
 __global__ void __launch_bounds__(256)
 k_seg_moments(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
-              const int64_t *__restrict__ inst_off, const double *__restrict__ poses, const int32_t *__restrict__ sidx,
+              const int64_t *__restrict__ inst_off, const int32_t *__restrict__ pt_frame, const double *__restrict__ poses, const int32_t *__restrict__ sidx,
               const uint32_t *__restrict__ k1, const int32_t *__restrict__ seg_start, int64_t nseg, double *__restrict__ segm,
               int32_t *__restrict__ segN, int32_t *__restrict__ segF) {
   const int64_t s = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / GL;
@@ -133,7 +135,7 @@ k_seg_moments(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_o
   const int32_t b = on ? seg_start[s] : 0, e = on ? seg_start[s + 1] : 0;
   const int g = on ? (int)(k1[b] & ((1u << FRAME_BITS) - 1u)) : 0;
   const double *ps = poses + 12 * (int64_t)g;
-  const int64_t base = on ? cloud_off[frame_cloud[g]] - inst_off[g] : 0;
+  const int64_t base = (on && !pt_frame) ? cloud_off[frame_cloud[g]] - inst_off[g] : 0;
   double a[18];
 #pragma unroll
   for (int k = 0; k < 18; k++) a[k] = 0.0;
@@ -355,31 +357,35 @@ struct View { const void *p; template <class X> const X *as() const { return (co
 }
 namespace vx {
 // d_xyz / d_coff: the clouds already on the device (uploaded once per HBA_add_edge call); cloud_off: host copy.
+// explicit mode (d_pt_frame != nullptr): d_xyz_in holds n_pts routed points, point j belongs to frame d_pt_frame[j]; points of
+// one frame must appear in their original cloud order (cloud_off / frame_cloud are then unused).
 int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
-                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f) {
-  VX_ARG(f != nullptr && params != nullptr && cloud_off != nullptr && poses != nullptr && n_clouds >= 1);
+                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f, const int32_t *d_pt_frame, int64_t n_pts) {
+  const bool explicit_pts = d_pt_frame != nullptr;
+  VX_ARG(f != nullptr && params != nullptr && poses != nullptr && (explicit_pts || (cloud_off != nullptr && n_clouds >= 1)));
   VX_TRY(bind(ctx));
   cudaStream_t st = ctx->stream;
   const int W = f->W, NW = f->n_win, F = W * NW;
   VX_ARG(params->max_layer >= 0 && params->max_layer <= MAXL && params->voxel_size > 0);
   VX_ARG(F < (1 << FRAME_BITS));
-  VX_ARG(frame_cloud != nullptr || n_clouds == F);
+  VX_ARG(explicit_pts || frame_cloud != nullptr || n_clouds == F);
   GbaP prm;
   prm.vs = params->voxel_size; prm.min_eig = params->min_eigen_value; prm.L = params->max_layer;
   for (int k = 0; k < 4; k++) prm.thr[k] = params->eigen_value_array[k];
   const int L = prm.L;
-  const int64_t NP = cloud_off[n_clouds];
-  std::vector<int32_t> fc(F);
+  const int64_t NP = explicit_pts ? n_pts : cloud_off[n_clouds];
+  std::vector<int32_t> fc(F, 0);
   std::vector<int64_t> inst_off(F + 1, 0);
-  for (int g = 0; g < F; g++) {
-    fc[g] = frame_cloud ? frame_cloud[g] : g;
-    VX_ARG(fc[g] >= 0 && fc[g] < n_clouds);
-    inst_off[g + 1] = inst_off[g] + (cloud_off[fc[g] + 1] - cloud_off[fc[g]]);
-  }
-  const int64_t NI = inst_off[F];
+  if (!explicit_pts)
+    for (int g = 0; g < F; g++) {
+      fc[g] = frame_cloud ? frame_cloud[g] : g;
+      VX_ARG(fc[g] >= 0 && fc[g] < n_clouds);
+      inst_off[g + 1] = inst_off[g] + (cloud_off[fc[g] + 1] - cloud_off[fc[g]]);
+    }
+  const int64_t NI = explicit_pts ? n_pts : inst_off[F];
   VX_ARG(NI < ((int64_t)1 << 31) && NP >= 0);
   if (NI == 0) return vx_factor_clear(f);
-  VX_ARG(d_xyz_in != nullptr && d_coff_in != nullptr);
+  VX_ARG(d_xyz_in != nullptr && (explicit_pts || d_coff_in != nullptr));
 
   Tmp T;
   View d_xyz{d_xyz_in}, d_coff{d_coff_in};
@@ -395,7 +401,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   DevBuf &k1i = T.make(), &k2i = T.make(), &k1t = T.make(), &k2t = T.make(), &k2u = T.make(), &ia = T.make(), &ib = T.make();
   VX_TRY(k1i.reserve(4 * NI)); VX_TRY(k2i.reserve(8 * NI)); VX_TRY(k1t.reserve(4 * NI)); VX_TRY(k2t.reserve(8 * NI)); VX_TRY(k2u.reserve(8 * NI));
   VX_TRY(ia.reserve(4 * NI)); VX_TRY(ib.reserve(4 * NI));
-  VX_KERNEL(ctx, "k_gba_point", k_gba_point<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), F,
+  VX_KERNEL(ctx, "k_gba_point", k_gba_point<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
                                                                                 d_poses.as<double>(), prm, NI, k1i.as<uint32_t>(), k2i.as<uint64_t>(), ia.as<int32_t>(), d_bad.as<int>()));
   // ---- 2. stable sorts: (path, frame), then root key, then window
   VX_TRY(sort_pairs<uint32_t>(ctx, k1i.as<uint32_t>(), k1t.as<uint32_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, FRAME_BITS + 3 * L));
@@ -448,7 +454,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
     static const int gl = getenv("VX_SEG_LANES") ? atoi(getenv("VX_SEG_LANES")) : 4;
 #define VX_SEG_LAUNCH(GL)                                                                                                                    \
     VX_KERNEL(ctx, "k_seg_moments", k_seg_moments<GL><<<blocks_for((int64_t)nseg * GL, 256), 256, 0, st>>>(                                    \
-        d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg, \
+        d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg, \
         segm.as<double>(), segN.as<int32_t>(), segF.as<int32_t>()))
     if (gl == 32) { VX_SEG_LAUNCH(32); } else if (gl == 16) { VX_SEG_LAUNCH(16); } else if (gl == 8) { VX_SEG_LAUNCH(8); } else if (gl == 2) { VX_SEG_LAUNCH(2); } else { VX_SEG_LAUNCH(4); }
 #undef VX_SEG_LAUNCH
@@ -545,7 +551,7 @@ extern "C" int vx_gba_build(vx_ctx *ctx, const float *xyz, const int64_t *cloud_
     VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
     if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, ctx->stream));
     VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
-    return gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f);
+    return gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f, nullptr, 0);
   };
   s = body();
   cudaStreamSynchronize(ctx->stream);
@@ -596,10 +602,175 @@ extern "C" int vx_gba_build_device(vx_ctx *ctx, const float *d_xyz, const int64_
   auto body = [&]() -> int {
     VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
     VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
-    return gba_build_impl(ctx, d_xyz, d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f);
+    return gba_build_impl(ctx, d_xyz, d_coff.as<int64_t>(), cloud_off, n_clouds, frame_cloud, poses, params, f, nullptr, 0);
   };
   const int s = body();
   cudaStreamSynchronize(ctx->stream);
   d_coff.release();
+  return s;
+}
+
+// ---- sharded build: the exchange inside the library ---------------------------------
+// Every rank holds some of the clouds (one frame each).  k_owner_frame keys every local point at the CURRENT poses and names the
+// rank that owns its root voxel; a stable bucket partition (k_part_count -> scan -> k_part_scatter: points of one destination keep
+// their order, so a frame's points arrive in cloud order and every (leaf, frame) moment is summed in the single-GPU order, bit for
+// bit) lays them out by destination; one grouped ncclSend / ncclRecv round moves 16 B per point (float xyz + frame id); the
+// receiver runs the ordinary sort / segment / recut on what it owns.  Hess / JacT / cost are then sums over ranks.
+#include "vx_comm.cuh"
+namespace {
+constexpr int PART_THREADS = 256;
+constexpr int PART_TILE = 2048;      // points per block, walked in order in chunks of PART_THREADS
+constexpr int PART_MAXR = 64;        // ranks
+
+__global__ void k_owner_frame(const float *__restrict__ xyz, const int64_t *__restrict__ coff, const int32_t *__restrict__ cloud_frame, int n_clouds, int64_t n,
+                              const double *__restrict__ poses, double vs, int n_ranks, uint8_t *__restrict__ owner, int32_t *__restrict__ frame,
+                              int *__restrict__ bad) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int lo = 0, hi = n_clouds;   // largest c with coff[c] <= i
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (coff[mid] <= i) lo = mid; else hi = mid; }
+  const int g = cloud_frame[lo];
+  const d3 w = world_of(poses + 12 * (int64_t)g, (double)xyz[3 * i], (double)xyz[3 * i + 1], (double)xyz[3 * i + 2]);
+  uint64_t k;
+  if (!pack_key(key_axis_d(w.x, vs), key_axis_d(w.y, vs), key_axis_d(w.z, vs), k)) *bad = 1;
+  owner[i] = (uint8_t)(mix64(k) % (uint64_t)n_ranks);
+  frame[i] = g;
+}
+// cnt[o * n_blocks + b] = points of tile b that go to rank o
+__global__ void __launch_bounds__(PART_THREADS)
+k_part_count(const uint8_t *__restrict__ owner, int64_t n, int n_ranks, int n_blocks, int32_t *__restrict__ cnt) {
+  __shared__ int sc[PART_MAXR];
+  if (threadIdx.x < PART_MAXR) sc[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * PART_TILE;
+  for (int k = threadIdx.x; k < PART_TILE; k += PART_THREADS) {
+    const int64_t i = base + k;
+    if (i < n) atomicAdd(&sc[owner[i]], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x < n_ranks) cnt[(size_t)threadIdx.x * n_blocks + blockIdx.x] = sc[threadIdx.x];
+}
+// stable scatter: point i of tile b goes to off[owner * n_blocks + b] + (its rank among the tile's earlier points of that owner)
+__global__ void __launch_bounds__(PART_THREADS)
+k_part_scatter(const float *__restrict__ xyz, const uint8_t *__restrict__ owner, const int32_t *__restrict__ frame, int64_t n, int n_ranks, int n_blocks,
+               const int32_t *__restrict__ off, float *__restrict__ sxyz, int32_t *__restrict__ sframe) {
+  __shared__ int run[PART_MAXR];                       // points of each owner already placed by earlier chunks
+  __shared__ int wc[PART_THREADS / 32][PART_MAXR];     // per-warp counts of the current chunk
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  if (threadIdx.x < PART_MAXR) run[threadIdx.x] = 0;
+  for (int k = threadIdx.x; k < (PART_THREADS / 32) * PART_MAXR; k += PART_THREADS) (&wc[0][0])[k] = 0;
+  __syncthreads();
+  const int64_t base = (int64_t)blockIdx.x * PART_TILE;
+  for (int c = 0; c < PART_TILE; c += PART_THREADS) {
+    const int64_t i = base + c + threadIdx.x;
+    const int o = i < n ? (int)owner[i] : 255;
+    const unsigned m = __match_any_sync(0xffffffffu, o);
+    const int rw = __popc(m & ((1u << lane) - 1u));
+    if (o != 255 && rw == 0) wc[wp][o] = __popc(m);
+    __syncthreads();
+    if (o != 255) {
+      int pre = run[o];
+      for (int w2 = 0; w2 < wp; w2++) pre += wc[w2][o];
+      const int64_t pos = (int64_t)off[(size_t)o * n_blocks + blockIdx.x] + pre + rw;
+      sxyz[3 * pos] = xyz[3 * i]; sxyz[3 * pos + 1] = xyz[3 * i + 1]; sxyz[3 * pos + 2] = xyz[3 * i + 2];
+      sframe[pos] = frame[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < n_ranks) {
+      int s = 0;
+      for (int w2 = 0; w2 < PART_THREADS / 32; w2++) { s += wc[w2][threadIdx.x]; wc[w2][threadIdx.x] = 0; }
+      run[threadIdx.x] += s;
+    }
+    __syncthreads();
+  }
+}
+}  // namespace
+
+namespace vx {
+// d_xyz: this rank's clouds on the device (cloud c = points [cloud_off[c], cloud_off[c+1]), all of frame cloud_frame[c]);
+// poses: ALL F frames (replicated).  *n_owned = points this rank received.  stats (may be null): [0] ms partition, [1] ms exchange.
+int gba_build_sharded_impl(vx_ctx *ctx, vx_comm *comm, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *cloud_frame,
+                           const vx_pose *poses, const vx_gba_params *params, vx_factor *f, int64_t *n_owned) {
+  VX_ARG(ctx && comm && comm->ctx == ctx && f && params && poses && cloud_off && n_clouds >= 0 && comm->size <= PART_MAXR);
+  VX_TRY(bind(ctx));
+  cudaStream_t st = ctx->stream;
+  const int G = comm->size, F = f->W * f->n_win;
+  const int64_t n = n_clouds > 0 ? cloud_off[n_clouds] : 0;
+  VX_ARG(n < ((int64_t)1 << 31) && (n == 0 || (d_xyz && cloud_frame)));
+  for (int c = 0; c < n_clouds; c++) VX_ARG(cloud_frame[c] >= 0 && cloud_frame[c] < F);
+  const int nb = (int)std::max<int64_t>(1, (n + PART_TILE - 1) / PART_TILE);
+  DevBuf d_coff, d_cf, d_poses, d_owner, d_frame, d_cnt, d_off, d_sxyz, d_sframe, d_rxyz, d_rframe, d_bad;
+  std::vector<DevBuf *> all = {&d_coff, &d_cf, &d_poses, &d_owner, &d_frame, &d_cnt, &d_off, &d_sxyz, &d_sframe, &d_rxyz, &d_rframe, &d_bad};
+  auto body = [&]() -> int {
+    std::vector<int64_t> send_cnt(G, 0), send_off(G, 0), recv_cnt(G, 0), recv_off(G, 0);
+    if (n > 0) {
+      VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1))); VX_TRY(d_cf.reserve(4 * (size_t)n_clouds)); VX_TRY(d_poses.reserve(sizeof(vx_pose) * (size_t)F));
+      VX_TRY(d_owner.reserve(n)); VX_TRY(d_frame.reserve(4 * n)); VX_TRY(d_cnt.reserve(4 * ((size_t)G * nb + 1))); VX_TRY(d_off.reserve(4 * ((size_t)G * nb + 1)));
+      VX_TRY(d_sxyz.reserve(12 * n)); VX_TRY(d_sframe.reserve(4 * n)); VX_TRY(d_bad.reserve(4));
+      VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemcpyAsync(d_cf.p, cloud_frame, 4 * (size_t)n_clouds, cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemcpyAsync(d_poses.p, poses, sizeof(vx_pose) * (size_t)F, cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
+      VX_KERNEL(ctx, "k_owner_frame", k_owner_frame<<<blocks_for(n, 256), 256, 0, st>>>(d_xyz, d_coff.as<int64_t>(), d_cf.as<int32_t>(), n_clouds, n, d_poses.as<double>(),
+                                                                                       params->voxel_size, G, d_owner.as<uint8_t>(), d_frame.as<int32_t>(), d_bad.as<int>()));
+      VX_KERNEL(ctx, "k_part_count", k_part_count<<<nb, PART_THREADS, 0, st>>>(d_owner.as<uint8_t>(), n, G, nb, d_cnt.as<int32_t>()));
+      VX_TRY(excl_scan(ctx, d_cnt.as<int32_t>(), d_off.as<int32_t>(), (int64_t)G * nb));
+      VX_KERNEL(ctx, "k_part_scatter", k_part_scatter<<<nb, PART_THREADS, 0, st>>>(d_xyz, d_owner.as<uint8_t>(), d_frame.as<int32_t>(), n, G, nb, d_off.as<int32_t>(),
+                                                                                 d_sxyz.as<float>(), d_sframe.as<int32_t>()));
+      // first slot of every destination = off[o * nb]
+      std::vector<int32_t> first(G);
+      int bad = 0;
+      VX_CUDA(cudaMemcpy2DAsync(first.data(), 4, d_off.p, 4 * (size_t)nb, 4, G, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+      if (bad) { set_error("sharded GBA build: a root cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+      for (int o = 0; o < G; o++) { send_off[o] = first[o]; send_cnt[o] = (o + 1 < G ? first[o + 1] : n) - first[o]; }
+    }
+    // counts: every rank learns the whole matrix M[s][d]
+    std::vector<int64_t> M((size_t)G * G, 0);
+    if (G > 1) {
+      VX_TRY(comm->counts.reserve(8 * (size_t)G * (G + 1)));
+      int64_t *d_m = comm->counts.as<int64_t>();
+      VX_CUDA(cudaMemcpyAsync(d_m + (size_t)G * G, send_cnt.data(), 8 * (size_t)G, cudaMemcpyHostToDevice, st));
+      VX_TRY(comm_allgather_bytes(comm, d_m + (size_t)G * G, d_m, 8 * (size_t)G));
+      VX_CUDA(cudaMemcpyAsync(M.data(), d_m, 8 * (size_t)G * G, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+    } else {
+      M[0] = send_cnt[0];
+    }
+    int64_t nrecv = 0;
+    for (int s = 0; s < G; s++) { recv_cnt[s] = M[(size_t)s * G + comm->rank]; recv_off[s] = nrecv; nrecv += recv_cnt[s]; }
+    VX_ARG(nrecv < ((int64_t)1 << 31));
+    if (n_owned) *n_owned = nrecv;
+    VX_TRY(d_rxyz.reserve(12 * (size_t)std::max<int64_t>(nrecv, 1))); VX_TRY(d_rframe.reserve(4 * (size_t)std::max<int64_t>(nrecv, 1)));
+    VX_TRY(comm_alltoallv(comm, d_sxyz.p, send_off.data(), send_cnt.data(), d_rxyz.p, recv_off.data(), recv_cnt.data(), 12));
+    VX_TRY(comm_alltoallv(comm, d_sframe.p, send_off.data(), send_cnt.data(), d_rframe.p, recv_off.data(), recv_cnt.data(), 4));
+    d_owner.release(); d_frame.release(); d_cnt.release(); d_off.release();
+    if (nrecv == 0) return vx_factor_clear(f);
+    return gba_build_impl(ctx, d_rxyz.as<float>(), nullptr, nullptr, 0, nullptr, poses, params, f, d_rframe.as<int32_t>(), nrecv);
+  };
+  const int s = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : all) b->release();
+  return s;
+}
+}  // namespace vx
+
+// OctreeGBA::cut_voxel + OctreeGBA_multi_recut (loop_refine.hpp:446-537) with the ROOT voxels partitioned over the ranks of `comm`.
+extern "C" int vx_gba_build_sharded(vx_ctx *ctx, vx_comm *comm, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *cloud_frame,
+                                    const vx_pose *poses, const vx_gba_params *params, vx_factor *f, int64_t *n_points_owned) {
+  VX_ARG(ctx && comm && cloud_off && n_clouds >= 0);
+  VX_TRY(bind(ctx));
+  const int64_t NP = n_clouds > 0 ? cloud_off[n_clouds] : 0;
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  DevBuf d_xyz;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(12 * (size_t)std::max<int64_t>(NP, 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, 12 * (size_t)NP, cudaMemcpyHostToDevice, ctx->stream));
+    return gba_build_sharded_impl(ctx, comm, d_xyz.as<float>(), cloud_off, n_clouds, cloud_frame, poses, params, f, n_points_owned);
+  };
+  const int s = body();
+  cudaStreamSynchronize(ctx->stream);
+  d_xyz.release();
   return s;
 }

@@ -7,104 +7,78 @@
 // want the coarse and the fine thresholds in the same outer iteration are built as two sub-batches.
 #include "vx_factor.cuh"
 #include "vx_voxelize.cuh"
+#include "vx_hba.cuh"
 #include <cmath>
 #include <algorithm>
 
-namespace vx {
-int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
-                   const vx_pose *poses, const vx_gba_params *params, vx_factor *f);
-int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
-                  int *converged, int *accept_trace, int *n_iters, int *win_status);
-}
 using namespace vx;
 
-extern "C" int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
-                               const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int n_windows,
-                               const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
-                               double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out) {
-  VX_ARG(prm != nullptr && poses != nullptr && cloud_off != nullptr && W >= 2 && n_windows >= 1 && max_iter >= 0 && n_clouds >= 1);
-  VX_TRY(bind(ctx));
-  const int NW = n_windows, F = W * NW, jl = 6 * W;
+namespace vx {
+// One HBA_add_edge (voxelslam.cpp:2860-2951) over NW independent windows of W frames each.  `build` makes the LidarFactor of
+// the windows `ws` at the poses `ps` (ns * W entries) with the thresholds `gp`: the single-GPU map build, or the sharded one
+// (then NW == 1 and `comm` sums every evaluation over the ranks).
+int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int NW,
+             const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges, double *hess_out, double *resis_out,
+             int32_t *n_voxels_out, int32_t *status_out, int64_t *n_voxel_frames_evaluated) {
+  const int jl = 6 * W;
   const size_t hsz = (size_t)jl * jl;
-  const int64_t NP = cloud_off[n_clouds];
-  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
   const int64_t cap = (int64_t)W * (W - 1) / 2;   // edge slots per window
-
-  // clouds go to the device once for the whole call
-  DevBuf d_xyz, d_coff;
-  int rc = VX_OK;
   std::vector<double> hess(hsz * NW, 0.0);
   std::vector<int> cflag(NW, 0), done(NW, 0), status(NW, VX_OK), nvox(NW, 0);
   std::vector<double> cthre(NW, 0.05);
-  auto body = [&]() -> int {
-    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
-    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
-    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, ctx->stream));
-    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
-    const int up = 4;   // voxelslam.cpp:2867
-    for (int iterCnt = 0; iterCnt < max_iter; iterCnt++) {
-      // which thresholds does each live window use in this outer iteration?
-      std::vector<int> group[2];
-      for (int w = 0; w < NW; w++) {
-        if (done[w]) continue;
-        const bool fine = cflag[w] == 1 || iterCnt == max_iter - 1;   // voxelslam.cpp:2873
-        group[fine ? 1 : 0].push_back(w);
+  const int up = 4;   // voxelslam.cpp:2867
+  for (int iterCnt = 0; iterCnt < max_iter; iterCnt++) {
+    // which thresholds does each live window use in this outer iteration?
+    std::vector<int> group[2];
+    for (int w = 0; w < NW; w++) {
+      if (done[w]) continue;
+      const bool fine = cflag[w] == 1 || iterCnt == max_iter - 1;   // voxelslam.cpp:2873
+      group[fine ? 1 : 0].push_back(w);
+    }
+    if (group[0].empty() && group[1].empty()) break;
+    for (int gi = 0; gi < 2; gi++) {
+      const std::vector<int> &ws = group[gi];
+      if (ws.empty()) continue;
+      const int ns = (int)ws.size();
+      vx_gba_params gp = prm->gba;
+      if (gi == 1) {   // gba_* <- LocalBA thresholds (voxelslam.cpp:2875-2882)
+        gp.voxel_size = prm->voxel_size; gp.min_eigen_value = prm->min_eigen_value;
+        for (int k = 0; k < 4; k++) gp.eigen_value_array[k] = prm->plane_eigen_value_thre[k];
       }
-      if (group[0].empty() && group[1].empty()) break;
-      for (int gi = 0; gi < 2; gi++) {
-        const std::vector<int> &ws = group[gi];
-        if (ws.empty()) continue;
-        const int ns = (int)ws.size();
-        vx_gba_params gp = prm->gba;
-        if (gi == 1) {   // gba_* <- LocalBA thresholds (voxelslam.cpp:2875-2882)
-          gp.voxel_size = prm->voxel_size; gp.min_eigen_value = prm->min_eigen_value;
-          for (int k = 0; k < 4; k++) gp.eigen_value_array[k] = prm->plane_eigen_value_thre[k];
-        }
-        std::vector<int32_t> fc((size_t)ns * W);
-        std::vector<vx_pose> ps((size_t)ns * W);
-        for (int a = 0; a < ns; a++)
-          for (int i = 0; i < W; i++) {
-            const int g = ws[a] * W + i;
-            fc[(size_t)a * W + i] = frame_cloud ? frame_cloud[g] : g;
-            ps[(size_t)a * W + i] = poses[g];
-          }
-        vx_factor *fac = nullptr;
-        VX_TRY(vx_factor_create(ctx, W, ns, &fac));
-        std::vector<double> hs(hsz * ns), rs(2 * (size_t)ns);
-        std::vector<int> conv(ns), wst(ns);
-        int s = gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, fc.data(), ps.data(), &gp, fac);
-        if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hs.data(), rs.data(), up, thread_num, conv.data(), nullptr, nullptr, wst.data());
-        std::vector<int32_t> wv(ns + 1, 0);
-        if (s == VX_OK && fac->V > 0) {
-          cudaMemcpyAsync(wv.data(), fac->wv_off.p, sizeof(int32_t) * (ns + 1), cudaMemcpyDeviceToHost, ctx->stream);
-          cudaStreamSynchronize(ctx->stream);
-        }
-        vx_factor_free(fac);
-        VX_TRY(s);
-        for (int a = 0; a < ns; a++) {
-          const int w = ws[a];
-          nvox[w] = wv[a + 1] - wv[a];
-          if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
-          for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
-          std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
-          const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
-          if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
-          // voxelslam.cpp:2906-2917
-          if ((std::fabs(r0 - r1) / r0 < cthre[w] && conv[a]) || (iterCnt == max_iter - 2 && cflag[w] == 0)) {
-            cthre[w] = 0.01;
-            if (cflag[w] == 0) cflag[w] = 1;
-            else if (cflag[w] == 1) done[w] = 1;
-          }
+      std::vector<vx_pose> ps((size_t)ns * W);
+      for (int a = 0; a < ns; a++)
+        for (int i = 0; i < W; i++) ps[(size_t)a * W + i] = poses[ws[a] * W + i];
+      vx_factor *fac = nullptr;
+      VX_TRY(vx_factor_create(ctx, W, ns, &fac));
+      std::vector<double> hs(hsz * ns), rs(2 * (size_t)ns);
+      std::vector<int> conv(ns), wst(ns), nit(ns, 0);
+      int s = build(ws, ps.data(), gp, fac);
+      if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hs.data(), rs.data(), up, thread_num, conv.data(), nullptr, nit.data(), wst.data(), comm);
+      std::vector<int32_t> wv(ns + 1, 0);
+      if (s == VX_OK && fac->V > 0) {
+        cudaMemcpyAsync(wv.data(), fac->wv_off.p, sizeof(int32_t) * (ns + 1), cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+      }
+      if (n_voxel_frames_evaluated) *n_voxel_frames_evaluated += fac->nnz * fac->n_hess_evals;
+      vx_factor_free(fac);
+      VX_TRY(s);
+      for (int a = 0; a < ns; a++) {
+        const int w = ws[a];
+        nvox[w] = wv[a + 1] - wv[a];
+        if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
+        for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
+        std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
+        const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
+        if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
+        // voxelslam.cpp:2906-2917
+        if ((std::fabs(r0 - r1) / r0 < cthre[w] && conv[a]) || (iterCnt == max_iter - 2 && cflag[w] == 0)) {
+          cthre[w] = 0.01;
+          if (cflag[w] == 0) cflag[w] = 1;
+          else if (cflag[w] == 1) done[w] = 1;
         }
       }
     }
-    return VX_OK;
-  };
-  rc = body();
-  cudaStreamSynchronize(ctx->stream);
-  d_xyz.release(); d_coff.release();
-  VX_TRY(rc);
-
+  }
   // pose-graph edges (voxelslam.cpp:2926-2951): cov_k = 1/|hess(6i+k, 6j+k)| of the pre-gauge snapshot
   for (int w = 0; w < NW; w++) {
     int64_t ne = 0;
@@ -143,6 +117,37 @@ extern "C" int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *clo
   }
   if (hess_out) std::copy(hess.begin(), hess.end(), hess_out);
   return VX_OK;
+}
+}  // namespace vx
+
+extern "C" int vx_hba_add_edge(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
+                               const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int n_windows,
+                               const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges,
+                               double *hess_out, double *resis_out, int32_t *n_voxels_out, int32_t *status_out) {
+  VX_ARG(prm != nullptr && poses != nullptr && cloud_off != nullptr && W >= 2 && n_windows >= 1 && max_iter >= 0 && n_clouds >= 1);
+  VX_TRY(bind(ctx));
+  const int64_t NP = cloud_off[n_clouds];
+  VX_ARG(NP >= 0 && (NP == 0 || xyz != nullptr));
+  // clouds go to the device once for the whole call
+  DevBuf d_xyz, d_coff;
+  auto body = [&]() -> int {
+    VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
+    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1)));
+    if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, ctx->stream));
+    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, ctx->stream));
+    HbaBuildFn build = [&](const std::vector<int> &ws, const vx_pose *ps, const vx_gba_params &gp, vx_factor *fac) -> int {
+      std::vector<int32_t> fc(ws.size() * (size_t)W);
+      for (size_t a = 0; a < ws.size(); a++)
+        for (int i = 0; i < W; i++) { const int g = ws[a] * W + i; fc[a * W + i] = frame_cloud ? frame_cloud[g] : g; }
+      return gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), cloud_off, n_clouds, fc.data(), ps, &gp, fac, nullptr, 0);
+    };
+    return hba_core(ctx, nullptr, build, frame_id, frame_mp, poses, W, n_windows, prm, max_iter, thread_num, edges, n_edges, hess_out, resis_out,
+                    n_voxels_out, status_out, nullptr);
+  };
+  const int rc = body();
+  cudaStreamSynchronize(ctx->stream);
+  d_xyz.release(); d_coff.release();
+  return rc;
 }
 
 // ---- merged submap cloud of HBA_add_edge (voxelslam.cpp:2954-2985) ---------------------------------------------------
@@ -198,6 +203,167 @@ static int assemble_window(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud
   return downsample_device(ctx, d_in.p, total, leaf, DS_MEAN, d_out.as<vx_point48>(), ncell);
 }
 
+// ---- all windows at once -----------------------------------------------------------------------------------------------------
+#include <cub/cub.cuh>
+namespace {
+struct RelPoseD { double dR[9]; double dp[3]; };   // dR row-major, per frame
+constexpr int MK_BITS = 18;                        // bits per axis of the batched cell key (+-131072 cells), window id above them
+constexpr int64_t MK_BIAS = (int64_t)1 << (MK_BITS - 1);
+
+__device__ __forceinline__ int frame_of_inst(const int64_t *__restrict__ inst_off, int F, int64_t j) {
+  int lo = 0, hi = F;
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (inst_off[mid] <= j) lo = mid; else hi = mid; }
+  return lo;
+}
+// every point instance of every window into its window's frame (:2958-2969, the arithmetic of k_merge_transform) + its batched key
+__global__ void k_merge_all(const float *__restrict__ xyz, const int64_t *__restrict__ coff, const int32_t *__restrict__ frame_cloud,
+                            const int64_t *__restrict__ inst_off, int F, const RelPoseD *__restrict__ rel, const int32_t *__restrict__ frame_win, double leaf,
+                            int64_t NI, float *__restrict__ out, uint64_t *__restrict__ keys, int32_t *__restrict__ idx, int *__restrict__ bad) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= NI) return;
+  const int g = frame_of_inst(inst_off, F, j);
+  const float *s = xyz + 3 * (coff[frame_cloud[g]] + (j - inst_off[g]));
+  const double x = (double)s[0], y = (double)s[1], z = (double)s[2];
+  const RelPoseD &rp = rel[g];
+  float v[3];
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+    v[r] = (float)__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(rp.dR[r * 3], x), __dmul_rn(rp.dR[r * 3 + 1], y)), __dmul_rn(rp.dR[r * 3 + 2], z)), rp.dp[r]);
+  out[3 * j] = v[0]; out[3 * j + 1] = v[1]; out[3 * j + 2] = v[2];
+  const int64_t kx = key_axis_f(v[0], leaf) + MK_BIAS, ky = key_axis_f(v[1], leaf) + MK_BIAS, kz = key_axis_f(v[2], leaf) + MK_BIAS;
+  const int64_t lim = (int64_t)1 << MK_BITS;
+  if (kx < 0 || ky < 0 || kz < 0 || kx >= lim || ky >= lim || kz >= lim) *bad = 1;
+  keys[j] = ((uint64_t)frame_win[g] << (3 * MK_BITS)) | ((uint64_t)(kx & (lim - 1)) << (2 * MK_BITS)) | ((uint64_t)(ky & (lim - 1)) << MK_BITS) | (uint64_t)(kz & (lim - 1));
+  idx[j] = (int32_t)j;
+}
+__global__ void k_mheads(const uint64_t *__restrict__ keys, int64_t n, int32_t *__restrict__ flag) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) flag[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1 : 0;
+}
+__global__ void k_mstarts(const int32_t *__restrict__ flag, const int32_t *__restrict__ incl, int64_t n, int32_t *__restrict__ start) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flag[i]) start[incl[i] - 1] = (int32_t)i;
+  if (i == n - 1) start[incl[i]] = (int32_t)n;
+}
+// one thread per cell: the reference's sequential float running mean (tools.hpp:227-230) over the cell's points in input order
+__global__ void k_mmean(const float *__restrict__ pts, const int32_t *__restrict__ idx, const int32_t *__restrict__ start, int64_t ncell,
+                        const int64_t *__restrict__ inst_off, int F, const int32_t *__restrict__ frame_mp, float *__restrict__ out, vx_point48 *__restrict__ out48) {
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= ncell) return;
+  const int32_t b = start[c], e = start[c + 1];
+  const int32_t j0 = idx[b];
+  float x = pts[3 * (int64_t)j0], y = pts[3 * (int64_t)j0 + 1], z = pts[3 * (int64_t)j0 + 2], cnt = 1.0f;
+  for (int32_t k = b + 1; k < e; k++) {
+    const float *q = pts + 3 * (int64_t)idx[k];
+    const float c1 = __fadd_rn(cnt, 1.0f);
+    x = __fdiv_rn(__fadd_rn(__fmul_rn(x, cnt), q[0]), c1);
+    y = __fdiv_rn(__fadd_rn(__fmul_rn(y, cnt), q[1]), c1);
+    z = __fdiv_rn(__fadd_rn(__fmul_rn(z, cnt), q[2]), c1);
+    cnt = c1;
+  }
+  out[3 * c] = x; out[3 * c + 1] = y; out[3 * c + 2] = z;
+  if (out48) {
+    vx_point48 ap;
+    ap.x = x; ap.y = y; ap.z = z; ap._p0 = 0.0f; ap.normal_x = ap.normal_y = ap.normal_z = ap._p1 = 0.0f;
+    ap.intensity = frame_mp ? (float)frame_mp[frame_of_inst(inst_off, F, j0)] : 0.0f;
+    ap.curvature = cnt; ap._p2 = ap._p3 = 0.0f;
+    out48[c] = ap;
+  }
+}
+// win_off[w] = first cell whose window id >= w
+__global__ void k_mwin_off(const uint64_t *__restrict__ keys, const int32_t *__restrict__ start, int64_t ncell, int NW, int64_t *__restrict__ win_off) {
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w > NW) return;
+  int64_t lo = 0, hi = ncell;
+  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if ((int)(keys[start[mid]] >> (3 * MK_BITS)) < w) lo = mid + 1; else hi = mid; }
+  win_off[w] = lo;
+}
+}  // namespace
+
+namespace vx {
+int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud, const int32_t *frame_mp,
+                         const vx_pose *poses, const int32_t *wf_off, int n_windows, double leaf, DevBuf &d_out_xyz, int64_t *win_off, DevBuf *d_out48,
+                         int *overflow) {
+  cudaStream_t st = ctx->stream;
+  const int NW = n_windows, F = wf_off[NW];
+  if (overflow) *overflow = 0;
+  VX_ARG(NW >= 1 && NW < (1 << (64 - 3 * MK_BITS)) && F >= NW);
+  std::vector<int64_t> inst_off(F + 1, 0);
+  std::vector<int32_t> fc(F), fwin(F);
+  std::vector<RelPoseD> rel(F);
+  for (int w = 0; w < NW; w++) {
+    const vx_pose &xc = poses[wf_off[w]];
+    for (int g = wf_off[w]; g < wf_off[w + 1]; g++) {
+      fc[g] = frame_cloud ? frame_cloud[g] : g;
+      VX_ARG(fc[g] >= 0 && fc[g] < n_clouds);
+      fwin[g] = w;
+      inst_off[g + 1] = inst_off[g] + (cloud_off[fc[g] + 1] - cloud_off[fc[g]]);
+      const vx_pose &xi = poses[g];
+      // dp = x_0.R^T (x_i.p - x_0.p), dR = x_0.R^T x_i.R  (voxelslam.cpp:2960-2961); R column-major: R(r,c) = R[c*3+r]
+      const double d[3] = {xi.p[0] - xc.p[0], xi.p[1] - xc.p[1], xi.p[2] - xc.p[2]};
+      for (int r = 0; r < 3; r++) {
+        double sacc = 0; for (int k = 0; k < 3; k++) sacc += xc.R[r * 3 + k] * d[k];
+        rel[g].dp[r] = sacc;
+        for (int cc = 0; cc < 3; cc++) { double t = 0; for (int k = 0; k < 3; k++) t += xc.R[r * 3 + k] * xi.R[cc * 3 + k]; rel[g].dR[r * 3 + cc] = t; }
+      }
+    }
+  }
+  const int64_t NI = inst_off[F];
+  VX_ARG(NI < ((int64_t)1 << 31));
+  for (int w = 0; w <= NW; w++) win_off[w] = 0;
+  if (NI == 0) return VX_OK;
+  DevBuf d_coff, d_fc, d_io, d_rel, d_fw, d_mp, d_pts, d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad, d_woff;
+  std::vector<DevBuf *> all = {&d_coff, &d_fc, &d_io, &d_rel, &d_fw, &d_mp, &d_pts, &d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad, &d_woff};
+  auto body = [&]() -> int {
+    VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1))); VX_TRY(d_fc.reserve(4 * (size_t)F)); VX_TRY(d_io.reserve(8 * (size_t)(F + 1)));
+    VX_TRY(d_rel.reserve(sizeof(RelPoseD) * (size_t)F)); VX_TRY(d_fw.reserve(4 * (size_t)F)); VX_TRY(d_mp.reserve(4 * (size_t)F));
+    VX_TRY(d_pts.reserve(12 * (size_t)NI)); VX_TRY(d_k0.reserve(8 * (size_t)NI)); VX_TRY(d_k1.reserve(8 * (size_t)NI));
+    VX_TRY(d_i0.reserve(4 * (size_t)NI)); VX_TRY(d_i1.reserve(4 * (size_t)NI)); VX_TRY(d_flag.reserve(4 * (size_t)NI)); VX_TRY(d_incl.reserve(4 * (size_t)NI));
+    VX_TRY(d_start.reserve(4 * ((size_t)NI + 1))); VX_TRY(d_bad.reserve(4)); VX_TRY(d_woff.reserve(8 * (size_t)(NW + 1)));
+    VX_CUDA(cudaMemcpyAsync(d_coff.p, cloud_off, 8 * (size_t)(n_clouds + 1), cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_fc.p, fc.data(), 4 * (size_t)F, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_io.p, inst_off.data(), 8 * (size_t)(F + 1), cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_rel.p, rel.data(), sizeof(RelPoseD) * (size_t)F, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_fw.p, fwin.data(), 4 * (size_t)F, cudaMemcpyHostToDevice, st));
+    if (frame_mp) VX_CUDA(cudaMemcpyAsync(d_mp.p, frame_mp, 4 * (size_t)F, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
+    VX_KERNEL(ctx, "k_merge_all", k_merge_all<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz, d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_io.as<int64_t>(), F, d_rel.as<RelPoseD>(),
+                                                                                d_fw.as<int32_t>(), leaf, NI, d_pts.as<float>(), d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
+    int wbits = 1; while ((1 << wbits) < NW) wbits++;
+    size_t tb = 0;
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, 3 * MK_BITS + wbits, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, 3 * MK_BITS + wbits, st));
+    ctx->launches += 4;
+    VX_KERNEL(ctx, "k_mheads", k_mheads<<<blocks_for(NI, 256), 256, 0, st>>>(d_k1.as<uint64_t>(), NI, d_flag.as<int32_t>()));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tb, d_flag.as<int32_t>(), d_incl.as<int32_t>(), (int)NI, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceScan::InclusiveSum(ctx->scratch.p, tb, d_flag.as<int32_t>(), d_incl.as<int32_t>(), (int)NI, st));
+    ctx->launches += 2;
+    VX_KERNEL(ctx, "k_mstarts", k_mstarts<<<blocks_for(NI, 256), 256, 0, st>>>(d_flag.as<int32_t>(), d_incl.as<int32_t>(), NI, d_start.as<int32_t>()));
+    int32_t ncell = 0; int bad = 0;
+    VX_CUDA(cudaMemcpyAsync(&ncell, d_incl.as<int32_t>() + (NI - 1), 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (bad) { if (overflow) *overflow = 1; set_error("merged submap clouds: a cell index does not fit the %d-bit batched key", MK_BITS); return VX_ERR_ARG; }
+    VX_TRY(d_out_xyz.reserve(12 * (size_t)ncell));
+    if (d_out48) VX_TRY(d_out48->reserve(sizeof(vx_point48) * (size_t)ncell));
+    VX_KERNEL(ctx, "k_mmean", k_mmean<<<blocks_for(ncell, 128), 128, 0, st>>>(d_pts.as<float>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_io.as<int64_t>(), F,
+                                                                           frame_mp ? d_mp.as<int32_t>() : nullptr, d_out_xyz.as<float>(),
+                                                                           d_out48 ? d_out48->as<vx_point48>() : nullptr));
+    VX_KERNEL(ctx, "k_mwin_off", k_mwin_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(d_k1.as<uint64_t>(), d_start.as<int32_t>(), ncell, NW, d_woff.as<int64_t>()));
+    VX_CUDA(cudaMemcpyAsync(win_off, d_woff.p, 8 * (size_t)(NW + 1), cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : all) b->release();
+  return rc;
+}
+}  // namespace vx
+
 extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud,
                                    const int32_t *frame_mp, const vx_pose *poses, int W, int n_windows, double voxel_size, vx_point48 *out,
                                    int64_t out_cap, int64_t *win_off) {
@@ -210,6 +376,24 @@ extern "C" int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t 
   auto body = [&]() -> int {
     VX_TRY(d_xyz.reserve(sizeof(float) * 3 * std::max<int64_t>(NP, 1)));
     if (NP) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(float) * 3 * NP, cudaMemcpyHostToDevice, st));
+    {   // all windows in one sort / segment pass; a scene too wide for the batched key falls through to the per-window loop
+      std::vector<int32_t> wf(n_windows + 1);
+      for (int w = 0; w <= n_windows; w++) wf[w] = w * W;
+      DevBuf d_cells, d_cells48;
+      int overflow = 0;
+      int rcb = merge_clouds_batched(ctx, d_xyz.as<float>(), cloud_off, n_clouds, frame_cloud, frame_mp, poses, wf.data(), n_windows, voxel_size / 8, d_cells, win_off,
+                                     &d_cells48, &overflow);
+      if (rcb == VX_OK) {
+        if (win_off[n_windows] > out_cap) { rcb = VX_ERR_ARG; set_error("vx_hba_merge_clouds: output capacity %lld too small", (long long)out_cap); }
+        else if (win_off[n_windows] > 0) {
+          const cudaError_t ce = cudaMemcpyAsync(out, d_cells48.p, sizeof(vx_point48) * (size_t)win_off[n_windows], cudaMemcpyDeviceToHost, st);
+          cudaStreamSynchronize(st);
+          if (ce != cudaSuccess) rcb = VX_ERR_CUDA;
+        }
+      }
+      d_cells.release(); d_cells48.release();
+      if (rcb == VX_OK || !overflow) return rcb;
+    }
     int64_t written = 0;
     win_off[0] = 0;
     for (int w = 0; w < n_windows; w++) {
