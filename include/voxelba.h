@@ -144,6 +144,16 @@ int vx_factor_device_buffers(vx_factor *f, void **Hess, void **JacT, void **cost
  * is_float_input (tools.hpp:211 promotes a float coordinate).  out_keys: n x 3 int64 (VOXEL_LOC x,y,z). */
 int vx_keys(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_float_input, int64_t *out_keys);
 
+/* vx_keys that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel, same
+ * arguments and results as vx_keys, but the device staging (coordinates in, keys out) is a fixed file-scope device array of
+ * VX_KEYS_STATIC_MAX_POINTS points (12 MiB, held by every GPU that loads the library until exit) instead of the context's
+ * grow-on-demand scratch; no cudaMalloc / cudaFree / allocating library call is made.  n > VX_KEYS_STATIC_MAX_POINTS ->
+ * VX_ERR_ARG (vx_last_error names the limit).  All calls on one GPU share the array, which keeps the last call's contents:
+ * calls that overlap on the same GPU (two contexts / threads) race — serialise them. */
+#define VX_KEYS_STATIC_MAX_POINTS 262144
+int vx_keys_static(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_float_input, int64_t *out_keys);
+
 /* ---- A2: void down_sampling_voxel(pcl::PointCloud<PointType>&, double)  tools.hpp:201-238.
  * out must hold n points; *out_n = occupied cells.  Per cell the reference's sequential float running
  * mean is replayed exactly (bit-identical x,y,z and curvature = count; other fields of the cell's first

@@ -141,6 +141,18 @@ def keys(ctx, xyz, voxel_size):
     return out
 
 
+KEYS_STATIC_MAX_POINTS = 262144   # VX_KEYS_STATIC_MAX_POINTS, include/voxelba.h
+
+
+def keys_static(ctx, xyz, voxel_size):
+    """vx_keys_static: vx_keys on the library's fixed device scratch (no allocation); at most KEYS_STATIC_MAX_POINTS points."""
+    xyz = np.ascontiguousarray(xyz)
+    assert xyz.dtype in (np.float32, np.float64)
+    out = np.zeros(xyz.shape, dtype=np.int64)
+    _chk(ctx.lib.vx_keys_static(ctx.h, _p(xyz), C.c_int64(xyz.size // 3), C.c_double(voxel_size), C.c_int(int(xyz.dtype == np.float32)), _p(out)))
+    return out
+
+
 def downsample_voxel(ctx, pts, voxel_size):
     """A2: down_sampling_voxel (tools.hpp:201-238); returns the cells in ascending packed-key order."""
     pts = np.ascontiguousarray(pts, dtype=point48_dtype)

@@ -10,6 +10,7 @@
 #include "vx_voxelize.cuh"
 #include "vx_math.cuh"
 #include <cub/cub.cuh>
+#include <mutex>
 
 using namespace vx;
 
@@ -276,6 +277,56 @@ int vx_keys(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_f
                                                                                3 * n, voxel_size, out.as<int64_t>()));
   VX_CUDA(cudaMemcpyAsync(out_keys, out.p, sizeof(int64_t) * 3 * n, cudaMemcpyDeviceToHost, ctx->stream));
   VX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return VX_OK;
+}
+
+// ---- vx_keys without any allocation (no counterpart in the reference) ----------
+// vx_keys stages the caller's host coordinates and the keys in the context's grow-on-demand device scratch (cached_malloc ->
+// cudaMalloc).  Callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get
+// the same kernel on a FIXED scratch: a file-scope device array, [coordinates | keys], sized for VX_KEYS_STATIC_MAX_POINTS
+// double-precision points (6 MiB + 6 MiB; every GPU that loads the library holds it until exit).  In host code the array's name
+// is only a stand-in: the device address comes from cudaGetSymbolAddress, once per device with that device current.
+// All calls on a device share the array and it keeps the last call's contents; nothing in it has to start at zero (the kernel
+// writes every key that is read back), but two calls that overlap on one GPU race on it.
+namespace {
+constexpr int64_t KEYS_STATIC_MAX = VX_KEYS_STATIC_MAX_POINTS;
+constexpr size_t KEYS_STATIC_IN_BYTES = sizeof(double) * 3 * KEYS_STATIC_MAX;
+constexpr size_t KEYS_STATIC_BYTES = KEYS_STATIC_IN_BYTES + sizeof(int64_t) * 3 * KEYS_STATIC_MAX;
+static __device__ __align__(256) unsigned char g_keys_static_scratch[KEYS_STATIC_BYTES];
+constexpr int KEYS_MAX_DEVICES = 64;
+std::mutex g_keys_static_mu;
+unsigned char *g_keys_static_ptr[KEYS_MAX_DEVICES] = {};
+}  // namespace
+
+int vx_keys_static(vx_ctx *ctx, const void *xyz, int64_t n, double voxel_size, int is_float_input, int64_t *out_keys) {
+  VX_TRY(bind(ctx));                       // cudaSetDevice(ctx->device): the symbol is looked up with its device current
+  VX_ARG(n >= 0 && (n == 0 || (xyz && out_keys)) && voxel_size > 0);
+  if (n > KEYS_STATIC_MAX) {
+    set_error("vx_keys_static: %lld points exceed the static scratch of %lld points (VX_KEYS_STATIC_MAX_POINTS); use vx_keys",
+              (long long)n, (long long)KEYS_STATIC_MAX);
+    return VX_ERR_ARG;
+  }
+  VX_ARG(ctx->device >= 0 && ctx->device < KEYS_MAX_DEVICES);
+  if (n == 0) return VX_OK;
+  unsigned char *base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_keys_static_mu);
+    if (!g_keys_static_ptr[ctx->device]) {
+      void *p = nullptr;
+      VX_CUDA(cudaGetSymbolAddress(&p, g_keys_static_scratch));
+      g_keys_static_ptr[ctx->device] = (unsigned char *)p;
+    }
+    base = g_keys_static_ptr[ctx->device];
+  }
+  const size_t esz = is_float_input ? sizeof(float) : sizeof(double);
+  void *d_in = base;
+  int64_t *d_out = reinterpret_cast<int64_t *>(base + KEYS_STATIC_IN_BYTES);
+  cudaStream_t st = ctx->stream;
+  VX_CUDA(cudaMemcpyAsync(d_in, xyz, esz * 3 * n, cudaMemcpyHostToDevice, st));
+  k_keys<<<blocks_for(3 * n, 256), 256, 0, st>>>(is_float_input ? nullptr : (const double *)d_in, is_float_input ? (const float *)d_in : nullptr, 3 * n, voxel_size, d_out);
+  VX_LAUNCH_CHECK(ctx);
+  VX_CUDA(cudaMemcpyAsync(out_keys, d_out, sizeof(int64_t) * 3 * n, cudaMemcpyDeviceToHost, st));
+  VX_CUDA(cudaStreamSynchronize(st));
   return VX_OK;
 }
 
