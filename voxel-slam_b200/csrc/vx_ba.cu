@@ -220,6 +220,22 @@ k_lm_solve(const double *__restrict__ Hk, const double *__restrict__ Jk, const d
 #undef LM_AT
 }
 
+// The numbers HBA_add_edge reads off the Hessian snapshot (voxelslam.cpp:2926-2951): hess(6i+k, 6j+k), i < j, k < 6, in the
+// order the edges are made; 6 W (W-1)/2 doubles per window instead of the (6W)^2 matrix (3.8 MB instead of 46 MB at W = 400).
+__global__ void k_edge_diag(const double *__restrict__ H, int W, double *__restrict__ out) {
+  const int n = 6 * W, w = blockIdx.y;
+  const int64_t npair = (int64_t)W * (W - 1) / 2;
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= npair * 6) return;
+  const int64_t p = t / 6; const int k = (int)(t % 6);
+  // pair p -> (i, j): p = i (2W - i - 1) / 2 + (j - i - 1)
+  int i = (int)((2.0 * W - 1.0 - sqrt((2.0 * W - 1.0) * (2.0 * W - 1.0) - 8.0 * (double)p)) * 0.5);
+  while ((int64_t)i * (2 * W - i - 1) / 2 > p) i--;
+  while ((int64_t)(i + 1) * (2 * W - i - 2) / 2 <= p) i++;
+  const int j = (int)(p - (int64_t)i * (2 * W - i - 1) / 2) + i + 1;
+  out[(size_t)w * npair * 6 + t] = H[(size_t)n * n * w + (size_t)(6 * j + k) * n + (6 * i + k)];
+}
+
 // ---- voxel-sharded evaluation: [lower triangle of Hess | JacT | cost] of every window, packed for ONE all-reduce ------------
 // (the reference adds its per-thread partial Hess / JacT / residual the same way, voxel_map.hpp:382-384).  Hess is symmetric
 // block-wise (acc_evaluate2 mirrors the upper blocks, :279-281) except for the antisymmetric -0.5*hat(jjt) term inside the
@@ -286,8 +302,9 @@ int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, doubl
 // VX_ERR_TOO_FEW and left untouched instead of failing the whole batch.
 // comm (optional): the factor holds only this rank's voxels of every window; Hess / JacT / cost are all-reduced after each
 // evaluation, the LM step is replicated (every rank sees bitwise the same sums, so every rank takes the same decisions).
+// edge_diag (optional, n_windows x W(W-1)/2 x 6): hess(6i+k, 6j+k) of the snapshot *hess would hold, without moving the matrix.
 int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
-                  int *converged, int *accept_trace, int *n_iters, int *win_status, vx_comm *comm) {
+                  int *converged, int *accept_trace, int *n_iters, int *win_status, vx_comm *comm, double *edge_diag) {
   VX_ARG(f != nullptr && poses != nullptr && max_iter >= 0);
   VX_TRY(bind(ctx));
   const int W = f->W, NW = f->n_win, jl = 6 * W, F = W * NW;
@@ -338,7 +355,8 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   for (int w = 0; w < NW; w++) if (few[w]) { active[w] = 0; conv[w] = 0; }
 
   std::vector<int32_t> mask(NW);
-  std::vector<double> dx_all;
+  std::vector<double> dx_all, Hsnap;
+  if (edge_diag && host_mats) Hsnap.assign(hsz * NW, 0.0);
   cudaStream_t st = ctx->stream;
   if (dev) {
     VX_TRY(f->lm_H.reserve(sizeof(double) * hsz * NW)); VX_TRY(f->lm_J.reserve(sizeof(double) * jl * NW));
@@ -352,6 +370,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   }
   bool evaluated = false;
 
+  PhaseTimer pt("ba_lidar", ctx->stream);
   for (int it = 0; it < max_iter; it++) {
     bool any_active = false, any_calc = false;
     for (int w = 0; w < NW; w++) { any_active |= active[w] != 0; any_calc |= (active[w] && calc[w]); }
@@ -368,6 +387,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       VX_CUDA(cudaStreamSynchronize(st));
       for (int w = 0; w < NW; w++) if (mask[w]) r1[w] = r_new[w];
       evaluated = true;
+      pt.lap("hessian");
     } else if (any_calc) {
       VX_TRY(vx_factor_hessian(ctx, f, x.data(), 0, -1, Hnew.data(), Jnew.data(), r_new.data()));
       for (int w = 0; w < NW; w++)
@@ -376,6 +396,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
           std::copy(Jnew.begin() + (size_t)jl * w, Jnew.begin() + (size_t)jl * (w + 1), JacT.begin() + (size_t)jl * w);
           r1[w] = r_new[w];
           if (hess_out) std::copy(Hnew.begin() + hsz * w, Hnew.begin() + hsz * (w + 1), hess_out + hsz * w);   // *hess = Hess, before the gauge fix (:446)
+          if (!Hsnap.empty()) std::copy(Hnew.begin() + hsz * w, Hnew.begin() + hsz * (w + 1), Hsnap.begin() + hsz * w);
         }
     }
     if (dev && !small) {
@@ -399,6 +420,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       VX_CUDA(cudaMemcpyAsync(q1s.data(), f->lm_q1.p, sizeof(double) * NW, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaStreamSynchronize(st));
     }
+    pt.lap("solve");
     for (int w = 0; w < NW; w++) {
       if (!active[w]) continue;
       if (it == 0 && resis) resis[2 * w] = r1[w];
@@ -438,6 +460,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
     } else {
       VX_TRY(vx_factor_residual(ctx, f, xt.data(), 0, -1, r_new.data()));
     }
+    pt.lap("residual");
     for (int w = 0; w < NW; w++) {
       if (!active[w]) continue;
       r2[w] = r_new[w];
@@ -473,6 +496,25 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   } else if (dev && hess_out && max_iter > 0) {
     std::fill(hess_out, hess_out + hsz * NW, 0.0);
   }
+  if (edge_diag) {
+    const int64_t npair = (int64_t)W * (W - 1) / 2;
+    std::fill(edge_diag, edge_diag + (size_t)NW * npair * 6, 0.0);
+    if (dev && evaluated) {
+      VX_TRY(ctx->scratch2.reserve(sizeof(double) * (size_t)NW * npair * 6));
+      VX_KERNEL(ctx, "k_edge_diag", k_edge_diag<<<dim3((unsigned)blocks_for(npair * 6, 256), NW), 256, 0, st>>>(f->lm_H.as<double>(), W, ctx->scratch2.as<double>()));
+      VX_CUDA(cudaMemcpyAsync(edge_diag, ctx->scratch2.p, sizeof(double) * (size_t)NW * npair * 6, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+      for (int w = 0; w < NW; w++) if (few[w]) std::fill(edge_diag + (size_t)w * npair * 6, edge_diag + (size_t)(w + 1) * npair * 6, 0.0);
+    } else if (!dev && !Hsnap.empty()) {
+      for (int w = 0; w < NW; w++) {
+        int64_t p = 0;
+        for (int i = 0; i < W - 1; i++)
+          for (int j = i + 1; j < W; j++, p++)
+            for (int k = 0; k < 6; k++) edge_diag[((size_t)w * npair + p) * 6 + k] = Hsnap[hsz * w + (size_t)(6 * j + k) * jl + (6 * i + k)];
+      }
+    }
+  }
+  pt.lap("hess_out");
   for (int w = 0; w < NW; w++) {
     if (resis) resis[2 * w + 1] = r2[w];
     if (converged) converged[w] = conv[w];
@@ -485,7 +527,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
 
 extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
                            int *converged, int *accept_trace, int *n_iters) {
-  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, nullptr);
+  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, nullptr, nullptr);
 }
 
 // Lidar_BA_Optimizer::damping_iter on a factor whose voxels are sharded over the ranks of `comm` (each rank's `f` holds the
@@ -494,5 +536,5 @@ extern "C" int vx_ba_lidar(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *he
 extern "C" int vx_ba_lidar_sharded(vx_ctx *ctx, vx_comm *comm, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter,
                                    int thd_num, int *converged, int *accept_trace, int *n_iters) {
   VX_ARG(comm != nullptr && comm->ctx == ctx);
-  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, comm);
+  return vx::ba_lidar_impl(ctx, f, poses, hess_out, resis, max_iter, thd_num, converged, accept_trace, n_iters, nullptr, comm, nullptr);
 }

@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstdarg>
 #include <cstring>
+#include <cstdlib>
+#include <ctime>
 #include <string>
 #include <vector>
 #include "../../include/voxelba.h"
@@ -51,6 +53,9 @@ struct DevBuf {
   size_t cap = 0;
   int reserve(size_t bytes) {
     if (bytes <= cap) return VX_OK;
+    // a LIVE block is being replaced: kernels still queued may read it, and the cache would hand it to another context on
+    // another stream at once (the cudaFree this cache replaced synchronised implicitly).  Growth is rare: wait for the device.
+    if (p) cudaDeviceSynchronize();
     release();
     size_t want = bytes + bytes / 4 + 256, got = 0;
     p = cached_malloc(want, &got);
@@ -60,6 +65,21 @@ struct DevBuf {
   }
   void release() { if (p) cached_free(p, cap); p = nullptr; cap = 0; }
   template <class T> T *as() const { return (T *)p; }
+};
+
+// Wall-clock phase timer for the drivers (VX_TIMING=1 in the environment: synchronises the stream at every lap and prints
+// "[tag] phase ms" on stderr; off: no synchronisation, no output).
+struct PhaseTimer {
+  const char *tag; cudaStream_t st; bool on; double t0;
+  static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return 1e3 * ts.tv_sec + 1e-6 * ts.tv_nsec; }
+  PhaseTimer(const char *tag_, cudaStream_t st_) : tag(tag_), st(st_) { static const bool e = getenv("VX_TIMING") != nullptr; on = e; t0 = on ? now() : 0.0; }
+  void lap(const char *what) {
+    if (!on) return;
+    cudaStreamSynchronize(st);
+    const double t = now();
+    fprintf(stderr, "[%s] %s %.3f ms\n", tag, what, t - t0);
+    t0 = t;
+  }
 };
 
 // Optional per-kernel device timing (bench.py's roofline leg): when enabled every VX_LAUNCH_CHECK'd

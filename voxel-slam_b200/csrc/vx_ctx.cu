@@ -1,6 +1,7 @@
 // vx_ctx.cu — context, error text, version.
 #include <algorithm>
 #include <mutex>
+#include <cstdlib>
 #include "vx_common.cuh"
 
 namespace vx {
@@ -10,8 +11,12 @@ struct FreeBlock { void *p; size_t bytes; int device; };
 std::mutex g_cache_mu;
 std::vector<FreeBlock> g_cache;
 size_t g_cache_bytes = 0;
-constexpr size_t CACHE_MAX_BYTES = (size_t)8 << 30;   // retained at most; beyond it blocks go back to the driver
-constexpr size_t CACHE_MAX_BLOCKS = 256;
+// retained at most (per process, all devices); beyond it blocks go back to the driver.  A 2,000-keyframe global BA cycles through
+// ~6 GB of work buffers per map build at two very different sizes (80 M point instances at the bottom level, 35 M at the top):
+// with 8 GiB retained every build paid cudaFree (device-wide synchronisation) + cudaMalloc for most of them — 100 of the 135 ms
+// of a bottom-level build.  B200 has 180 GB; VX_CACHE_MAX_GB overrides.
+const size_t CACHE_MAX_BYTES = [] { const char *e = std::getenv("VX_CACHE_MAX_GB"); return (size_t)(e ? std::atoi(e) : 48) << 30; }();
+constexpr size_t CACHE_MAX_BLOCKS = 2048;
 }  // namespace
 
 void *cached_malloc(size_t bytes, size_t *got) {
@@ -89,6 +94,7 @@ extern "C" {
 const char *vx_last_error(void) { return vx::g_err; }
 int vx_version(void) { return 100; }
 
+int vx_ctx_destroy(vx_ctx *ctx);
 int vx_ctx_create(int device, vx_ctx **out) {
   VX_ARG(out != nullptr);
   *out = nullptr;
@@ -102,21 +108,24 @@ int vx_ctx_create(int device, vx_ctx **out) {
   VX_CUDA(cudaSetDevice(device));
   vx_ctx *c = new vx_ctx();
   c->device = device;
-  cudaDeviceProp prop;
-  VX_CUDA(cudaGetDeviceProperties(&prop, device));
-  c->sm_count = prop.multiProcessorCount;
-  VX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  {
+  auto init = [&]() -> int {
+    cudaDeviceProp prop;
+    VX_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    VX_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     // earlier groups get the higher priority: the block scheduler then drains them first, so their copies start early
     int least = 0, greatest = 0;
     VX_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     for (int g = 0; g < 8; g++)
       VX_CUDA(cudaStreamCreateWithPriority(&c->group_stream[g], cudaStreamNonBlocking, std::min(least, greatest + g)));
-  }
-  for (auto &e : c->group_ev) VX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  VX_CUDA(cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
-  c->pinned_cap = 1 << 16;
-  VX_CUDA(cudaMallocHost(&c->pinned, c->pinned_cap));
+    for (auto &e : c->group_ev) VX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    VX_CUDA(cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
+    c->pinned_cap = 1 << 16;
+    VX_CUDA(cudaMallocHost(&c->pinned, c->pinned_cap));
+    return VX_OK;
+  };
+  const int rc = init();
+  if (rc != VX_OK) { vx_ctx_destroy(c); return rc; }   // no leak of the context and its streams on a failed set-up
   *out = c;
   return VX_OK;
 }

@@ -89,6 +89,84 @@ __global__ void k_gather_win(const uint32_t *__restrict__ key1, const int32_t *_
   if (i < n) win[i] = (key1[idx[i]] & ((1u << FRAME_BITS) - 1u)) / (uint32_t)W;
 }
 
+// ---- single-key path: (window | root cell re-biased by the scene's minimum cell | path | frame in window) in ONE 64-bit key,
+// one radix sort over exactly the bits in use (43 bits for the 399-window bottom level of C4, 39 for its top level) instead of
+// three stable sorts over 28 + 63 + 9 bits with gathers in between.  Cells are re-biased per axis by the minimum over all point
+// instances (monotone per axis, so the voxel order (window, root cell x/y/z, path) is the multi-sort path's).
+struct CellRange { int lo[3], hi[3]; };
+__device__ __forceinline__ void inst_point(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
+                                           const int64_t *__restrict__ inst_off, const int32_t *__restrict__ pt_frame, int F, const double *__restrict__ poses,
+                                           int64_t j, int &g, d3 &w) {
+  g = pt_frame ? pt_frame[j] : frame_of(inst_off, F, j);
+  const int64_t pt = pt_frame ? j : cloud_off[frame_cloud[g]] + (j - inst_off[g]);
+  w = world_of(poses + 12 * (int64_t)g, (double)xyz[3 * pt], (double)xyz[3 * pt + 1], (double)xyz[3 * pt + 2]);
+}
+__global__ void __launch_bounds__(256)
+k_gba_cell_range(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
+                 const int64_t *__restrict__ inst_off, const int32_t *__restrict__ pt_frame, int F, const double *__restrict__ poses, double vs, int64_t NI,
+                 CellRange *__restrict__ range, int *__restrict__ bad) {
+  int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, hi[3] = {-0x7fffffff, -0x7fffffff, -0x7fffffff};
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < NI; j += (int64_t)gridDim.x * blockDim.x) {
+    int g; d3 w;
+    inst_point(xyz, cloud_off, frame_cloud, inst_off, pt_frame, F, poses, j, g, w);
+    const int64_t k[3] = {key_axis_d(w.x, vs), key_axis_d(w.y, vs), key_axis_d(w.z, vs)};
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      if (k[a] < -(int64_t)KEY_BIAS || k[a] >= (int64_t)KEY_BIAS) *bad = 1;
+      const int c = (int)max((int64_t)-0x7ffffff0, min((int64_t)0x7ffffff0, k[a]));
+      lo[a] = min(lo[a], c); hi[a] = max(hi[a], c);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    lo[a] = __reduce_min_sync(0xffffffffu, lo[a]); hi[a] = __reduce_max_sync(0xffffffffu, hi[a]);
+    if ((threadIdx.x & 31) == 0) { atomicMin(&range->lo[a], lo[a]); atomicMax(&range->hi[a], hi[a]); }
+  }
+}
+struct KeyLayout { int lo[3]; int bx, by, bz, pbits, fbits, W; };
+__global__ void __launch_bounds__(256)
+k_gba_key64(const float *__restrict__ xyz, const int64_t *__restrict__ cloud_off, const int32_t *__restrict__ frame_cloud,
+            const int64_t *__restrict__ inst_off, const int32_t *__restrict__ pt_frame, int F, const double *__restrict__ poses, GbaP prm, KeyLayout kl,
+            int64_t NI, uint64_t *__restrict__ key, int32_t *__restrict__ idx) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= NI) return;
+  int g; d3 w;
+  inst_point(xyz, cloud_off, frame_cloud, inst_off, pt_frame, F, poses, j, g, w);
+  const int64_t kx = key_axis_d(w.x, prm.vs), ky = key_axis_d(w.y, prm.vs), kz = key_axis_d(w.z, prm.vs);
+  double cx = __dmul_rn(__dadd_rn(0.5, (double)kx), prm.vs), cy = __dmul_rn(__dadd_rn(0.5, (double)ky), prm.vs), cz = __dmul_rn(__dadd_rn(0.5, (double)kz), prm.vs);
+  float q = (float)(prm.vs / 4.0);
+  uint32_t path = 0;
+  for (int l = 0; l < prm.L; l++) {      // the descent of k_gba_point
+    const int bx = w.x > cx, by = w.y > cy, bz = w.z > cz;
+    path = (path << 3) | (uint32_t)(4 * bx + 2 * by + bz);
+    const double dq = (double)q;
+    cx = __dadd_rn(cx, bx ? dq : -dq); cy = __dadd_rn(cy, by ? dq : -dq); cz = __dadd_rn(cz, bz ? dq : -dq);
+    q = q / 2.0f;
+  }
+  const uint64_t win = (uint64_t)(g / kl.W), fiw = (uint64_t)(g % kl.W);
+  uint64_t k = win;
+  k = (k << kl.bx) | (uint64_t)(kx - kl.lo[0]);
+  k = (k << kl.by) | (uint64_t)(ky - kl.lo[1]);
+  k = (k << kl.bz) | (uint64_t)(kz - kl.lo[2]);
+  k = (k << kl.pbits) | path;
+  k = (k << kl.fbits) | fiw;
+  key[j] = k;
+  idx[j] = (int32_t)j;
+}
+// sorted single key -> the (key1, key2) pair the head / segment kernels read: key1 = path << FRAME_BITS | global frame,
+// key2 = window | re-biased root cell (only compared for equality)
+__global__ void k_gba_unpack64(const uint64_t *__restrict__ key, KeyLayout kl, int64_t NI, uint32_t *__restrict__ k1, uint64_t *__restrict__ k2) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= NI) return;
+  const uint64_t k = key[i];
+  const uint32_t fiw = (uint32_t)(k & ((1ull << kl.fbits) - 1ull));
+  const uint32_t path = (uint32_t)((k >> kl.fbits) & ((1ull << kl.pbits) - 1ull));
+  const uint64_t root = k >> (kl.fbits + kl.pbits);
+  const uint32_t win = (uint32_t)(root >> (kl.bx + kl.by + kl.bz));
+  k1[i] = (path << FRAME_BITS) | (win * (uint32_t)kl.W + fiw);
+  k2[i] = root;
+}
+
 // 3. head flags for the segments and for the nodes of every layer (sorted order)
 __global__ void k_gba_heads(const uint32_t *__restrict__ k1, const uint64_t *__restrict__ k2, int W, int L, int64_t n, int32_t *__restrict__ hseg,
                             int32_t *__restrict__ hn0, int32_t *__restrict__ hn1, int32_t *__restrict__ hn2, int32_t *__restrict__ hn3) {
@@ -397,33 +475,71 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   VX_CUDA(cudaMemcpyAsync(d_poses.p, poses, sizeof(vx_pose) * F, cudaMemcpyHostToDevice, st));
   VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
 
-  // ---- 1. keys (kept in instance order; only the permutation travels through the sorts)
-  DevBuf &k1i = T.make(), &k2i = T.make(), &k1t = T.make(), &k2t = T.make(), &k2u = T.make(), &ia = T.make(), &ib = T.make();
-  VX_TRY(k1i.reserve(4 * NI)); VX_TRY(k2i.reserve(8 * NI)); VX_TRY(k1t.reserve(4 * NI)); VX_TRY(k2t.reserve(8 * NI)); VX_TRY(k2u.reserve(8 * NI));
-  VX_TRY(ia.reserve(4 * NI)); VX_TRY(ib.reserve(4 * NI));
-  VX_KERNEL(ctx, "k_gba_point", k_gba_point<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
-                                                                                d_poses.as<double>(), prm, NI, k1i.as<uint32_t>(), k2i.as<uint64_t>(), ia.as<int32_t>(), d_bad.as<int>()));
-  // ---- 2. stable sorts: (path, frame), then root key, then window
-  VX_TRY(sort_pairs<uint32_t>(ctx, k1i.as<uint32_t>(), k1t.as<uint32_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, FRAME_BITS + 3 * L));
-  VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), ib.as<int32_t>(), k2t.as<uint64_t>(), NI));
-  VX_TRY(sort_pairs<uint64_t>(ctx, k2t.as<uint64_t>(), k2u.as<uint64_t>(), ib.as<int32_t>(), ia.as<int32_t>(), NI, 0, 63));
-  int32_t *sidx = ia.as<int32_t>();
-  if (NW > 1) {
-    VX_KERNEL(ctx, "k_gather_win", k_gather_win<<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), ia.as<int32_t>(), W, k1t.as<uint32_t>(), NI));
-    VX_TRY(sort_pairs<uint32_t>(ctx, k1t.as<uint32_t>(), reinterpret_cast<uint32_t *>(k2t.p), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, bits_for(NW)));
-    sidx = ib.as<int32_t>();
-  }
+  // ---- 1 + 2. keys and order.  Single-key path when (window | re-biased root cell | path | frame in window) fits 64 bits.
+  DevBuf &k1t = T.make(), &k2u = T.make(), &ia = T.make(), &ib = T.make();
+  VX_TRY(k1t.reserve(4 * NI)); VX_TRY(k2u.reserve(8 * NI)); VX_TRY(ia.reserve(4 * NI)); VX_TRY(ib.reserve(4 * NI));
+  int32_t *sidx = nullptr;
   uint32_t *k1s = k1t.as<uint32_t>();
   uint64_t *k2s = k2u.as<uint64_t>();
-  VX_KERNEL(ctx, "k_gather", k_gather<uint32_t><<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), sidx, k1s, NI));
-  VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), sidx, k2s, NI));
-  {
+  bool single_key = getenv("VX_GBA_MULTISORT") == nullptr;
+  KeyLayout kl;
+  if (single_key) {
+    DevBuf &d_rng = T.make();
+    VX_TRY(d_rng.reserve(sizeof(CellRange)));
+    CellRange r0;
+    for (int a = 0; a < 3; a++) { r0.lo[a] = 0x7fffffff; r0.hi[a] = -0x7fffffff; }
+    VX_CUDA(cudaMemcpyAsync(d_rng.p, &r0, sizeof(r0), cudaMemcpyHostToDevice, st));
+    const int grid = (int)std::min<int64_t>(blocks_for(NI, 256), (int64_t)ctx->sm_count * 8);
+    VX_KERNEL(ctx, "k_gba_cell_range", k_gba_cell_range<<<grid, 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
+                                                                             d_poses.as<double>(), prm.vs, NI, d_rng.as<CellRange>(), d_bad.as<int>()));
     int bad = 0;
+    VX_CUDA(cudaMemcpyAsync(&r0, d_rng.p, sizeof(r0), cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
     if (bad) { set_error("OctreeGBA::cut_voxel: a root cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+    for (int a = 0; a < 3; a++) kl.lo[a] = r0.lo[a];
+    kl.bx = bits_for((int64_t)r0.hi[0] - r0.lo[0] + 1); kl.by = bits_for((int64_t)r0.hi[1] - r0.lo[1] + 1); kl.bz = bits_for((int64_t)r0.hi[2] - r0.lo[2] + 1);
+    kl.pbits = std::max(1, 3 * L); kl.fbits = bits_for(W); kl.W = W;
+    const int total = bits_for(NW) + kl.bx + kl.by + kl.bz + kl.pbits + kl.fbits;
+    if (total > 64) single_key = false;
+    else {
+      DevBuf &ka = T.make(), &kb = T.make();
+      VX_TRY(ka.reserve(8 * NI)); VX_TRY(kb.reserve(8 * NI));
+      VX_KERNEL(ctx, "k_gba_key64", k_gba_key64<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
+                                                                                  d_poses.as<double>(), prm, kl, NI, ka.as<uint64_t>(), ia.as<int32_t>()));
+      VX_TRY(sort_pairs<uint64_t>(ctx, ka.as<uint64_t>(), kb.as<uint64_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, total));
+      VX_KERNEL(ctx, "k_gba_unpack64", k_gba_unpack64<<<blocks_for(NI, 256), 256, 0, st>>>(kb.as<uint64_t>(), kl, NI, k1s, k2s));
+      sidx = ib.as<int32_t>();
+      VX_CUDA(cudaStreamSynchronize(st));
+      ka.release(); kb.release();
+    }
   }
-  k2i.release(); k2t.release();
+  if (!single_key) {
+    // three stable sorts: (path, frame), then root key, then window (any scene extent)
+    DevBuf &k1i = T.make(), &k2i = T.make(), &k2t = T.make();
+    VX_TRY(k1i.reserve(4 * NI)); VX_TRY(k2i.reserve(8 * NI)); VX_TRY(k2t.reserve(8 * NI));
+    VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
+    VX_KERNEL(ctx, "k_gba_point", k_gba_point<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
+                                                                                  d_poses.as<double>(), prm, NI, k1i.as<uint32_t>(), k2i.as<uint64_t>(), ia.as<int32_t>(), d_bad.as<int>()));
+    VX_TRY(sort_pairs<uint32_t>(ctx, k1i.as<uint32_t>(), k1t.as<uint32_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, FRAME_BITS + 3 * L));
+    VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), ib.as<int32_t>(), k2t.as<uint64_t>(), NI));
+    VX_TRY(sort_pairs<uint64_t>(ctx, k2t.as<uint64_t>(), k2u.as<uint64_t>(), ib.as<int32_t>(), ia.as<int32_t>(), NI, 0, 63));
+    sidx = ia.as<int32_t>();
+    if (NW > 1) {
+      VX_KERNEL(ctx, "k_gather_win", k_gather_win<<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), ia.as<int32_t>(), W, k1t.as<uint32_t>(), NI));
+      VX_TRY(sort_pairs<uint32_t>(ctx, k1t.as<uint32_t>(), reinterpret_cast<uint32_t *>(k2t.p), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, bits_for(NW)));
+      sidx = ib.as<int32_t>();
+    }
+    VX_KERNEL(ctx, "k_gather", k_gather<uint32_t><<<blocks_for(NI, 256), 256, 0, st>>>(k1i.as<uint32_t>(), sidx, k1s, NI));
+    VX_KERNEL(ctx, "k_gather", k_gather<uint64_t><<<blocks_for(NI, 256), 256, 0, st>>>(k2i.as<uint64_t>(), sidx, k2s, NI));
+    {
+      int bad = 0;
+      VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaStreamSynchronize(st));
+      if (bad) { set_error("OctreeGBA::cut_voxel: a root cell index does not fit the 21-bit packed key"); return VX_ERR_ARG; }
+    }
+    k1i.release(); k2i.release(); k2t.release();
+  }
 
   // ---- 3. heads, ids, starts
   DevBuf &hseg = T.make(), &iseg = T.make(), &seg_start = T.make();

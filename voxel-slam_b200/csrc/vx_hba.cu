@@ -23,7 +23,8 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
   const int jl = 6 * W;
   const size_t hsz = (size_t)jl * jl;
   const int64_t cap = (int64_t)W * (W - 1) / 2;   // edge slots per window
-  std::vector<double> hess(hsz * NW, 0.0);
+  // the full snapshot only when the caller wants it; the edges need 6 numbers per frame pair (k_edge_diag)
+  std::vector<double> hess(hess_out ? hsz * NW : 0, 0.0), ediag((size_t)NW * cap * 6, 0.0);
   std::vector<int> cflag(NW, 0), done(NW, 0), status(NW, VX_OK), nvox(NW, 0);
   std::vector<double> cthre(NW, 0.05);
   const int up = 4;   // voxelslam.cpp:2867
@@ -50,15 +51,18 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         for (int i = 0; i < W; i++) ps[(size_t)a * W + i] = poses[ws[a] * W + i];
       vx_factor *fac = nullptr;
       VX_TRY(vx_factor_create(ctx, W, ns, &fac));
-      std::vector<double> hs(hsz * ns), rs(2 * (size_t)ns);
+      std::vector<double> hs(hess_out ? hsz * ns : 0), rs(2 * (size_t)ns), ed((size_t)ns * cap * 6);
       std::vector<int> conv(ns), wst(ns), nit(ns, 0);
+      PhaseTimer pt("hba_core", ctx->stream);
       int s = build(ws, ps.data(), gp, fac);
-      if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hs.data(), rs.data(), up, thread_num, conv.data(), nullptr, nit.data(), wst.data(), comm);
+      pt.lap("build");
+      if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hess_out ? hs.data() : nullptr, rs.data(), up, thread_num, conv.data(), nullptr, nit.data(), wst.data(), comm, ed.data());
       std::vector<int32_t> wv(ns + 1, 0);
       if (s == VX_OK && fac->V > 0) {
         cudaMemcpyAsync(wv.data(), fac->wv_off.p, sizeof(int32_t) * (ns + 1), cudaMemcpyDeviceToHost, ctx->stream);
         cudaStreamSynchronize(ctx->stream);
       }
+      pt.lap("damping_iter");
       if (n_voxel_frames_evaluated) *n_voxel_frames_evaluated += fac->nnz * fac->n_hess_evals;
       vx_factor_free(fac);
       VX_TRY(s);
@@ -67,7 +71,8 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         nvox[w] = wv[a + 1] - wv[a];
         if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
         for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
-        std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
+        if (hess_out) std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
+        std::copy(ed.begin() + (size_t)a * cap * 6, ed.begin() + (size_t)(a + 1) * cap * 6, ediag.begin() + (size_t)w * cap * 6);
         const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
         if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
         // voxelslam.cpp:2906-2917
@@ -83,13 +88,14 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
   for (int w = 0; w < NW; w++) {
     int64_t ne = 0;
     if (status[w] == VX_OK && edges) {
-      const double *H = hess.data() + hsz * w;
+      const double *D = ediag.data() + (size_t)w * cap * 6;
+      int64_t pr = 0;
       for (int i = 0; i < W - 1; i++)
-        for (int j = i + 1; j < W; j++) {
+        for (int j = i + 1; j < W; j++, pr++) {
           vx_pgo_edge e;
           bool add = true;
           for (int k = 0; k < 6; k++) {
-            const double hc = std::fabs(H[(size_t)(6 * j + k) * jl + (6 * i + k)]);
+            const double hc = std::fabs(D[pr * 6 + k]);
             if (hc < 1e-6) { add = false; break; }
             e.cov[k] = 1.0 / hc;
           }

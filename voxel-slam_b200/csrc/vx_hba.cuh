@@ -10,7 +10,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
 int gba_build_sharded_impl(vx_ctx *ctx, vx_comm *comm, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *cloud_frame,
                            const vx_pose *poses, const vx_gba_params *params, vx_factor *f, int64_t *n_owned);
 int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, double *resis, int max_iter, int thd_num,
-                  int *converged, int *accept_trace, int *n_iters, int *win_status, vx_comm *comm);
+                  int *converged, int *accept_trace, int *n_iters, int *win_status, vx_comm *comm, double *edge_diag);
 using HbaBuildFn = std::function<int(const std::vector<int> &ws, const vx_pose *ps, const vx_gba_params &gp, vx_factor *fac)>;
 int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int NW,
              const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges, double *hess_out, double *resis_out,

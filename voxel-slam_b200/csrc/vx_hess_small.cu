@@ -460,10 +460,13 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo,
   const int64_t items = (int64_t)f->n_win * splits;     // partials are indexed by the global item
   VX_TRY(f->part_t.reserve(sizeof(double) * items * Cfg::T8 * 64));
   VX_TRY(f->part_d.reserve(sizeof(double) * items * W * NF_E));
-  static bool attr_set = false;
-  if (!attr_set) {
-    VX_CUDA(cudaFuncSetAttribute(k_hess_small<W, NROLES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-    attr_set = true;
+  {   // the opt-in is per DEVICE, not per process: one flag per device ordinal
+    static bool attr_set[64] = {};
+    const int d = ctx->device & 63;
+    if (!attr_set[d]) {
+      VX_CUDA(cudaFuncSetAttribute(k_hess_small<W, NROLES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+      attr_set[d] = true;
+    }
   }
   VX_KERNEL(ctx, "k_hess_small", k_hess_small<W, NROLES, MINB><<<(unsigned)((w_hi - w_lo) * splits), Cfg::NT, Cfg::SMEM, st>>>(
       f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz,
