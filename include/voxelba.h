@@ -395,7 +395,8 @@ int vx_hba_schedule(const int32_t *session_sizes, int n_sessions, int wdsize, in
  *   top_poses / top_kf  optimized pose and first keyframe of every top-level frame (n_top written; capacity = number of windows)
  *   stats (16 doubles, may be NULL): [0] windows, [1] top-level frames, [2] voxel-frames through acc_evaluate2 in all LM passes
  *           (this rank), [3..8] ms upload / bottom / merge / gather / top / total, [9] points in the top-level map,
- *           [10] bottom voxel-frame evaluations, [11] top voxel-frame evaluations (this rank) */
+ *           [10] bottom voxel-frame evaluations, [11] top voxel-frame evaluations (this rank), [12] / [13] voxel-frames through
+ *           evaluate_only_residual at the bottom / top, [14] / [15] acc_evaluate2 / evaluate_only_residual passes at the top level */
 typedef struct vx_hba_global_params {
   vx_hba_params hba;
   int32_t wdsize, mgsize;            /* 10, 5     voxelslam.cpp:3033-3034 */
@@ -403,11 +404,20 @@ typedef struct vx_hba_global_params {
   int32_t bottom_thread_num;         /* 2         :3096 */
   int32_t total_max_iter;            /* GBA/total_max_iter :3025 */
   int32_t top_thread_num;            /* 5         :3035 */
+  int32_t xyz_on_device;             /* != 0: `xyz` is a DEVICE pointer to ALL keyframe clouds (resident keyframes: no upload) */
+  int32_t keep_factors;              /* != 0: the LidarFactors of the last outer iteration are kept for vx_hba_global_take_factor */
 } vx_hba_global_params;
 int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const int64_t *cloud_off, int n_kf, const int32_t *kf_session,
                   const int32_t *kf_id, const vx_pose *kf_x0, const vx_pose *kf_x, const int32_t *cnct_map, int n_cnct,
                   const vx_hba_global_params *prm, vx_pgo_edge *edges1, int64_t cap1, int64_t *n1, vx_pgo_edge *edges2, int64_t cap2,
                   int64_t *n2, vx_pose *top_poses, int32_t *top_kf, int32_t *n_top, double *stats);
+/* The LidarFactor (this rank's share) a vx_hba_global call with keep_factors left behind: which = 0 the batch of full bottom
+ * windows, which = 1 the top level; poses (may be NULL, n_windows * W entries) = the poses it was last evaluated at.  The caller
+ * owns the handle (vx_factor_free).  *out = NULL when nothing was kept. */
+int vx_hba_global_take_factor(vx_ctx *ctx, int which, vx_factor **out);
+/* acc_evaluate2 on a factor whose voxels are sharded over the ranks, results summed over the ranks on the device (one packed
+ * all-reduce, voxel_map.hpp:382-384 across GPUs); asynchronous on the ctx stream, results in vx_factor_device_buffers. */
+int vx_factor_hessian_sharded_async(vx_ctx *ctx, vx_comm *comm, vx_factor *f);
 
 /* ---- D1 / D2: LIO ESIKF point-to-plane update -----------------------------------------------------------
  * The voxel map as OctoTree::match reads it (voxel_map.hpp:1649-1721), flattened by the caller: one record per

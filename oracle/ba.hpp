@@ -7,12 +7,16 @@
 // in range order" which is arithmetically what the reference's join loop does
 // (voxel_map.hpp:376-386); `use_threads` only decides whether the ranges run concurrently.
 #pragma once
+#include <atomic>
 #include "types.hpp"
 #include <thread>
 #include <cstdio>
 #include <cstdlib>
 
 namespace orc {
+
+// bench bookkeeping: voxel-frames that went through acc_evaluate2 since the last reset (orc_vf_counter)
+inline std::atomic<int64_t> g_voxel_frames_evaluated{0};
 
 class LidarFactor {
 public:
@@ -50,6 +54,11 @@ public:
     for (int a = head; a < end; a++) {
       const std::vector<PointCluster> &sig_orig = plvec_voxels[a];
       double coe = coeffs[a];
+      {   // bench bookkeeping only (no reference counterpart): voxel-frames this call goes through, for the CPU arm's metric
+        int64_t k = 0;
+        for (const PointCluster &pc : sig_orig) k += pc.N != 0;
+        g_voxel_frames_evaluated.fetch_add(k, std::memory_order_relaxed);
+      }
 
       V3 lmbd = eig_values[a];
       M3 U = eig_vectors[a];

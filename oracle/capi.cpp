@@ -655,6 +655,12 @@ void orc_btc_plane_cloud(const float *xyz, int64_t n, double voxel_size, double 
   for (size_t k = 0; k < pl.size() && (int64_t)k < cap; k++) std::memcpy(out + 10 * k, &pl[k], sizeof(BtcPlane));
 }
 
+// voxel-frames evaluated by acc_evaluate2 since the last reset (bench.py's CPU arm); reset != 0 clears after reading
+int64_t orc_vf_counter(int reset) {
+  const int64_t v = g_voxel_frames_evaluated.load();
+  if (reset) g_voxel_frames_evaluated.store(0);
+  return v;
+}
 double orc_now() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }

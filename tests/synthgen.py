@@ -21,7 +21,7 @@ _lib = None
 def build(force=False):
     if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(_SRC):
         tmp = _LIB + ".%d.tmp" % os.getpid()
-        subprocess.run(["gcc", "-O3", "-march=native", "-fopenmp", "-shared", "-fPIC", "-o", tmp, _SRC, "-lm"], check=True)
+        subprocess.run(["gcc", "-O3", "-fopenmp", "-shared", "-fPIC", "-o", tmp, _SRC, "-lm"], check=True)
         os.replace(tmp, _LIB)
     return _LIB
 

@@ -226,8 +226,9 @@ def hba_merge_clouds(ctx, clouds, poses, W, n_windows, voxel_size, frame_cloud=N
 
 # ---- multi-GPU (vx_comm_*) and the two-level hierarchical GBA ----------------------------------------------------------------
 hba_global_params_dtype = np.dtype([("hba", hba_params_dtype), ("wdsize", "<i4"), ("mgsize", "<i4"), ("bottom_max_iter", "<i4"),
-                                    ("bottom_thread_num", "<i4"), ("total_max_iter", "<i4"), ("top_thread_num", "<i4")])
-assert hba_global_params_dtype.itemsize == 104 + 24
+                                    ("bottom_thread_num", "<i4"), ("total_max_iter", "<i4"), ("top_thread_num", "<i4"), ("xyz_on_device", "<i4"),
+                                    ("keep_factors", "<i4")])
+assert hba_global_params_dtype.itemsize == 104 + 32
 
 
 def comm_unique_id():
@@ -294,8 +295,14 @@ def hba_global_params(local, gba, max_layer, total_max_iter=1, wdsize=10, mgsize
 class HbaGlobalJob:
     """Host buffers of one vx_hba_global call, prepared once (bench.py times run() only)."""
 
-    def __init__(self, xyz, off, kf_session, kf_x0, prm, kf_x=None, kf_id=None, cnct_map=None):
-        self.xyz = xyz if (isinstance(xyz, np.ndarray) and xyz.dtype == np.float32 and xyz.flags.c_contiguous) else np.ascontiguousarray(xyz, dtype=np.float32)
+    def __init__(self, xyz, off, kf_session, kf_x0, prm, kf_x=None, kf_id=None, cnct_map=None, xyz_device_ptr=None):
+        """xyz: host float32 (n,3) array (pinned or pageable), or None with xyz_device_ptr = device address of all clouds."""
+        prm = prm.copy()
+        if xyz_device_ptr is not None:
+            self.xyz = None; self.xyz_arg = C.c_void_p(int(xyz_device_ptr)); prm["xyz_on_device"] = 1
+        else:
+            self.xyz = xyz if (isinstance(xyz, np.ndarray) and xyz.dtype == np.float32 and xyz.flags.c_contiguous) else np.ascontiguousarray(xyz, dtype=np.float32)
+            self.xyz_arg = _p(self.xyz)
         self.off = np.ascontiguousarray(off, dtype=np.int64)
         self.n_kf = self.off.size - 1
         self.sess = np.ascontiguousarray(kf_session, dtype=np.int32)
@@ -316,14 +323,15 @@ class HbaGlobalJob:
 
     def run(self, ctx, comm=None):
         n1, n2, nt = C.c_int64(0), C.c_int64(0), C.c_int32(0)
-        _chk(ctx.lib.vx_hba_global(ctx.h, comm.h if comm is not None else None, _p(self.xyz), _p(self.off), C.c_int(self.n_kf), _p(self.sess), _p(self.ids),
+        _chk(ctx.lib.vx_hba_global(ctx.h, comm.h if comm is not None else None, self.xyz_arg, _p(self.off), C.c_int(self.n_kf), _p(self.sess), _p(self.ids),
                                    _p(self.x0), _p(self.x), _p(self.cnct), C.c_int(0 if self.cnct is None else self.cnct.size), _p(self.prm),
                                    _p(self.e1), C.c_int64(self.cap1), C.byref(n1), _p(self.e2), C.c_int64(self.cap2), C.byref(n2), _p(self.tp), _p(self.tk),
                                    C.byref(nt), _p(self.stats)))
         st = self.stats
         return dict(edges1=self.e1[:n1.value], edges2=self.e2[:n2.value], top_poses=self.tp[:nt.value], top_kf=self.tk[:nt.value],
                     stats=dict(windows=int(st[0]), top_frames=int(st[1]), voxel_frame_evals=int(st[2]), ms_upload=st[3], ms_bottom=st[4], ms_merge=st[5],
-                               ms_gather=st[6], ms_top=st[7], ms_total=st[8], top_points=int(st[9]), vf_evals_bottom=int(st[10]), vf_evals_top=int(st[11])))
+                               ms_gather=st[6], ms_top=st[7], ms_total=st[8], top_points=int(st[9]), vf_evals_bottom=int(st[10]), vf_evals_top=int(st[11]), vf_res_bottom=int(st[12]),
+                               vf_res_top=int(st[13]), top_hess_passes=int(st[14]), top_res_passes=int(st[15])))
 
 
 def hba_global(ctx, clouds, kf_session, kf_x0, local, gba, max_layer, total_max_iter=1, kf_x=None, kf_id=None, cnct_map=None, comm=None, **kw):
@@ -630,12 +638,28 @@ class DevArray:
 class Factor:
     """Device-resident LidarFactor / VOX_HESS (voxel_map.hpp:124-339)."""
 
-    def __init__(self, ctx, win_size, n_windows=1):
+    def __init__(self, ctx, win_size, n_windows=1, handle=None):
         self.ctx, self.lib = ctx, ctx.lib
         self.W, self.n_win = win_size, n_windows
+        if handle is not None:
+            self.h = handle
+            return
         h = C.c_void_p()
         _chk(self.lib.vx_factor_create(ctx.h, C.c_int(win_size), C.c_int(n_windows), C.byref(h)))
         self.h = h
+
+    @classmethod
+    def taken_from_hba_global(cls, ctx, which):
+        """vx_hba_global_take_factor: the factor a keep_factors run left behind (0 bottom batch, 1 top level) or None."""
+        h = C.c_void_p()
+        _chk(ctx.lib.vx_hba_global_take_factor(ctx.h, C.c_int(which), C.byref(h)))
+        if not h.value:
+            return None
+        ctx.lib.vx_factor_win_size.argtypes = [C.c_void_p]; ctx.lib.vx_factor_num_windows.argtypes = [C.c_void_p]
+        return cls(ctx, int(ctx.lib.vx_factor_win_size(h)), int(ctx.lib.vx_factor_num_windows(h)), handle=h)
+
+    def hessian_sharded_async(self, comm):
+        _chk(self.lib.vx_factor_hessian_sharded_async(self.ctx.h, comm.h if comm is not None else None, self.h))
 
     def free(self):
         if self.h:

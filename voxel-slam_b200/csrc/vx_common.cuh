@@ -110,6 +110,7 @@ struct vx_ctx {
   int64_t ldlt_launches = 0;
   double *ldlt_B = nullptr, *ldlt_F = nullptr;
   size_t pinned_cap = 0;
+  struct vx_factor *kept[2] = {nullptr, nullptr};   // vx_hba_global(keep_factors): bottom batch, top level
 };
 
 namespace vx {

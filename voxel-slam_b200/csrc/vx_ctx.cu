@@ -138,6 +138,7 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   for (auto &e : ctx->group_ev) if (e) cudaEventDestroy(e);
   if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
   for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+  for (auto &k : ctx->kept) if (k) { vx_factor_free(k); k = nullptr; }
   ctx->scratch.release();
   ctx->scratch2.release();
   if (ctx->ldlt_exec) cudaGraphExecDestroy(ctx->ldlt_exec);

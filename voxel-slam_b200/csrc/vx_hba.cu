@@ -19,7 +19,7 @@ namespace vx {
 // (then NW == 1 and `comm` sums every evaluation over the ranks).
 int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int NW,
              const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges, double *hess_out, double *resis_out,
-             int32_t *n_voxels_out, int32_t *status_out, int64_t *n_voxel_frames_evaluated) {
+             int32_t *n_voxels_out, int32_t *status_out, int64_t *n_voxel_frames_evaluated, vx_factor **keep) {
   const int jl = 6 * W;
   const size_t hsz = (size_t)jl * jl;
   const int64_t cap = (int64_t)W * (W - 1) / 2;   // edge slots per window
@@ -63,8 +63,12 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         cudaStreamSynchronize(ctx->stream);
       }
       pt.lap("damping_iter");
-      if (n_voxel_frames_evaluated) *n_voxel_frames_evaluated += fac->nnz * fac->n_hess_evals;
-      vx_factor_free(fac);
+      if (n_voxel_frames_evaluated) {   // [0] voxel-frames through acc_evaluate2, [1] through evaluate_only_residual, [2] / [3] passes of each
+        n_voxel_frames_evaluated[0] += fac->nnz * fac->n_hess_evals; n_voxel_frames_evaluated[1] += fac->nnz * fac->n_res_evals;
+        n_voxel_frames_evaluated[2] += fac->n_hess_evals; n_voxel_frames_evaluated[3] += fac->n_res_evals;
+      }
+      if (keep && s == VX_OK) { if (*keep) vx_factor_free(*keep); *keep = fac; }   // the latest factor stays with the caller
+      else vx_factor_free(fac);
       VX_TRY(s);
       for (int a = 0; a < ns; a++) {
         const int w = ws[a];

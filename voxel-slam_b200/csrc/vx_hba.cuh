@@ -14,7 +14,8 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
 using HbaBuildFn = std::function<int(const std::vector<int> &ws, const vx_pose *ps, const vx_gba_params &gp, vx_factor *fac)>;
 int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t *frame_id, const int32_t *frame_mp, vx_pose *poses, int W, int NW,
              const vx_hba_params *prm, int max_iter, int thread_num, vx_pgo_edge *edges, int64_t *n_edges, double *hess_out, double *resis_out,
-             int32_t *n_voxels_out, int32_t *status_out, int64_t *n_voxel_frames_evaluated);
+             int32_t *n_voxels_out, int32_t *status_out, int64_t *n_voxel_frames_evaluated, vx_factor **keep = nullptr);
+int allreduce_evaluation(vx_ctx *ctx, vx_comm *comm, vx_factor *f);
 // Merged submap clouds of a batch of windows on the device (voxelslam.cpp:2954-2985): window w = frames [wf_off[w], wf_off[w+1]),
 // every frame's cloud moved into the frame of the window's first pose, down_sampling_voxel(leaf) per window.
 //   d_out_xyz   float triples of the cells, windows back to back (ascending packed cell key inside a window); reserved here

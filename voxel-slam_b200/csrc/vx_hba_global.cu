@@ -94,15 +94,20 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
   std::vector<vx_pgo_edge> eall((size_t)NWt * ecap);
   std::vector<int64_t> ecnt(NWt, 0);
   std::vector<int64_t> sub_off(NWl + 1, 0);
-  int64_t vf_bottom = 0, vf_top = 0, top_points = 0;
+  int64_t vf_bottom[4] = {0, 0, 0, 0}, vf_top[4] = {0, 0, 0, 0}, top_points = 0;
   double t_upload = 0, t_bottom = 0, t_merge = 0, t_gather = 0, t_top = 0;
   int ntop = 0;
 
   auto body = [&]() -> int {
     double t0 = now_ms();
-    VX_TRY(d_xyz.reserve(12 * (size_t)std::max<int64_t>(NPl, 1)));
+    const float *d_kf = nullptr;                 // this rank's keyframe clouds on the device
+    if (prm->xyz_on_device) d_kf = xyz + 3 * cloud_off[kf_lo];
+    else {
+      VX_TRY(d_xyz.reserve(12 * (size_t)std::max<int64_t>(NPl, 1)));
+      if (NPl) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz + 3 * cloud_off[kf_lo], 12 * (size_t)NPl, cudaMemcpyHostToDevice, st));
+      d_kf = d_xyz.as<float>();
+    }
     VX_TRY(d_coff.reserve(8 * (size_t)(n_lc + 1)));
-    if (NPl) VX_CUDA(cudaMemcpyAsync(d_xyz.p, xyz + 3 * cloud_off[kf_lo], 12 * (size_t)NPl, cudaMemcpyHostToDevice, st));
     VX_CUDA(cudaMemcpyAsync(d_coff.p, lcoff.data(), 8 * (size_t)(n_lc + 1), cudaMemcpyHostToDevice, st));
     VX_CUDA(cudaStreamSynchronize(st));
     t_upload = now_ms() - t0; t0 = now_ms();
@@ -144,10 +149,10 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
         std::vector<int32_t> fc(ws.size() * (size_t)W);
         for (size_t b = 0; b < ws.size(); b++)
           for (int i = 0; i < W; i++) fc[b * W + i] = fcl[(size_t)ws[b] * W + i];
-        return gba_build_impl(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), lcoff.data(), n_lc, fc.data(), p, &gp, fac, nullptr, 0);
+        return gba_build_impl(ctx, d_kf, d_coff.as<int64_t>(), lcoff.data(), n_lc, fc.data(), p, &gp, fac, nullptr, 0);
       };
       VX_TRY(hba_core(ctx, nullptr, build, ids.data(), mps.data(), ps.data(), W, ng, &prm->hba, prm->bottom_max_iter, prm->bottom_thread_num, ge.data(), gn.data(),
-                      nullptr, nullptr, nullptr, gst.data(), &vf_bottom));
+                      nullptr, nullptr, nullptr, gst.data(), vf_bottom, (prm->keep_factors && W == prm->wdsize) ? &ctx->kept[0] : nullptr));
       for (int b = 0; b < ng; b++) {
         const int a = grp[b], w = lo + a;
         if (gst[b] != VX_OK) { set_error("Too Less Voxel: bottom window %d (keyframes %d..%d)", w, wkf[w], wkf[w] + W - 1); return gst[b]; }
@@ -162,7 +167,7 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
     // ---- one submap per window: merged cloud in the frame of the window's first keyframe, down-sampled at voxel_size / 8 ---------
     if (NWl > 0) {
       int overflow = 0;
-      VX_TRY(merge_clouds_batched(ctx, d_xyz.as<float>(), lcoff.data(), n_lc, fcloud.data(), fmp.data(), wposes.data(), wf_off.data(), NWl,
+      VX_TRY(merge_clouds_batched(ctx, d_kf, lcoff.data(), n_lc, fcloud.data(), fmp.data(), wposes.data(), wf_off.data(), NWl,
                                   prm->hba.voxel_size / 8, d_sub, sub_off.data(), nullptr, &overflow));
     }
     d_xyz.release();
@@ -267,7 +272,7 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
       int64_t tn = 0;
       int32_t tst = VX_OK;
       VX_TRY(hba_core(ctx, comm, build, tid.data(), tmp.data(), tp.data(), ntop, 1, &prm->hba, prm->total_max_iter, prm->top_thread_num, te.data(), &tn, nullptr, nullptr,
-                      nullptr, &tst, &vf_top));
+                      nullptr, &tst, vf_top, prm->keep_factors ? &ctx->kept[1] : nullptr));
       if (tst != VX_OK) { set_error("Too Less Voxel: top-level map over %d submaps", ntop); return tst; }
       if (edges2) {
         if (tn > cap2) { set_error("vx_hba_global: edges2 capacity %lld too small for %lld", (long long)cap2, (long long)tn); return VX_ERR_ARG; }
@@ -286,9 +291,23 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
   cudaStreamSynchronize(st);
   for (DevBuf *b : all) b->release();
   if (stats) {
-    stats[0] = NWt; stats[1] = ntop; stats[2] = (double)(vf_bottom + vf_top);
+    stats[0] = NWt; stats[1] = ntop; stats[2] = (double)(vf_bottom[0] + vf_top[0]);
     stats[3] = t_upload; stats[4] = t_bottom; stats[5] = t_merge; stats[6] = t_gather; stats[7] = t_top; stats[8] = now_ms() - t_begin;
-    stats[9] = (double)top_points; stats[10] = (double)vf_bottom; stats[11] = (double)vf_top;
+    stats[9] = (double)top_points; stats[10] = (double)vf_bottom[0]; stats[11] = (double)vf_top[0];
+    stats[12] = (double)vf_bottom[1]; stats[13] = (double)vf_top[1]; stats[14] = (double)vf_top[2]; stats[15] = (double)vf_top[3];
   }
   return rc;
+}
+
+extern "C" int vx_hba_global_take_factor(vx_ctx *ctx, int which, vx_factor **out) {
+  VX_ARG(ctx && out && (which == 0 || which == 1));
+  *out = ctx->kept[which];
+  ctx->kept[which] = nullptr;
+  return VX_OK;
+}
+
+extern "C" int vx_factor_hessian_sharded_async(vx_ctx *ctx, vx_comm *comm, vx_factor *f) {
+  VX_ARG(ctx && f && (comm == nullptr || comm->ctx == ctx));
+  VX_TRY(vx_factor_hessian_async(ctx, f, 0, -1));
+  return allreduce_evaluation(ctx, comm, f);
 }
