@@ -241,6 +241,91 @@ __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, d
 }
 
 
+// The same update on the FP64 tensor pipe (mma.sync.m8n8k4.f64, SASS DMMA.8x8x4): 128 x 128 tiles of the lower triangle, 8 warps,
+// each warp a 32 x 64 sub-tile = 4 x 8 accumulator tiles held in registers and INITIALISED WITH C (the panel strip is stored negated,
+// so D = (-L_I) (L_J D)^T + C is the updated entry: one pass, no separate subtraction).  Operand strips live in shared memory as
+// [k][row] with leading dimension 132 (= 4 mod 16): fragment loads and the transposing stores are both conflict-free.
+// Per k-step a warp issues 12 fragment loads for 32 DMMAs (the 4 x 4-per-thread DFMA tile needed 8 loads per 16 FMAs).
+// The north_star's "tensor cores only if the solve proves to be a dense contraction": this is that contraction (4.6 GFLOP at W = 400).
+constexpr int TT = 128, LDT = TT + 4;
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(256, 1) k_ldlt_trailing_mma(double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb) {
+  extern __shared__ double tsm[];
+  double *Li = tsm, *Lj = tsm + NB * LDT;          // [t][row]; Li negated, Lj pre-scaled by D_t
+  const int t0 = c0 + nb;
+  int bi = (int)((sqrtf(8.0f * (float)blockIdx.x + 1.0f) - 1.0f) * 0.5f);      // lower-triangular tiles only: blockIdx.x = bi (bi + 1) / 2 + bj
+  while (bi * (bi + 1) / 2 > (int)blockIdx.x) bi--;
+  while ((bi + 1) * (bi + 2) / 2 <= (int)blockIdx.x) bi++;
+  const int bj = (int)blockIdx.x - bi * (bi + 1) / 2;
+  const int r0 = t0 + bi * TT, q0 = t0 + bj * TT;
+  const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+  const int wm = wp & 3, wn = wp >> 2;
+  const int lr = lane >> 2, lc = lane & 3;
+  // accumulators <- C (issued first: the longest latency), then the strips
+  double acc[4][8][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int r = r0 + wm * 32 + i * 8 + lr, c = q0 + wn * 64 + j * 8 + 2 * lc;
+      const bool rin = r < n;
+      acc[i][j][0] = (rin && c < n) ? B[(size_t)c * n + r] : 0.0;
+      acc[i][j][1] = (rin && c + 1 < n) ? B[(size_t)(c + 1) * n + r] : 0.0;
+    }
+  const double *Fd = F + (size_t)(c0 / NB) * NB * NB;
+#pragma unroll 4
+  for (int q = 0; q < NB * TT / 256; q++) {
+    const int k = tid + 256 * q;
+    const int rr = k % TT, t = k / TT;
+    const bool tin = t < nb;
+    Li[t * LDT + rr] = (tin && r0 + rr < n) ? -B[(size_t)(c0 + t) * n + r0 + rr] : 0.0;
+    Lj[t * LDT + rr] = (tin && q0 + rr < n) ? B[(size_t)(c0 + t) * n + q0 + rr] * Fd[t * NB + t] : 0.0;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int ks = 0; ks < NB / 4; ks++) {
+    const double *la = Li + (4 * ks + lc) * LDT + wm * 32 + lr;
+    const double *lb = Lj + (4 * ks + lc) * LDT + wn * 64 + lr;
+    double a[4], b[8];
+#pragma unroll
+    for (int i = 0; i < 4; i++) a[i] = la[8 * i];
+#pragma unroll
+    for (int j = 0; j < 8; j++) b[j] = lb[8 * j];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int r = r0 + wm * 32 + i * 8 + lr, c = q0 + wn * 64 + j * 8 + 2 * lc;
+      if (r < n && c < n && r >= c) B[(size_t)c * n + r] = acc[i][j][0];
+      if (r < n && c + 1 < n && r >= c + 1) B[(size_t)(c + 1) * n + r] = acc[i][j][1];
+    }
+  if (bi == 0 && bj == 0) {               // this tile completes the next panel's diagonal block: factor it here, off the panel's chain
+    __syncthreads();                      // everybody is done with the strips
+    double (*L11)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(tsm);
+    if (wp == 0) {                        // warp 0 holds rows 0..31 x columns 0..63 of the tile
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            const int rr = i * 8 + lr, cc = j * 8 + 2 * lc + e;
+            L11[rr][cc] = (t0 + rr < n && t0 + cc < n && rr >= cc) ? acc[i][j][e] : 0.0;
+          }
+    }
+    __syncthreads();
+    ldlt_diag_block<256>(L11, tid);
+    for (int e = tid; e < NB * NB; e += 256) F[(size_t)(t0 / NB) * NB * NB + e] = L11[e % NB][e / NB];
+  }
+}
+
 // gauged diagonal of the un-gauged device Hessian: D[r] = 1 for the six gauge rows (voxel_map.hpp:452-455), else H(r,r)
 __global__ void k_diag_gauged(const double *__restrict__ H, int n, double *__restrict__ D) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -340,16 +425,34 @@ static void pivot_order(std::vector<double> d, std::vector<int32_t> &pos, std::v
 
 // the sweep: panel + trailing update per 32-column panel, left to right (the forward substitution rides in the panel kernel),
 // then the backward substitution right to left: 3 launches per panel, 225 at n = 2394
+constexpr size_t TRAIL_SMEM = sizeof(double) * 2 * NB * LDT;
 static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx, double *dz, double *dxo) {
   cudaStream_t st = ctx->stream;
+  {   // > 48 KB of dynamic shared memory: opt in once per device
+    static bool attr_set[64] = {};
+    if (!attr_set[ctx->device & 63]) {
+      VX_CUDA(cudaFuncSetAttribute(k_ldlt_trailing_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRAIL_SMEM));
+      attr_set[ctx->device & 63] = true;
+    }
+  }
   VX_KERNEL(ctx, "k_ldlt_diag0", k_ldlt_diag0<<<1, 256, 0, st>>>(dB, dF, n, std::min(NB, n)));
   for (int c0 = 0; c0 < n; c0 += NB) {
     const int nb = std::min(NB, n - c0);
     const int below = n - c0 - nb;
     VX_KERNEL(ctx, "k_ldlt_panel", k_ldlt_panel<<<std::max(1, blocks_for(below, PR)), PR * 32, 0, st>>>(dB, dF, n, c0, nb, dx, dz));
     if (below > 0) {
-      const int nt = (below + TR - 1) / TR;
-      VX_KERNEL(ctx, "k_ldlt_trailing", k_ldlt_trailing<<<nt * (nt + 1) / 2, 256, 0, st>>>(dB, dF, n, c0, nb));
+      // Measured on B200 at n = 2400 (scripts/ldlt_time.py): 64 x 64 DFMA tiles 1.25 ms per solve (3.7 TFLOP/s), 128 x 128 DMMA tiles
+      // 1.80 ms (2.6 TFLOP/s).  With a 32-column panel the update moves 16 B of C per 64 flop and every launch is a short wave of
+      // tiles: it is bound by L2 latency and wave quantisation (190 tiles on 148 SMs at one CTA per SM), not by the FP64 pipe, so
+      // the tensor-pipe formulation buys nothing here.  VX_LDLT_DMMA=1 selects it for the A/B record.
+      static const bool dfma_tiles = std::getenv("VX_LDLT_DMMA") == nullptr;
+      if (dfma_tiles) {
+        const int nt = (below + TR - 1) / TR;
+        VX_KERNEL(ctx, "k_ldlt_trailing", k_ldlt_trailing<<<nt * (nt + 1) / 2, 256, 0, st>>>(dB, dF, n, c0, nb));
+      } else {
+        const int nt = (below + TT - 1) / TT;
+        VX_KERNEL(ctx, "k_ldlt_trailing_mma", k_ldlt_trailing_mma<<<nt * (nt + 1) / 2, 256, TRAIL_SMEM, st>>>(dB, dF, n, c0, nb));
+      }
     }
   }
   for (int c0 = ((n - 1) / NB) * NB; c0 >= 0; c0 -= NB) {
