@@ -265,6 +265,11 @@ int vx_imu_pre_add(vx_imu_pre *pre, const vx_imu_noise *nz, const double *gyr3, 
  * jtj (nc x nc col-major) and gg (nc) are written when both are non-NULL (the reference's jac_enable); *cost = rr^T cov^-1 rr. */
 int vx_imu_pre_evaluate(const vx_imu_pre *pre, const vx_imu_state *st1, const vx_imu_state *st2, int with_gravity, double *jtj,
                         double *gg, double *cost);
+/* The same factor evaluation on the device for a CHAIN of n_factors factors (factor i between states[i] and states[i+1]), the
+ * kernel vx_ba_li / vx_ba_li_gravity evaluate the IMU chain with: jtj n_factors x (nc x nc), gg n_factors x nc
+ * (both may be NULL: costs only), cost n_factors; nc = 30 or 33 (with_gravity). */
+int vx_imu_pre_evaluate_device(vx_ctx *ctx, const vx_imu_pre *pres, const vx_imu_state *states, int n_factors, int with_gravity, double *jtj,
+                               double *gg, double *cost);
 int vx_imu_pre_update_state(vx_imu_pre *pre, const double *dxi15);                          /* :296-303 */
 
 /* ---- B4: LI_BA_Optimizer::damping_iter(x_stats, voxhess, imus_factor, hess*)  voxel_map.hpp:624-713.

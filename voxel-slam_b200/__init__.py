@@ -628,6 +628,18 @@ def imu_pre_evaluate(pre, st1, st2, with_gravity=False, jac=True, lib=None):
     return float(cost[0]), jtj.T.copy(), gg
 
 
+def imu_pre_evaluate_device(ctx, pres, states, with_gravity=False, jac=True):
+    """vx_imu_pre_evaluate_device: the chain of len(pres) IMU factors on the device -> (costs (n,), jtj (n,nc,nc), gg (n,nc))."""
+    pres = np.ascontiguousarray(pres, dtype=imu_pre_dtype); states = np.ascontiguousarray(states, dtype=imu_state_dtype)
+    n = pres.shape[0]
+    assert states.shape[0] == n + 1
+    nc = 33 if with_gravity else 30
+    jtj = np.zeros((n, nc, nc)); gg = np.zeros((n, nc)); cost = np.zeros(n)
+    _chk(ctx.lib.vx_imu_pre_evaluate_device(ctx.h, _p(pres), _p(states), C.c_int(n), C.c_int(int(with_gravity)), _p(jtj) if jac else None,
+                                            _p(gg) if jac else None, _p(cost)))
+    return cost, np.transpose(jtj, (0, 2, 1)).copy(), gg
+
+
 class DevArray:
     """__cuda_array_interface__ view of a device buffer owned by the library (for torch.as_tensor)."""
 

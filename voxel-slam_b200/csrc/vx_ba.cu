@@ -297,7 +297,7 @@ int allreduce_evaluation(vx_ctx *ctx, vx_comm *comm, vx_factor *f) {
 }
 
 int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b, double *x);   // vx_ldlt.cu
-int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1);   // vx_ldlt.cu
+int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1, int nfix = 6);   // vx_ldlt.cu
 // win_status (optional, n_windows): when given, a window with fewer voxels than thd_num is flagged
 // VX_ERR_TOO_FEW and left untouched instead of failing the whole batch.
 // comm (optional): the factor holds only this rank's voxels of every window; Hess / JacT / cost are all-reduced after each
@@ -337,7 +337,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
       }
     }
   }
-  static const int ldlt_device_min = [] { const char *e = std::getenv("VX_LDLT_DEVICE_MIN"); return e ? std::atoi(e) : 384; }();
+  static const int ldlt_device_min = [] { const char *e = std::getenv("VX_LDLT_DEVICE_MIN"); return e ? std::atoi(e) : 129; }();
   const size_t hsz = (size_t)jl * jl;
   // device LM step: k_lm_keep + k_lm_solve for windows of up to LM_MAXN unknowns, the blocked factorisation of vx_ldlt.cu from
   // ldlt_device_min unknowns on (top-level GBA); Hess and JacT never leave the device.  In between (129...383 unknowns) and

@@ -9,44 +9,57 @@
 #include <utility>
 #include <vector>
 
+#ifdef __CUDACC__
+#define VX_HD __host__ __device__
+#else
+#define VX_HD
+#endif
+
 namespace vx {
 namespace hm {
 
 template <int R, int C>
 struct M {
   double a[R * C];
-  M() { std::memset(a, 0, sizeof(a)); }
-  double &operator()(int r, int c) { return a[c * R + r]; }
-  double operator()(int r, int c) const { return a[c * R + r]; }
-  double &operator[](int i) { return a[i]; }
-  double operator[](int i) const { return a[i]; }
-  static M eye() { M m; for (int i = 0; i < (R < C ? R : C); i++) m(i, i) = 1.0; return m; }
-  static M from(const double *p) { M m; std::memcpy(m.a, p, sizeof(m.a)); return m; }
-  void to(double *p) const { std::memcpy(p, a, sizeof(a)); }
-  M<C, R> T() const { M<C, R> t; for (int r = 0; r < R; r++) for (int c = 0; c < C; c++) t(c, r) = (*this)(r, c); return t; }
-  template <int BR, int BC> M<BR, BC> blk(int r0, int c0) const {
+  VX_HD M() { for (int i = 0; i < R * C; i++) a[i] = 0.0; }
+  VX_HD double &operator()(int r, int c) { return a[c * R + r]; }
+  VX_HD double operator()(int r, int c) const { return a[c * R + r]; }
+  VX_HD double &operator[](int i) { return a[i]; }
+  VX_HD double operator[](int i) const { return a[i]; }
+  VX_HD static M eye() { M m; for (int i = 0; i < (R < C ? R : C); i++) m(i, i) = 1.0; return m; }
+  VX_HD static M from(const double *p) { M m; for (int i = 0; i < R * C; i++) m.a[i] = p[i]; return m; }
+  VX_HD void to(double *p) const { for (int i = 0; i < R * C; i++) p[i] = a[i]; }
+  VX_HD M<C, R> T() const { M<C, R> t; for (int r = 0; r < R; r++) for (int c = 0; c < C; c++) t(c, r) = (*this)(r, c); return t; }
+  template <int BR, int BC> VX_HD M<BR, BC> blk(int r0, int c0) const {
     M<BR, BC> b; for (int c = 0; c < BC; c++) for (int r = 0; r < BR; r++) b(r, c) = (*this)(r0 + r, c0 + c); return b;
   }
-  template <int BR, int BC> void put(int r0, int c0, const M<BR, BC> &b) {
+  template <int BR, int BC> VX_HD void put(int r0, int c0, const M<BR, BC> &b) {
     for (int c = 0; c < BC; c++) for (int r = 0; r < BR; r++) (*this)(r0 + r, c0 + c) = b(r, c);
   }
-  M &operator+=(const M &o) { for (int i = 0; i < R * C; i++) a[i] += o.a[i]; return *this; }
-  M &operator-=(const M &o) { for (int i = 0; i < R * C; i++) a[i] -= o.a[i]; return *this; }
-  M &operator*=(double s) { for (int i = 0; i < R * C; i++) a[i] *= s; return *this; }
-  double dot(const M &o) const { double s = 0; for (int i = 0; i < R * C; i++) s += a[i] * o.a[i]; return s; }
-  double norm() const { return std::sqrt(dot(*this)); }
-  double trace() const { double s = 0; for (int i = 0; i < (R < C ? R : C); i++) s += (*this)(i, i); return s; }
+  VX_HD M &operator+=(const M &o) { for (int i = 0; i < R * C; i++) a[i] += o.a[i]; return *this; }
+  VX_HD M &operator-=(const M &o) { for (int i = 0; i < R * C; i++) a[i] -= o.a[i]; return *this; }
+  VX_HD M &operator*=(double s) { for (int i = 0; i < R * C; i++) a[i] *= s; return *this; }
+  VX_HD double dot(const M &o) const { double s = 0; for (int i = 0; i < R * C; i++) s += a[i] * o.a[i]; return s; }
+  VX_HD double norm() const { return std::sqrt(dot(*this)); }
+  VX_HD double trace() const { double s = 0; for (int i = 0; i < (R < C ? R : C); i++) s += (*this)(i, i); return s; }
 };
-template <int R, int C> M<R, C> operator+(M<R, C> x, const M<R, C> &y) { x += y; return x; }
-template <int R, int C> M<R, C> operator-(M<R, C> x, const M<R, C> &y) { x -= y; return x; }
-template <int R, int C> M<R, C> operator-(M<R, C> x) { for (int i = 0; i < R * C; i++) x.a[i] = -x.a[i]; return x; }
-template <int R, int C> M<R, C> operator*(M<R, C> x, double s) { x *= s; return x; }
-template <int R, int C> M<R, C> operator*(double s, M<R, C> x) { x *= s; return x; }
-template <int R, int C> M<R, C> operator/(M<R, C> x, double s) { for (int i = 0; i < R * C; i++) x.a[i] /= s; return x; }
-template <int R, int K, int C> M<R, C> operator*(const M<R, K> &x, const M<K, C> &y) {
+template <int R, int C> VX_HD M<R, C> operator+(M<R, C> x, const M<R, C> &y) { x += y; return x; }
+template <int R, int C> VX_HD M<R, C> operator-(M<R, C> x, const M<R, C> &y) { x -= y; return x; }
+template <int R, int C> VX_HD M<R, C> operator-(M<R, C> x) { for (int i = 0; i < R * C; i++) x.a[i] = -x.a[i]; return x; }
+template <int R, int C> VX_HD M<R, C> operator*(M<R, C> x, double s) { x *= s; return x; }
+template <int R, int C> VX_HD M<R, C> operator*(double s, M<R, C> x) { x *= s; return x; }
+template <int R, int C> VX_HD M<R, C> operator/(M<R, C> x, double s) { for (int i = 0; i < R * C; i++) x.a[i] /= s; return x; }
+template <int R, int K, int C> VX_HD M<R, C> operator*(const M<R, K> &x, const M<K, C> &y) {
   M<R, C> m;
   for (int c = 0; c < C; c++)
     for (int r = 0; r < R; r++) { double s = 0; for (int k = 0; k < K; k++) s += x(r, k) * y(k, c); m(r, c) = s; }
+  return m;
+}
+// x^T y without forming the transpose (same sums, same order as x.T() * y)
+template <int K, int R, int C> VX_HD M<R, C> mul_tn(const M<K, R> &x, const M<K, C> &y) {
+  M<R, C> m;
+  for (int c = 0; c < C; c++)
+    for (int r = 0; r < R; r++) { double s = 0; for (int k = 0; k < K; k++) s += x(k, r) * y(k, c); m(r, c) = s; }
   return m;
 }
 using V3 = M<3, 1>;
@@ -54,34 +67,34 @@ using M3 = M<3, 3>;
 using V15 = M<15, 1>;
 using M15 = M<15, 15>;
 
-inline V3 v3(double x, double y, double z) { V3 v; v[0] = x; v[1] = y; v[2] = z; return v; }
-inline M3 hat(const V3 &v) {   // tools.hpp:93-100
+VX_HD inline V3 v3(double x, double y, double z) { V3 v; v[0] = x; v[1] = y; v[2] = z; return v; }
+VX_HD inline M3 hat(const V3 &v) {   // tools.hpp:93-100
   M3 m;
   m(0, 1) = -v[2]; m(0, 2) = v[1];
   m(1, 0) = v[2];  m(1, 2) = -v[0];
   m(2, 0) = -v[1]; m(2, 1) = v[0];
   return m;
 }
-inline M3 so3_exp(const V3 &w) {   // tools.hpp:51-66
+VX_HD inline M3 so3_exp(const V3 &w) {   // tools.hpp:51-66
   const double n = w.norm();
   if (n < 1e-11) return M3::eye();
   const M3 K = hat(w / n);
   return M3::eye() + std::sin(n) * K + (1.0 - std::cos(n)) * (K * K);
 }
-inline M3 so3_exp(const V3 &rate, double dt) {   // tools.hpp:68-84
+VX_HD inline M3 so3_exp(const V3 &rate, double dt) {   // tools.hpp:68-84
   const double n = rate.norm();
   if (!(n > 1e-7)) return M3::eye();
   const M3 K = hat(rate / n);
   const double ang = n * dt;
   return M3::eye() + std::sin(ang) * K + (1.0 - std::cos(ang)) * (K * K);
 }
-inline V3 so3_log(const M3 &R) {   // tools.hpp:86-91
+VX_HD inline V3 so3_log(const M3 &R) {   // tools.hpp:86-91
   const double tr = R.trace();
   const double th = (tr > 3.0 - 1e-6) ? 0.0 : std::acos(0.5 * (tr - 1));
   const V3 k = v3(R(2, 1) - R(1, 2), R(0, 2) - R(2, 0), R(1, 0) - R(0, 1));
   return (std::fabs(th) < 0.001) ? 0.5 * k : (0.5 * th / std::sin(th)) * k;
 }
-inline M3 so3_jr(V3 w) {   // tools.hpp:102-116
+VX_HD inline M3 so3_jr(V3 w) {   // tools.hpp:102-116
   const double ang = w.norm();
   if (ang < 1e-9) return M3::eye();
   w = w / ang;
@@ -90,7 +103,7 @@ inline M3 so3_jr(V3 w) {   // tools.hpp:102-116
 }
 // tools.hpp:118-133 builds an Eigen::AngleAxisd from the matrix: matrix -> quaternion (largest-diagonal branch
 // selection) -> angle = 2 atan2(|xyz|, |w|), axis = xyz / (+-|xyz|).
-inline M3 so3_jr_inv(const M3 &m) {
+VX_HD inline M3 so3_jr_inv(const M3 &m) {
   double q[4], t = m.trace();
   if (t > 0.0) {
     t = std::sqrt(t + 1.0); q[3] = 0.5 * t; t = 0.5 / t;
@@ -114,14 +127,14 @@ inline M3 so3_jr_inv(const M3 &m) {
 }
 
 // inverse by partial-pivot LU — what Eigen's fixed-size inverse() does above 4x4 (preintegration.hpp:166, voxelslam.cpp:1054)
-template <int N> M<N, N> inverse(const M<N, N> &in) {
+template <int N> VX_HD M<N, N> inverse(const M<N, N> &in) {
   M<N, N> A = in, inv;
   int perm[N];
   for (int i = 0; i < N; i++) perm[i] = i;
   for (int k = 0; k < N; k++) {
     int p = k; double best = std::fabs(A(k, k));
     for (int i = k + 1; i < N; i++) if (std::fabs(A(i, k)) > best) { best = std::fabs(A(i, k)); p = i; }
-    if (p != k) { for (int c = 0; c < N; c++) std::swap(A(k, c), A(p, c)); std::swap(perm[k], perm[p]); }
+    if (p != k) { for (int c = 0; c < N; c++) { const double t_ = A(k, c); A(k, c) = A(p, c); A(p, c) = t_; } const int tp = perm[k]; perm[k] = perm[p]; perm[p] = tp; }
     const double piv = A(k, k);
     for (int i = k + 1; i < N; i++) A(i, k) /= piv;
     for (int c = k + 1; c < N; c++) { const double akc = A(k, c); for (int i = k + 1; i < N; i++) A(i, c) -= A(i, k) * akc; }

@@ -327,19 +327,19 @@ __global__ void __launch_bounds__(256, 1) k_ldlt_trailing_mma(double *__restrict
 }
 
 // gauged diagonal of the un-gauged device Hessian: D[r] = 1 for the six gauge rows (voxel_map.hpp:452-455), else H(r,r)
-__global__ void k_diag_gauged(const double *__restrict__ H, int n, double *__restrict__ D) {
+__global__ void k_diag_gauged(const double *__restrict__ H, int n, int nfix, double *__restrict__ D) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r < n) D[r] = r < 6 ? 1.0 : H[(size_t)r * n + r];
+  if (r < n) D[r] = r < nfix ? 1.0 : H[(size_t)r * n + r];
 }
 
 // B(i,j) = Ag(max(p_i,p_j), min(p_i,p_j)), i >= j, where Ag = gauge-fixed H + u * diag (voxel_map.hpp:452-458) formed on the fly
-__global__ void k_permute_gauged(const double *__restrict__ H, int n, const int32_t *__restrict__ pos, double u, double *__restrict__ B) {
+__global__ void k_permute_gauged(const double *__restrict__ H, int n, int nfix, const int32_t *__restrict__ pos, double u, double *__restrict__ B) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
   if (i >= n || i < j) return;
   const int pi = pos[i], pj = pos[j];
   const int r = max(pi, pj), c = min(pi, pj);
   double v;
-  if (r < 6 || c < 6) v = r == c ? 1.0 : 0.0;
+  if (r < nfix || c < nfix) v = r == c ? 1.0 : 0.0;
   else v = H[(size_t)c * n + r];
   if (r == c) v = __dadd_rn(v, __dmul_rn(u, v));     // A(r,r) += u * D[r], D = the gauged diagonal
   B[(size_t)j * n + i] = v;
@@ -530,7 +530,8 @@ int ldlt_lower_solve_device(vx_ctx *ctx, const double *A, int n, const double *b
 
 // The LM step of one LARGE window on the device Hessian: dH (n x n, un-gauged, column-major) and dJ (n) stay where they are.
 // dx = (gauge(H) + u diag(gauge(H))).ldlt().solve(-gauge(JacT)),  q1 = 0.5 dx^T (u D dx - JacT)   (voxel_map.hpp:452-470)
-int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1) {
+// nfix: leading unknowns held by the gauge (6 = pose 0 of the LiDAR-only / gravity optimizers, 15 = state 0 of LI_BA_Optimizer).
+int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1, int nfix) {
   VX_TRY(bind(ctx));
   cudaStream_t st = ctx->stream;
   std::vector<double> D(n), J(n), d(n);
@@ -541,11 +542,11 @@ int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, doubl
     VX_TRY(dB.reserve(sizeof(double) * (size_t)n * n)); VX_TRY(dP.reserve(sizeof(int32_t) * n)); VX_TRY(dD.reserve(sizeof(double) * n));
     auto T0 = std::chrono::steady_clock::now();
     auto lap = [&](const char *w) { if (getenv("VX_LDLT_TIMING")) { cudaStreamSynchronize(st); auto t = std::chrono::steady_clock::now(); fprintf(stderr, "[ldlt] %s %.3f ms\n", w, std::chrono::duration<double, std::milli>(t - T0).count()); T0 = t; } };
-    VX_KERNEL(ctx, "k_diag_gauged", k_diag_gauged<<<blocks_for(n, 256), 256, 0, st>>>(dH, n, dD.as<double>()));
+    VX_KERNEL(ctx, "k_diag_gauged", k_diag_gauged<<<blocks_for(n, 256), 256, 0, st>>>(dH, n, nfix, dD.as<double>()));
     VX_CUDA(cudaMemcpyAsync(D.data(), dD.p, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaMemcpyAsync(J.data(), dJ, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
-    for (int r = 0; r < 6 && r < n; r++) J[r] = 0.0;
+    for (int r = 0; r < nfix && r < n; r++) J[r] = 0.0;
     for (int r = 0; r < n; r++) d[r] = std::fabs(D[r] + u * D[r]);
     lap("diag");
     pivot_order(d, pos, tr);
@@ -553,7 +554,7 @@ int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, doubl
     for (int i = 0; i < n; i++) dx[i] = -J[i];
     for (int k = 0; k < n; k++) if (tr[k] != k) std::swap(dx[k], dx[tr[k]]);
     VX_CUDA(cudaMemcpyAsync(dP.p, pos.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
-    VX_KERNEL(ctx, "k_permute_gauged", k_permute_gauged<<<dim3(blocks_for(n, 128), n), 128, 0, st>>>(dH, n, dP.as<int32_t>(), u, dB.as<double>()));
+    VX_KERNEL(ctx, "k_permute_gauged", k_permute_gauged<<<dim3(blocks_for(n, 128), n), 128, 0, st>>>(dH, n, nfix, dP.as<int32_t>(), u, dB.as<double>()));
     lap("permute");
     const int r = factor_and_substitute(ctx, dB.as<double>(), n, dx);
     lap("factor");

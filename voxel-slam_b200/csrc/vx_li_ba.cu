@@ -2,12 +2,15 @@
 //   B6  IMU_PRE                        preintegration.hpp:11-303   (host, a POD the caller owns)
 //   B4  LI_BA_Optimizer::damping_iter  voxel_map.hpp:624-713      (15W unknowns)
 //   B5  LI_BA_OptimizerGravity::damping_iter  voxel_map.hpp:878-975 (15W+3 unknowns)
-// The LiDAR part (acc_evaluate2 / evaluate_only_residual) runs on the device; the W-1 IMU chain factors (15x15
-// inverse + 15x33 Jacobian each), the scatter stride 6 -> 15, the gauge fix and the (15W[+3])^2 LDL^T stay on the
-// host: W <= 20 means <= 303 unknowns, microseconds of work that sits between two device passes either way.
+// Everything between two LM decisions runs on the device: acc_evaluate2 / evaluate_only_residual, the W-1 IMU
+// chain factors (give_evaluate / give_evaluate_g, one thread each: 15x15 inverse + 15x33 Jacobian), the assembly (IMU blocks in
+// chain order, * imu_coef, LiDAR blocks scattered stride 6 -> 15: the reference's own order of additions), the gauge fix and the
+// blocked (15W[+3])^2 LDL^T of vx_ldlt.cu.  Per LM iteration the states go up and dx, q1 and W costs come back; the host keeps the
+// LM control flow, the retraction and the IMU_PRE bias bookkeeping.  VX_LI_HOST=1 selects the round-1 host assembly + host sweep.
 #include "vx_factor.cuh"
 #include "vx_hostmat.hpp"
 #include <algorithm>
+#include <cstdlib>
 
 using namespace vx;
 using namespace vx::hm;
@@ -22,7 +25,7 @@ struct Pre {   // unpacked vx_imu_pre
   double dtime;
   M15 cov;
 };
-Pre unpack(const vx_imu_pre *p) {
+VX_HD Pre unpack(const vx_imu_pre *p) {
   Pre q;
   q.R_delta = M3::from(p->R_delta); q.R_bg = M3::from(p->R_bg);
   q.p_bg = M3::from(p->p_bg); q.p_ba = M3::from(p->p_ba); q.v_bg = M3::from(p->v_bg); q.v_ba = M3::from(p->v_ba);
@@ -33,7 +36,7 @@ Pre unpack(const vx_imu_pre *p) {
   return q;
 }
 struct State { M3 R; V3 p, v, bg, ba, g; };
-State unpack(const vx_imu_state *s) {
+VX_HD State unpack(const vx_imu_state *s) {
   State x;
   x.R = M3::from(s->R); x.p = V3::from(s->p); x.v = V3::from(s->v); x.bg = V3::from(s->bg); x.ba = V3::from(s->ba); x.g = V3::from(s->g);
   return x;
@@ -79,9 +82,10 @@ void add_imu(vx_imu_pre *out, const vx_imu_noise *nz, const V3 &gyr, const V3 &a
   q.cov.to(out->cov);
 }
 
-// give_evaluate (preintegration.hpp:137-212) for NC = 30, give_evaluate_g (:214-294) for NC = 33.
+// give_evaluate (preintegration.hpp:137-212) for NC = 30, give_evaluate_g (:214-294) for NC = 33: residual rr, information
+// cov^-1 and (when J != nullptr) the 15 x NC Jacobian.  Shared by the host evaluation and the device kernel.
 template <int NC>
-double imu_evaluate(const vx_imu_pre *pre, const State &s1, const State &s2, M<NC, NC> *jtj, M<NC, 1> *gg) {
+VX_HD void imu_parts(const vx_imu_pre *pre, const State &s1, const State &s2, V15 &rr, M15 &info, M<DIM, NC> *Jp) {
   const Pre q = unpack(pre);
   const M3 R_corr = q.R_delta * so3_exp(q.R_bg * q.dbg);
   const V3 t_corr = q.p_delta + q.p_bg * q.dbg + q.p_ba * q.dba;
@@ -92,18 +96,17 @@ double imu_evaluate(const vx_imu_pre *pre, const State &s1, const State &s2, M<N
   const M3 res_r = R_corr.T() * R1t * s2.R;
   const V3 exp_v = R1t * (s2.v - s1.v - dt * s1.g);
   const V3 exp_t = R1t * (s2.p - s1.p - s1.v * dt - (0.5 * dt * dt) * s1.g);
-  V15 rr;
   rr.put(0, 0, so3_log(res_r));
   rr.put(3, 0, exp_t - t_corr);
   rr.put(6, 0, exp_v - v_corr);
   rr.put(9, 0, s2.bg - s1.bg);
   rr.put(12, 0, s2.ba - s1.ba);
-  const M15 info = inverse(q.cov);   // a dense inverse per call, as the reference (:166 / :244)
+  info = inverse(q.cov);   // a dense inverse per call, as the reference (:166 / :244)
 
-  if (jtj && gg) {
+  if (Jp) {
+    M<DIM, NC> &J = *Jp;
     const M3 I = M3::eye();
     const M3 Jri = so3_jr_inv(res_r);
-    M<DIM, NC> J;
     // d/d(state 1)
     J.put(0, 0, -(Jri * s2.R.T() * s1.R));
     J.put(0, 9, -(Jri * res_r.T() * so3_jr(q.R_bg * q.dbg) * q.R_bg));
@@ -128,9 +131,19 @@ double imu_evaluate(const vx_imu_pre *pre, const State &s1, const State &s2, M<N
       J.put(3, 2 * DIM, R1t * (-0.5 * dt * dt));
       J.put(6, 2 * DIM, R1t * (-dt));
     }
+  }
+}
+template <int NC>
+double imu_evaluate(const vx_imu_pre *pre, const State &s1, const State &s2, M<NC, NC> *jtj, M<NC, 1> *gg) {
+  V15 rr; M15 info;
+  if (jtj && gg) {
+    M<DIM, NC> J;
+    imu_parts<NC>(pre, s1, s2, rr, info, &J);
     const M<NC, DIM> JtI = J.T() * info;
     *jtj = JtI * J;
     *gg = JtI * rr;
+  } else {
+    imu_parts<NC>(pre, s1, s2, rr, info, (M<DIM, NC> *)nullptr);
   }
   return rr.dot(info * rr);
 }
@@ -143,6 +156,105 @@ void retract(const vx_imu_state &s, const double *d, vx_imu_state &o) {
     o.p[k] = s.p[k] + d[3 + k]; o.v[k] = s.v[k] + d[6 + k]; o.bg[k] = s.bg[k] + d[9 + k]; o.ba[k] = s.ba[k] + d[12 + k];
   }
 }
+
+// ---- device path -----------------------------------------------------------------------------------------------------------------
+// One WARP per IMU factor i (states i, i+1): lane 0 forms the residual, cov^-1 and the 15 x NC Jacobian (3 x 3 algebra and one
+// 15 x 15 inverse) in shared memory; the warp then takes J^T cov^-1 (NC x 15), J^T cov^-1 J (NC x NC) and J^T cov^-1 r entry by
+// entry, each a sum over k in ascending order from 0.0 — the host's sequence of products and sums.  jtj column-major, cost always.
+template <int NC>
+__global__ void __launch_bounds__(32) k_li_imu(const vx_imu_pre *__restrict__ imus, const vx_imu_state *__restrict__ xs, int nf, int jac,
+                                              double *__restrict__ jtj, double *__restrict__ gg, double *__restrict__ cost) {
+  __shared__ double sJ[DIM * NC], sI[DIM * DIM], sT[NC * DIM], sr[DIM], sIr[DIM];     // J [k][c] col-major (k + 15 c), info col-major, JtI (r + NC k)
+  const int i = blockIdx.x, lane = threadIdx.x;
+  if (i >= nf) return;
+  if (lane == 0) {
+    const State s1 = unpack(&xs[i]), s2 = unpack(&xs[i + 1]);
+    V15 rr; M15 info;
+    if (jac) {
+      M<DIM, NC> J;
+      imu_parts<NC>(&imus[i], s1, s2, rr, info, &J);
+      for (int e = 0; e < DIM * NC; e++) sJ[e] = J[e];
+    } else {
+      imu_parts<NC>(&imus[i], s1, s2, rr, info, (M<DIM, NC> *)nullptr);
+    }
+    for (int e = 0; e < DIM * DIM; e++) sI[e] = info[e];
+    for (int e = 0; e < DIM; e++) sr[e] = rr[e];
+  }
+  __syncwarp();
+  if (lane < DIM) {                          // info * rr, then rr . (info rr)
+    double s = 0;
+    for (int k = 0; k < DIM; k++) s += sI[lane + DIM * k] * sr[k];
+    sIr[lane] = s;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    double s = 0;
+    for (int k = 0; k < DIM; k++) s += sr[k] * sIr[k];
+    cost[i] = s;
+  }
+  if (!jac) return;
+  for (int e = lane; e < NC * DIM; e += 32) {           // JtI(r, c) = sum_k J(k, r) info(k, c)
+    const int r = e % NC, c = e / NC;
+    double s = 0;
+    for (int k = 0; k < DIM; k++) s += sJ[k + DIM * r] * sI[k + DIM * c];
+    sT[r + NC * c] = s;
+  }
+  __syncwarp();
+  double *out = jtj + (size_t)i * NC * NC;
+  for (int e = lane; e < NC * NC; e += 32) {            // jtj(r, c) = sum_k JtI(r, k) J(k, c)
+    const int r = e % NC, c = e / NC;
+    double s = 0;
+    for (int k = 0; k < DIM; k++) s += sT[r + NC * k] * sJ[k + DIM * c];
+    out[e] = s;
+  }
+  for (int r = lane; r < NC; r += 32) {                 // gg(r) = sum_k JtI(r, k) rr(k)
+    double s = 0;
+    for (int k = 0; k < DIM; k++) s += sT[r + NC * k] * sr[k];
+    gg[(size_t)i * NC + r] = s;
+  }
+}
+// Hess / JacT of divide_thread (voxel_map.hpp:519-584 / :746-825) + hess_plus (:509-517 / :726-738), one thread per entry: the IMU
+// contributions of an entry are added in chain order from 0.0, scaled by imu_coef, then the LiDAR block entry is added — the
+// sequence of roundings of the reference's loops.  NC = 30 (no gravity) or 33 (gravity: last 3 unknowns).
+template <int NC>
+__global__ void k_li_assemble(const double *__restrict__ jtj, const double *__restrict__ gg, int W, double coef, const double *__restrict__ Hl,
+                              const double *__restrict__ Jl, int n, double *__restrict__ H, double *__restrict__ J) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.y;
+  if (r >= n) return;
+  const int nf = W - 1, nx = DIM * W, jl = 6 * W;
+  auto factor_index = [&](int i, int a) -> int {   // index of unknown a inside factor i's NC-vector, or -1
+    if (a >= nx) return NC == 33 ? 30 + (a - nx) : -1;
+    const int b = a / DIM;
+    if (b == i) return a % DIM;
+    if (b == i + 1) return DIM + a % DIM;
+    return -1;
+  };
+  int lo = 0, hi = nf - 1;                          // factors that can touch (r, c)
+  if (r < nx) { lo = max(lo, r / DIM - 1); hi = min(hi, r / DIM); }
+  if (c < nx) { lo = max(lo, c / DIM - 1); hi = min(hi, c / DIM); }
+  double s = 0.0;
+  for (int i = lo; i <= hi; i++) {
+    const int a = factor_index(i, r), b = factor_index(i, c);
+    if (a >= 0 && b >= 0) s = __dadd_rn(s, jtj[(size_t)i * NC * NC + (size_t)b * NC + a]);
+  }
+  s = __dmul_rn(s, coef);
+  if (r < nx && c < nx && r % DIM < 6 && c % DIM < 6) s = __dadd_rn(s, Hl[(size_t)((c / DIM) * 6 + c % DIM) * jl + (r / DIM) * 6 + r % DIM]);
+  H[(size_t)c * n + r] = s;
+  if (c == 0) {
+    double g = 0.0;
+    lo = 0; hi = nf - 1;
+    if (r < nx) { lo = max(lo, r / DIM - 1); hi = min(hi, r / DIM); }
+    for (int i = lo; i <= hi; i++) { const int a = factor_index(i, r); if (a >= 0) g = __dadd_rn(g, gg[(size_t)i * NC + a]); }
+    g = __dmul_rn(g, coef);
+    if (r < nx && r % DIM < 6) g = __dadd_rn(g, Jl[(r / DIM) * 6 + r % DIM]);
+    J[r] = g;
+  }
+}
+}  // namespace
+namespace vx {
+int lm_solve_large_device(vx_ctx *ctx, const double *dH, const double *dJ, double u, int n, double *dx, double *q1, int nfix);   // vx_ldlt.cu
+}
+namespace {
 
 // Common body of the two damping_iter()s (they differ in unknown count, factor width, gauge, iteration cap, g update).
 int li_damping(vx_ctx *ctx, vx_factor *f, vx_imu_state *xs, vx_imu_pre *imus, double imu_coef, bool gravity, int max_iter, double *resis2,
@@ -166,9 +278,49 @@ int li_damping(vx_ctx *ctx, vx_factor *f, vx_imu_state *xs, vx_imu_pre *imus, do
   bool calc = true;
   int iters = 0;
   if (resis2) resis2[0] = resis2[1] = 0;
+  // device path: see the file header
+  const bool devp = std::getenv("VX_LI_HOST") == nullptr && W >= 2 && f->V > 0 && f->nnz > 0;
+  const int nf = W - 1, NCf = gravity ? 33 : 30;
+  cudaStream_t st = ctx->stream;
+  DevBuf d_imus, d_x, d_jtj, d_gg, d_cost, d_H, d_J;
+  struct Rel { std::vector<DevBuf *> b; ~Rel() { for (DevBuf *x : b) x->release(); } } rel{{&d_imus, &d_x, &d_jtj, &d_gg, &d_cost, &d_H, &d_J}};
+  std::vector<double> costs(std::max(nf, 1));
+  if (devp) {
+    VX_TRY(d_imus.reserve(sizeof(vx_imu_pre) * nf)); VX_TRY(d_x.reserve(sizeof(vx_imu_state) * W));
+    VX_TRY(d_jtj.reserve(sizeof(double) * NCf * NCf * nf)); VX_TRY(d_gg.reserve(sizeof(double) * NCf * nf)); VX_TRY(d_cost.reserve(sizeof(double) * nf));
+    VX_TRY(d_H.reserve(sizeof(double) * nn)); VX_TRY(d_J.reserve(sizeof(double) * n));
+  }
+  // IMU chain at the states s (device): costs[] <- per-factor rr^T cov^-1 rr; with jac also jtj / gg
+  auto imu_device = [&](const std::vector<vx_imu_state> &s, bool jac) -> int {
+    VX_CUDA(cudaMemcpyAsync(d_x.p, s.data(), sizeof(vx_imu_state) * W, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_imus.p, imus, sizeof(vx_imu_pre) * nf, cudaMemcpyHostToDevice, st));
+    if (gravity) VX_KERNEL(ctx, "k_li_imu", k_li_imu<33><<<nf, 32, 0, st>>>(d_imus.as<vx_imu_pre>(), d_x.as<vx_imu_state>(), nf, jac ? 1 : 0, d_jtj.as<double>(),
+                                                                                     d_gg.as<double>(), d_cost.as<double>()));
+    else VX_KERNEL(ctx, "k_li_imu", k_li_imu<30><<<nf, 32, 0, st>>>(d_imus.as<vx_imu_pre>(), d_x.as<vx_imu_state>(), nf, jac ? 1 : 0, d_jtj.as<double>(),
+                                                                              d_gg.as<double>(), d_cost.as<double>()));
+    VX_CUDA(cudaMemcpyAsync(costs.data(), d_cost.p, sizeof(double) * nf, cudaMemcpyDeviceToHost, st));
+    return VX_OK;
+  };
 
   for (int it = 0; it < max_iter; it++) {
-    if (calc) {
+    if (calc && devp) {
+      VX_TRY(imu_device(x, true));
+      lidar_poses(x);
+      VX_TRY(vx_factor_set_poses(ctx, f, lp.data()));
+      VX_TRY(vx_factor_hessian_async(ctx, f, 0, -1));
+      if (gravity) VX_KERNEL(ctx, "k_li_assemble", k_li_assemble<33><<<dim3(blocks_for(n, 128), n), 128, 0, st>>>(d_jtj.as<double>(), d_gg.as<double>(), W, imu_coef, f->H.as<double>(),
+                                                                                                      f->J.as<double>(), n, d_H.as<double>(), d_J.as<double>()));
+      else VX_KERNEL(ctx, "k_li_assemble", k_li_assemble<30><<<dim3(blocks_for(n, 128), n), 128, 0, st>>>(d_jtj.as<double>(), d_gg.as<double>(), W, imu_coef, f->H.as<double>(),
+                                                                                               f->J.as<double>(), n, d_H.as<double>(), d_J.as<double>()));
+      double lc = 0;
+      VX_CUDA(cudaMemcpyAsync(&lc, f->cost_h.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (hess_out) VX_CUDA(cudaMemcpyAsync(hess_out, d_H.p, sizeof(double) * nn, cudaMemcpyDeviceToHost, st));   // *hess = Hess, before the gauge fix
+      VX_CUDA(cudaStreamSynchronize(st));
+      double cost = 0;
+      for (int i = 0; i < nf; i++) cost += costs[i];
+      cost *= imu_coef * 0.5;
+      r1 = cost + lc;
+    } else if (calc) {
       // divide_thread (voxel_map.hpp:519-584 / :746-825): IMU chain first, scaled by imu_coef, then the LiDAR blocks on top
       std::fill(Hess.begin(), Hess.end(), 0.0);
       std::fill(JacT.begin(), JacT.end(), 0.0);
@@ -207,13 +359,20 @@ int li_damping(vx_ctx *ctx, vx_factor *f, vx_imu_state *xs, vx_imu_pre *imus, do
     }
     if (it == 0 && resis2) resis2[0] = r1;
 
-    for (int c = 0; c < n; c++) for (int r = 0; r < nfix; r++) H_(r, c) = 0.0;
-    for (int c = 0; c < nfix; c++) for (int r = 0; r < n; r++) H_(r, c) = 0.0;
-    for (int r = 0; r < nfix; r++) { H_(r, r) = 1.0; JacT[r] = 0.0; }
-    for (int r = 0; r < n; r++) D[r] = H_(r, r);
-    A = Hess;
-    for (int r = 0; r < n; r++) { A[(size_t)r * n + r] += u * D[r]; nb[r] = -JacT[r]; }
-    ldlt_lower_solve(A.data(), n, nb.data(), dxi.data(), tr, tmp);
+    double q1 = 0;
+    if (devp) {
+      VX_TRY(vx::lm_solve_large_device(ctx, d_H.as<double>(), d_J.as<double>(), u, n, dxi.data(), &q1, nfix));
+    } else {
+      for (int c = 0; c < n; c++) for (int r = 0; r < nfix; r++) H_(r, c) = 0.0;
+      for (int c = 0; c < nfix; c++) for (int r = 0; r < n; r++) H_(r, c) = 0.0;
+      for (int r = 0; r < nfix; r++) { H_(r, r) = 1.0; JacT[r] = 0.0; }
+      for (int r = 0; r < n; r++) D[r] = H_(r, r);
+      A = Hess;
+      for (int r = 0; r < n; r++) { A[(size_t)r * n + r] += u * D[r]; nb[r] = -JacT[r]; }
+      ldlt_lower_solve(A.data(), n, nb.data(), dxi.data(), tr, tmp);
+      for (int r = 0; r < n; r++) q1 += dxi[r] * (u * D[r] * dxi[r] - JacT[r]);
+      q1 *= 0.5;
+    }
 
     for (int j = 0; j < W; j++) retract(x[j], &dxi[DIM * j], xt[j]);
     if (gravity) {   // voxel_map.hpp:921-930: the trial g accumulates on x_stats_temp[0] even across rejected steps
@@ -226,15 +385,18 @@ int li_damping(vx_ctx *ctx, vx_factor *f, vx_imu_state *xs, vx_imu_pre *imus, do
         imus[j].dbg[k] += dxi[DIM * j + 9 + k]; imus[j].dba[k] += dxi[DIM * j + 12 + k];
       }
     }
-    double q1 = 0;
-    for (int r = 0; r < n; r++) q1 += dxi[r] * (u * D[r] * dxi[r] - JacT[r]);
-    q1 *= 0.5;
 
     // only_residual (voxel_map.hpp:586-622 / :831-870) at the trial states
     double ci = 0;
-    for (int i = 0; i + 1 < W; i++) {
-      const State s1 = unpack(&xt[i]), s2 = unpack(&xt[i + 1]);
-      ci += gravity ? imu_evaluate<33>(&imus[i], s1, s2, nullptr, nullptr) : imu_evaluate<30>(&imus[i], s1, s2, nullptr, nullptr);
+    if (devp) {
+      VX_TRY(imu_device(xt, false));
+      VX_CUDA(cudaStreamSynchronize(st));
+      for (int i = 0; i < nf; i++) ci += costs[i];
+    } else {
+      for (int i = 0; i + 1 < W; i++) {
+        const State s1 = unpack(&xt[i]), s2 = unpack(&xt[i + 1]);
+        ci += gravity ? imu_evaluate<33>(&imus[i], s1, s2, nullptr, nullptr) : imu_evaluate<30>(&imus[i], s1, s2, nullptr, nullptr);
+      }
     }
     ci *= imu_coef * 0.5;
     double lc = 0;
@@ -313,6 +475,38 @@ int vx_imu_pre_evaluate(const vx_imu_pre *pre, const vx_imu_state *st1, const vx
     if (jac) { h.to(jtj); g.to(gg); }
   }
   return VX_OK;
+}
+
+// give_evaluate / give_evaluate_g of n_factors chained factors on the device (factor i between states i and i+1), the kernel the
+// LI optimizers use (k_li_imu): jtj n_factors x (nc x nc) column-major, gg n_factors x nc, cost n_factors; nc = 30 or 33.
+int vx_imu_pre_evaluate_device(vx_ctx *ctx, const vx_imu_pre *pres, const vx_imu_state *states, int n_factors, int with_gravity, double *jtj,
+                               double *gg, double *cost) {
+  VX_ARG(ctx && pres && states && cost && n_factors >= 1);
+  VX_TRY(bind(ctx));
+  cudaStream_t st = ctx->stream;
+  const int nc = with_gravity ? 33 : 30, jac = (jtj && gg) ? 1 : 0;
+  DevBuf d_p, d_s, d_h, d_g, d_c;
+  auto body = [&]() -> int {
+    VX_TRY(d_p.reserve(sizeof(vx_imu_pre) * n_factors)); VX_TRY(d_s.reserve(sizeof(vx_imu_state) * (n_factors + 1)));
+    VX_TRY(d_h.reserve(sizeof(double) * nc * nc * n_factors)); VX_TRY(d_g.reserve(sizeof(double) * nc * n_factors)); VX_TRY(d_c.reserve(sizeof(double) * n_factors));
+    VX_CUDA(cudaMemcpyAsync(d_p.p, pres, sizeof(vx_imu_pre) * n_factors, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_s.p, states, sizeof(vx_imu_state) * (n_factors + 1), cudaMemcpyHostToDevice, st));
+    if (with_gravity) VX_KERNEL(ctx, "k_li_imu", k_li_imu<33><<<n_factors, 32, 0, st>>>(d_p.as<vx_imu_pre>(), d_s.as<vx_imu_state>(), n_factors, jac, d_h.as<double>(),
+                                                                                                 d_g.as<double>(), d_c.as<double>()));
+    else VX_KERNEL(ctx, "k_li_imu", k_li_imu<30><<<n_factors, 32, 0, st>>>(d_p.as<vx_imu_pre>(), d_s.as<vx_imu_state>(), n_factors, jac, d_h.as<double>(),
+                                                                                          d_g.as<double>(), d_c.as<double>()));
+    if (jac) {
+      VX_CUDA(cudaMemcpyAsync(jtj, d_h.p, sizeof(double) * nc * nc * n_factors, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaMemcpyAsync(gg, d_g.p, sizeof(double) * nc * n_factors, cudaMemcpyDeviceToHost, st));
+    }
+    VX_CUDA(cudaMemcpyAsync(cost, d_c.p, sizeof(double) * n_factors, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : {&d_p, &d_s, &d_h, &d_g, &d_c}) b->release();
+  return rc;
 }
 
 int vx_imu_pre_update_state(vx_imu_pre *pre, const double *dxi15) {
