@@ -518,6 +518,19 @@ int vx_map_export(vx_map *map, vx_map_node_state *states, vx_map_node *nodes);  
 int vx_var_init(vx_ctx *ctx, const float *xyz, int64_t n, const vx_pose *ext, double dept_err, double beam_err, vx_point_var *out);
 int vx_pvec_update(vx_ctx *ctx, const vx_point_var *pv_in, int64_t n, const vx_pose *x, const double *rot_var9, const double *tsl_var9,
                    vx_point_var *pv_out, double *pwld);
+/* ---- IMU de-skew — the per-point half of IMUEKF::motion_blur (ekf_imu.hpp:138-163): every point of a sweep
+ * is moved into the sensor frame at the END of the sweep with the IMU-propagated pose that precedes its time stamp
+ * (PointType::curvature).  The propagation that produces `poses` (ekf_imu.hpp:57-120) is the EKF and stays with the caller.
+ *   pts      in/out host, x / y / z / curvature are read, x / y / z rewritten (float, as the reference stores them)
+ *   poses    the reference's imu_poses, ascending t: IMUST(offt, R_imu, pos_imu, vel_imu, angvel_avr, acc_imu)
+ *   xc       state at the end of the sweep (R, p);  lidar_to_imu: Lid_rot_to_IMU, Lid_offset_to_IMU
+ *   assign   (may be NULL) index of the pose applied to each point, -1 = untouched (stamp not after any pose)
+ * The reference's walk is reproduced: a point takes the latest pose whose time is below the MINIMUM stamp from that point to the
+ * end of the sweep (for time-sorted sweeps: below its own stamp), and the first point is compensated again by every earlier pose. */
+typedef struct vx_imu_pose { double t, R[9], p[3], v[3], angvel[3], acc[3]; } vx_imu_pose;
+int vx_deskew(vx_ctx *ctx, vx_point48 *pts, int64_t n, const vx_imu_pose *poses, int n_poses, const vx_pose *xc, const vx_pose *lidar_to_imu,
+              int32_t *assign);
+
 /* lio_state_estimation fed with the raw scan: xyz is uploaded (12 B/point instead of 96), var_init runs on the device
  * (voxelslam.cpp:1880-1890 call order: var_init(extrin_para, pl, pptr, dept_err, beam_err) then lio_state_estimation(pptr)). */
 int vx_lio_state_estimation_xyz(vx_ctx *ctx, vx_planemap *map, const float *xyz, int64_t n, const vx_pose *ext, double dept_err,

@@ -11,6 +11,7 @@
 #include "icp.hpp"
 #include "session.hpp"
 #include "btc.hpp"
+#include "deskew.hpp"
 #include <chrono>
 
 using namespace orc;
@@ -653,6 +654,22 @@ void orc_btc_plane_cloud(const float *xyz, int64_t n, double voxel_size, double 
   std::vector<BtcPlane> pl = btc_plane_cloud(xyz, n, voxel_size, plane_thre, init_num);
   *n_out = (int64_t)pl.size();
   for (size_t k = 0; k < pl.size() && (int64_t)k < cap; k++) std::memcpy(out + 10 * k, &pl[k], sizeof(BtcPlane));
+}
+
+// IMUEKF::motion_blur, per-point half (ekf_imu.hpp:138-163).  pts: n x {x, y, z, curvature} floats (in place); poses: n_poses x 22 doubles
+// {t, R[9] column-major, p[3], v[3], angvel[3], acc[3]}; xc / lidar_to_imu: {R[9] column-major, p[3]}.
+void orc_deskew(float *pts, int64_t n, const double *poses, int n_poses, const oc_pose *xc, const oc_pose *lidar_to_imu, int32_t *assign) {
+  std::vector<ImuPose> ip(n_poses);
+  for (int i = 0; i < n_poses; i++) {
+    const double *q = poses + 22 * (size_t)i;
+    ip[i].t = q[0];
+    for (int k = 0; k < 9; k++) ip[i].R[k] = q[1 + k];
+    for (int k = 0; k < 3; k++) { ip[i].p[k] = q[10 + k]; ip[i].v[k] = q[13 + k]; ip[i].angvel[k] = q[16 + k]; ip[i].acc[k] = q[19 + k]; }
+  }
+  M3 xR, lR; V3 xp, lp;
+  for (int k = 0; k < 9; k++) { xR[k] = xc->R[k]; lR[k] = lidar_to_imu->R[k]; }
+  for (int k = 0; k < 3; k++) { xp[k] = xc->p[k]; lp[k] = lidar_to_imu->p[k]; }
+  motion_blur_points(reinterpret_cast<SkewPoint *>(pts), (long)n, ip, xR, xp, lR, lp, assign);
 }
 
 // voxel-frames evaluated by acc_evaluate2 since the last reset (bench.py's CPU arm); reset != 0 clears after reading

@@ -323,6 +323,15 @@ def icp_normal(src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
                 resis=rs[:it.value].copy(), eig=eig, is_converge=conv.value)
 
 
+def deskew(pts4, poses22, xc, lidar_to_imu):
+    """orc_deskew: pts4 (n,4) float32 x y z stamp; poses22 (m,22) float64 -> (points (n,4), assign (n,))."""
+    out = np.ascontiguousarray(pts4, dtype=np.float32).copy()
+    ps = np.ascontiguousarray(poses22, dtype=np.float64)
+    a = np.full(out.shape[0], -2, dtype=np.int32)
+    lib().orc_deskew(_p(out), C.c_int64(out.shape[0]), _p(ps), C.c_int(ps.shape[0]), _p(as_poses(xc)), _p(as_poses(lidar_to_imu)), _p(a))
+    return out, a
+
+
 def var_init(xyz, dept_err, beam_err):
     """calcBodyVar + var_init (voxelslam.hpp:180-234), identity extrinsic -> (n,12): pnt 3 + var 9 (col-major)."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32)

@@ -440,6 +440,20 @@ def icp_normal(ctx, src_xyz, src_nrm, tar_xyz, tar_nrm, pose, icp_eigval):
                 resis=rs[:it.value].copy(), eig=eig, is_converge=conv.value)
 
 
+imu_pose_dtype = np.dtype([("t", "<f8"), ("R", "<f8", (9,)), ("p", "<f8", (3,)), ("v", "<f8", (3,)), ("angvel", "<f8", (3,)), ("acc", "<f8", (3,))])
+assert imu_pose_dtype.itemsize == 22 * 8
+
+
+def deskew(ctx, pts, poses, xc, lidar_to_imu, want_assign=True):
+    """vx_deskew: IMUEKF::motion_blur's per-point loop (ekf_imu.hpp:138-163).  pts: point48 array (x, y, z, curvature = stamp);
+    poses: imu_pose_dtype array (ascending t); xc / lidar_to_imu: (R (1,3,3), p (1,3)) or pose_dtype.  -> (points, assign)."""
+    out = np.ascontiguousarray(pts, dtype=point48_dtype).copy()
+    ps = np.ascontiguousarray(poses, dtype=imu_pose_dtype)
+    a = np.full(out.shape[0], -2, dtype=np.int32) if want_assign else None
+    _chk(ctx.lib.vx_deskew(ctx.h, _p(out), C.c_int64(out.shape[0]), _p(ps), C.c_int(ps.shape[0]), _p(as_poses(xc)), _p(as_poses(lidar_to_imu)), _p(a)))
+    return out, a
+
+
 def var_init(ctx, xyz, ext, dept_err, beam_err):
     """calcBodyVar + var_init (voxelslam.hpp:180-234) on the device -> (n,12): pnt 3 + var 9 (col-major)."""
     xyz = np.ascontiguousarray(xyz, dtype=np.float32); n = xyz.shape[0]

@@ -156,3 +156,121 @@ int vx_pvec_update(vx_ctx *ctx, const vx_point_var *pv_in, int64_t n, const vx_p
 }
 
 }  // extern "C"
+
+// ---- IMU de-skew: the per-point half of IMUEKF::motion_blur (ekf_imu.hpp:138-163) -----------------------------------------------------
+#include <cub/cub.cuh>
+#include <thrust/iterator/reverse_iterator.h>
+namespace {
+struct MinOp { __device__ __forceinline__ float operator()(float a, float b) const { return a < b ? a : b; } };
+__global__ void k_deskew_stamp(const vx_point48 *__restrict__ pts, int64_t n, float *__restrict__ stamp) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) stamp[i] = pts[i].curvature;
+}
+// row-by-row products in the order of a plain triple loop (s = 0; s += a(r,k) * b(k)), no contraction: the oracle's arithmetic
+__device__ __forceinline__ void mv(const double *M, const double *v, double *o) {      // M column-major
+#pragma unroll
+  for (int r = 0; r < 3; r++) o[r] = __dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(M[r], v[0])), __dmul_rn(M[3 + r], v[1])), __dmul_rn(M[6 + r], v[2]));
+}
+__device__ __forceinline__ void mtv(const double *M, const double *v, double *o) {     // M^T v
+#pragma unroll
+  for (int r = 0; r < 3; r++) o[r] = __dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(M[3 * r], v[0])), __dmul_rn(M[3 * r + 1], v[1])), __dmul_rn(M[3 * r + 2], v[2]));
+}
+// Exp(ang_vel, dt), tools.hpp:68-84: I + sin(a) K + (1 - cos(a)) K K, K = hat(axis), a = |w| dt; identity when |w| <= 1e-7
+__device__ __forceinline__ void exp_rate(const double *w, double dt, double *E) {
+  const double n = sqrt(__dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(w[0], w[0])), __dmul_rn(w[1], w[1])), __dmul_rn(w[2], w[2])));
+  E[0] = E[4] = E[8] = 1.0; E[1] = E[2] = E[3] = E[5] = E[6] = E[7] = 0.0;
+  if (!(n > 1e-7)) return;
+  const double x = w[0] / n, y = w[1] / n, z = w[2] / n;
+  const double K[9] = {0, z, -y, -z, 0, x, y, -x, 0};     // column-major hat(axis)
+  const double a = __dmul_rn(n, dt), s = sin(a), c1 = __dadd_rn(1.0, -cos(a));
+#pragma unroll
+  for (int c = 0; c < 3; c++)
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      const double kk = __dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(K[r], K[3 * c])), __dmul_rn(K[3 + r], K[3 * c + 1])), __dmul_rn(K[6 + r], K[3 * c + 2]));
+      E[3 * c + r] = __dadd_rn(__dadd_rn(E[3 * c + r], __dmul_rn(s, K[3 * c + r])), __dmul_rn(c1, kk));
+    }
+}
+struct DeskewFrame { double xR[9], xp[3], lR[9], lp[3]; };
+__device__ __forceinline__ void deskew_one(const vx_imu_pose &h, const DeskewFrame &F, float stamp, float &x, float &y, float &z) {
+  const double dt = __dadd_rn((double)stamp, -h.t);
+  double E[9], Ri[9];
+  exp_rate(h.angvel, dt, E);
+#pragma unroll
+  for (int c = 0; c < 3; c++) mv(h.R, E + 3 * c, Ri + 3 * c);             // R_i = R_imu * Exp(angvel_avr, dt)
+  double T[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++)                                             // pos + vel dt + 0.5 acc dt dt - xc.p, left to right
+    T[k] = __dadd_rn(__dadd_rn(__dadd_rn(h.p[k], __dmul_rn(h.v[k], dt)), __dmul_rn(__dmul_rn(__dmul_rn(0.5, h.acc[k]), dt), dt)), -F.xp[k]);
+  const double P[3] = {(double)x, (double)y, (double)z};
+  double a[3], b[3], c[3], d[3];
+  mv(F.lR, P, a);
+#pragma unroll
+  for (int k = 0; k < 3; k++) a[k] = __dadd_rn(a[k], F.lp[k]);            // Lid_rot_to_IMU * P_i + Lid_offset_to_IMU
+  mv(Ri, a, b);
+#pragma unroll
+  for (int k = 0; k < 3; k++) b[k] = __dadd_rn(b[k], T[k]);
+  mtv(F.xR, b, c);
+#pragma unroll
+  for (int k = 0; k < 3; k++) c[k] = __dadd_rn(c[k], -F.lp[k]);
+  mtv(F.lR, c, d);
+  x = (float)d[0]; y = (float)d[1]; z = (float)d[2];
+}
+__global__ void k_deskew(vx_point48 *__restrict__ pts, const float *__restrict__ sufmin, int64_t n, const vx_imu_pose *__restrict__ poses, int np, DeskewFrame F,
+                         int32_t *__restrict__ assign) {
+  const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const double m = (double)sufmin[j];
+  int lo = -1, hi = np;                       // largest i with poses[i].t < m (t ascending)
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (poses[mid].t < m) lo = mid; else hi = mid; }
+  if (assign) assign[j] = lo;
+  if (lo < 0) return;
+  float x = pts[j].x, y = pts[j].y, z = pts[j].z;
+  const float stamp = pts[j].curvature;
+  deskew_one(poses[lo], F, stamp, x, y, z);
+  if (j == 0) {                               // pcl_in.begin() is compensated again by every earlier pose (the walk never moves past it)
+    for (int i = lo - 1; i >= 0; i--)
+      if ((double)stamp > poses[i].t) { deskew_one(poses[i], F, stamp, x, y, z); if (assign) assign[0] = i; }
+  }
+  pts[j].x = x; pts[j].y = y; pts[j].z = z;
+}
+}  // namespace
+
+extern "C" int vx_deskew(vx_ctx *ctx, vx_point48 *pts, int64_t n, const vx_imu_pose *poses, int n_poses, const vx_pose *xc, const vx_pose *lidar_to_imu,
+                         int32_t *assign) {
+  VX_ARG(ctx && n >= 0 && n < ((int64_t)1 << 31) && n_poses >= 0 && xc && lidar_to_imu && (n == 0 || pts) && (n_poses == 0 || poses));
+  VX_TRY(bind(ctx));
+  if (n == 0) return VX_OK;
+  if (n_poses == 0) { if (assign) for (int64_t k = 0; k < n; k++) assign[k] = -1; return VX_OK; }
+  for (int i = 1; i < n_poses; i++) VX_ARG(poses[i].t >= poses[i - 1].t);
+  cudaStream_t st = ctx->stream;
+  DevBuf d_pts, d_st, d_min, d_poses, d_as;
+  DeskewFrame F;
+  for (int k = 0; k < 9; k++) { F.xR[k] = xc->R[k]; F.lR[k] = lidar_to_imu->R[k]; }
+  for (int k = 0; k < 3; k++) { F.xp[k] = xc->p[k]; F.lp[k] = lidar_to_imu->p[k]; }
+  auto body = [&]() -> int {
+    VX_TRY(d_pts.reserve(sizeof(vx_point48) * n)); VX_TRY(d_st.reserve(4 * n)); VX_TRY(d_min.reserve(4 * n));
+    VX_TRY(d_poses.reserve(sizeof(vx_imu_pose) * n_poses)); VX_TRY(d_as.reserve(4 * n));
+    VX_CUDA(cudaMemcpyAsync(d_pts.p, pts, sizeof(vx_point48) * n, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_poses.p, poses, sizeof(vx_imu_pose) * n_poses, cudaMemcpyHostToDevice, st));
+    VX_KERNEL(ctx, "k_deskew_stamp", k_deskew_stamp<<<blocks_for(n, 256), 256, 0, st>>>(d_pts.as<vx_point48>(), n, d_st.as<float>()));
+    // minimum stamp from each point to the end of the sweep: an inclusive min-scan over the reversed array
+    auto rin = thrust::make_reverse_iterator(d_st.as<float>() + n);
+    auto rout = thrust::make_reverse_iterator(d_min.as<float>() + n);
+    size_t tb = 0;
+    VX_CUDA(cub::DeviceScan::InclusiveScan(nullptr, tb, rin, rout, MinOp(), (int)n, st));
+    VX_TRY(ctx->scratch.reserve(tb));
+    VX_CUDA(cub::DeviceScan::InclusiveScan(ctx->scratch.p, tb, rin, rout, MinOp(), (int)n, st));
+    ctx->launches += 2;
+    VX_KERNEL(ctx, "k_deskew", k_deskew<<<blocks_for(n, 128), 128, 0, st>>>(d_pts.as<vx_point48>(), d_min.as<float>(), n, d_poses.as<vx_imu_pose>(), n_poses, F,
+                                                                         assign ? d_as.as<int32_t>() : nullptr));
+    VX_CUDA(cudaMemcpyAsync(pts, d_pts.p, sizeof(vx_point48) * n, cudaMemcpyDeviceToHost, st));
+    if (assign) VX_CUDA(cudaMemcpyAsync(assign, d_as.p, 4 * n, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : {&d_pts, &d_st, &d_min, &d_poses, &d_as}) b->release();
+  return rc;
+}
