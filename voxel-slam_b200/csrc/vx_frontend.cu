@@ -166,7 +166,7 @@ __global__ void k_deskew_stamp(const vx_point48 *__restrict__ pts, int64_t n, fl
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < n) stamp[i] = pts[i].curvature;
 }
-// row-by-row products in the order of a plain triple loop (s = 0; s += a(r,k) * b(k)), no contraction: the oracle's arithmetic
+// row-by-row products in the order of a plain triple loop (s = 0; s += a(r,k) * b(k)), no contraction: the arithmetic of a sequential host loop
 __device__ __forceinline__ void mv(const double *M, const double *v, double *o) {      // M column-major
 #pragma unroll
   for (int r = 0; r < 3; r++) o[r] = __dadd_rn(__dadd_rn(__dadd_rn(0.0, __dmul_rn(M[r], v[0])), __dmul_rn(M[3 + r], v[1])), __dmul_rn(M[6 + r], v[2]));
