@@ -452,6 +452,11 @@ int vx_planemap_free(vx_planemap *map);
 int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, const vx_pose *pose,
                             const double *rot_var9, const double *tsl_var9, int32_t *leaf_cache, double *HTH36, double *HTz6,
                             double *nnt9, int32_t *match_num, int32_t *flags);
+/* int match(feat_map, wld, pla, var_wld, sigma_d, oc)  voxel_map.hpp:2167-2205 for a batch of n WORLD points (wld3: n x 3) with their
+ * world covariances (var_wld9: n x 9 column-major): flags (the reference's return value), leaf (node index of `oc`, -1), sigma_d, and
+ * — when planes != NULL — a copy of the matched leaf's record (the Plane behind `pla`).  leaf / sigma_d / planes may be NULL. */
+int vx_planemap_match(vx_ctx *ctx, vx_planemap *map, const double *wld3, const double *var_wld9, int64_t n, int32_t *flags, int32_t *leaf,
+                      double *sigma_d, vx_map_node *planes);
 /* bool VOXEL_SLAM::lio_state_estimation(PVecPtr pptr)  voxelslam.cpp:962-1098: <= 4 iterations, 15x15 gain on the host,
  * points and leaf cache stay on the device.  *healthy = the reference's return (lambda_min(sum n n^T) >= 14). */
 int vx_lio_state_estimation(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, vx_lio_state *x, int32_t *healthy,

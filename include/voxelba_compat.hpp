@@ -23,6 +23,8 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <cstdint>
 #include <cstring>
 #include <deque>
 #include <vector>
@@ -149,6 +151,14 @@ template <class PRE> inline void pre_back(const vx_imu_pre &p, PRE &q) {   // da
   std::memcpy(q.dbg_buf.data(), p.dbg_buf, 24); std::memcpy(q.dba_buf.data(), p.dba_buf, 24);
 }
 
+// pcl::PointCloud keeps width / height beside points; any cloud type without them is left alone
+template <class Cloud> inline auto set_cloud_dims(Cloud &c, uint32_t n, int) -> decltype(c.width = n, void()) { c.width = n; c.height = 1; }
+template <class Cloud> inline void set_cloud_dims(Cloud &, uint32_t, long) {}
+#ifdef VOXELBA_COMPAT_STANDALONE
+inline Eigen::FixedMat<6, 1> vec6() { return Eigen::FixedMat<6, 1>(); }
+#else
+inline Eigen::Matrix<double, 6, 1> vec6() { return Eigen::Matrix<double, 6, 1>::Zero(); }
+#endif
 }  // namespace vxc
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -172,6 +182,7 @@ public:
   // voxel_map.hpp:139-147
   void push_voxel(std::vector<PointCluster> &vec_orig, PointCluster &fix, double coe, Eigen::Vector3d &eig_value, Eigen::Matrix3d &eig_vector,
                   PointCluster &pcr_add) {
+    on_device_ = false;
     plvec_voxels.push_back(vec_orig);
     sig_vecs.push_back(fix);
     coeffs.push_back(coe);
@@ -203,15 +214,39 @@ public:
   // voxel_map.hpp:328-336
   void clear() {
     sig_vecs.clear(); plvec_voxels.clear(); eig_values.clear(); eig_vectors.clear(); pcr_adds.clear(); coeffs.clear();
-    dirty_ = true;
+    dirty_ = true; on_device_ = false;
   }
 
   // ---- adaptor plumbing ----
   vx_factor *device() { sync_device(); return dev_; }
+  // the handle for a producer that fills the factor ON THE DEVICE (multi_recut's tras_opt, OctreeGBA_multi_recut): the public member
+  // vectors stay empty (nothing on this path reads them: margi takes the cache from the device handle), pull_host() fills them on demand
+  vx_factor *device_for_fill() {
+    if (dev_ && dev_w_ != win_size) { vx_factor_free(dev_); dev_ = nullptr; }
+    if (!dev_) { VXC_CHECK(vx_factor_create(vxc::context(), win_size, 1, &dev_)); dev_w_ = win_size; }
+    sig_vecs.clear(); plvec_voxels.clear(); eig_values.clear(); eig_vectors.clear(); pcr_adds.clear(); coeffs.clear();
+    dirty_ = false; on_device_ = true;
+    return dev_;
+  }
+  int64_t num_voxels() const { return on_device_ && dev_ ? vx_factor_num_voxels(dev_) : (int64_t)plvec_voxels.size(); }
+  // device -> public member vectors (plvec_voxels dense per window slot, coeffs, cache), for callers that read them
+  void pull_host() {
+    if (!on_device_ || !dev_) return;
+    const int64_t V = vx_factor_num_voxels(dev_), nnz = vx_factor_num_voxel_frames(dev_);
+    std::vector<int64_t> off(V + 1); std::vector<int32_t> fr(nnz); std::vector<vx_cluster> cl(nnz), mrg(V); std::vector<double> coe(V), ev(3 * V), evec(9 * V);
+    VXC_CHECK(vx_factor_download_csr(dev_, off.data(), fr.data(), cl.data(), coe.data()));
+    VXC_CHECK(vx_factor_download_cache(dev_, ev.data(), evec.data(), mrg.data()));
+    plvec_voxels.assign(V, std::vector<PointCluster>(win_size)); sig_vecs.assign(V, PointCluster()); coeffs = coe;
+    eig_values.resize(V); eig_vectors.resize(V); pcr_adds.resize(V);
+    for (int64_t a = 0; a < V; a++) {
+      for (int64_t e = off[a]; e < off[a + 1]; e++) vxc::from_c(cl[e], plvec_voxels[a][fr[e]]);
+      std::memcpy(eig_values[a].data(), &ev[3 * a], 24); std::memcpy(eig_vectors[a].data(), &evec[9 * a], 72); vxc::from_c(mrg[a], pcr_adds[a]);
+    }
+  }
   // after an optimizer ran on the device handle: bring the cache the reference would have left in the member vectors
   void pull_cache(int head, int end) {
     const size_t V = plvec_voxels.size();
-    if (V == 0) return;
+    if (V == 0 || on_device_) return;
     std::vector<double> ev(3 * V), evec(9 * V);
     std::vector<vx_cluster> mrg(V);
     VXC_CHECK(vx_factor_download_cache(dev_, ev.data(), evec.data(), mrg.data()));
@@ -227,6 +262,7 @@ private:
   vx_factor *dev_ = nullptr;
   int dev_w_ = -1;
   bool dirty_ = true;
+  bool on_device_ = false;     // filled by a device producer: the member vectors are not authoritative
 
   std::vector<vx_pose> poses(const std::vector<IMUST> &xs) const {
     std::vector<vx_pose> ps(win_size);
@@ -263,12 +299,12 @@ public:
   // voxel_map.hpp:347-389 (the worker threads are the device; the split into thd_num ranges only re-orders the sum)
   double divide_thread(std::vector<IMUST> &x_stats, LidarFactor &voxhess, Eigen::MatrixXd &Hess, Eigen::VectorXd &JacT) {
     double residual = 0;
-    voxhess.acc_evaluate2(x_stats, 0, (int)voxhess.plvec_voxels.size(), Hess, JacT, residual);
+    voxhess.acc_evaluate2(x_stats, 0, (int)voxhess.num_voxels(), Hess, JacT, residual);
     return residual;
   }
   // voxel_map.hpp:391-420, including the exit of :399-403
   double only_residual(std::vector<IMUST> &x_stats, LidarFactor &voxhess) {
-    const int g_size = (int)voxhess.plvec_voxels.size();
+    const int g_size = (int)voxhess.num_voxels();
     if (g_size < thd_num) { std::printf("Too Less Voxel"); std::exit(0); }
     double residual = 0;
     voxhess.evaluate_only_residual(x_stats, 0, g_size, residual);
@@ -356,4 +392,9 @@ inline void down_sampling_voxel(Cloud &pl_feat, double voxel_size) {
   VXC_CHECK(vx_downsample_voxel(vxc::context(), reinterpret_cast<const vx_point48 *>(pl_feat.points.data()), n, voxel_size, out.data(), &m));
   pl_feat.points.resize(m);
   std::memcpy(pl_feat.points.data(), out.data(), sizeof(vx_point48) * m);
+  vxc::set_cloud_dims(pl_feat, (uint32_t)m, 0);     // the reference clear()s and push_back()s: width follows the size, height 1
 }
+
+using VOX_HESS = LidarFactor;      // north_star's name for the factor
+
+#include "voxelba_compat_map.hpp"

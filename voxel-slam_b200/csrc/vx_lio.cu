@@ -14,6 +14,7 @@
 #include "vx_planemap.cuh"
 #include <cmath>
 #include <algorithm>
+#include <vector>
 
 using namespace vx;
 
@@ -192,7 +193,33 @@ k_lio_pass(const vx_point_var *__restrict__ pts, int64_t n, LioPose X, const uin
     partial[(size_t)blockIdx.x * NACC + threadIdx.x] = s;
   }
 }
-// fixed-order sum of the block partials
+// int match(feat_map, wld, pla, var_wld, sigma_d, oc)  voxel_map.hpp:2167-2205 for a batch of WORLD points with their world
+// covariances: root lookup, descent (OctoTree::match :1693-1720), the leaf gates.  flag / leaf node / sigma_d per point.
+__global__ void k_match_points(const double *__restrict__ wld3, const double *__restrict__ var9, int64_t n, const uint64_t *__restrict__ hkeys,
+                               const int32_t *__restrict__ hvals, uint64_t hmask, const vx_map_node *__restrict__ nodes, double voxel_size,
+                               int32_t *__restrict__ flags, int32_t *__restrict__ leaf, double *__restrict__ sigma) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double wld[3] = {wld3[3 * i], wld3[3 * i + 1], wld3[3 * i + 2]};
+  const M3d vw = from_colmajor(var9 + 9 * i);
+  int flag = 0, lf = -1;
+  double sigma_d = 0.0;
+  int32_t node = -1;
+  uint64_t key;
+  if (pack_key(key_axis_d(wld[0], voxel_size), key_axis_d(wld[1], voxel_size), key_axis_d(wld[2], voxel_size), key)) node = root_lookup(hkeys, hvals, hmask, key);
+  while (node >= 0) {
+    const vx_map_node &nd = nodes[node];
+    if (nd.octo_state == 0) {
+      flag = leaf_match(nd, wld, vw, sigma_d);
+      if (flag) lf = node;
+      break;
+    }
+    node = nd.child[4 * (wld[0] > nd.center[0]) + 2 * (wld[1] > nd.center[1]) + (wld[2] > nd.center[2])];
+  }
+  flags[i] = flag; leaf[i] = lf; sigma[i] = flag ? sigma_d : 0.0;
+}
+
+// fixed-order sum of the block partials// fixed-order sum of the block partials
 __global__ void __launch_bounds__(256) k_lio_fin(const double *__restrict__ partial, int nblocks, double *__restrict__ out) {
   __shared__ double sh[256];
   const int k = blockIdx.x;
@@ -361,6 +388,38 @@ int vx_planemap_free(vx_planemap *m) {
   m->hkeys.release(); m->hvals.release(); m->nodes.release();
   delete m;
   return VX_OK;
+}
+
+int vx_planemap_match(vx_ctx *ctx, vx_planemap *map, const double *wld3, const double *var_wld9, int64_t n, int32_t *flags, int32_t *leaf, double *sigma_d,
+                      vx_map_node *planes) {
+  VX_ARG(map != nullptr && n >= 0 && (n == 0 || (wld3 && var_wld9 && flags)));
+  VX_TRY(bind(ctx));
+  if (n == 0) return VX_OK;
+  cudaStream_t st = ctx->stream;
+  DevBuf d_w, d_v, d_f, d_l, d_s;
+  std::vector<int32_t> lf(n);
+  auto body = [&]() -> int {
+    VX_TRY(d_w.reserve(24 * n)); VX_TRY(d_v.reserve(72 * n)); VX_TRY(d_f.reserve(4 * n)); VX_TRY(d_l.reserve(4 * n)); VX_TRY(d_s.reserve(8 * n));
+    VX_CUDA(cudaMemcpyAsync(d_w.p, wld3, 24 * n, cudaMemcpyHostToDevice, st));
+    VX_CUDA(cudaMemcpyAsync(d_v.p, var_wld9, 72 * n, cudaMemcpyHostToDevice, st));
+    VX_KERNEL(ctx, "k_match_points", k_match_points<<<blocks_for(n, 128), 128, 0, st>>>(d_w.as<double>(), d_v.as<double>(), n, map->hkeys.as<uint64_t>(), map->hvals.as<int32_t>(),
+                                                                                     map->hmask, map->nodes.as<vx_map_node>(), map->voxel_size, d_f.as<int32_t>(),
+                                                                                     d_l.as<int32_t>(), d_s.as<double>()));
+    VX_CUDA(cudaMemcpyAsync(flags, d_f.p, 4 * n, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaMemcpyAsync(lf.data(), d_l.p, 4 * n, cudaMemcpyDeviceToHost, st));
+    if (sigma_d) VX_CUDA(cudaMemcpyAsync(sigma_d, d_s.p, 8 * n, cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (planes)        // the Plane the reference hands back through `pla` (a copy of the matched leaf's record)
+      for (int64_t k = 0; k < n; k++)
+        if (lf[k] >= 0) VX_CUDA(cudaMemcpyAsync(&planes[k], map->nodes.as<vx_map_node>() + lf[k], sizeof(vx_map_node), cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (leaf) std::copy(lf.begin(), lf.end(), leaf);
+    return VX_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(st);
+  for (DevBuf *b : {&d_w, &d_v, &d_f, &d_l, &d_s}) b->release();
+  return rc;
 }
 
 int vx_lio_match_accumulate(vx_ctx *ctx, vx_planemap *map, const vx_point_var *pts, int64_t n, const vx_pose *pose, const double *rot_var9,
