@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--keyframes", type=int, default=2000)
     ap.add_argument("--n-az", type=int, default=625, help="azimuth steps of the 32-ring scan: 625 -> 20,000 rays per keyframe")
     ap.add_argument("--total-max-iter", type=int, default=3, help="GBA/total_max_iter (hesai.yaml)")
-    ap.add_argument("--cpu-sample-windows", type=int, default=0, help="bottom windows per CPU step (0: 8 x host cores)")
+    ap.add_argument("--cpu-sample-windows", type=int, default=0, help="bottom windows of the CPU arm's mini-job (0: 40)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extras", action="store_true", help="skip the per-row roofline / other-rows legs")
     return ap.parse_args()
@@ -135,39 +135,47 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons), "when": "sampled only while the timed regions (resident + e2e) ran"}
 
 
-# ---- CPU arm: the oracle's HBA_add_edge on a bounded sample of the bottom windows ---------------------------------------------
+# ---- CPU arm: a complete, smaller hierarchical job through the oracle (CPU restatement of the reference) -----------------------------
 def cpu_windows(args, d, n_sample):
+    """The first n_sample full bottom windows (consecutive: their submaps form a connected top level)."""
     n_full, _ = n_windows_of(args.keyframes)
-    n_sample = max(1, min(n_sample, n_full))
-    idx = np.unique(np.linspace(0, n_full - 1, n_sample).astype(int))      # spread over the trajectory
-    Rs, ps = d["start"]
-    items = []
-    for w in idx:
-        s = 5 * int(w)
-        cl = [d["xyz"][d["off"][i]:d["off"][i + 1]] for i in range(s, s + 10)]
-        items.append((cl, (Rs[s:s + 10], ps[s:s + 10]), np.arange(s, s + 10)))
-    return items
+    return list(range(max(2, min(n_sample, n_full))))
 
 
-def cpu_pass(items, threads):
-    """One pass of the oracle's HBA_add_edge(max_iter = 1, thread_num = 2: voxelslam.cpp:3096) over the sample, one window per task.
-    -> (voxel-frames through the oracle's acc_evaluate2, seconds)."""
+def cpu_pass(d, windows, threads):
+    """thd_globalmapping over the keyframes of `windows` with the oracle: every bottom window through HBA_add_edge(max_iter 1, thread_num 2,
+    plptr) (voxelslam.cpp:3096; one window per host thread), then the top-level HBA_add_edge over their submaps (total_max_iter 3, all
+    host threads inside).  -> (voxel-frames through the oracle's acc_evaluate2, seconds, (bottom s, top s))."""
     import concurrent.futures as cf
     import ctypes
     import oracle_bind as ob
     lib = ob.lib()
     lib.orc_vf_counter.restype = ctypes.c_int64
+    Rs, ps = d["start"]
+
+    def one(w):
+        s = 5 * w
+        cl = [d["xyz"][d["off"][i]:d["off"][i + 1]] for i in range(s, s + 10)]
+        r = ob.hba_add_edge(cl, (Rs[s:s + 10], ps[s:s + 10]), LOCAL, GBA, MAX_LAYER, 1, thread_num=2, ids=np.arange(s, s + 10), mps=np.zeros(10), want_cloud=True)
+        m = r["merged"]
+        return np.stack([m["x"], m["y"], m["z"]], axis=1).astype(np.float32)
+
     lib.orc_vf_counter(1)
     t0 = time.perf_counter()
     with cf.ThreadPoolExecutor(max_workers=threads) as ex:
-        list(ex.map(lambda it: ob.hba_add_edge(it[0], it[1], LOCAL, GBA, MAX_LAYER, 1, thread_num=2, ids=it[2], mps=np.zeros(10)), items))
-    dt = time.perf_counter() - t0
-    return int(lib.orc_vf_counter(1)), dt
+        subs = list(ex.map(one, windows))
+    t1 = time.perf_counter()
+    tk = [5 * w for w in windows]
+    ob.hba_add_edge(subs, (Rs[tk], ps[tk]), LOCAL, GBA, MAX_LAYER, 3, thread_num=threads, ids=tk, mps=np.zeros(len(tk)))
+    t2 = time.perf_counter()
+    return int(lib.orc_vf_counter(1)), t2 - t0, (t1 - t0, t2 - t1)
 
 
 def cpu_sample_text(args, n_items, cores):
-    return "%d of the %d full bottom windows per step (map build + damping_iter(up=4) + edges each; the top level is not sampled: one W=400 " \
-           "pass over 35 M points takes minutes on the host), oracle HBA_add_edge, one window per task on %d threads" % (n_items, n_windows_of(args.keyframes)[0], cores)
+    return "a complete hierarchical job over the first %d of the %d bottom windows (%d keyframes): every window through the oracle's HBA_add_edge(max_iter 1) " \
+           "(map build + damping_iter(up=4) + edges + submap cloud), one window per task on %d threads, then the top-level HBA_add_edge over the %d submaps " \
+           "(total_max_iter 3, %d threads inside); the full job's top level (W = 400, 2,400 unknowns, 35 M points) costs the host relatively more" % \
+           (n_items, n_windows_of(args.keyframes)[0], 5 * n_items + 5, cores, n_items, cores)
 
 
 def run_reference(args, rank, world):
@@ -178,12 +186,12 @@ def run_reference(args, rank, world):
     ge.build_oracle()
     d = c4_workload(args, 1)
     cores = os.cpu_count() or 1
-    items = cpu_windows(args, d, args.cpu_sample_windows or 8 * cores)
+    items = cpu_windows(args, d, args.cpu_sample_windows or 40)
     for _ in range(max(1, min(args.warmup, 1))):
-        cpu_pass(items, cores)
+        cpu_pass(d, items[:max(2, len(items) // 4)], cores)
     vf = 0; tot = 0.0
     for _ in range(args.steps):
-        v, t = cpu_pass(items, cores)
+        v, t, _ = cpu_pass(d, items, cores)
         vf += v; tot += t
     val = vf / tot
     print(json.dumps({
@@ -283,21 +291,22 @@ def extra_benches(pkg, ctx, peak_hbm, fp64):
         "B2": {"ms": ms_r, "voxel_frames_per_s": nnz / (ms_r * 1e-3), "hbm_gbs": b2 / (ms_r * 1e-3) / 1e9, "hbm_frac": b2 / (ms_r * 1e-3) / 1e9 / peak_hbm}}
     f.free()
 
-    # --- C2: LIO on ONE map for both arms: 10 XT32 sweeps (64,000 rays) through the device sliding-window map and, the same sweeps
+    # --- C2: LIO on ONE map for both arms: 14 XT32 sweeps (64,000 rays) through the device sliding-window map and, the same sweeps
     #     with the same covariances, through the oracle's map; the 11th sweep is registered against each
     import oracle_bind as ob
     rng = np.random.Generator(np.random.PCG64(20241008 + 2))
     rects = scene.room()
     Wl = 10
-    Rl, pl = scene.arc_trajectory(Wl + 1, 5, step=0.5, yaw_step_deg=3.0)
+    n_sw = Wl + 4
+    Rl, pl = scene.arc_trajectory(n_sw + 1, 5, step=0.5, yaw_step_deg=3.0)
     cov = ob.default_cov()
     vm = pkg.VoxelMap(ctx, win_size=Wl, voxel_size=1.0, thre=(1, 1, 1, 1), max_layer=2)
     om = ob.LocalMap(win_size=Wl, voxel_size=1.0, thre=(1, 1, 1, 1), max_layer=2, dept_err=0.01, beam_err=0.01)
     fl_ = pkg.Factor(ctx, Wl)
     win = np.zeros(0, dtype=pkg.pose_dtype)
-    t_ins, t_rec, t_cpu_ins, npts = [], [], [], []
+    t_ins, t_rec, t_mar, t_cpu_ins, npts = [], [], [], [], []
     ctx.profile(True)
-    for i in range(Wl):
+    for i in range(n_sw):     # the local-mapping loop without the optimizer: insert, recut, marginalise the oldest scan once the window is full
         xyz = scene.scan(rects, Rl[i], pl[i], scene.xt32_dirs(2000), rng, range_noise=0.01, blind=0.7).astype(np.float32)
         t0 = time.perf_counter()
         pv, pw = om.insert(xyz, (Rl[i:i + 1], pl[i:i + 1]), cov); om.recut()
@@ -307,25 +316,29 @@ def extra_benches(pkg, ctx, peak_hbm, fp64):
         vm.cut_voxel(pv, pw, win.shape[0] - 1)
         t1 = time.perf_counter()
         vm.recut(win, fl_)
-        t_ins.append(t1 - t0); t_rec.append(time.perf_counter() - t1); npts.append(xyz.shape[0])
+        t2 = time.perf_counter()
+        t_ins.append(t1 - t0); t_rec.append(t2 - t1); npts.append(xyz.shape[0])
+        if om.margi():
+            t3 = time.perf_counter()
+            vm.margi(win, fl_); vm.shift_window(1); win = win[1:].copy()
+            t_mar.append(time.perf_counter() - t3)
     prof = ctx.profile_read(); ctx.profile(False)
     n_pt = float(np.mean(npts[2:]))
-    kacc = prof.get("k_accumulate", (0.0, 1))
-    ins_kernel_ms = sum(v[0] for kname, v in prof.items() if kname.startswith("k_") and kname not in ("k_leaf_decide",)) / Wl
+    ins_kernel_ms = sum(v[0] for kname, v in prof.items() if kname.startswith("k_")) / n_sw
     out["local_map"] = {"points_per_scan": int(n_pt), "nodes": vm.num_nodes, "roots": vm.num_roots, "factor_voxels": fl_.num_voxels,
                         "ms_cut_voxel_e2e": 1e3 * float(np.median(t_ins[2:])), "ms_recut_tras_opt_e2e": 1e3 * float(np.median(t_rec[2:])),
+                        "ms_margi_e2e": 1e3 * float(np.median(t_mar)) if t_mar else None,
                         "cut_voxel_points_per_s_e2e": n_pt / float(np.median(t_ins[2:])),
-                        "roofline": {"bound": "hbm", "kernel": "all map kernels of one insertion + recut (k_accumulate is the moment accumulation)",
+                        "roofline": {"bound": "hbm", "kernel": "all map kernels of one sweep (insertion + recut + tras_opt + margi)",
                                      "achieved": 124 * n_pt / (ins_kernel_ms * 1e-3) / 1e9, "peak": peak_hbm, "unit": "GB/s",
                                      "frac": 124 * n_pt / (ins_kernel_ms * 1e-3) / 1e9 / peak_hbm, "ms_kernels_per_scan": ins_kernel_ms,
-                                     "k_accumulate_ms_per_launch": kacc[0] / max(kacc[1], 1),
                                      "note": "A1+A6: 120 B/point read + 4 B label written (SURVEY §8d); 64 k points per call: launch-latency bound, tens of kernels of a few us"},
                         "cpu_baseline": {"ms_insert_recut": 1e3 * float(np.median(t_cpu_ins[2:])), "cores": 1, "kind": "port",
                                          "sample": "the same sweeps through the oracle's cut_voxel + recut (single-threaded; the reference uses 5 threads)"},
                         "what": "vx_map_cut_voxel + vx_map_recut (+ tras_opt into the device factor) per 64k-ray XT32 sweep, W=10, voxel 1 m, host buffers in (wall clock)"}
-    q = scene.scan(rects, Rl[Wl], pl[Wl], scene.xt32_dirs(2000), rng, range_noise=0.01, blind=0.7).astype(np.float32)
+    q = scene.scan(rects, Rl[n_sw], pl[n_sw], scene.xt32_dirs(2000), rng, range_noise=0.01, blind=0.7).astype(np.float32)
     opv = ob.var_init(q, 0.01, 0.01)
-    R0, p0 = synth.perturb_poses((Rl[Wl:Wl + 1], pl[Wl:Wl + 1]), 3, 0.003, 0.02, fix_first=False)
+    R0, p0 = synth.perturb_poses((Rl[n_sw:n_sw + 1], pl[n_sw:n_sw + 1]), 3, 0.003, 0.02, fix_first=False)
     gm = vm.planemap()
     best = 1e30
     for _ in range(3):
@@ -351,7 +364,7 @@ def extra_benches(pkg, ctx, peak_hbm, fp64):
                      "frac": lio_bytes / (kms * 1e-3) / 1e9 / peak_hbm if kms > 0 else None, "ms_per_launch": kms, "points_per_s_kernel": q.shape[0] / (kms * 1e-3) if kms > 0 else None,
                      "note": "D2: 96 B/point-iteration + 228 B plane record per matched point (SURVEY §8d); 60 k points do not fill a B200: launch-latency bound"},
         "cpu_baseline": {"ms": 1e3 * best, "point_iterations_per_s": q.shape[0] * oref["iters"] / best, "cores": 1, "kind": "port",
-                         "sample": "the same sweep against the oracle's map of the SAME 10 sweeps and covariances (the device map equals it node for node), best of 3"},
+                         "sample": "the same sweep against the oracle's map of the SAME 14 sweeps and covariances (the device map equals it node for node), best of 3"},
         "what": "vx_lio_state_estimation on the device-built sliding-window map: whole ESIKF update of one ~60k-point sweep, host pointVar in, state out (wall clock)"}
     fl_.free(); vm.free()
 
@@ -573,14 +586,11 @@ def run_b200(args, rank, world, local_rank):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        items = cpu_windows(args, d, args.cpu_sample_windows or 8 * cores)
-        cpu_pass(items[:max(1, cores // 2)], cores)                   # warm-up
-        vf_c, t_c = cpu_pass(items, cores)
+        items = cpu_windows(args, d, args.cpu_sample_windows or 40)
+        cpu_pass(d, items[:max(2, len(items) // 4)], cores)           # warm-up
+        vf_c, t_c, (t_b, t_t) = cpu_pass(d, items, cores)
         cpu = {"value": vf_c / t_c, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(args, len(items), cores) +
-               "; %.1f s, %d voxel-frames through the oracle's acc_evaluate2" % (t_c, vf_c)}
-        # the reference's own thread count for this call (thread_num = 2, voxelslam.cpp:3096): one window at a time, 2 threads inside
-        vf_2, t_2 = cpu_pass(items[:max(2, len(items) // 8)], 1)
-        cpu["at_reference_thread_num_2"] = {"value": vf_2 / t_2, "windows": max(2, len(items) // 8)}
+               "; %.1f s (bottom %.1f s, top %.1f s), %d voxel-frames through the oracle's acc_evaluate2" % (t_c, t_b, t_t, vf_c)}
     if rank == 0 and world == 1 and not args.no_extras:
         extra["other_rows"] = extra_benches(pkg, ctx, peak_hbm, fp64)
     if rank == 0:

@@ -586,12 +586,16 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   DevBuf &segm = T.make(), &segN = T.make(), &segF = T.make();
   VX_TRY(segm.reserve(sizeof(double) * 18 * (size_t)nseg)); VX_TRY(segN.reserve(4 * (size_t)nseg)); VX_TRY(segF.reserve(4 * (size_t)nseg));
   {
-    static const int gl = getenv("VX_SEG_LANES") ? atoi(getenv("VX_SEG_LANES")) : 4;
+    // One thread per (leaf, frame) segment: points are added in scan order (the reference's own order of pushes), no shuffles, and the
+    // result does not depend on how many windows share the launch.  A segment holds a handful of points (2 on average in the fine
+    // pass of a bottom-level build, ~10 in the coarse top-level pass).  VX_SEG_LANES = 2 ... 32 selects the cooperative variants.
+    static const int gl = getenv("VX_SEG_LANES") ? atoi(getenv("VX_SEG_LANES")) : 1;
 #define VX_SEG_LAUNCH(GL)                                                                                                                    \
     VX_KERNEL(ctx, "k_seg_moments", k_seg_moments<GL><<<blocks_for((int64_t)nseg * GL, 256), 256, 0, st>>>(                                    \
         d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, d_poses.as<double>(), sidx, k1s, seg_start.as<int32_t>(), nseg, \
         segm.as<double>(), segN.as<int32_t>(), segF.as<int32_t>()))
-    if (gl == 32) { VX_SEG_LAUNCH(32); } else if (gl == 16) { VX_SEG_LAUNCH(16); } else if (gl == 8) { VX_SEG_LAUNCH(8); } else if (gl == 2) { VX_SEG_LAUNCH(2); } else { VX_SEG_LAUNCH(4); }
+    if (gl == 32) { VX_SEG_LAUNCH(32); } else if (gl == 16) { VX_SEG_LAUNCH(16); } else if (gl == 8) { VX_SEG_LAUNCH(8); } else if (gl == 2) { VX_SEG_LAUNCH(2); }
+    else if (gl == 1) { VX_SEG_LAUNCH(1); } else { VX_SEG_LAUNCH(4); }
 #undef VX_SEG_LAUNCH
   }
 
