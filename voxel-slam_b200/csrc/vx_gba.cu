@@ -340,28 +340,29 @@ struct LevelPtrs {
   const int32_t *incl[MAXL + 1];
   const int32_t *flags[MAXL + 1];
 };
-// 6b. segment -> key (voxel << 32 | frame) of the emitted ancestor, or ~0
+// 6b. segment -> key (voxel << fb | frame) of the emitted ancestor; segments under no emitted node get voxel = V (they sort last).
+// The key uses exactly bits_for(V + 1) + fb bits, so the radix sort that follows runs 4 passes where (voxel << 32 | frame) ran 8.
 __global__ void k_seg_voxel(const int32_t *__restrict__ seg_start, const int32_t *__restrict__ segF, int64_t nseg, LevelPtrs lp, int L,
-                            const int32_t *__restrict__ vid_excl, uint64_t *__restrict__ key, int32_t *__restrict__ val) {
+                            const int32_t *__restrict__ vid_excl, int64_t V, int fb, uint64_t *__restrict__ key, int32_t *__restrict__ val) {
   const int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (s >= nseg) return;
   const int32_t i0 = seg_start[s];
-  uint64_t kk = ~0ull;
+  uint64_t kk = (uint64_t)V << fb;
   for (int l = L; l >= 0; l--) {
     const int32_t k = lp.incl[l][i0] - 1;
-    if (lp.flags[l][k] & 16) { kk = ((uint64_t)(uint32_t)vid_excl[lp.start[l][k]] << 32) | (uint32_t)segF[s]; break; }
+    if (lp.flags[l][k] & 16) { kk = ((uint64_t)(uint32_t)vid_excl[lp.start[l][k]] << fb) | (uint32_t)segF[s]; break; }
   }
   key[s] = kk;
   val[s] = (int32_t)s;
 }
-__global__ void k_vf_heads(const uint64_t *__restrict__ key, int64_t n, int32_t *__restrict__ flag) {
+__global__ void k_vf_heads(const uint64_t *__restrict__ key, int64_t n, int64_t V, int fb, int32_t *__restrict__ flag) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  flag[i] = (key[i] != ~0ull && (i == 0 || key[i] != key[i - 1])) ? 1 : 0;
+  flag[i] = ((int64_t)(key[i] >> fb) != V && (i == 0 || key[i] != key[i - 1])) ? 1 : 0;
 }
 // 6c. one thread per voxel-frame: sum its segments' scan-local moments in order
 __global__ void k_vf_fill(const uint64_t *__restrict__ key, const int32_t *__restrict__ sval, const int32_t *__restrict__ vf_start, int64_t nnz,
-                          int64_t nvalid, const double *__restrict__ segm, const int32_t *__restrict__ segN, int64_t nseg, double *__restrict__ mom,
+                          int64_t nvalid, const double *__restrict__ segm, const int32_t *__restrict__ segN, int64_t nseg, int fb, double *__restrict__ mom,
                           int32_t *__restrict__ cnt, int32_t *__restrict__ frame, int32_t *__restrict__ vox) {
   const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (e >= nnz) return;
@@ -379,8 +380,8 @@ __global__ void k_vf_fill(const uint64_t *__restrict__ key, const int32_t *__res
 #pragma unroll
   for (int c = 0; c < 9; c++) mom[(size_t)c * nnz + e] = a[c];
   cnt[e] = N;
-  frame[e] = (int32_t)(key[b] & 0xffffffffu);
-  vox[e] = (int32_t)(key[b] >> 32);
+  frame[e] = (int32_t)(key[b] & ((1ull << fb) - 1ull));
+  vox[e] = (int32_t)(key[b] >> fb);
 }
 // off[v] = first voxel-frame of voxel v (vox[] ascending), off[V] = nnz ; win[v], wv_off
 __global__ void k_vox_off(const int32_t *__restrict__ vox, int64_t nnz, int64_t V, int32_t *__restrict__ off) {
@@ -644,10 +645,11 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
     lp.incl[l] = l <= L ? in[l]->as<int32_t>() : nullptr;
     lp.flags[l] = l <= L ? nflag[l]->as<int32_t>() : nullptr;
   }
-  VX_KERNEL(ctx, "k_seg_voxel", k_seg_voxel<<<blocks_for(nseg, 256), 256, 0, st>>>(seg_start.as<int32_t>(), segF.as<int32_t>(), nseg, lp, L, vid.as<int32_t>(),
+  const int fb = bits_for(F);
+  VX_KERNEL(ctx, "k_seg_voxel", k_seg_voxel<<<blocks_for(nseg, 256), 256, 0, st>>>(seg_start.as<int32_t>(), segF.as<int32_t>(), nseg, lp, L, vid.as<int32_t>(), V, fb,
                                                                                 sk.as<uint64_t>(), sv.as<int32_t>()));
-  VX_TRY(sort_pairs<uint64_t>(ctx, sk.as<uint64_t>(), sk2.as<uint64_t>(), sv.as<int32_t>(), sv2.as<int32_t>(), nseg, 0, 64));
-  VX_KERNEL(ctx, "k_vf_heads", k_vf_heads<<<blocks_for(nseg, 256), 256, 0, st>>>(sk2.as<uint64_t>(), nseg, vfh.as<int32_t>()));
+  VX_TRY(sort_pairs<uint64_t>(ctx, sk.as<uint64_t>(), sk2.as<uint64_t>(), sv.as<int32_t>(), sv2.as<int32_t>(), nseg, 0, fb + bits_for((int64_t)V + 1)));
+  VX_KERNEL(ctx, "k_vf_heads", k_vf_heads<<<blocks_for(nseg, 256), 256, 0, st>>>(sk2.as<uint64_t>(), nseg, V, fb, vfh.as<int32_t>()));
   VX_TRY(incl_scan(ctx, vfh.as<int32_t>(), vfi.as<int32_t>(), nseg));
   int32_t nnz = 0;
   VX_TRY(read_last(ctx, vfi.as<int32_t>(), nseg, &nnz));
@@ -664,7 +666,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
       int64_t mid = (lo + hi) >> 1; uint64_t kv = 0;
       VX_CUDA(cudaMemcpyAsync(&kv, sk2.as<uint64_t>() + mid, 8, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaStreamSynchronize(st));
-      if (kv != ~0ull) lo = mid + 1; else hi = mid;
+      if ((int64_t)(kv >> fb) != (int64_t)V) lo = mid + 1; else hi = mid;
     }
     nvalid = lo;
   }
@@ -673,7 +675,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
   // ---- 7. the device LidarFactor
   VX_TRY(factor_alloc(f, V, nnz));
   VX_KERNEL(ctx, "k_vf_fill", k_vf_fill<<<blocks_for(nnz, 128), 128, 0, st>>>(sk2.as<uint64_t>(), sv2.as<int32_t>(), vfs.as<int32_t>(), nnz, nvalid, segm.as<double>(),
-                                                                             segN.as<int32_t>(), nseg, f->mom.as<double>(), f->cnt.as<int32_t>(), f->frame.as<int32_t>(),
+                                                                             segN.as<int32_t>(), nseg, fb, f->mom.as<double>(), f->cnt.as<int32_t>(), f->frame.as<int32_t>(),
                                                                              f->vox.as<int32_t>()));
   for (int l = 0; l <= L; l++)
     VX_KERNEL(ctx, "k_emit_voxels", k_emit_voxels<<<blocks_for(nn[l], 256), 256, 0, st>>>(nstart[l]->as<int32_t>(), nflag[l]->as<int32_t>(), nn[l], vid.as<int32_t>(),
