@@ -244,9 +244,10 @@ def kernel_models(st, rb, rt, inst_bottom, top_points, top_builds):
     vpv = (rb or rt or {"v_per_vf": 0.25})["v_per_vf"]
     m["k_residual"] = (76 * (Rb + Rt) + 304 * vpv * (Rb + Rt), 0, "B2 evaluate_only_residual, both levels: 76 B/voxel-frame + 104 B read + 200 B written per voxel")
     inst = inst_bottom + top_points * top_builds
-    m["k_seg_moments"] = (16 * inst, 0, "A8 per-(leaf, frame) PointCluster accumulation: 12 B xyz + 4 B index per point instance read (the 152 B per segment written are not counted)")
+    m["k_leaf_stats"] = (16 * inst, 0, "A8 / A10 finest-layer PointCluster accumulation straight from the sorted points: 12 B xyz + 4 B point index per point instance read")
+    m["k_vf_fill"] = (16 * inst, 0, "A10 scan-local cluster of every (voxel, frame): 12 B xyz + 4 B point index per point instance of an accepted plane (upper bound: all instances)")
     m["k_gba_key64"] = (12 * inst + 12 * inst, 0, "A1 / A8 keys: 12 B/point instance read, 8 B key + 4 B index written")
-    m["k_gba_cell_range"] = (12 * inst, 0, "A1 cell range of the scene: 12 B/point instance read")
+    m["k_hb_emit"] = (1 * inst, 0, "A8 fused head-counter scan: 1 B of head bits per point instance read (compact index arrays written at the heads)")
     return m
 
 
@@ -527,7 +528,7 @@ def run_b200(args, rank, world, local_rank):
     sizes = np.diff(d["off"])
     inst_bottom = int(sum(sizes[wst[w]:wst[w] + wsz[w]].sum() for w in range(lo_w, hi_w)))
     n_groups = len(set(int(x) for x in wsz[lo_w:hi_w]))
-    top_builds = max(prof.get("k_seg_moments", (0.0, n_groups))[1] - n_groups, 0)
+    top_builds = max(prof.get("k_leaf_stats", (0.0, n_groups))[1] - n_groups, 0)
     models = kernel_models(stp, rb, rt, inst_bottom, stp["top_points"], top_builds)
     kern = {k: {"ms_per_step": v[0], "launches_per_step": v[1]} for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
     kernel_ms_total = sum(v[0] for v in prof.values())

@@ -349,6 +349,106 @@ k_residual(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, c
   prep[6 * V + v] = invN;
 }
 
+// B2, staged form (opt-in, see launch_residual for the measurement).  The thread-per-voxel loop above walks each voxel's records with a stride of one voxel's record count between
+// neighbouring lanes and one record in flight per lane: latency-bound (long scoreboard 55 %, r01n capture).  Here a CTA owns RES_THREADS
+// consecutive voxels = ONE contiguous record range; its threads stream that range lane-per-record (every plane load a full coalesced
+// line, RS_PER records in flight per thread), transform each record by its pose and park the 10 transformed moments in shared memory;
+// then thread v adds the parked records of voxel v in record order (the order of the loop above; the compiler contracts the two
+// forms differently, so the caches agree to rounding, not bit for bit) and does the eigen-solve and the cache write-back.
+constexpr int RS_PER = 2;                          // records per thread per chunk
+constexpr int RS_CHUNK = RES_THREADS * RS_PER;     // records parked at a time: 10 x 256 doubles = 20 KB
+template <int MINB>
+__global__ void __launch_bounds__(RES_THREADS, MINB)
+k_residual_staged(const int32_t *__restrict__ off, const int32_t *__restrict__ frame, const double *__restrict__ mom,
+                  const int32_t *__restrict__ cnt, int64_t nnz, const double *__restrict__ fix, const double *__restrict__ coe,
+                  const double *__restrict__ poses, double *__restrict__ lam, double *__restrict__ U, double *__restrict__ mrg,
+                  double *__restrict__ res_v, double *__restrict__ prep, int64_t V, int64_t head, int64_t end) {
+  __shared__ double park[10][RS_CHUNK];
+  const int64_t v0 = blockIdx.x * (int64_t)RES_THREADS;
+  const int64_t vlo = max(v0, max(head, (int64_t)0)), vhi = min(v0 + RES_THREADS, min(end, V));
+  if (vlo >= vhi) return;                                         // uniform per CTA
+  const int64_t v = v0 + threadIdx.x;
+  const bool mine = v >= vlo && v < vhi;
+  const int32_t xb = off[vlo], xe = off[vhi];
+  const int32_t b = mine ? off[v] : 0, e = mine ? off[v + 1] : 0;
+  s33 P; d3 sv; double N = 0.0;
+  P.xx = P.xy = P.xz = P.yy = P.yz = P.zz = 0.0; sv = mk3(0.0, 0.0, 0.0);
+  if (mine) {
+    P.xx = fix[0 * V + v]; P.xy = fix[1 * V + v]; P.xz = fix[2 * V + v];
+    P.yy = fix[3 * V + v]; P.yz = fix[4 * V + v]; P.zz = fix[5 * V + v];
+    sv = mk3(fix[6 * V + v], fix[7 * V + v], fix[8 * V + v]);
+    N = fix[9 * V + v];
+  }
+  for (int32_t c0 = xb; c0 < xe; c0 += RS_CHUNK) {
+    // ---- stream: every load of the chunk is issued before the first transform
+    double m[RS_PER][9]; int32_t fr[RS_PER], cn[RS_PER];
+#pragma unroll
+    for (int q = 0; q < RS_PER; q++) {
+      const int32_t x = c0 + q * RES_THREADS + threadIdx.x;
+      const bool in = x < xe;
+      fr[q] = in ? frame[x] : 0; cn[q] = in ? cnt[x] : 0;
+#pragma unroll
+      for (int k = 0; k < 9; k++) m[q][k] = in ? mom[(int64_t)k * nnz + x] : 0.0;
+    }
+#pragma unroll
+    for (int q = 0; q < RS_PER; q++) {
+      const int slot = q * RES_THREADS + threadIdx.x;
+      const double *ps = poses + 12 * (int64_t)fr[q];
+      const rot R = load_rot(ps);
+      const d3 p = mk3(ps[9], ps[10], ps[11]);
+      s33 Pi;
+      Pi.xx = m[q][0]; Pi.xy = m[q][1]; Pi.xz = m[q][2]; Pi.yy = m[q][3]; Pi.yz = m[q][4]; Pi.zz = m[q][5];
+      const d3 vi = mk3(m[q][6], m[q][7], m[q][8]);
+      const double n = (double)cn[q];
+      const d3 Rv = rmul(R, vi);
+      const s33 RPR = rprt(R, Pi);
+      // the record's whole contribution, summed exactly as the loop of k_residual sums it into P (left to right)
+      park[0][slot] = RPR.xx + 2.0 * Rv.x * p.x + n * p.x * p.x;
+      park[1][slot] = RPR.xy + Rv.x * p.y + p.x * Rv.y + n * p.x * p.y;
+      park[2][slot] = RPR.xz + Rv.x * p.z + p.x * Rv.z + n * p.x * p.z;
+      park[3][slot] = RPR.yy + 2.0 * Rv.y * p.y + n * p.y * p.y;
+      park[4][slot] = RPR.yz + Rv.y * p.z + p.y * Rv.z + n * p.y * p.z;
+      park[5][slot] = RPR.zz + 2.0 * Rv.z * p.z + n * p.z * p.z;
+      park[6][slot] = Rv.x; park[7][slot] = Rv.y; park[8][slot] = Rv.z;
+      park[9][slot] = n;
+    }
+    __syncthreads();
+    // ---- gather: voxel v takes its records of this chunk in record order
+    const int32_t lo = max(b, c0), hi = min(e, c0 + RS_CHUNK);
+    for (int32_t x = lo; x < hi; x++) {
+      const int s = x - c0;
+      const double n = park[9][s];
+      const d3 p = mk3(poses[12 * (int64_t)frame[x] + 9], poses[12 * (int64_t)frame[x] + 10], poses[12 * (int64_t)frame[x] + 11]);
+      P.xx += park[0][s]; P.xy += park[1][s]; P.xz += park[2][s]; P.yy += park[3][s]; P.yz += park[4][s]; P.zz += park[5][s];
+      sv = sv + mk3(park[6][s], park[7][s], park[8][s]) + n * p;
+      N += n;
+    }
+    __syncthreads();
+  }
+  if (!mine) return;
+  double invN = 1.0 / N;
+  d3 vb = mk3(sv.x / N, sv.y / N, sv.z / N);
+  s33 C;
+  C.xx = P.xx / N - vb.x * vb.x; C.xy = P.xy / N - vb.x * vb.y; C.xz = P.xz / N - vb.x * vb.z;
+  C.yy = P.yy / N - vb.y * vb.y; C.yz = P.yz / N - vb.y * vb.z; C.zz = P.zz / N - vb.z * vb.z;
+  double l[3], u[9];
+  eig3_jacobi(C, l, u);
+  lam[0 * V + v] = l[0]; lam[1 * V + v] = l[1]; lam[2 * V + v] = l[2];
+#pragma unroll
+  for (int k = 0; k < 9; k++) U[k * V + v] = u[k];
+  mrg[0 * V + v] = P.xx; mrg[1 * V + v] = P.xy; mrg[2 * V + v] = P.xz;
+  mrg[3 * V + v] = P.yy; mrg[4 * V + v] = P.yz; mrg[5 * V + v] = P.zz;
+  mrg[6 * V + v] = sv.x; mrg[7 * V + v] = sv.y; mrg[8 * V + v] = sv.z;
+  mrg[9 * V + v] = N;
+  const double cf = coe[v];
+  res_v[v] = cf * l[0];
+  prep[v] = cf * (2.0 / (l[0] - l[1]));
+  prep[V + v] = cf * (2.0 / (l[0] - l[2]));
+  prep[2 * V + v] = cf * (-2.0 / N / N);
+  prep[3 * V + v] = vb.x; prep[4 * V + v] = vb.y; prep[5 * V + v] = vb.z;
+  prep[6 * V + v] = invN;
+}
+
 // cost[w] = sum over voxels of window w (restricted to [head,end)) of coe*lambda_0, fixed-shape tree.
 template <bool FROM_LAM>
 __global__ void __launch_bounds__(256)
@@ -623,11 +723,28 @@ static int launch_residual(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end)
         f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(), \
         f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), \
         f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end))
-    if (res_minb >= 8) VX_RES_LAUNCH(8);
+    // Measured on B200, round-1 workload (399,000 voxels, 2.39 M records; scripts/b12_prof.py): thread-per-voxel loop 0.103 ms per
+    // launch, staged form 0.112 (6 CTAs/SM) ... 0.131 (3 CTAs/SM).  The pass issues ~2,800 instructions per voxel, two thirds of
+    // them the FP64 eigen-solve: the two barriers per chunk cost more than the coalescing returns.  VX_RES_STAGED=1 selects it.
+    static const bool staged = std::getenv("VX_RES_STAGED") != nullptr;
+    static const int stg_minb = [] { const char *e = std::getenv("VX_RES_STAGED_MINB"); return e ? std::atoi(e) : 6; }();
+#define VX_RES_LAUNCH_STAGED(MB) VX_KERNEL(ctx, "k_residual", k_residual_staged<MB><<<blocks_for(f->V, RES_THREADS), RES_THREADS, 0, st>>>( \
+        f->off.as<int32_t>(), f->frame.as<int32_t>(), f->mom.as<double>(), f->cnt.as<int32_t>(), f->nnz, f->fix.as<double>(), \
+        f->coe.as<double>(), f->poses.as<double>(), f->lam.as<double>(), f->U.as<double>(), f->mrg.as<double>(), \
+        f->res_v.as<double>(), f->cS.as<double>(), f->V, head, end))
+    if (staged) {
+      if (stg_minb >= 6) VX_RES_LAUNCH_STAGED(6);
+      else if (stg_minb >= 5) VX_RES_LAUNCH_STAGED(5);
+      else if (stg_minb >= 4) VX_RES_LAUNCH_STAGED(4);
+      else if (stg_minb >= 3) VX_RES_LAUNCH_STAGED(3);
+      else VX_RES_LAUNCH_STAGED(0);
+    }
+    else if (res_minb >= 8) VX_RES_LAUNCH(8);
     else if (res_minb >= 7) VX_RES_LAUNCH(7);
     else if (res_minb >= 6) VX_RES_LAUNCH(6);
     else VX_RES_LAUNCH(0);
 #undef VX_RES_LAUNCH
+#undef VX_RES_LAUNCH_STAGED
     f->prep_lo = std::max<int64_t>(head, 0); f->prep_hi = std::min<int64_t>(end, f->V);
   }
   VX_KERNEL(ctx, "k_cost", k_cost<false><<<f->n_win, 256, 0, st>>>(f->res_v.as<double>(), nullptr, f->wv_off.as<int32_t>(), f->cost_r.as<double>(), head, end));
