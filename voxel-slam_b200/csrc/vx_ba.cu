@@ -498,7 +498,7 @@ int ba_lidar_impl(vx_ctx *ctx, vx_factor *f, vx_pose *poses, double *hess_out, d
   }
   if (edge_diag) {
     const int64_t npair = (int64_t)W * (W - 1) / 2;
-    std::fill(edge_diag, edge_diag + (size_t)NW * npair * 6, 0.0);
+    if (!(dev && evaluated)) std::fill(edge_diag, edge_diag + (size_t)NW * npair * 6, 0.0);      // the device path overwrites every slot
     if (dev && evaluated) {
       VX_TRY(ctx->scratch2.reserve(sizeof(double) * (size_t)NW * npair * 6));
       VX_KERNEL(ctx, "k_edge_diag", k_edge_diag<<<dim3((unsigned)blocks_for(npair * 6, 256), NW), 256, 0, st>>>(f->lm_H.as<double>(), W, ctx->scratch2.as<double>()));

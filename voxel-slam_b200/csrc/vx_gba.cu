@@ -702,6 +702,11 @@ namespace {
 struct View { const void *p; template <class X> const X *as() const { return (const X *)p; } };
 }
 namespace vx {
+// bbox[c] = {min x, min y, min z, max x, max y, max z} of cloud c (scan-local floats); an empty cloud gets min > max
+int cloud_bboxes(vx_ctx *ctx, const float *d_xyz, const int64_t *d_coff, int n_clouds, float *d_bbox) {
+  VX_KERNEL(ctx, "k_cloud_bbox", k_cloud_bbox<<<n_clouds, 256, 0, ctx->stream>>>(d_xyz, d_coff, d_bbox));
+  return VX_OK;
+}
 // d_xyz / d_coff: the clouds already on the device (uploaded once per HBA_add_edge call); cloud_off: host copy.
 // explicit mode (d_pt_frame != nullptr): d_xyz_in holds n_pts routed points, point j belongs to frame d_pt_frame[j]; points of
 // one frame must appear in their original cloud order (cloud_off / frame_cloud are then unused).
@@ -767,7 +772,7 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
     } else {
       DevBuf &d_bbox = T.make();
       VX_TRY(d_bbox.reserve(sizeof(float) * 6 * (size_t)n_clouds));
-      VX_KERNEL(ctx, "k_cloud_bbox", k_cloud_bbox<<<n_clouds, 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_bbox.as<float>()));
+      VX_TRY(cloud_bboxes(ctx, d_xyz.as<float>(), d_coff.as<int64_t>(), n_clouds, d_bbox.as<float>()));
       VX_KERNEL(ctx, "k_frame_cells", k_frame_cells<<<blocks_for(F, 128), 128, 0, st>>>(d_bbox.as<float>(), d_fc.as<int32_t>(), F, d_poses.as<double>(), prm.vs,
                                                                                    d_rng.as<CellRange>()));
     }

@@ -10,6 +10,7 @@
 #include "vx_hba.cuh"
 #include <cmath>
 #include <algorithm>
+#include <memory>
 
 using namespace vx;
 
@@ -24,10 +25,14 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
   const size_t hsz = (size_t)jl * jl;
   const int64_t cap = (int64_t)W * (W - 1) / 2;   // edge slots per window
   // the full snapshot only when the caller wants it; the edges need 6 numbers per frame pair (k_edge_diag)
-  std::vector<double> hess(hess_out ? hsz * NW : 0, 0.0), ediag((size_t)NW * cap * 6, 0.0);
+  // ediag / ed are written in full before they are read (k_edge_diag fills every slot of every window that reports VX_OK): no zero
+  // fill — at the top level (W = 400) each is 3.8 MB of fresh pages, and the fill showed as 0.6-1.3 ms per outer iteration
+  std::vector<double> hess(hess_out ? hsz * NW : 0, 0.0);
+  std::unique_ptr<double[]> ediag(new double[(size_t)NW * cap * 6]);
   std::vector<int> cflag(NW, 0), done(NW, 0), status(NW, VX_OK), nvox(NW, 0);
   std::vector<double> cthre(NW, 0.05);
   const int up = 4;   // voxelslam.cpp:2867
+  PhaseTimer pt("hba_core", ctx->stream);
   for (int iterCnt = 0; iterCnt < max_iter; iterCnt++) {
     // which thresholds does each live window use in this outer iteration?
     std::vector<int> group[2];
@@ -51,12 +56,13 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         for (int i = 0; i < W; i++) ps[(size_t)a * W + i] = poses[ws[a] * W + i];
       vx_factor *fac = nullptr;
       VX_TRY(vx_factor_create(ctx, W, ns, &fac));
-      std::vector<double> hs(hess_out ? hsz * ns : 0), rs(2 * (size_t)ns), ed((size_t)ns * cap * 6);
+      std::vector<double> hs(hess_out ? hsz * ns : 0), rs(2 * (size_t)ns);
+      std::unique_ptr<double[]> ed(new double[(size_t)ns * cap * 6]);
       std::vector<int> conv(ns), wst(ns), nit(ns, 0);
-      PhaseTimer pt("hba_core", ctx->stream);
+      pt.lap("iteration setup");
       int s = build(ws, ps.data(), gp, fac);
       pt.lap("build");
-      if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hess_out ? hs.data() : nullptr, rs.data(), up, thread_num, conv.data(), nullptr, nit.data(), wst.data(), comm, ed.data());
+      if (s == VX_OK) s = ba_lidar_impl(ctx, fac, ps.data(), hess_out ? hs.data() : nullptr, rs.data(), up, thread_num, conv.data(), nullptr, nit.data(), wst.data(), comm, ed.get());
       std::vector<int32_t> wv(ns + 1, 0);
       if (s == VX_OK && fac->V > 0) {
         cudaMemcpyAsync(wv.data(), fac->wv_off.p, sizeof(int32_t) * (ns + 1), cudaMemcpyDeviceToHost, ctx->stream);
@@ -69,6 +75,7 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
       }
       if (keep && s == VX_OK) { if (*keep) vx_factor_free(*keep); *keep = fac; }   // the latest factor stays with the caller
       else vx_factor_free(fac);
+      pt.lap("factor_free");
       VX_TRY(s);
       for (int a = 0; a < ns; a++) {
         const int w = ws[a];
@@ -76,7 +83,7 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
         for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
         if (hess_out) std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
-        std::copy(ed.begin() + (size_t)a * cap * 6, ed.begin() + (size_t)(a + 1) * cap * 6, ediag.begin() + (size_t)w * cap * 6);
+        std::copy(ed.get() + (size_t)a * cap * 6, ed.get() + (size_t)(a + 1) * cap * 6, ediag.get() + (size_t)w * cap * 6);
         const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
         if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
         // voxelslam.cpp:2906-2917
@@ -88,11 +95,12 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
       }
     }
   }
+  pt.lap("iteration close");
   // pose-graph edges (voxelslam.cpp:2926-2951): cov_k = 1/|hess(6i+k, 6j+k)| of the pre-gauge snapshot
   for (int w = 0; w < NW; w++) {
     int64_t ne = 0;
     if (status[w] == VX_OK && edges) {
-      const double *D = ediag.data() + (size_t)w * cap * 6;
+      const double *D = ediag.get() + (size_t)w * cap * 6;
       int64_t pr = 0;
       for (int i = 0; i < W - 1; i++)
         for (int j = i + 1; j < W; j++, pr++) {
@@ -126,6 +134,7 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
     if (n_voxels_out) n_voxels_out[w] = nvox[w];
   }
   if (hess_out) std::copy(hess.begin(), hess.end(), hess_out);
+  pt.lap("edges");
   return VX_OK;
 }
 }  // namespace vx
@@ -217,21 +226,54 @@ static int assemble_window(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud
 #include <cub/cub.cuh>
 namespace {
 struct RelPoseD { double dR[9]; double dp[3]; };   // dR row-major, per frame
-constexpr int MK_BITS = 18;                        // bits per axis of the batched cell key (+-131072 cells), window id above them
-constexpr int64_t MK_BIAS = (int64_t)1 << (MK_BITS - 1);
 
 __device__ __forceinline__ int frame_of_inst(const int64_t *__restrict__ inst_off, int F, int64_t j) {
   int lo = 0, hi = F;
   while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (inst_off[mid] <= j) lo = mid; else hi = mid; }
   return lo;
 }
+// Key layout of the batched merge: window | x | y | z, each axis re-biased by the smallest cell any window holds and given
+// exactly the bits its range needs (42 bits = 6 radix passes on the 2,000-keyframe job; the fixed 3 x 18 + 9 = 63-bit layout ran 8).
+// The range comes from the clouds' bounding boxes (vx::cloud_bboxes): per frame the cells of the 8 transformed corners, one cell of margin.
+struct MergeLayout { int lo[3]; int bx, by, bz; };
+struct MergeRange { int lo[3], hi[3]; };
+__global__ void k_merge_cells(const float *__restrict__ bbox, const int32_t *__restrict__ frame_cloud, int F, const RelPoseD *__restrict__ rel, double leaf,
+                              MergeRange *__restrict__ range) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= F) return;
+  const float *bb = bbox + 6 * (size_t)frame_cloud[g];
+  if (!(bb[0] <= bb[3])) return;                       // empty cloud
+  const RelPoseD &rp = rel[g];
+  int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, hi[3] = {-0x7fffffff, -0x7fffffff, -0x7fffffff};
+  for (int c = 0; c < 8; c++) {
+    const double x = (double)bb[(c & 1) ? 3 : 0], y = (double)bb[(c & 2) ? 4 : 1], z = (double)bb[(c & 4) ? 5 : 2];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      const float v = (float)__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(rp.dR[r * 3], x), __dmul_rn(rp.dR[r * 3 + 1], y)), __dmul_rn(rp.dR[r * 3 + 2], z)), rp.dp[r]);
+      const int64_t k = key_axis_f(v, leaf);
+      const int q = (int)max((int64_t)-0x7ffffff0, min((int64_t)0x7ffffff0, k));
+      lo[r] = min(lo[r], q - 1); hi[r] = max(hi[r], q + 1);
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) { atomicMin(&range->lo[a], lo[a]); atomicMax(&range->hi[a], hi[a]); }
+}
+// frame of instance j given g0 <= frame(j): a walk of 0 or 1 steps for real clouds
+__device__ __forceinline__ int frame_walk_inst(const int64_t *__restrict__ inst_off, int F, int g0, int64_t j) {
+  int g = g0;
+  while (g + 1 < F && inst_off[g + 1] <= j) g++;
+  return g;
+}
 // every point instance of every window into its window's frame (:2958-2969, the arithmetic of k_merge_transform) + its batched key
 __global__ void k_merge_all(const float *__restrict__ xyz, const int64_t *__restrict__ coff, const int32_t *__restrict__ frame_cloud,
                             const int64_t *__restrict__ inst_off, int F, const RelPoseD *__restrict__ rel, const int32_t *__restrict__ frame_win, double leaf,
-                            int64_t NI, float *__restrict__ out, uint64_t *__restrict__ keys, int32_t *__restrict__ idx, int *__restrict__ bad) {
+                            MergeLayout ml, int64_t NI, float *__restrict__ out, uint64_t *__restrict__ keys, int32_t *__restrict__ idx, int *__restrict__ bad) {
+  __shared__ int g0s;
+  if (threadIdx.x == 0) g0s = frame_of_inst(inst_off, F, blockIdx.x * (int64_t)blockDim.x);
+  __syncthreads();
   const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (j >= NI) return;
-  const int g = frame_of_inst(inst_off, F, j);
+  const int g = frame_walk_inst(inst_off, F, g0s, j);
   const float *s = xyz + 3 * (coff[frame_cloud[g]] + (j - inst_off[g]));
   const double x = (double)s[0], y = (double)s[1], z = (double)s[2];
   const RelPoseD &rp = rel[g];
@@ -240,10 +282,9 @@ __global__ void k_merge_all(const float *__restrict__ xyz, const int64_t *__rest
   for (int r = 0; r < 3; r++)
     v[r] = (float)__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(rp.dR[r * 3], x), __dmul_rn(rp.dR[r * 3 + 1], y)), __dmul_rn(rp.dR[r * 3 + 2], z)), rp.dp[r]);
   out[3 * j] = v[0]; out[3 * j + 1] = v[1]; out[3 * j + 2] = v[2];
-  const int64_t kx = key_axis_f(v[0], leaf) + MK_BIAS, ky = key_axis_f(v[1], leaf) + MK_BIAS, kz = key_axis_f(v[2], leaf) + MK_BIAS;
-  const int64_t lim = (int64_t)1 << MK_BITS;
-  if (kx < 0 || ky < 0 || kz < 0 || kx >= lim || ky >= lim || kz >= lim) *bad = 1;
-  keys[j] = ((uint64_t)frame_win[g] << (3 * MK_BITS)) | ((uint64_t)(kx & (lim - 1)) << (2 * MK_BITS)) | ((uint64_t)(ky & (lim - 1)) << MK_BITS) | (uint64_t)(kz & (lim - 1));
+  const int64_t kx = key_axis_f(v[0], leaf) - ml.lo[0], ky = key_axis_f(v[1], leaf) - ml.lo[1], kz = key_axis_f(v[2], leaf) - ml.lo[2];
+  if (kx < 0 || ky < 0 || kz < 0 || kx >= ((int64_t)1 << ml.bx) || ky >= ((int64_t)1 << ml.by) || kz >= ((int64_t)1 << ml.bz)) *bad = 1;   // never, by construction
+  keys[j] = ((uint64_t)frame_win[g] << (ml.bx + ml.by + ml.bz)) | ((uint64_t)kx << (ml.by + ml.bz)) | ((uint64_t)ky << ml.bz) | (uint64_t)kz;
   idx[j] = (int32_t)j;
 }
 __global__ void k_mheads(const uint64_t *__restrict__ keys, int64_t n, int32_t *__restrict__ flag) {
@@ -282,11 +323,11 @@ __global__ void k_mmean(const float *__restrict__ pts, const int32_t *__restrict
   }
 }
 // win_off[w] = first cell whose window id >= w
-__global__ void k_mwin_off(const uint64_t *__restrict__ keys, const int32_t *__restrict__ start, int64_t ncell, int NW, int64_t *__restrict__ win_off) {
+__global__ void k_mwin_off(const uint64_t *__restrict__ keys, const int32_t *__restrict__ start, int64_t ncell, int NW, int wshift, int64_t *__restrict__ win_off) {
   const int w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w > NW) return;
   int64_t lo = 0, hi = ncell;
-  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if ((int)(keys[start[mid]] >> (3 * MK_BITS)) < w) lo = mid + 1; else hi = mid; }
+  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if ((int)(keys[start[mid]] >> wshift) < w) lo = mid + 1; else hi = mid; }
   win_off[w] = lo;
 }
 }  // namespace
@@ -298,7 +339,7 @@ int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_o
   cudaStream_t st = ctx->stream;
   const int NW = n_windows, F = wf_off[NW];
   if (overflow) *overflow = 0;
-  VX_ARG(NW >= 1 && NW < (1 << (64 - 3 * MK_BITS)) && F >= NW);
+  VX_ARG(NW >= 1 && F >= NW);
   std::vector<int64_t> inst_off(F + 1, 0);
   std::vector<int32_t> fc(F), fwin(F);
   std::vector<RelPoseD> rel(F);
@@ -323,8 +364,8 @@ int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_o
   VX_ARG(NI < ((int64_t)1 << 31));
   for (int w = 0; w <= NW; w++) win_off[w] = 0;
   if (NI == 0) return VX_OK;
-  DevBuf d_coff, d_fc, d_io, d_rel, d_fw, d_mp, d_pts, d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad, d_woff;
-  std::vector<DevBuf *> all = {&d_coff, &d_fc, &d_io, &d_rel, &d_fw, &d_mp, &d_pts, &d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad, &d_woff};
+  DevBuf d_coff, d_fc, d_io, d_rel, d_fw, d_mp, d_pts, d_k0, d_k1, d_i0, d_i1, d_flag, d_incl, d_start, d_bad, d_woff, d_bbox, d_rng;
+  std::vector<DevBuf *> all = {&d_coff, &d_fc, &d_io, &d_rel, &d_fw, &d_mp, &d_pts, &d_k0, &d_k1, &d_i0, &d_i1, &d_flag, &d_incl, &d_start, &d_bad, &d_woff, &d_bbox, &d_rng};
   auto body = [&]() -> int {
     VX_TRY(d_coff.reserve(8 * (size_t)(n_clouds + 1))); VX_TRY(d_fc.reserve(4 * (size_t)F)); VX_TRY(d_io.reserve(8 * (size_t)(F + 1)));
     VX_TRY(d_rel.reserve(sizeof(RelPoseD) * (size_t)F)); VX_TRY(d_fw.reserve(4 * (size_t)F)); VX_TRY(d_mp.reserve(4 * (size_t)F));
@@ -338,13 +379,29 @@ int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_o
     VX_CUDA(cudaMemcpyAsync(d_fw.p, fwin.data(), 4 * (size_t)F, cudaMemcpyHostToDevice, st));
     if (frame_mp) VX_CUDA(cudaMemcpyAsync(d_mp.p, frame_mp, 4 * (size_t)F, cudaMemcpyHostToDevice, st));
     VX_CUDA(cudaMemsetAsync(d_bad.p, 0, 4, st));
-    VX_KERNEL(ctx, "k_merge_all", k_merge_all<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz, d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_io.as<int64_t>(), F, d_rel.as<RelPoseD>(),
-                                                                                d_fw.as<int32_t>(), leaf, NI, d_pts.as<float>(), d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
+    // cell range of all windows -> key layout
+    MergeRange r0;
+    for (int a = 0; a < 3; a++) { r0.lo[a] = 0x7fffffff; r0.hi[a] = -0x7fffffff; }
+    VX_TRY(d_bbox.reserve(sizeof(float) * 6 * (size_t)n_clouds)); VX_TRY(d_rng.reserve(sizeof(MergeRange)));
+    VX_CUDA(cudaMemcpyAsync(d_rng.p, &r0, sizeof(r0), cudaMemcpyHostToDevice, st));
+    VX_TRY(cloud_bboxes(ctx, d_xyz, d_coff.as<int64_t>(), n_clouds, d_bbox.as<float>()));
+    VX_KERNEL(ctx, "k_merge_cells", k_merge_cells<<<blocks_for(F, 128), 128, 0, st>>>(d_bbox.as<float>(), d_fc.as<int32_t>(), F, d_rel.as<RelPoseD>(), leaf, d_rng.as<MergeRange>()));
+    VX_CUDA(cudaMemcpyAsync(&r0, d_rng.p, sizeof(r0), cudaMemcpyDeviceToHost, st));
+    VX_CUDA(cudaStreamSynchronize(st));
+    if (r0.lo[0] > r0.hi[0]) { for (int a = 0; a < 3; a++) { r0.lo[a] = 0; r0.hi[a] = 0; } }
+    auto bits_of = [](int64_t n) { int b = 1; while (((int64_t)1 << b) < n) b++; return b; };
+    MergeLayout ml;
+    for (int a = 0; a < 3; a++) ml.lo[a] = r0.lo[a];
+    ml.bx = bits_of((int64_t)r0.hi[0] - r0.lo[0] + 1); ml.by = bits_of((int64_t)r0.hi[1] - r0.lo[1] + 1); ml.bz = bits_of((int64_t)r0.hi[2] - r0.lo[2] + 1);
     int wbits = 1; while ((1 << wbits) < NW) wbits++;
+    const int cbits = ml.bx + ml.by + ml.bz;
+    if (cbits + wbits > 64) { if (overflow) *overflow = 1; set_error("merged submap clouds: the cell range needs %d + %d key bits", cbits, wbits); return VX_ERR_ARG; }
+    VX_KERNEL(ctx, "k_merge_all", k_merge_all<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz, d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_io.as<int64_t>(), F, d_rel.as<RelPoseD>(),
+                                                                                d_fw.as<int32_t>(), leaf, ml, NI, d_pts.as<float>(), d_k0.as<uint64_t>(), d_i0.as<int32_t>(), d_bad.as<int>()));
     size_t tb = 0;
-    VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, 3 * MK_BITS + wbits, st));
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, cbits + wbits, st));
     VX_TRY(ctx->scratch.reserve(tb));
-    VX_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, 3 * MK_BITS + wbits, st));
+    VX_CUDA(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, tb, d_k0.as<uint64_t>(), d_k1.as<uint64_t>(), d_i0.as<int32_t>(), d_i1.as<int32_t>(), (int)NI, 0, cbits + wbits, st));
     ctx->launches += 4;
     VX_KERNEL(ctx, "k_mheads", k_mheads<<<blocks_for(NI, 256), 256, 0, st>>>(d_k1.as<uint64_t>(), NI, d_flag.as<int32_t>()));
     VX_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tb, d_flag.as<int32_t>(), d_incl.as<int32_t>(), (int)NI, st));
@@ -356,13 +413,13 @@ int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_o
     VX_CUDA(cudaMemcpyAsync(&ncell, d_incl.as<int32_t>() + (NI - 1), 4, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
-    if (bad) { if (overflow) *overflow = 1; set_error("merged submap clouds: a cell index does not fit the %d-bit batched key", MK_BITS); return VX_ERR_ARG; }
+    if (bad) { if (overflow) *overflow = 1; set_error("merged submap clouds: a cell index left the range its cloud's bounding box gave"); return VX_ERR_ARG; }
     VX_TRY(d_out_xyz.reserve(12 * (size_t)ncell));
     if (d_out48) VX_TRY(d_out48->reserve(sizeof(vx_point48) * (size_t)ncell));
     VX_KERNEL(ctx, "k_mmean", k_mmean<<<blocks_for(ncell, 128), 128, 0, st>>>(d_pts.as<float>(), d_i1.as<int32_t>(), d_start.as<int32_t>(), ncell, d_io.as<int64_t>(), F,
                                                                            frame_mp ? d_mp.as<int32_t>() : nullptr, d_out_xyz.as<float>(),
                                                                            d_out48 ? d_out48->as<vx_point48>() : nullptr));
-    VX_KERNEL(ctx, "k_mwin_off", k_mwin_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(d_k1.as<uint64_t>(), d_start.as<int32_t>(), ncell, NW, d_woff.as<int64_t>()));
+    VX_KERNEL(ctx, "k_mwin_off", k_mwin_off<<<blocks_for(NW + 1, 128), 128, 0, st>>>(d_k1.as<uint64_t>(), d_start.as<int32_t>(), ncell, NW, cbits, d_woff.as<int64_t>()));
     VX_CUDA(cudaMemcpyAsync(win_off, d_woff.p, 8 * (size_t)(NW + 1), cudaMemcpyDeviceToHost, st));
     VX_CUDA(cudaStreamSynchronize(st));
     return VX_OK;

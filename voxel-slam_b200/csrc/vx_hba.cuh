@@ -22,6 +22,7 @@ int allreduce_evaluation(vx_ctx *ctx, vx_comm *comm, vx_factor *f);
 //   win_off     host, n_windows + 1
 //   d_out48     optional vx_point48 records (intensity = frame_mp of the cell's first point, curvature = count)
 // Returns VX_ERR_ARG with *overflow = 1 when a cell index does not fit the 18-bit batched key (caller falls back per window).
+int cloud_bboxes(vx_ctx *ctx, const float *d_xyz, const int64_t *d_coff, int n_clouds, float *d_bbox);   // vx_gba.cu
 int merge_clouds_batched(vx_ctx *ctx, const float *d_xyz, const int64_t *cloud_off, int n_clouds, const int32_t *frame_cloud, const int32_t *frame_mp,
                          const vx_pose *poses, const int32_t *wf_off, int n_windows, double leaf, DevBuf &d_out_xyz, int64_t *win_off, DevBuf *d_out48,
                          int *overflow);

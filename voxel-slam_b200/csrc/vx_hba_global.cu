@@ -6,6 +6,7 @@
 #include "vx_voxelize.cuh"
 #include <chrono>
 #include <algorithm>
+#include <memory>
 #include <map>
 
 using namespace vx;
@@ -268,17 +269,23 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
         };
       }
       const int64_t tcap = (int64_t)ntop * (ntop - 1) / 2;
-      std::vector<vx_pgo_edge> te((size_t)tcap);
+      PhaseTimer ptt("hba_global top", st);
+      // the caller's edges2 takes the records directly when it can hold every pair; else an UNINITIALISED scratch (12.8 MB at 400 submaps:
+      // value-initialising it cost 1-2.7 ms per job)
+      std::unique_ptr<vx_pgo_edge[]> te_own;
+      vx_pgo_edge *te = edges2;
+      if (!edges2 || cap2 < tcap) { te_own.reset(new vx_pgo_edge[(size_t)tcap]); te = te_own.get(); }
       int64_t tn = 0;
       int32_t tst = VX_OK;
-      VX_TRY(hba_core(ctx, comm, build, tid.data(), tmp.data(), tp.data(), ntop, 1, &prm->hba, prm->total_max_iter, prm->top_thread_num, te.data(), &tn, nullptr, nullptr,
+      VX_TRY(hba_core(ctx, comm, build, tid.data(), tmp.data(), tp.data(), ntop, 1, &prm->hba, prm->total_max_iter, prm->top_thread_num, te, &tn, nullptr, nullptr,
                       nullptr, &tst, vf_top, prm->keep_factors ? &ctx->kept[1] : nullptr));
       if (tst != VX_OK) { set_error("Too Less Voxel: top-level map over %d submaps", ntop); return tst; }
       if (edges2) {
         if (tn > cap2) { set_error("vx_hba_global: edges2 capacity %lld too small for %lld", (long long)cap2, (long long)tn); return VX_ERR_ARG; }
-        std::copy(te.begin(), te.begin() + tn, edges2);
+        if (te != edges2) std::copy(te, te + tn, edges2);
       }
       *n2 = tn;
+      ptt.lap("hba_core + copy out");
       for (int g = 0; g < ntop; g++) { if (top_poses) top_poses[g] = tp[g]; if (top_kf) top_kf[g] = wkf[tw[g]]; }
     } else {
       for (int g = 0; g < ntop; g++) { const int kf = wkf[tw[g]]; if (top_poses) top_poses[g] = kf_x ? kf_x[kf] : kf_x0[kf]; if (top_kf) top_kf[g] = kf; }
