@@ -790,7 +790,12 @@ int gba_build_impl(vx_ctx *ctx, const float *d_xyz_in, const int64_t *d_coff_in,
       VX_TRY(ka.reserve(8 * NI)); VX_TRY(kb.reserve(8 * NI));
       VX_KERNEL(ctx, "k_gba_key64", k_gba_key64<<<blocks_for(NI, 256), 256, 0, st>>>(d_xyz.as<float>(), d_coff.as<int64_t>(), d_fc.as<int32_t>(), d_ioff.as<int64_t>(), d_pt_frame, F,
                                                                                   d_poses.as<double>(), prm, kl, NI, ka.as<uint64_t>(), ia.as<int32_t>(), d_bad.as<int>()));
-      VX_TRY(sort_pairs<uint64_t>(ctx, ka.as<uint64_t>(), kb.as<uint64_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, 0, total));
+      // Cloud mode: instances are generated in (window, frame, scan) order, and the radix sort is stable — so among equal
+      // (window, root cell, path) the frames are ALREADY ascending and the frame field (the low fbits) need not be sorted:
+      // 39 bits = 5 passes instead of 43 = 6 at the bottom level, 30 = 4 instead of 39 = 5 at the top level (W = 400: 9 frame bits).
+      // Routed points (explicit mode) promise scan order within a frame only, so they sort every bit.
+      const int begin_bit = explicit_pts ? 0 : kl.fbits;
+      VX_TRY(sort_pairs<uint64_t>(ctx, ka.as<uint64_t>(), kb.as<uint64_t>(), ia.as<int32_t>(), ib.as<int32_t>(), NI, begin_bit, total));
       VX_KERNEL(ctx, "k_gba_unpack64", k_gba_unpack64<<<blocks_for(NI, 256), 256, 0, st>>>(kb.as<uint64_t>(), kl, NI, k1s, k2s));
       sidx = ib.as<int32_t>();
       VX_CUDA(cudaMemcpyAsync(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost, st));

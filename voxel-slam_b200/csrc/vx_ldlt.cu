@@ -33,6 +33,25 @@ namespace {
 constexpr int NB = 32;     // panel width
 constexpr int TR = 64;     // trailing tile
 
+// Programmatic dependent launch (sm_90+), opt-in (VX_LDLT_PDL=1) and a measured dead end: launched with the programmatic-
+// serialisation attribute a kernel's CTAs may be placed before its predecessor has drained and block in pdl_wait() until the
+// predecessor's writes are visible; the edges survive stream capture.  On the 2,394-unknown sweep (scripts/top_wall.py, one LM
+// iteration): 2.27 ms with the edges, 2.28 ms without; with an early griddepcontrol.launch_dependents in every kernel 6.70 ms
+// against 6.34 for three iterations (the waiting CTAs take slots from the predecessor's tail).  Inside a replayed graph the
+// dependent launches are already back to back; what remains between two kernels is the drain of the predecessor, which a
+// dependent that needs ALL of its output cannot skip.  Every kernel of the sweep calls pdl_wait() first, so the edges are safe.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <class... KArgs, class... Args>
+cudaError_t launch_chain(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 __global__ void k_permute_lower(const double *__restrict__ A, int n, const int32_t *__restrict__ pos, double *__restrict__ B) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
   if (i >= n || i < j) return;
@@ -103,6 +122,7 @@ __device__ __forceinline__ void ldlt_diag_block(double (*L11)[NB + 1], int tid) 
 // the first diagonal block; the others are factored by tile (0,0) of the trailing update that completes them
 __global__ void __launch_bounds__(256) k_ldlt_diag0(const double *__restrict__ B, double *__restrict__ F, int n, int nb) {
   __shared__ double L11[NB][NB + 1];
+  pdl_wait();
   for (int e = threadIdx.x; e < NB * NB; e += 256) {
     const int i = e % NB, j = e / NB;
     L11[i][j] = (i < nb && j < nb && i >= j) ? B[(size_t)j * n + i] : 0.0;
@@ -123,6 +143,7 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
   __shared__ double D[NB], Y[NB];
   __shared__ double T[PR][NB + 1];    // [row in tile][column of the panel]
   const int tid = threadIdx.x, tx = tid % 32, ty = tid / 32;
+  pdl_wait();
   for (int e = tid; e < NB * NB; e += PR * 32) L11[e % NB][e / NB] = F[(size_t)(c0 / NB) * NB * NB + e];
   const int r0 = c0 + nb + blockIdx.x * PR;
   for (int e = tid; e < PR * NB; e += PR * 32) {
@@ -179,6 +200,7 @@ __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, d
   __shared__ double Li[NB][TR + 1], Lj[NB][TR + 1];    // [t][row]; Lj pre-scaled by D_t
   const int r0 = t0 + bi * TR, q0 = t0 + bj * TR;
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;     // 16 x 16 threads, 4 x 4 outputs each
+  pdl_wait();
   // every global load of the tile is issued before anything waits: the C entries first (used last), then the two L strips
   double cc[4][4];
 #pragma unroll
@@ -263,6 +285,7 @@ __global__ void __launch_bounds__(256, 1) k_ldlt_trailing_mma(double *__restrict
   const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
   const int wm = wp & 3, wn = wp >> 2;
   const int lr = lane >> 2, lc = lane & 3;
+  pdl_wait();
   // accumulators <- C (issued first: the longest latency), then the strips
   double acc[4][8][2];
 #pragma unroll
@@ -355,6 +378,7 @@ __global__ void __launch_bounds__(256) k_ldlt_back(const double *__restrict__ B,
   __shared__ double L11[NB][NB + 1];
   __shared__ double X[NB];
   const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+  pdl_wait();
   for (int e = tid; e < NB * NB; e += 256) L11[e % NB][e / NB] = F[(size_t)(c0 / NB) * NB * NB + e];
   __syncthreads();
   if (wp == 0) {
@@ -442,11 +466,12 @@ static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx,
       attr_set[ctx->device & 63] = true;
     }
   }
-  VX_KERNEL(ctx, "k_ldlt_diag0", k_ldlt_diag0<<<1, 256, 0, st>>>(dB, dF, n, std::min(NB, n)));
+  static const bool pdl = std::getenv("VX_LDLT_PDL") != nullptr;
+  VX_KERNEL(ctx, "k_ldlt_diag0", launch_chain(false, k_ldlt_diag0, dim3(1), dim3(256), 0, st, dB, dF, n, std::min(NB, n)));   // head of the chain: a full dependency on what wrote dB
   for (int c0 = 0; c0 < n; c0 += NB) {
     const int nb = std::min(NB, n - c0);
     const int below = n - c0 - nb;
-    VX_KERNEL(ctx, "k_ldlt_panel", k_ldlt_panel<<<std::max(1, blocks_for(below, PR)), PR * 32, 0, st>>>(dB, dF, n, c0, nb, dx, dz));
+    VX_KERNEL(ctx, "k_ldlt_panel", launch_chain(pdl, k_ldlt_panel, dim3(std::max(1, blocks_for(below, PR))), dim3(PR * 32), 0, st, dB, dF, n, c0, nb, dx, dz));
     if (below > 0) {
       // Measured on B200 at n = 2400 (scripts/ldlt_time.py): 64 x 64 DFMA tiles 1.25 ms per solve (3.7 TFLOP/s), 128 x 128 DMMA tiles
       // 1.80 ms (2.6 TFLOP/s).  With a 32-column panel the update moves 16 B of C per 64 flop and every launch is a short wave of
@@ -455,16 +480,16 @@ static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx,
       static const bool dfma_tiles = std::getenv("VX_LDLT_DMMA") == nullptr;
       if (dfma_tiles) {
         const int nt = (below + TR - 1) / TR;
-        VX_KERNEL(ctx, "k_ldlt_trailing", k_ldlt_trailing<<<nt * (nt + 1) / 2, 256, 0, st>>>(dB, dF, n, c0, nb));
+        VX_KERNEL(ctx, "k_ldlt_trailing", launch_chain(pdl, k_ldlt_trailing, dim3(nt * (nt + 1) / 2), dim3(256), 0, st, dB, dF, n, c0, nb));
       } else {
         const int nt = (below + TT - 1) / TT;
-        VX_KERNEL(ctx, "k_ldlt_trailing_mma", k_ldlt_trailing_mma<<<nt * (nt + 1) / 2, 256, TRAIL_SMEM, st>>>(dB, dF, n, c0, nb));
+        VX_KERNEL(ctx, "k_ldlt_trailing_mma", launch_chain(pdl, k_ldlt_trailing_mma, dim3(nt * (nt + 1) / 2), dim3(256), TRAIL_SMEM, st, dB, dF, n, c0, nb));
       }
     }
   }
   for (int c0 = ((n - 1) / NB) * NB; c0 >= 0; c0 -= NB) {
     const int nb = std::min(NB, n - c0);
-    VX_KERNEL(ctx, "k_ldlt_back", k_ldlt_back<<<std::max(1, blocks_for(c0, 8 * BC)), 256, 0, st>>>(dB, dF, n, c0, nb, dz, dxo));
+    VX_KERNEL(ctx, "k_ldlt_back", launch_chain(pdl, k_ldlt_back, dim3(std::max(1, blocks_for(c0, 8 * BC))), dim3(256), 0, st, (const double *)dB, (const double *)dF, n, c0, nb, dz, dxo));
   }
   return VX_OK;
 }
