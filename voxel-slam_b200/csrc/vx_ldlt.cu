@@ -30,6 +30,12 @@ using namespace vx;
 
 namespace {
 
+// Panel width 32.  Tried and removed (round 2): 64-column panels (the 64 x 64 diagonal block as a 2 x 2 arrangement of the 32 x 32
+// routine, a lane holding two columns in the panel / backward kernels, the trailing K loop run twice over the same strips) halve
+// the steps to 38 — and every kernel took twice as long per launch (serialised: trailing 29 us against 16.8, panel 15.7 against
+// 9.4, backward 14 against 8.9), so one LM iteration at 2,394 unknowns came out at 2.37 ms against 2.29.  What a step costs is not
+// the kernel boundary but work proportional to the columns it retires: the diagonal block's pivot chain (~135 cycles per column),
+// the 8 / 32 KB of L11 every panel and backward CTA loads, the strips of the update.
 constexpr int NB = 32;     // panel width
 constexpr int TR = 64;     // trailing tile
 
