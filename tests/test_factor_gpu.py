@@ -47,7 +47,8 @@ def test_residual_parity(pkg, ob, ctx, V, W, occ):
     f.free()
 
 
-@pytest.mark.parametrize("V,W,occ", [(1, 2, 1.0), (2, 3, 1.0), (257, 4, 0.5), (3000, 10, 0.6), (500, 20, 0.3), (4000, 10, 1.0)])
+@pytest.mark.parametrize("V,W,occ", [(1, 2, 1.0), (2, 3, 1.0), (257, 4, 0.5), (3000, 10, 0.6), (500, 20, 0.3), (4000, 10, 1.0),
+                                     (1000, 5, 0.7), (1000, 8, 0.6), (800, 12, 0.5), (600, 15, 0.5), (600, 16, 0.4)])
 def test_hessian_parity(pkg, ob, ctx, V, W, occ):
     fac = synth.random_factor(200 + V, V, W, occupancy=occ)
     poses = synth.perturb_poses(fac["poses"], 9, 0.01, 0.03)

@@ -60,5 +60,5 @@ int factor_alloc(vx_factor *f, int64_t V, int64_t nnz);
 // Fused tensor-core path for small windows (vx_hess_small.cu); *handled=false when W has no instantiation.
 // with_cost: the finaliser also writes the windows' cost (cost_h) from the cached eigenvalues, bitwise what k_cost gives.
 int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *handled, int w_lo = 0, int w_hi = -1, bool with_cost = false);
-inline bool hessian_small_handles(int W) { return W == 10 || W == 20; }
+inline bool hessian_small_handles(int W) { return W == 5 || W == 8 || W == 10 || W == 12 || W == 15 || W == 16 || W == 20; }
 }  // namespace vx

@@ -496,6 +496,13 @@ int hessian_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, bool *ha
       return launch_small<10, 4, 3>(ctx, f, head, end, w_lo, w_hi, with_cost);
     }
     case 20: return launch_small<20, 8, 1>(ctx, f, head, end, w_lo, w_hi, with_cost);
+    // other window sizes a caller may configure (win_size / wdsize are ROS parameters, voxelslam.cpp:919, :3033); anything else
+    // takes the pair-list formulation of vx_factor.cu
+    case 5: return launch_small<5, 4, 3>(ctx, f, head, end, w_lo, w_hi, with_cost);
+    case 8: return launch_small<8, 4, 3>(ctx, f, head, end, w_lo, w_hi, with_cost);
+    case 12: return launch_small<12, 4, 2>(ctx, f, head, end, w_lo, w_hi, with_cost);
+    case 15: return launch_small<15, 8, 1>(ctx, f, head, end, w_lo, w_hi, with_cost);
+    case 16: return launch_small<16, 8, 1>(ctx, f, head, end, w_lo, w_hi, with_cost);
     default: *handled = false; return VX_OK;
   }
 }
