@@ -36,6 +36,13 @@ namespace {
 // 9.4, backward 14 against 8.9), so one LM iteration at 2,394 unknowns came out at 2.37 ms against 2.29.  What a step costs is not
 // the kernel boundary but work proportional to the columns it retires: the diagonal block's pivot chain (~135 cycles per column),
 // the 8 / 32 KB of L11 every panel and backward CTA loads, the strips of the update.
+// Also tried and removed: the trailing update FUSED with the next panel's work (tile (0,0) factors the next diagonal block, runs
+// the forward substitution and publishes both behind a release flag; the tiles of tile column 0 spin on the flag and apply the
+// panel's triangular solve to their own rows in place — bit-identical factor, one launch per step instead of two): 2.78 ms per LM
+// iteration against 2.29.  After the flag a waiting tile still pays a global round trip for L11, two barriers, the 32-step solve
+// and a store — the ~4.5 us the separate panel kernel costs — and the column-0 tiles of the later waves lengthen the kernel's tail.
+// Together with the programmatic-launch result: kernel boundaries are NOT what the sweep spends its time on; its chain is
+// update (~2.5 us) -> diagonal block (~4.5 us) -> panel solve (~4.5 us) per 32 columns, each a load / compute / store round.
 constexpr int NB = 32;     // panel width
 constexpr int TR = 64;     // trailing tile
 
