@@ -13,7 +13,12 @@ ctx = pkg.Context(0)
 job = pkg.HbaGlobalJob(d["xyz"], d["off"], np.zeros(n_kf, dtype=np.int32), d["start"], pkg.hba_global_params(LOCAL, GBA, 2, tmi))
 for k in range(2):
     t = time.perf_counter(); out = job.run(ctx); dt = time.perf_counter() - t
-    print(json.dumps({"run": k, "s": dt, "stats": out["stats"], "edges1": len(out["edges1"]), "edges2": len(out["edges2"])}))
+    import hashlib
+    sha = lambda a: hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()[:12]
+    e1, e2 = out["edges1"], out["edges2"]
+    print(json.dumps({"run": k, "s": dt, "stats": out["stats"], "edges1": len(e1), "edges2": len(e2),
+                      "sha_edges1": sha(np.stack([e1[f] for f in ("id1", "id2")] , 1)) + sha(e1["tra"]) + sha(e1["cov"]),
+                      "sha_edges2": sha(e2["tra"]) + sha(e2["cov"]), "sha_top": sha(out["top_poses"]["p"])}))
 ctx.profile(True); out = job.run(ctx); prof = ctx.profile_read(); ctx.profile(False)
 tot = sum(v[0] for v in prof.values())
 print(json.dumps({"profiled_stats": out["stats"], "kernel_ms_total": tot,

@@ -92,7 +92,8 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
   const int64_t NPl = lcoff[n_lc];
   DevBuf d_xyz, d_coff, d_sub, d_edges, d_tsub, d_tcoff;
   std::vector<DevBuf *> all = {&d_xyz, &d_coff, &d_sub, &d_edges, &d_tsub, &d_tcoff};
-  std::vector<vx_pgo_edge> eall((size_t)NWt * ecap);
+  std::unique_ptr<vx_pgo_edge[]> eall_own(new vx_pgo_edge[(size_t)NWt * ecap]);      // every slot that is read is written first (the multi-GPU gather zero-fills the rest itself)
+  vx_pgo_edge *eall = eall_own.get();
   std::vector<int64_t> ecnt(NWt, 0);
   std::vector<int64_t> sub_off(NWl + 1, 0);
   int64_t vf_bottom[4] = {0, 0, 0, 0}, vf_top[4] = {0, 0, 0, 0}, top_points = 0;
@@ -101,6 +102,10 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
 
   auto body = [&]() -> int {
     double t0 = now_ms();
+    // (Tried and removed: the full windows in 2-4 batches with the clouds of batch p + 1 crossing PCIe while batch p is optimised.
+    //  The fused Hessian kernel cuts a window into items whose number depends on how many windows share the launch, so the
+    //  partial sums associate differently and the edges move in the last bits — 4 of 29,867 top-level edges then fall on the other
+    //  side of the |hess| < 1e-6 test.  A job must not give different bits for host and device clouds; the 8.6 ms upload stays serial.)
     const float *d_kf = nullptr;                 // this rank's keyframe clouds on the device
     if (prm->xyz_on_device) d_kf = xyz + 3 * cloud_off[kf_lo];
     else {
@@ -159,7 +164,7 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
         if (gst[b] != VX_OK) { set_error("Too Less Voxel: bottom window %d (keyframes %d..%d)", w, wkf[w], wkf[w] + W - 1); return gst[b]; }
         for (int i = 0; i < W; i++) wposes[wf_off[a] + i] = ps[(size_t)b * W + i];
         ecnt[w] = gn[b];
-        std::copy(ge.begin() + (size_t)b * gcap, ge.begin() + (size_t)b * gcap + gn[b], eall.begin() + (size_t)w * ecap);
+        std::copy(ge.begin() + (size_t)b * gcap, ge.begin() + (size_t)b * gcap + gn[b], eall + (size_t)w * ecap);
       }
     }
     VX_CUDA(cudaStreamSynchronize(st));
@@ -183,10 +188,10 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
       VX_TRY(d_edges.reserve(8 * words));
       for (int w = 0; w < NWt; w++) if (w < lo || w >= hi) { ecnt[w] = 0; std::fill((char *)&eall[(size_t)w * ecap], (char *)(&eall[(size_t)w * ecap] + ecap), 0); }
       for (int w = lo; w < hi; w++) std::fill((char *)(&eall[(size_t)w * ecap] + ecnt[w]), (char *)(&eall[(size_t)w * ecap] + ecap), 0);
-      VX_CUDA(cudaMemcpyAsync(d_edges.p, eall.data(), eb, cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemcpyAsync(d_edges.p, eall, eb, cudaMemcpyHostToDevice, st));
       VX_CUDA(cudaMemcpyAsync(d_edges.as<char>() + eb, ecnt.data(), 8 * (size_t)NWt, cudaMemcpyHostToDevice, st));
       VX_TRY(comm_allreduce_i64(comm, d_edges.as<int64_t>(), (int64_t)words));
-      VX_CUDA(cudaMemcpyAsync(eall.data(), d_edges.p, eb, cudaMemcpyDeviceToHost, st));
+      VX_CUDA(cudaMemcpyAsync(eall, d_edges.p, eb, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaMemcpyAsync(ecnt.data(), d_edges.as<char>() + eb, 8 * (size_t)NWt, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaStreamSynchronize(st));
     }
@@ -195,7 +200,7 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
       for (int w = 0; w < NWt; w++) {
         if (edges1) {
           if (tot + ecnt[w] > cap1) { set_error("vx_hba_global: edges1 capacity %lld too small", (long long)cap1); return VX_ERR_ARG; }
-          std::copy(eall.begin() + (size_t)w * ecap, eall.begin() + (size_t)w * ecap + ecnt[w], edges1 + tot);
+          std::copy(eall + (size_t)w * ecap, eall + (size_t)w * ecap + ecnt[w], edges1 + tot);
         }
         tot += ecnt[w];
       }
