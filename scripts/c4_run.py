@@ -10,6 +10,9 @@ pkg = ge.load_package(); pkg.load_library()
 t = time.time(); d = sg.c4_session(n_kf=n_kf, n_az=n_az); print("gen %.1fs, %d points" % (time.time() - t, d["off"][-1]), file=sys.stderr)
 LOCAL = (0.5, 0.0025, [0.25] * 4); GBA = (1.0, 0.01, [0.5] * 4)
 ctx = pkg.Context(0)
+if os.environ.get("VX_PIN"):     # pinned host clouds, as bench.py's e2e leg passes them
+    import bench
+    xyz_pin, _pin_owner = bench.pinned_like(d["xyz"]); d["xyz"] = xyz_pin
 job = pkg.HbaGlobalJob(d["xyz"], d["off"], np.zeros(n_kf, dtype=np.int32), d["start"], pkg.hba_global_params(LOCAL, GBA, 2, tmi))
 for k in range(2):
     t = time.perf_counter(); out = job.run(ctx); dt = time.perf_counter() - t

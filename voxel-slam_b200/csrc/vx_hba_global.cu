@@ -103,9 +103,9 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
   auto body = [&]() -> int {
     double t0 = now_ms();
     // (Tried and removed: the full windows in 2-4 batches with the clouds of batch p + 1 crossing PCIe while batch p is optimised.
-    //  The fused Hessian kernel cuts a window into items whose number depends on how many windows share the launch, so the
-    //  partial sums associate differently and the edges move in the last bits — 4 of 29,867 top-level edges then fall on the other
-    //  side of the |hess| < 1e-6 test.  A job must not give different bits for host and device clouds; the 8.6 ms upload stays serial.)
+    //  Bit-identical edges once the fused Hessian kernel's item split was fixed, but slower: bench e2e 102.2 ms with one batch, 104.5
+    //  with two, 107.2 with three — a batch's fixed cost (the host round trips of one build + three LM iterations) is larger than
+    //  the share of the 8.6 ms upload it hides.)
     const float *d_kf = nullptr;                 // this rank's keyframe clouds on the device
     if (prm->xyz_on_device) d_kf = xyz + 3 * cloud_off[kf_lo];
     else {

@@ -454,6 +454,12 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo,
     int64_t s = (want_items + f->n_win / 2) / f->n_win;
     s = std::min<int64_t>(s, std::max<int64_t>(1, vox_per_win / 96));
     splits = (int)std::max<int64_t>(1, s);
+    // Batched regime: a FIXED number of items per window.  The items' partial tiles are added in item order, so the split decides
+    // how a window's sum is associated; with the adaptive rule above a window's Hessian changed in the last bits with the number
+    // of windows that happened to share its launch (400 on one GPU, 50 per rank on eight), and the top level of a hierarchical
+    // job turns such bits into a handful of edges on the other side of its |hess| < 1e-6 test.  4 is what the rule gives for the
+    // 400-window bottom level (measured best there); 32 windows x 4 items already cover the machine's first wave at W = 10.
+    if (f->n_win >= 32) splits = 4;
     static const int forced = getenv("VX_HS_SPLITS") ? atoi(getenv("VX_HS_SPLITS")) : 0;
     if (forced > 0) splits = forced;
   }
