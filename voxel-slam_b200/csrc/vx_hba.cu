@@ -57,7 +57,12 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
       vx_factor *fac = nullptr;
       VX_TRY(vx_factor_create(ctx, W, ns, &fac));
       std::vector<double> hs(hess_out ? hsz * ns : 0), rs(2 * (size_t)ns);
-      std::unique_ptr<double[]> ed(new double[(size_t)ns * cap * 6]);
+      // the edge diagonals of an outer iteration are only read for windows that END with it: the last iteration, or a window that
+      // entered it with cflag == 1 (voxelslam.cpp:2906-2917 — only such a window can become done).  Otherwise skip the kernel + copy
+      // (0.6 ms per top-level iteration at W = 400).
+      bool need_ed = iterCnt == max_iter - 1;
+      for (int w : ws) need_ed = need_ed || cflag[w] == 1;
+      std::unique_ptr<double[]> ed(need_ed ? new double[(size_t)ns * cap * 6] : nullptr);
       std::vector<int> conv(ns), wst(ns), nit(ns, 0);
       pt.lap("iteration setup");
       int s = build(ws, ps.data(), gp, fac);
@@ -83,7 +88,7 @@ int hba_core(vx_ctx *ctx, vx_comm *comm, const HbaBuildFn &build, const int32_t 
         if (wst[a] != VX_OK) { status[w] = wst[a]; done[w] = 1; continue; }   // reference: "Too Less Voxel", exit(0)
         for (int i = 0; i < W; i++) poses[w * W + i] = ps[(size_t)a * W + i];
         if (hess_out) std::copy(hs.begin() + hsz * a, hs.begin() + hsz * (a + 1), hess.begin() + hsz * w);
-        std::copy(ed.get() + (size_t)a * cap * 6, ed.get() + (size_t)(a + 1) * cap * 6, ediag.get() + (size_t)w * cap * 6);
+        if (need_ed) std::copy(ed.get() + (size_t)a * cap * 6, ed.get() + (size_t)(a + 1) * cap * 6, ediag.get() + (size_t)w * cap * 6);
         const double r0 = rs[2 * a], r1 = rs[2 * a + 1];
         if (resis_out) { resis_out[2 * w] = r0; resis_out[2 * w + 1] = r1; }
         // voxelslam.cpp:2906-2917
