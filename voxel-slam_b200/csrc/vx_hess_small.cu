@@ -458,8 +458,8 @@ int launch_small(vx_ctx *ctx, vx_factor *f, int64_t head, int64_t end, int w_lo,
     // how a window's sum is associated; with the adaptive rule above a window's Hessian changed in the last bits with the number
     // of windows that happened to share its launch (400 on one GPU, 50 per rank on eight), and the top level of a hierarchical
     // job turns such bits into a handful of edges on the other side of its |hess| < 1e-6 test.  4 is what the rule gives for the
-    // 400-window bottom level (measured best there); 32 windows x 4 items already cover the machine's first wave at W = 10.
-    if (f->n_win >= 32) splits = 4;
+    // 400-window bottom level (measured best there).
+    if (f->n_win >= 4) splits = 4;      // one to three windows (local BA): the adaptive rule above, for latency
     static const int forced = getenv("VX_HS_SPLITS") ? atoi(getenv("VX_HS_SPLITS")) : 0;
     if (forced > 0) splits = forced;
   }
