@@ -86,3 +86,12 @@ def test_hba_merged_submap_cloud(pkg, ob, ctx):
         sl = slice(s0, s0 + W)
         one = pkg.hba_merge_clouds(ctx, clouds[sl], (start[0][sl], start[1][sl]), W, 1, LOCAL[0], mps=mps[sl])[0]
         assert np.array_equal(both[b].view(np.uint8), one.view(np.uint8))
+    # ragged input: an empty scan and a one-point scan inside the window (the key fields are sized from the clouds' bounding boxes)
+    rag = [c for c in clouds[:W]]
+    rag[3] = rag[3][:0]; rag[6] = rag[6][:1]
+    sl = slice(0, W)
+    ref = ob.hba_add_edge(clouds[sl], (start[0][sl], start[1][sl]), LOCAL, GBA, 2, 1, ids=np.arange(W), mps=mps[sl], want_cloud=True)
+    got = pkg.hba_merge_clouds(ctx, rag, ref["poses"], W, 1, LOCAL[0], mps=mps[sl])[0]
+    assert int(got["curvature"].sum()) == sum(c.shape[0] for c in rag)
+    full = pkg.hba_merge_clouds(ctx, clouds[sl], ref["poses"], W, 1, LOCAL[0], mps=mps[sl])[0]
+    assert 0 < got.shape[0] <= full.shape[0]

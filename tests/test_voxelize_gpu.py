@@ -147,6 +147,35 @@ def test_gba_build_matches_oracle(pkg, ob, ctx, vs, min_eig, thr, L):
     f.free()
 
 
+def test_gba_build_ragged_and_empty_clouds(pkg, ob, ctx):
+    # empty scans, a one-point scan and a seven-point scan inside a window: the per-cloud bounding boxes, the frame walk of the key
+    # kernel and the compact index arrays must cope with frames that own no instance at all
+    clouds, (R, p) = scene.config1(pts_per_scan=4000)
+    W = len(clouds)
+    clouds = list(clouds)
+    clouds[0] = clouds[0][:0]; clouds[2] = clouds[2][:0]; clouds[5] = clouds[5][:1]; clouds[7] = clouds[7][:7]; clouds[W - 1] = clouds[W - 1][:0]
+    start = synth.perturb_poses((R, p), 5, 0.004, 0.03)
+    of = ob.gba_build(clouds, start, 1.0, 0.01, [0.5] * 4, 2)
+    cpu = of.get_dense()
+    f = pkg.Factor(ctx, W)
+    f.gba_build(clouds, start, 1.0, 0.01, [0.5] * 4, 2)
+    assert f.num_voxels == of.num_voxels and f.num_voxel_frames == of.num_voxel_frames and f.num_voxels > 0
+    g = f.download_csr()
+    pl = dense_from_csr(g, W)
+    og, oc = canon(g, W), canon(cpu, W)
+    assert np.array_equal(g["merged"]["N"][og], cpu["merged"]["N"][oc])
+    assert np.array_equal(pl["N"][og], cpu["plvec"]["N"][oc])
+    assert not np.any(pl["N"][:, [0, 2, W - 1]])                     # the empty scans own nothing
+    rel = lambda a, b: np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300)
+    assert rel(pl["P"][og], cpu["plvec"]["P"][oc]) < 1e-12 and rel(g["merged"]["P"][og], cpu["merged"]["P"][oc]) < 1e-12
+    f.free()
+    # every scan empty: an empty factor, not an error
+    f0 = pkg.Factor(ctx, W)
+    f0.gba_build([c[:0] for c in clouds], start, 1.0, 0.01, [0.5] * 4, 2)
+    assert f0.num_voxels == 0 and f0.num_voxel_frames == 0
+    f0.free()
+
+
 def test_gba_build_batched_windows(pkg, ob, ctx):
     # 3 overlapping windows (stride 5, size 10 over 20 keyframes) in one call == each window built alone
     clouds, (R, p) = scene.config1(W=20, pts_per_scan=3000)
