@@ -44,7 +44,7 @@ SEED = 20241008 + 4
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--keyframes", type=int, default=2000)
@@ -249,6 +249,15 @@ def kernel_models(st, rb, rt, inst_bottom, top_points, top_builds):
     m["k_gba_key64"] = (12 * inst + 12 * inst, 0, "A1 / A8 keys: 12 B/point instance read, 8 B key + 4 B index written")
     m["k_hb_emit"] = (1 * inst, 0, "A8 fused head-counter scan: 1 B of head bits per point instance read (compact index arrays written at the heads)")
     return m
+
+
+def traffic_of(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture summary (profiles/ncu_traffic.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return t.get(kernel, {}).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        return None
 
 
 def extra_benches(pkg, ctx, peak_hbm, fp64):
@@ -566,8 +575,9 @@ def run_b200(args, rank, world, local_rank):
         else:
             roofline = {"bound": "hbm", "achieved": r["hbm_gbs"], "peak": peak_hbm, "unit": "GB/s", "frac": r["hbm_frac"], "peak_source": peak_src}
         roofline.update({"kernel": top, "what": r["what"], "ms_per_launch": r["ms_per_step"] / max(r["launches_per_step"], 1),
-                         "launches_per_step": r["launches_per_step"], "share_of_kernel_time": r["share_of_kernel_time"], "traffic": None,
-                         "traffic_source": "see profiles/ for the ncu --set full capture of this kernel",
+                         "launches_per_step": r["launches_per_step"], "share_of_kernel_time": r["share_of_kernel_time"],
+                         "traffic": traffic_of(top), "traffic_unit": "bytes of DRAM traffic per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
+                         "traffic_source": "profiles/ncu_traffic.json: mean over the launches of one ncu --set full capture (scripts/final_profile.sh); null when this kernel has no capture",
                          "ridge_flop_per_byte": ridge, "rows": rows,
                          "library_kernels_not_listed": "cub::DeviceRadixSort / DeviceScan launches of the map build are not bracketed by the library's profiler",
                          "kernels_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in list(kern.items())[:16]}})
