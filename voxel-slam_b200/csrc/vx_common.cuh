@@ -109,6 +109,8 @@ struct vx_ctx {
   int ldlt_n = 0;
   int64_t ldlt_launches = 0;
   double *ldlt_B = nullptr, *ldlt_F = nullptr;
+  cudaStream_t ldlt_aux = nullptr;                  // second branch of the sweep (the next diagonal block, beside the trailing update)
+  cudaEvent_t ldlt_ev[2] = {nullptr, nullptr};
   size_t pinned_cap = 0;
   struct vx_factor *kept[2] = {nullptr, nullptr};   // vx_hba_global(keep_factors): bottom batch, top level
 };

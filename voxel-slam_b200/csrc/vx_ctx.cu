@@ -142,6 +142,8 @@ int vx_ctx_destroy(vx_ctx *ctx) {
   ctx->scratch.release();
   ctx->scratch2.release();
   if (ctx->ldlt_exec) cudaGraphExecDestroy(ctx->ldlt_exec);
+  if (ctx->ldlt_aux) cudaStreamDestroy(ctx->ldlt_aux);
+  for (cudaEvent_t e : ctx->ldlt_ev) if (e) cudaEventDestroy(e);
   ctx->ldlt_side.release();
   ctx->ldlt_mat.release();
   if (ctx->pinned) cudaFreeHost(ctx->pinned);

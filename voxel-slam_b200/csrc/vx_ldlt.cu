@@ -203,7 +203,41 @@ __global__ void __launch_bounds__(PR * 32) k_ldlt_panel(double *__restrict__ B, 
   }
 }
 
-// trailing update of the lower triangle: C(I,J) -= L(I,:) D L(J,:)^T over the panel's nb columns
+// The next panel's diagonal block on its own: C(I,I) -= L(I,:) D L(I,:)^T for the 32 x 32 block at t0 = c0 + nb — the sums of
+// k_ldlt_trailing's tile (0,0), operation for operation — then its factorisation.  One CTA, launched on a second branch of the sweep
+// beside the trailing update (which then leaves that block alone), so the block's ~4.5 us pivot chain no longer rides behind an update.
+__global__ void __launch_bounds__(256) k_ldlt_dnext(const double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb) {
+  __shared__ double S[NB][NB + 1];       // S[t][i] = L(t0 + i, c0 + t)
+  __shared__ double Dk[NB];
+  __shared__ double L11[NB][NB + 1];
+  const int t0 = c0 + nb, tid = threadIdx.x;
+  const double *Fd = F + (size_t)(c0 / NB) * NB * NB;
+  for (int e = tid; e < NB * NB; e += 256) {
+    const int i = e % NB, t = e / NB;
+    S[t][i] = (t < nb && t0 + i < n) ? B[(size_t)(c0 + t) * n + t0 + i] : 0.0;
+  }
+  if (tid < NB) Dk[tid] = tid < nb ? Fd[tid * NB + tid] : 0.0;
+  __syncthreads();
+  for (int e = tid; e < NB * NB; e += 256) {
+    const int i = e % NB, j = e / NB;
+    double v = 0.0;
+    if (i >= j && t0 + i < n && t0 + j < n) {
+      const double cc = B[(size_t)(t0 + j) * n + t0 + i];
+      double acc = 0.0;
+#pragma unroll 8
+      for (int t = 0; t < NB; t++) acc = fma(S[t][i], S[t][j] * Dk[t], acc);
+      v = cc - acc;
+    }
+    L11[i][j] = v;
+  }
+  __syncthreads();
+  ldlt_diag_block<256>(L11, tid);
+  for (int e = tid; e < NB * NB; e += 256) F[(size_t)(t0 / NB) * NB * NB + e] = L11[e % NB][e / NB];
+}
+
+// trailing update of the lower triangle: C(I,J) -= L(I,:) D L(J,:)^T over the panel's nb columns.  OWN_DIAG: tile (0,0) also
+// factors the next diagonal block (single-branch sweep); otherwise it leaves that block to k_ldlt_dnext and does not write it.
+template <bool OWN_DIAG>
 __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, double *__restrict__ F, int n, int c0, int nb) {
   const int t0 = c0 + nb;
   int bi = (int)((sqrtf(8.0f * (float)blockIdx.x + 1.0f) - 1.0f) * 0.5f);      // lower-triangular tiles only: blockIdx.x = bi (bi + 1) / 2 + bj
@@ -257,9 +291,10 @@ __global__ void __launch_bounds__(256) k_ldlt_trailing(double *__restrict__ B, d
 #pragma unroll
     for (int b = 0; b < 4; b++) {
       const int r = r0 + tx + 16 * a, c = q0 + ty + 16 * b;
-      if (r < n && c < n && r >= c) B[(size_t)c * n + r] = cc[a][b] - acc[a][b];
+      const bool dnext = !OWN_DIAG && r < t0 + NB && c < t0 + NB;      // the block k_ldlt_dnext is reading right now
+      if (r < n && c < n && r >= c && !dnext) B[(size_t)c * n + r] = cc[a][b] - acc[a][b];
     }
-  if (bi == 0 && bj == 0) {               // this tile completes the next panel's diagonal block: factor it here, off the panel's chain
+  if (OWN_DIAG && bi == 0 && bj == 0) {   // this tile completes the next panel's diagonal block: factor it here, off the panel's chain
     __syncthreads();                      // everybody is done with Li / Lj
     double (*L11)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(&Li[0][0]);
 #pragma unroll
@@ -480,6 +515,11 @@ static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx,
     }
   }
   static const bool pdl = std::getenv("VX_LDLT_PDL") != nullptr;
+  static const bool two_branch = std::getenv("VX_LDLT_ONE_BRANCH") == nullptr && std::getenv("VX_LDLT_DMMA") == nullptr;
+  if (two_branch && !ctx->ldlt_aux) {
+    VX_CUDA(cudaStreamCreateWithFlags(&ctx->ldlt_aux, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; k++) VX_CUDA(cudaEventCreateWithFlags(&ctx->ldlt_ev[k], cudaEventDisableTiming));
+  }
   VX_KERNEL(ctx, "k_ldlt_diag0", launch_chain(false, k_ldlt_diag0, dim3(1), dim3(256), 0, st, dB, dF, n, std::min(NB, n)));   // head of the chain: a full dependency on what wrote dB
   for (int c0 = 0; c0 < n; c0 += NB) {
     const int nb = std::min(NB, n - c0);
@@ -493,7 +533,18 @@ static int enqueue_sweep(vx_ctx *ctx, double *dB, double *dF, int n, double *dx,
       static const bool dfma_tiles = std::getenv("VX_LDLT_DMMA") == nullptr;
       if (dfma_tiles) {
         const int nt = (below + TR - 1) / TR;
-        VX_KERNEL(ctx, "k_ldlt_trailing", launch_chain(pdl, k_ldlt_trailing, dim3(nt * (nt + 1) / 2), dim3(256), 0, st, dB, dF, n, c0, nb));
+        if (two_branch) {
+          // fork: the next diagonal block on the aux stream beside the update of everything else; join before the next panel
+          cudaStream_t sd = ctx->profiling ? st : ctx->ldlt_aux;
+          if (sd != st) { VX_CUDA(cudaEventRecord(ctx->ldlt_ev[0], st)); VX_CUDA(cudaStreamWaitEvent(sd, ctx->ldlt_ev[0], 0)); }
+          if (ctx->profiling) { VX_KERNEL(ctx, "k_ldlt_dnext", k_ldlt_dnext<<<1, 256, 0, sd>>>(dB, dF, n, c0, nb)); }
+          else { k_ldlt_dnext<<<1, 256, 0, sd>>>(dB, dF, n, c0, nb); ctx->launches++; VX_CUDA(cudaGetLastError()); }
+          if (sd != st) VX_CUDA(cudaEventRecord(ctx->ldlt_ev[1], sd));
+          VX_KERNEL(ctx, "k_ldlt_trailing", launch_chain(false, k_ldlt_trailing<false>, dim3(nt * (nt + 1) / 2), dim3(256), 0, st, dB, dF, n, c0, nb));
+          if (sd != st) VX_CUDA(cudaStreamWaitEvent(st, ctx->ldlt_ev[1], 0));
+        } else {
+          VX_KERNEL(ctx, "k_ldlt_trailing", launch_chain(pdl, k_ldlt_trailing<true>, dim3(nt * (nt + 1) / 2), dim3(256), 0, st, dB, dF, n, c0, nb));
+        }
       } else {
         const int nt = (below + TT - 1) / TT;
         VX_KERNEL(ctx, "k_ldlt_trailing_mma", launch_chain(pdl, k_ldlt_trailing_mma, dim3(nt * (nt + 1) / 2), dim3(256), TRAIL_SMEM, st, dB, dF, n, c0, nb));
