@@ -588,6 +588,10 @@ def run_b200(args, rank, world, local_rank):
              "factors": {"bottom": rb, "top": rt}, "fp64_peak_tflops": fp64}
     if comm is not None:
         extra["comm"] = comm.stats(); extra["comm"]["nccl_version"] = int(pkg.load_library().vx_comm_nccl_version())
+        # every rank's phases: the wait inside `gather` is the skew between the ranks' bottom + merge times, not transfer time
+        allp = [None] * world
+        dist.all_gather_object(allp, {k: round(v, 3) for k, v in phase.items()})
+        extra["phases_ms_all_ranks"] = allp
     if fb is not None:
         fb.free()
     if ft is not None:

@@ -186,10 +186,13 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
       static_assert(sizeof(vx_pgo_edge) % 8 == 0, "edge records are whole int64 words");
       const size_t eb = sizeof(vx_pgo_edge) * (size_t)NWt * ecap, words = eb / 8 + NWt;
       VX_TRY(d_edges.reserve(8 * words));
-      for (int w = 0; w < NWt; w++) if (w < lo || w >= hi) { ecnt[w] = 0; std::fill((char *)&eall[(size_t)w * ecap], (char *)(&eall[(size_t)w * ecap] + ecap), 0); }
+      // the array is zeroed ON the device and only this rank's windows cross PCIe (their unused slots as zeros)
+      for (int w = 0; w < NWt; w++) if (w < lo || w >= hi) ecnt[w] = 0;
       for (int w = lo; w < hi; w++) std::fill((char *)(&eall[(size_t)w * ecap] + ecnt[w]), (char *)(&eall[(size_t)w * ecap] + ecap), 0);
-      VX_CUDA(cudaMemcpyAsync(d_edges.p, eall, eb, cudaMemcpyHostToDevice, st));
-      VX_CUDA(cudaMemcpyAsync(d_edges.as<char>() + eb, ecnt.data(), 8 * (size_t)NWt, cudaMemcpyHostToDevice, st));
+      VX_CUDA(cudaMemsetAsync(d_edges.p, 0, 8 * words, st));
+      if (hi > lo) VX_CUDA(cudaMemcpyAsync(d_edges.as<char>() + sizeof(vx_pgo_edge) * (size_t)lo * ecap, eall + (size_t)lo * ecap, sizeof(vx_pgo_edge) * (size_t)(hi - lo) * ecap,
+                                         cudaMemcpyHostToDevice, st));
+      if (hi > lo) VX_CUDA(cudaMemcpyAsync(d_edges.as<char>() + eb + 8 * (size_t)lo, ecnt.data() + lo, 8 * (size_t)(hi - lo), cudaMemcpyHostToDevice, st));
       VX_TRY(comm_allreduce_i64(comm, d_edges.as<int64_t>(), (int64_t)words));
       VX_CUDA(cudaMemcpyAsync(eall, d_edges.p, eb, cudaMemcpyDeviceToHost, st));
       VX_CUDA(cudaMemcpyAsync(ecnt.data(), d_edges.as<char>() + eb, 8 * (size_t)NWt, cudaMemcpyDeviceToHost, st));
