@@ -104,7 +104,11 @@ inline void die(const char *where, int code) {
 }
 #define VXC_CHECK(call) do { int _c = (call); if (_c != VX_OK) ::vxc::die(#call, _c); } while (0)
 
-// one context per calling thread (the reference's three threads work on different maps)
+// one context per calling thread (the reference's three threads work on different maps).  An object of this
+// adaptor (LidarFactor, the map sentinels) belongs to the thread that first used it: its device handle was created on that
+// thread's context, and every later call must come from the same thread — as in the reference, where a voxhess / surf_map is only
+// ever touched by the thread that owns it.  The public member vectors of LidarFactor may be READ freely; change them only through
+// push_voxel / clear (direct edits are not seen by the device copy).
 inline vx_ctx *context() {
   static thread_local vx_ctx *ctx = nullptr;
   if (!ctx) VXC_CHECK(vx_ctx_create(0, &ctx));

@@ -122,6 +122,7 @@ def sharded_gba_build(pkg, ctx, factor, xyz, frame, poses, gba_params, rank, wor
     F = ps.shape[0]
     xyz = xyz.contiguous(); frame = frame.to(torch.int32).contiguous()
     owner = torch.empty(n, dtype=torch.int32, device=xyz.device)
+    torch.cuda.current_stream(xyz.device).synchronize()      # the cast / copy above ran on torch's stream; the library reads on its own
     lib = ctx.lib
     rc = lib.vx_gba_point_owner(ctx.h, C.c_void_p(xyz.data_ptr()), C.c_void_p(frame.data_ptr()), C.c_int64(n), ps.ctypes.data_as(C.c_void_p), C.c_int(F),
                                 C.c_double(float(gba_params["voxel_size"][0])), C.c_int(world), C.c_void_p(owner.data_ptr()))
