@@ -533,7 +533,7 @@ def run_b200(args, rank, world, local_rank):
     stp = outp["stats"]
     # point instances this rank keys at the bottom level (every window re-references its 10 keyframe clouds)
     ws, wst, wsz = pkg.hba_schedule([n_kf])
-    lo_w = rank * (ws.size // world) + min(rank, ws.size % world); hi_w = lo_w + ws.size // world + (1 if rank < ws.size % world else 0)
+    lo_w, hi_w = pkg.hba_window_range(wsz, 10, rank, world)
     sizes = np.diff(d["off"])
     inst_bottom = int(sum(sizes[wst[w]:wst[w] + wsz[w]].sum() for w in range(lo_w, hi_w)))
     n_groups = len(set(int(x) for x in wsz[lo_w:hi_w]))

@@ -382,6 +382,11 @@ int vx_hba_merge_clouds(vx_ctx *ctx, const float *xyz, const int64_t *cloud_off,
 int vx_hba_schedule(const int32_t *session_sizes, int n_sessions, int wdsize, int mgsize, int32_t *win_session, int32_t *win_start,
                     int32_t *win_size, int cap, int32_t *n_windows);
 
+/* Which windows of the schedule rank `rank` of `n_ranks` optimises in vx_hba_global: the contiguous run [*lo, *hi), balanced by
+ * cost (a window shorter than wdsize is a batch of its own and weighs as much as 16 full ones).  The reference optimises its
+ * windows one after another on one host thread (voxelslam.cpp:3094-3096); this is the multi-GPU partition of that loop. */
+int vx_hba_window_range(const int32_t *win_size, int n_windows, int wdsize, int rank, int n_ranks, int32_t *lo, int32_t *hi);
+
 /* The whole hierarchical global BA of thd_globalmapping for stored sessions, bottom level + top level (voxelslam.cpp:3084-3127):
  *   bottom  every window of the schedule through HBA_add_edge(xs = Keyframe::x0, max_iter = bottom_max_iter (1), thread_num = 2,
  *           plptr) -> edges `edges1` (gba_edges1) and one submap per window: pose Keyframe::x0 of its first keyframe, id / mp of

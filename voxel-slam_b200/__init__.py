@@ -282,6 +282,14 @@ def hba_schedule(session_sizes, wdsize=10, mgsize=5):
     return a, b, c
 
 
+def hba_window_range(win_size, wdsize, rank, world):
+    """vx_hba_window_range: the windows [lo, hi) of the schedule that rank `rank` of `world` optimises in vx_hba_global."""
+    ws = np.ascontiguousarray(win_size, dtype=np.int32)
+    lo, hi = C.c_int32(0), C.c_int32(0)
+    _chk(load_library().vx_hba_window_range(_p(ws), C.c_int(ws.size), C.c_int(wdsize), C.c_int(rank), C.c_int(world), C.byref(lo), C.byref(hi)))
+    return lo.value, hi.value
+
+
 def hba_global_params(local, gba, max_layer, total_max_iter=1, wdsize=10, mgsize=5, bottom_max_iter=1, bottom_thread_num=2, top_thread_num=5):
     prm = np.zeros(1, dtype=hba_global_params_dtype)
     h = prm["hba"]

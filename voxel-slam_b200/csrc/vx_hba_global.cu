@@ -44,12 +44,39 @@ extern "C" int vx_hba_schedule(const int32_t *session_sizes, int n_sessions, int
 
 namespace {
 double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
-void block_range(int n, int rank, int world, int &lo, int &hi) {
-  const int base = n / world, extra = n % world;
-  lo = rank * base + std::min(rank, extra);
-  hi = lo + base + (rank < extra ? 1 : 0);
+// Windows of rank `rank`: a contiguous run, balanced by COST.  Full windows of a rank go through one batched build + one batched
+// LM; every window of another size is a batch of its own, and a batch has a fixed cost (the host round trips of one build and
+// its LM iterations: ~1.2 ms) worth about SHORT_WEIGHT full windows at the per-window rate of a many-window batch (0.06-0.07 ms).
+// With plain counts the rank that holds a session's short tail window finished its bottom level 1.2 ms after the others and the
+// whole job waited for it in the edge gather.
+constexpr int SHORT_WEIGHT = 16;
+void window_range(const int32_t *wsize, int n, int wdsize, int rank, int world, int &lo, int &hi) {
+  int64_t total = 0;
+  for (int w = 0; w < n; w++) total += wsize[w] == wdsize ? 1 : SHORT_WEIGHT;
+  // window w goes to the rank whose share [r total / world, (r + 1) total / world) holds the midpoint of its weight interval
+  auto owner = [&](int64_t before, int wt) { const int64_t mid2 = 2 * before + wt; return (int)std::min<int64_t>(world - 1, mid2 * world / (2 * total)); };
+  lo = n; hi = n;
+  int64_t acc = 0;
+  bool open = false;
+  for (int w = 0; w < n; w++) {
+    const int wt = wsize[w] == wdsize ? 1 : SHORT_WEIGHT;
+    const int r = owner(acc, wt);
+    if (r == rank && !open) { lo = w; open = true; }
+    if (r > rank && open) { hi = w; open = false; break; }
+    if (r > rank && !open) { lo = hi = w; break; }
+    acc += wt;
+  }
+  if (open) hi = n;
 }
 }  // namespace
+
+extern "C" int vx_hba_window_range(const int32_t *win_size, int n_windows, int wdsize, int rank, int n_ranks, int32_t *lo, int32_t *hi) {
+  VX_ARG(win_size && lo && hi && n_windows >= 0 && n_ranks >= 1 && rank >= 0 && rank < n_ranks);
+  int a = 0, b = 0;
+  window_range(win_size, n_windows, wdsize, rank, n_ranks, a, b);
+  *lo = a; *hi = b;
+  return VX_OK;
+}
 
 extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const int64_t *cloud_off, int n_kf, const int32_t *kf_session,
                              const int32_t *kf_id, const vx_pose *kf_x0, const vx_pose *kf_x, const int32_t *cnct_map, int n_cnct,
@@ -78,7 +105,7 @@ extern "C" int vx_hba_global(vx_ctx *ctx, vx_comm *comm, const float *xyz, const
   std::vector<int32_t> wkf(NWt);   // first keyframe (global index) of every window
   for (int w = 0; w < NWt; w++) { wkf[w] = sess_first[wsess[w]] + wstart[w]; VX_ARG(wsize[w] >= 2); }
   int lo = 0, hi = NWt;
-  block_range(NWt, rank, world, lo, hi);
+  window_range(wsize.data(), NWt, prm->wdsize, rank, world, lo, hi);
   const int NWl = hi - lo;
   const int64_t ecap = (int64_t)prm->wdsize * (prm->wdsize - 1) / 2;
 
