@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""gba_build kernel times on the bench's C4-shaped input (128 windows); VX_SEG_LANES picks k_seg_moments' lanes per segment."""
+"""gba_build kernel times on the bench's C4-shaped input (128 windows); VX_SEG_LANES picks the lanes per leaf / voxel-frame of k_leaf_stats / k_vf_fill."""
 import os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
