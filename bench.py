@@ -580,6 +580,10 @@ def run_b200(args, rank, world, local_rank):
                          "traffic_source": "profiles/ncu_traffic.json: mean over the launches of one ncu --set full capture (scripts/final_profile.sh); null when this kernel has no capture",
                          "ridge_flop_per_byte": ridge, "rows": rows,
                          "library_kernels_not_listed": "cub::DeviceRadixSort / DeviceScan launches of the map build are not bracketed by the library's profiler",
+                         "latency_kernels_without_a_model": "k_ldlt_dnext (ONE CTA: the 32 x 32 pivot chain of the next diagonal block, ~45 kflop per launch) runs on a second "
+                                                            "branch of the captured sweep beside k_ldlt_trailing; serialised under a profiler its share (about that of "
+                                                            "k_ldlt_trailing) overstates it, in the replayed graph it is hidden; k_ldlt_panel / k_ldlt_back are "
+                                                            "dependent 32-step chains as well (DESIGN section 5)",
                          "kernels_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in list(kern.items())[:16]}})
     extra = {"phases_ms_rank0": {k: round(v, 3) for k, v in phase.items()}, "voxel_frames_per_step": int(vf_step),
              "job": {"edges1": int(len(out["edges1"])), "edges2": int(len(out["edges2"])), "top_points": int(allsum(out["stats"]["top_points"])),
